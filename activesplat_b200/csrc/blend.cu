@@ -1,0 +1,372 @@
+// blend.cu -- per-tile alpha blending, forward and backward (sm_100a).
+//
+//   blend_forward_kernel<C>   replaces renderCUDA<3> (forward)   dgr/cuda_rasterizer/forward.cu:261-397
+//   blend_backward_kernel<C>  replaces renderCUDA<3> (backward)  dgr/cuda_rasterizer/backward.cu:399-557
+//
+// One CTA per 16x16 tile, one thread per pixel (same as the reference).  What differs:
+//   * the tile's instances were gathered into contiguous per-instance records in sorted order
+//     (ranges_gather_kernel), so a batch is THREE contiguous slabs that one elected thread pulls
+//     into shared memory with cp.async.bulk (TMA engine, SASS UBLKCP) on an mbarrier, double
+//     buffered: the copy of batch k+1/k+2 overlaps the blending of batch k;
+//   * C = 6 blends [rgb | z,1,z^2] in one sweep (the reference makes two full passes);
+//   * backward: each warp reduces a Gaussian's 6+C gradient terms with a transposing butterfly
+//     (16 shuffles instead of 80), adds them to a per-batch accumulator in shared memory, and the
+//     CTA flushes once per (tile, instance) with 128-bit vector reductions (REDG.ADD.F32x4)
+//     -- versus 9 scalar global atomics per (pixel, Gaussian) in the reference (backward.cu:523-554);
+//   * backward skips the tail of the list that no pixel of the warp/tile reached in the forward.
+// Per-pixel arithmetic, skip rules and termination are the reference's (SURVEY 8a' T10-T18) and are
+// spelled with rounding-explicit intrinsics so alpha decisions match the reference build bit for bit.
+#include "common.cuh"
+
+namespace asb {
+
+namespace {
+
+constexpr int BL_THREADS = TILE_PIX;  // 256
+constexpr int BL_BATCH = 128;
+
+__device__ __forceinline__ float eval_power(const float4& co, float dx, float dy) {
+    // forward.cu:342: -0.5f*(A*dx*dx + C*dy*dy) - B*dx*dy, contracted as nvcc contracts it
+    const float q = __fmaf_rn(__fmul_rn(co.x, dx), dx, __fmul_rn(__fmul_rn(co.z, dy), dy));
+    return __fmaf_rn(q, -0.5f, -__fmul_rn(__fmul_rn(co.y, dx), dy));
+}
+
+template <int C>
+struct BlendSmem {
+    static constexpr int FV = (C == 3) ? 1 : 2;
+    float4 conic[2][BL_BATCH];
+    float4 geom[2][BL_BATCH];
+    float4 feat[2][BL_BATCH * FV];
+    uint64_t bar[2];
+};
+
+template <int C>
+__device__ __forceinline__ void issue_batch(BlendSmem<C>& sm, int stage, const float4* __restrict__ inst_conic,
+                                            const float4* __restrict__ inst_geom,
+                                            const float4* __restrict__ inst_feat, uint32_t start, int cnt) {
+    constexpr int FV = BlendSmem<C>::FV;
+    const uint32_t bytes = (uint32_t)cnt * 16u;
+    mbar_expect_tx(&sm.bar[stage], bytes * (2 + FV));
+    bulk_g2s(sm.conic[stage], inst_conic + start, bytes, &sm.bar[stage]);
+    bulk_g2s(sm.geom[stage], inst_geom + start, bytes, &sm.bar[stage]);
+    bulk_g2s(sm.feat[stage], inst_feat + (size_t)start * FV, bytes * FV, &sm.bar[stage]);
+}
+
+template <int C>
+__global__ void __launch_bounds__(BL_THREADS)
+blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict__ inst_conic,
+                     const float4* __restrict__ inst_geom, const float4* __restrict__ inst_feat, int W, int H,
+                     int gx, const float* __restrict__ bg, float* __restrict__ out_color,
+                     float* __restrict__ out_depth, float* __restrict__ out_opacity, float* __restrict__ final_T,
+                     uint32_t* __restrict__ n_contrib) {
+    constexpr int FV = BlendSmem<C>::FV;
+    __shared__ __align__(128) BlendSmem<C> sm;
+    const int tile = blockIdx.x;
+    const int tx = tile % gx, ty = tile / gx;
+    const int px = tx * TILE_X + (threadIdx.x & (TILE_X - 1));
+    const int py = ty * TILE_Y + (threadIdx.x / TILE_X);
+    const bool inside = px < W && py < H;
+    const float pxf = (float)px, pyf = (float)py;
+    const uint2 range = ranges[tile];
+    const int len = (int)(range.y - range.x);
+    const int nb = (len + BL_BATCH - 1) / BL_BATCH;
+
+    if (threadIdx.x == 0) {
+        mbar_init(&sm.bar[0], 1);
+        mbar_init(&sm.bar[1], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (nb > 0) issue_batch<C>(sm, 0, inst_conic, inst_geom, inst_feat, range.x, min(BL_BATCH, len));
+        if (nb > 1) issue_batch<C>(sm, 1, inst_conic, inst_geom, inst_feat, range.x + BL_BATCH, min(BL_BATCH, len - BL_BATCH));
+    }
+
+    bool done = !inside;
+    float T = 1.0f;
+    float D = 15.0f;  // median depth default (forward.cu:309)
+    uint32_t contributor = 0, last_contributor = 0;
+    float acc[C];
+#pragma unroll
+    for (int ch = 0; ch < C; ch++) acc[ch] = 0.f;
+
+    int consumed = 0;
+    for (int b = 0; b < nb; b++) {
+        const int s = b & 1;
+        mbar_wait(&sm.bar[s], (uint32_t)((b >> 1) & 1));
+        const int cnt = min(BL_BATCH, len - b * BL_BATCH);
+        if (!done) {
+            for (int j = 0; j < cnt; j++) {
+                contributor++;  // forward.cu:335
+                const float4 co = sm.conic[s][j];
+                const float4 ge = sm.geom[s][j];
+                const float dx = __fsub_rn(ge.x, pxf), dy = __fsub_rn(ge.y, pyf);
+                const float power = eval_power(co, dx, dy);
+                if (power > 0.0f) continue;
+                const float alpha = fminf(0.99f, __fmul_rn(co.w, expf(power)));
+                if (alpha < 1.0f / 255.0f) continue;
+                const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
+                if (test_T < 0.0001f) {
+                    done = true;
+                    break;
+                }
+                const float4 f0 = sm.feat[s][j * FV];
+                acc[0] = __fmaf_rn(__fmul_rn(f0.x, alpha), T, acc[0]);
+                acc[1] = __fmaf_rn(__fmul_rn(f0.y, alpha), T, acc[1]);
+                acc[2] = __fmaf_rn(__fmul_rn(f0.z, alpha), T, acc[2]);
+                if (C == 6) {
+                    const float4 f1 = sm.feat[s][j * FV + FV - 1];
+                    acc[3 % C] = __fmaf_rn(__fmul_rn(f0.w, alpha), T, acc[3 % C]);
+                    acc[4 % C] = __fmaf_rn(__fmul_rn(f1.x, alpha), T, acc[4 % C]);
+                    acc[5 % C] = __fmaf_rn(__fmul_rn(f1.y, alpha), T, acc[5 % C]);
+                }
+                if (T > 0.5f && test_T < 0.5f) D = ge.z;  // forward.cu:370-374
+                T = test_T;
+                last_contributor = contributor;
+            }
+        }
+        consumed = b + 1;
+        // all 256 pixels finished => stop (forward.cu:315-317); the barrier also frees stage s for reuse
+        if (__syncthreads_count(done) == BL_THREADS) break;
+        if (threadIdx.x == 0 && b + 2 < nb) {
+            const int nstart = (b + 2) * BL_BATCH;
+            issue_batch<C>(sm, s, inst_conic, inst_geom, inst_feat, range.x + nstart, min(BL_BATCH, len - nstart));
+        }
+    }
+    // a copy that was issued but never consumed must land before this CTA's shared memory is released
+    if (consumed < nb && consumed >= 1) mbar_wait(&sm.bar[consumed & 1], (uint32_t)((consumed >> 1) & 1));
+
+    if (inside) {
+        const size_t pix_id = (size_t)W * py + px;
+        final_T[pix_id] = T;
+        n_contrib[pix_id] = last_contributor;
+#pragma unroll
+        for (int ch = 0; ch < C; ch++) out_color[(size_t)ch * H * W + pix_id] = __fmaf_rn(T, __ldg(bg + ch), acc[ch]);
+        out_depth[pix_id] = D;
+        out_opacity[pix_id] = __fsub_rn(1.f, T);
+    }
+}
+
+// Sum 16 per-lane values over the warp.  On return lane l holds in v[0] the warp total of value (l >> 1).
+__device__ __forceinline__ void warp_transpose_reduce16(float (&v)[16], int lane) {
+    {
+        const bool up = lane & 16;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const float send = up ? v[k] : v[k + 8];
+            const float keep = up ? v[k + 8] : v[k];
+            v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+        }
+    }
+    {
+        const bool up = lane & 8;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const float send = up ? v[k] : v[k + 4];
+            const float keep = up ? v[k + 4] : v[k];
+            v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+        }
+    }
+    {
+        const bool up = lane & 4;
+#pragma unroll
+        for (int k = 0; k < 2; k++) {
+            const float send = up ? v[k] : v[k + 2];
+            const float keep = up ? v[k + 2] : v[k];
+            v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+        }
+    }
+    {
+        const bool up = lane & 2;
+        const float send = up ? v[0] : v[1];
+        const float keep = up ? v[1] : v[0];
+        v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+    }
+    v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
+}
+
+template <int C>
+__global__ void __launch_bounds__(BL_THREADS)
+blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict__ inst_conic,
+                      const float4* __restrict__ inst_geom, const float4* __restrict__ inst_feat, int W, int H,
+                      int gx, const float* __restrict__ bg, const float* __restrict__ final_Ts,
+                      const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
+                      float* __restrict__ gacc) {
+    constexpr int FV = BlendSmem<C>::FV;
+    constexpr int NV = 6 + C;  // live gradient terms per (pixel, Gaussian)
+    __shared__ __align__(128) BlendSmem<C> sm;
+    __shared__ __align__(16) float s_acc[BL_BATCH * 16];
+    __shared__ int s_max_contrib;
+
+    const int tile = blockIdx.x;
+    const int tx = tile % gx, ty = tile / gx;
+    const int px = tx * TILE_X + (threadIdx.x & (TILE_X - 1));
+    const int py = ty * TILE_Y + (threadIdx.x / TILE_X);
+    const bool inside = px < W && py < H;
+    const float pxf = (float)px, pyf = (float)py;
+    const size_t pix_id = (size_t)W * py + px;
+    const int lane = threadIdx.x & 31;
+    const uint2 range = ranges[tile];
+
+    const float T_final = inside ? final_Ts[pix_id] : 0.f;
+    float T = T_final;
+    const int last_contributor = inside ? (int)n_contrib[pix_id] : 0;
+
+    if (threadIdx.x == 0) {
+        s_max_contrib = 0;
+        mbar_init(&sm.bar[0], 1);
+        mbar_init(&sm.bar[1], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    const int warp_max = __reduce_max_sync(0xffffffffu, last_contributor);
+    if (lane == 0 && warp_max > 0) atomicMax(&s_max_contrib, warp_max);
+    __syncthreads();
+    // Entries at list index >= len are skipped by every pixel of the tile (backward.cu:489-490).
+    const int len = s_max_contrib;
+    const int nb = (len + BL_BATCH - 1) / BL_BATCH;
+    // batch k covers list indices [hi_k - cnt_k, hi_k), hi_k = len - k*BATCH, walked back to front
+    if (threadIdx.x == 0) {
+        if (nb > 0) {
+            const int cnt = min(BL_BATCH, len);
+            issue_batch<C>(sm, 0, inst_conic, inst_geom, inst_feat, range.x + (uint32_t)(len - cnt), cnt);
+        }
+        if (nb > 1) {
+            const int hi = len - BL_BATCH, cnt = min(BL_BATCH, hi);
+            issue_batch<C>(sm, 1, inst_conic, inst_geom, inst_feat, range.x + (uint32_t)(hi - cnt), cnt);
+        }
+    }
+
+    float accum_rec[C], last_color[C], dL_dpixel[C];
+    float bg_dot_dpixel = 0.f;
+#pragma unroll
+    for (int ch = 0; ch < C; ch++) {
+        accum_rec[ch] = 0.f;
+        last_color[ch] = 0.f;
+        dL_dpixel[ch] = inside ? __ldg(dL_dpixels + (size_t)ch * H * W + pix_id) : 0.f;
+        bg_dot_dpixel += __ldg(bg + ch) * dL_dpixel[ch];
+    }
+    float last_alpha = 0.f;
+    const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;  // backward.cu:460-461
+
+    for (int b = 0; b < nb; b++) {
+        const int s = b & 1;
+        const int hi = len - b * BL_BATCH;
+        const int cnt = min(BL_BATCH, hi);
+        const int lo = hi - cnt;  // list index of record 0 of this batch
+        // clear the batch accumulator (16 floats per instance)
+        {
+            float4* a4 = reinterpret_cast<float4*>(s_acc);
+            for (int i = threadIdx.x; i < cnt * 4; i += BL_THREADS) a4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        mbar_wait(&sm.bar[s], (uint32_t)((b >> 1) & 1));
+        __syncthreads();
+
+        // records at list index >= warp_max are skipped by the whole warp
+        const int jstart = min(cnt, warp_max - lo) - 1;
+        for (int j = jstart; j >= 0; j--) {
+            const int idx = lo + j;  // the reference's `contributor` after its decrement
+            float v[16];
+#pragma unroll
+            for (int k = 0; k < 16; k++) v[k] = 0.f;
+            bool active = idx < last_contributor;
+            if (active) {
+                const float4 co = sm.conic[s][j];
+                const float4 ge = sm.geom[s][j];
+                const float dx = __fsub_rn(ge.x, pxf), dy = __fsub_rn(ge.y, pyf);
+                const float power = eval_power(co, dx, dy);
+                const float G = expf(power);
+                const float alpha = fminf(0.99f, __fmul_rn(co.w, G));
+                active = !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                if (active) {
+                    T = T / (1.f - alpha);
+                    const float dchannel_dcolor = alpha * T;
+                    const float4 f0 = sm.feat[s][j * FV];
+                    const float4 f1 = sm.feat[s][j * FV + FV - 1];
+                    float col[C];
+                    col[0] = f0.x; col[1] = f0.y; col[2] = f0.z;
+                    if (C == 6) { col[3 % C] = f0.w; col[4 % C] = f1.x; col[5 % C] = f1.y; }
+                    float dL_dalpha = 0.f;
+#pragma unroll
+                    for (int ch = 0; ch < C; ch++) {
+                        accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
+                        last_color[ch] = col[ch];
+                        dL_dalpha += (col[ch] - accum_rec[ch]) * dL_dpixel[ch];
+                        v[6 + ch] = dchannel_dcolor * dL_dpixel[ch];
+                    }
+                    dL_dalpha *= T;
+                    last_alpha = alpha;
+                    dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;  // backward.cu:531-534
+                    const float dL_dG = co.w * dL_dalpha;                     // straight-through clamp (:538)
+                    const float gdx = G * dx, gdy = G * dy;
+                    const float dG_ddelx = -gdx * co.x - gdy * co.y;
+                    const float dG_ddely = -gdy * co.z - gdx * co.y;
+                    v[0] = -0.5f * gdx * dx * dL_dG;
+                    v[1] = -0.5f * gdx * dy * dL_dG;
+                    v[2] = -0.5f * gdy * dy * dL_dG;
+                    v[3] = G * dL_dalpha;
+                    v[4] = dL_dG * dG_ddelx * ddelx_dx;
+                    v[5] = dL_dG * dG_ddely * ddely_dy;
+                }
+            }
+            if (!__any_sync(0xffffffffu, active)) continue;
+            warp_transpose_reduce16(v, lane);
+            if (!(lane & 1) && (lane >> 1) < NV) atomicAdd(&s_acc[j * 16 + (lane >> 1)], v[0]);
+        }
+        __syncthreads();
+        // flush: two threads per instance; 3 (C=6) or 2.25 (C=3) vector reductions per touched instance
+        {
+            const int inst = threadIdx.x >> 1, half = threadIdx.x & 1;
+            if (inst < cnt) {
+                const uint32_t id = __float_as_uint(sm.geom[s][inst].w);
+                float* dst = gacc + (size_t)id * GACC_STRIDE;
+                const float4* a4 = reinterpret_cast<const float4*>(s_acc + inst * 16);
+                if (half == 0) {
+                    const float4 x = a4[0], y = a4[1];
+                    if (x.x != 0.f || x.y != 0.f || x.z != 0.f || x.w != 0.f) red_add_v4(dst, x.x, x.y, x.z, x.w);
+                    if (y.x != 0.f || y.y != 0.f || y.z != 0.f || y.w != 0.f) red_add_v4(dst + 4, y.x, y.y, y.z, y.w);
+                } else {
+                    const float4 z = a4[2];
+                    if (z.x != 0.f || z.y != 0.f || z.z != 0.f || z.w != 0.f) red_add_v4(dst + 8, z.x, z.y, z.z, z.w);
+                }
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0 && b + 2 < nb) {
+            const int nhi = len - (b + 2) * BL_BATCH, ncnt = min(BL_BATCH, nhi);
+            issue_batch<C>(sm, s, inst_conic, inst_geom, inst_feat, range.x + (uint32_t)(nhi - ncnt), ncnt);
+        }
+    }
+}
+
+}  // namespace
+
+void launch_blend_forward(int channels, int W, int H, const uint2* ranges, const BinningState& b, const float* bg,
+                          float* out_color, float* out_depth, float* out_opacity, float* final_T,
+                          uint32_t* n_contrib, cudaStream_t st) {
+    const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
+    if (gx * gy <= 0) return;
+    if (channels == 3)
+        blend_forward_kernel<3><<<gx * gy, BL_THREADS, 0, st>>>(ranges, b.inst_conic, b.inst_geom, b.inst_feat, W, H,
+                                                                 gx, bg, out_color, out_depth, out_opacity, final_T,
+                                                                 n_contrib);
+    else
+        blend_forward_kernel<6><<<gx * gy, BL_THREADS, 0, st>>>(ranges, b.inst_conic, b.inst_geom, b.inst_feat, W, H,
+                                                                 gx, bg, out_color, out_depth, out_opacity, final_T,
+                                                                 n_contrib);
+}
+
+void launch_blend_backward(int channels, int W, int H, const uint2* ranges, const BinningState& b, const float* bg,
+                           const float* final_T, const uint32_t* n_contrib, const float* dL_dpix, float* gacc,
+                           cudaStream_t st) {
+    const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
+    if (gx * gy <= 0) return;
+    if (channels == 3)
+        blend_backward_kernel<3><<<gx * gy, BL_THREADS, 0, st>>>(ranges, b.inst_conic, b.inst_geom, b.inst_feat, W, H,
+                                                                  gx, bg, final_T, n_contrib, dL_dpix, gacc);
+    else
+        blend_backward_kernel<6><<<gx * gy, BL_THREADS, 0, st>>>(ranges, b.inst_conic, b.inst_geom, b.inst_feat, W, H,
+                                                                  gx, bg, final_T, n_contrib, dL_dpix, gacc);
+}
+
+}  // namespace asb

@@ -1,0 +1,297 @@
+// capi.cu -- host orchestration and the C ABI of libactivesplat_b200.so (see include/activesplat_b200.h).
+//
+//   as_forward   follows CudaRasterizer::Rasterizer::forward   dgr/cuda_rasterizer/rasterizer_impl.cu:198-342
+//   as_backward  follows CudaRasterizer::Rasterizer::backward  rasterizer_impl.cu:346-441
+//   scratch      follows GeometryState/ImageState/BinningState::fromChunk + required<T>
+//                rasterizer_impl.cu:155-194, rasterizer_impl.h:21-72
+#include <cstdio>
+#include <cstring>
+
+#include "common.cuh"
+
+namespace asb {
+
+static thread_local int g_last_cuda_error = 0;
+
+GeometryState GeometryState::fromChunk(char*& chunk, size_t P) {
+    GeometryState g;
+    Bump b(chunk);
+    g.depths = b.take<float>(P);
+    g.means2D = b.take<float2>(P);
+    g.conic_opacity = b.take<float4>(P);
+    g.tiles_touched = b.take<uint32_t>(P);
+    g.point_offsets = b.take<uint32_t>(P);
+    g.radii = b.take<int>(P);
+    g.gacc = b.take<float>(P * GACC_STRIDE);
+    g.scan_temp = b.take<uint32_t>((scan_temp_bytes((int)P) + 3) / 4);
+    g.num_rendered = b.take<uint32_t>(64);
+    chunk = b.p;
+    return g;
+}
+
+ImageState ImageState::fromChunk(char*& chunk, size_t N, size_t tiles) {
+    ImageState img;
+    Bump b(chunk);
+    img.final_T = b.take<float>(N);
+    img.n_contrib = b.take<uint32_t>(N);
+    img.ranges = b.take<uint2>(tiles);
+    chunk = b.p;
+    return img;
+}
+
+BinningState BinningState::fromChunk(char*& chunk, size_t R, int channels) {
+    BinningState s;
+    Bump b(chunk);
+    const size_t fv = channels == 3 ? 1 : 2;
+    s.keys_unsorted = b.take<uint64_t>(R);
+    s.keys_sorted = b.take<uint64_t>(R);
+    s.values_unsorted = b.take<uint32_t>(R);
+    s.point_list = b.take<uint32_t>(R);
+    s.inst_conic = b.take<float4>(R);
+    s.inst_geom = b.take<float4>(R);
+    s.inst_feat = b.take<float4>(R * fv);
+    s.sort_temp_bytes = asb::sort_temp_bytes((int)R);
+    s.sort_temp = b.take<char>(s.sort_temp_bytes);
+    chunk = b.p;
+    return s;
+}
+
+template <typename F>
+static size_t required_bytes(F make) {
+    char* p = nullptr;
+    make(p);
+    return reinterpret_cast<size_t>(p) + 256;
+}
+
+static int check(cudaError_t e) {
+    if (e == cudaSuccess) return AS_OK;
+    g_last_cuda_error = (int)e;
+    return AS_ERR_CUDA;
+}
+
+// auxiliary.h:166-173 CHECK_CUDA: in debug mode synchronise after the stage and surface failures
+static int stage_check(cudaStream_t st, int debug) {
+    if (debug) {
+        int r = check(cudaStreamSynchronize(st));
+        if (r) return r;
+    }
+    return check(cudaGetLastError());
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+}  // namespace asb
+
+using namespace asb;
+
+extern "C" {
+
+size_t as_geometry_bytes(int P) {
+    return required_bytes([&](char*& p) { GeometryState::fromChunk(p, (size_t)(P > 0 ? P : 0)); });
+}
+size_t as_image_bytes(int width, int height) {
+    const size_t N = (size_t)width * height;
+    const size_t tiles = (size_t)((width + TILE_X - 1) / TILE_X) * ((height + TILE_Y - 1) / TILE_Y);
+    return required_bytes([&](char*& p) { ImageState::fromChunk(p, N, tiles); });
+}
+size_t as_binning_bytes(int num_rendered, int channels) {
+    return required_bytes([&](char*& p) { BinningState::fromChunk(p, (size_t)(num_rendered > 0 ? num_rendered : 0), channels); });
+}
+
+int as_scratch_layout(int P, int width, int height, int num_rendered, int channels, AsScratchLayout* out) {
+    if (!out || P < 0 || width <= 0 || height <= 0 || num_rendered < 0 || (channels != 3 && channels != 6))
+        return AS_ERR_INVALID_ARG;
+    char* p = nullptr;
+    GeometryState g = GeometryState::fromChunk(p, (size_t)P);
+    out->depths = (size_t)g.depths;
+    out->means2D = (size_t)g.means2D;
+    out->conic_opacity = (size_t)g.conic_opacity;
+    out->cov3D = (size_t)-1;  // not stored: the backward recomputes it from scale/rotation
+    out->tiles_touched = (size_t)g.tiles_touched;
+    out->point_offsets = (size_t)g.point_offsets;
+    out->radii = (size_t)g.radii;
+    p = nullptr;
+    BinningState b = BinningState::fromChunk(p, (size_t)num_rendered, channels);
+    out->keys_unsorted = (size_t)b.keys_unsorted;
+    out->values_unsorted = (size_t)b.values_unsorted;
+    out->keys_sorted = (size_t)b.keys_sorted;
+    out->point_list = (size_t)b.point_list;
+    p = nullptr;
+    const size_t tiles = (size_t)((width + TILE_X - 1) / TILE_X) * ((height + TILE_Y - 1) / TILE_Y);
+    ImageState img = ImageState::fromChunk(p, (size_t)width * height, tiles);
+    out->final_T = (size_t)img.final_T;
+    out->n_contrib = (size_t)img.n_contrib;
+    out->ranges = (size_t)img.ranges;
+    return AS_OK;
+}
+
+uint32_t as_higher_msb(uint32_t n) {  // rasterizer_impl.cu:35-50
+    uint32_t msb = sizeof(n) * 4;
+    uint32_t step = msb;
+    while (step > 1) {
+        step /= 2;
+        if (n >> msb) msb += step;
+        else msb -= step;
+    }
+    if (n >> msb) msb++;
+    return msb;
+}
+
+int as_forward(const AsForwardArgs* a, AsAllocFn geometryBuffer, AsAllocFn binningBuffer, AsAllocFn imageBuffer,
+               void* alloc_ctx, void* cuda_stream) {
+    if (!a || !geometryBuffer || !binningBuffer || !imageBuffer) return AS_ERR_INVALID_ARG;
+    if (a->P < 0 || a->width <= 0 || a->height <= 0 || (a->channels != 3 && a->channels != 6)) return AS_ERR_INVALID_ARG;
+    if (!a->out_color || !a->out_depth || !a->out_opacity || !a->background) return AS_ERR_INVALID_ARG;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
+    const int P = a->P, W = a->width, H = a->height, C = a->channels;
+    const size_t N = (size_t)W * H;
+    if (P == 0) {  // rasterize_points.cu:83: nothing is launched, outputs stay at their fill value 0
+        int r = check(cudaMemsetAsync(a->out_color, 0, sizeof(float) * C * N, st));
+        if (!r) r = check(cudaMemsetAsync(a->out_depth, 0, sizeof(float) * N, st));
+        if (!r) r = check(cudaMemsetAsync(a->out_opacity, 0, sizeof(float) * N, st));
+        return r;
+    }
+    if (!a->colors_precomp) return AS_ERR_NO_COLORS;  // rasterizer_impl.cu:244-247
+    if (!a->means3D || !a->opacities || !a->viewmatrix || !a->projmatrix) return AS_ERR_INVALID_ARG;
+    if (!a->cov3D_precomp && (!a->scales || !a->rotations)) return AS_ERR_INVALID_ARG;
+    if (a->rotations && !aligned16(a->rotations)) return AS_ERR_INVALID_ARG;
+
+    const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
+    const int tiles = gx * gy;
+
+    char* gchunk = geometryBuffer(alloc_ctx, as_geometry_bytes(P));
+    if (!gchunk) return AS_ERR_ALLOC;
+    GeometryState g = GeometryState::fromChunk(gchunk, (size_t)P);
+    char* ichunk = imageBuffer(alloc_ctx, as_image_bytes(W, H));
+    if (!ichunk) return AS_ERR_ALLOC;
+    ImageState img = ImageState::fromChunk(ichunk, N, (size_t)tiles);
+
+    int r;
+    launch_preprocess_forward(P, a->means3D, a->scales, a->rotations, a->opacities, a->cov3D_precomp, a->viewmatrix,
+                              a->projmatrix, W, H, a->tan_fovx, a->tan_fovy, a->scale_modifier, a->radii, g, st);
+    if ((r = stage_check(st, a->debug))) return r;
+    launch_inclusive_scan(g.tiles_touched, g.point_offsets, P, g.num_rendered, g.scan_temp, st);
+    if ((r = stage_check(st, a->debug))) return r;
+
+    // The one host round trip of the reference (rasterizer_impl.cu:283): R sizes the binning buffer.
+    uint32_t R_host = 0;
+    if ((r = check(cudaMemcpyAsync(&R_host, g.num_rendered, sizeof(uint32_t), cudaMemcpyDeviceToHost, st)))) return r;
+    if ((r = check(cudaStreamSynchronize(st)))) return r;
+    const int R = (int)R_host;
+
+    char* bchunk = binningBuffer(alloc_ctx, as_binning_bytes(R, C));
+    if (!bchunk) return AS_ERR_ALLOC;
+    BinningState b = BinningState::fromChunk(bchunk, (size_t)R, C);
+
+    if (R > 0) {
+        launch_duplicate_with_keys(P, g, g.radii, W, H, b.keys_unsorted, b.values_unsorted, st);
+        if ((r = stage_check(st, a->debug))) return r;
+        const int bit = (int)as_higher_msb((uint32_t)tiles);
+        launch_sort_pairs(b.keys_unsorted, b.values_unsorted, b.keys_sorted, b.point_list, R, 32 + bit, b.sort_temp, st);
+        if ((r = stage_check(st, a->debug))) return r;
+    }
+    launch_ranges_and_gather(R, tiles, C, b.keys_sorted, b.point_list, g, a->colors_precomp, b, img.ranges, st);
+    if ((r = stage_check(st, a->debug))) return r;
+    launch_blend_forward(C, W, H, img.ranges, b, a->background, a->out_color, a->out_depth, a->out_opacity,
+                         img.final_T, img.n_contrib, st);
+    if ((r = stage_check(st, a->debug))) return r;
+    return R;
+}
+
+int as_backward(const AsBackwardArgs* a, void* cuda_stream) {
+    if (!a) return AS_ERR_INVALID_ARG;
+    if (a->P < 0 || a->R < 0 || a->width <= 0 || a->height <= 0 || (a->channels != 3 && a->channels != 6))
+        return AS_ERR_INVALID_ARG;
+    if (a->P == 0) return AS_OK;
+    if (!a->geom_buffer || !a->image_buffer || !a->dL_dpix || !a->means3D || !a->viewmatrix || !a->projmatrix ||
+        !a->background)
+        return AS_ERR_INVALID_ARG;
+    if (a->R > 0 && !a->binning_buffer) return AS_ERR_INVALID_ARG;
+    if (!a->cov3D_precomp && (!a->scales || !a->rotations)) return AS_ERR_INVALID_ARG;
+    if ((a->rotations && !aligned16(a->rotations)) || (a->dL_drot && !aligned16(a->dL_drot)) ||
+        (a->dL_dconic && !aligned16(a->dL_dconic)))
+        return AS_ERR_INVALID_ARG;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
+    const int P = a->P, W = a->width, H = a->height, C = a->channels, R = a->R;
+    const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
+
+    char* gchunk = a->geom_buffer;
+    GeometryState g = GeometryState::fromChunk(gchunk, (size_t)P);
+    char* ichunk = a->image_buffer;
+    ImageState img = ImageState::fromChunk(ichunk, (size_t)W * H, (size_t)gx * gy);
+    const int* radii = a->radii ? a->radii : g.radii;
+
+    int r;
+    if ((r = check(cudaMemsetAsync(g.gacc, 0, sizeof(float) * GACC_STRIDE * (size_t)P, st)))) return r;
+    if (R > 0) {
+        char* bchunk = a->binning_buffer;
+        BinningState b = BinningState::fromChunk(bchunk, (size_t)R, C);
+        launch_blend_backward(C, W, H, img.ranges, b, a->background, img.final_T, img.n_contrib, a->dL_dpix, g.gacc, st);
+        if ((r = stage_check(st, a->debug))) return r;
+    }
+    PreprocessBackwardOut o;
+    o.dL_dmean2D = a->dL_dmean2D;
+    o.dL_dconic = a->dL_dconic;
+    o.dL_dopacity = a->dL_dopacity;
+    o.dL_dcolor = a->dL_dcolor;
+    o.dL_dmean3D = a->dL_dmean3D;
+    o.dL_dcov3D = a->dL_dcov3D;
+    o.dL_dscale = a->dL_dscale;
+    o.dL_drot = a->dL_drot;
+    launch_preprocess_backward(P, C, a->means3D, radii, a->scales, a->rotations, a->cov3D_precomp, a->scale_modifier,
+                               a->viewmatrix, a->projmatrix, W, H, a->tan_fovx, a->tan_fovy, nullptr, g.gacc, o, st);
+    return stage_check(st, a->debug);
+}
+
+int as_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* /*projmatrix*/,
+                    uint8_t* present, void* cuda_stream) {
+    if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) return AS_ERR_INVALID_ARG;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
+    launch_mark_visible(P, means3D, viewmatrix, present, st);
+    return check(cudaGetLastError());
+}
+
+size_t as_sort_temp_bytes(int n) { return sort_temp_bytes(n); }
+
+int as_sort_pairs(const uint64_t* keys_in, const uint32_t* values_in, uint64_t* keys_out, uint32_t* values_out,
+                  int n, int end_bit, void* temp, size_t temp_bytes, void* cuda_stream) {
+    if (n < 0 || end_bit < 0 || end_bit > 64) return AS_ERR_INVALID_ARG;
+    if (n == 0) return AS_OK;
+    if (!keys_in || !values_in || !keys_out || !values_out || !temp) return AS_ERR_INVALID_ARG;
+    if (temp_bytes < sort_temp_bytes(n)) return AS_ERR_CAPACITY;
+    if (reinterpret_cast<uintptr_t>(temp) & 255) return AS_ERR_INVALID_ARG;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
+    launch_sort_pairs(keys_in, values_in, keys_out, values_out, n, end_bit, reinterpret_cast<char*>(temp), st);
+    return check(cudaGetLastError());
+}
+
+size_t as_scan_temp_bytes(int n) { return scan_temp_bytes(n); }
+
+int as_inclusive_scan_u32(const uint32_t* in, uint32_t* out, int n, uint32_t* total_out, void* temp,
+                          size_t temp_bytes, void* cuda_stream) {
+    if (n < 0) return AS_ERR_INVALID_ARG;
+    if (n > 0 && (!in || !out || !temp)) return AS_ERR_INVALID_ARG;
+    if (temp_bytes < scan_temp_bytes(n)) return AS_ERR_CAPACITY;
+    if (reinterpret_cast<uintptr_t>(temp) & 15) return AS_ERR_INVALID_ARG;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
+    launch_inclusive_scan(in, out, n, total_out, reinterpret_cast<uint32_t*>(temp), st);
+    return check(cudaGetLastError());
+}
+
+const char* as_error_string(int code) {
+    switch (code) {
+        case AS_OK: return "ok";
+        case AS_ERR_INVALID_ARG: return "invalid argument";
+        case AS_ERR_NO_COLORS: return "For non-RGB, provide precomputed Gaussian colors!";
+        case AS_ERR_ALLOC: return "scratch allocator returned NULL";
+        case AS_ERR_CUDA: return cudaGetErrorString((cudaError_t)g_last_cuda_error);
+        case AS_ERR_CAPACITY: return "buffer capacity too small";
+        default: return code > 0 ? "ok" : "unknown error";
+    }
+}
+
+int as_last_cuda_error(void) { return g_last_cuda_error; }
+
+const char* as_version(void) { return "activesplat_b200 0.1 (sm_100a)"; }
+
+}  // extern "C"

@@ -130,7 +130,7 @@ def room_pose(k, K, radius=1.5, height=0.0):
     return c2w
 
 
-def s_room(P, K, seed, W=640, H=480, hfov_deg=90.0):
+def s_room(P, K, seed, W=640, H=480, hfov_deg=90.0, scale_mult=1.0):
     """S-room(P, K, seed): points on the 6 faces of a 10 x 3 x 8 m box seen from K poses on a circle.
     Returns (params dict, [CameraSpec] * K).  Scales follow the 1-pixel rule w.r.t. camera 0's focal
     length at the point's distance from the room centre."""
@@ -144,7 +144,7 @@ def s_room(P, K, seed, W=640, H=480, hfov_deg=90.0):
     pts[torch.arange(P), axis] = sign * half[axis]
     fx, fy, cx, cy = compute_intrinsics(W, H, math.radians(hfov_deg))
     dist = pts.norm(dim=1).clamp_min(0.5)
-    params = _finish_params(pts, dist, fx, g)
+    params = _finish_params(pts, dist * scale_mult, fx, g)
     cams = [CameraSpec(W, H, fx, fy, cx, cy, np.linalg.inv(room_pose(k, K))) for k in range(K)]
     return params, cams
 

@@ -1,0 +1,164 @@
+/*
+ * activesplat_b200.h -- C ABI of libactivesplat_b200.so
+ *
+ * The drop-in boundary for ActiveSplat's rasterizer hot path.  Everything here is plain C:
+ * device pointers, sizes, a CUDA stream passed as void*.  No torch / C++ types cross it.
+ * The library keeps no state between calls and allocates no device memory of its own: outputs
+ * are caller-owned and scratch comes from caller-supplied allocator callbacks, exactly like the
+ * reference (dgr = /root/reference/submodules/diff-gaussian-rasterization):
+ *
+ *   as_forward       replaces CudaRasterizer::Rasterizer::forward      dgr/cuda_rasterizer/rasterizer.h:33-60
+ *                                                                       (impl rasterizer_impl.cu:198-342)
+ *   as_backward      replaces CudaRasterizer::Rasterizer::backward     rasterizer.h:62-86 (impl :346-441)
+ *   as_mark_visible  replaces CudaRasterizer::Rasterizer::markVisible  rasterizer.h:24-29 (impl :141-153)
+ *   AsAllocFn        replaces std::function<char*(size_t)>             rasterizer.h:34-36, rasterize_points.cu:27-33
+ *
+ * All functions return >= 0 on success and a negative AS_ERR_* code on failure;
+ * as_error_string() turns a code into text.  Every entry point is re-entrant and may be called
+ * concurrently on different streams / devices.
+ */
+#ifndef ACTIVESPLAT_B200_H
+#define ACTIVESPLAT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AS_OK 0
+#define AS_ERR_INVALID_ARG (-1)   /* null pointer / negative size / unsupported channel count */
+#define AS_ERR_NO_COLORS (-2)     /* colors_precomp == NULL: "For non-RGB, provide precomputed Gaussian colors!" (rasterizer_impl.cu:244-247); SH evaluation is not on the ActiveSplat path (sh_degree 0 + colors_precomp always) */
+#define AS_ERR_ALLOC (-3)         /* an allocator callback returned NULL */
+#define AS_ERR_CUDA (-4)          /* a CUDA runtime call or (debug mode) a kernel failed; see as_last_cuda_error() */
+#define AS_ERR_CAPACITY (-5)      /* a caller-sized buffer is too small (fused / no-sync entries) */
+
+/* Scratch allocator: returns a DEVICE pointer to at least `bytes` bytes (128-byte aligned or better),
+ * valid until the matching as_backward has run.  Mirrors the resize lambdas of rasterize_points.cu:27-33. */
+typedef char* (*AsAllocFn)(void* ctx, size_t bytes);
+
+/* Arguments of Rasterizer::forward (rasterizer.h:33-60), in the same order, as a POD.
+ * All pointers are device pointers to contiguous fp32 unless stated.  Optional inputs are NULL
+ * when absent (the reference passes the null data pointer of an empty CPU tensor). */
+typedef struct AsForwardArgs {
+    int P;                       /* number of Gaussians */
+    int D;                       /* SH degree (must be 0 on this path) */
+    int M;                       /* SH coefficients per Gaussian (ignored) */
+    int channels;                /* 3 = reference NUM_CHANNELS (config.h:15); 6 = fused [rgb | z,1,z^2] bundle */
+    const float* background;     /* [channels] */
+    int width, height;
+    const float* means3D;        /* [P,3] */
+    const float* shs;            /* unused, may be NULL */
+    const float* colors_precomp; /* [P,channels] */
+    const float* opacities;      /* [P] */
+    const float* scales;         /* [P,3] or NULL when cov3D_precomp is given */
+    float scale_modifier;
+    const float* rotations;      /* [P,4] (r,x,y,z), used as given (forward.cu:127) */
+    const float* cov3D_precomp;  /* [P,6] or NULL */
+    const float* viewmatrix;     /* [16] = w2c^T flattened (column-major w2c) */
+    const float* projmatrix;     /* [16] = (P_gl w2c)^T flattened */
+    const float* cam_pos;        /* [3], unused without SH */
+    float tan_fovx, tan_fovy;
+    int prefiltered;
+    float* out_color;            /* [channels,H,W] */
+    float* out_depth;            /* [1,H,W] median depth (15.0 where T never crosses 0.5) */
+    float* out_opacity;          /* [1,H,W] 1 - T */
+    int* radii;                  /* [P] int32, may be NULL */
+    int debug;                   /* non-zero: synchronise and check after every stage (auxiliary.h:166-173) */
+} AsForwardArgs;
+
+/* Arguments of Rasterizer::backward (rasterizer.h:62-86).  Gradient buffers are caller-owned;
+ * the library zero-fills what it needs itself (the caller does NOT have to pre-zero them). */
+typedef struct AsBackwardArgs {
+    int P, D, M, R;              /* R = num_rendered returned by as_forward */
+    int channels;
+    const float* background;
+    int width, height;
+    const float* means3D;
+    const float* shs;
+    const float* colors_precomp;
+    const float* scales;
+    float scale_modifier;
+    const float* rotations;
+    const float* cov3D_precomp;
+    const float* viewmatrix;
+    const float* projmatrix;
+    const float* cam_pos;
+    float tan_fovx, tan_fovy;
+    const int* radii;            /* may be NULL: the copy kept in the geometry buffer is used */
+    char* geom_buffer;           /* the three scratch buffers handed out during as_forward */
+    char* binning_buffer;
+    char* image_buffer;
+    const float* dL_dpix;        /* [channels,H,W] */
+    float* dL_dmean2D;           /* [P,3]  (x,y in NDC units, z = 0; backward.cu:460-461,545-546) */
+    float* dL_dconic;            /* [P,4]  (x,y,w used) -- may be NULL */
+    float* dL_dopacity;          /* [P] */
+    float* dL_dcolor;            /* [P,channels] */
+    float* dL_dmean3D;           /* [P,3] */
+    float* dL_dcov3D;            /* [P,6] -- may be NULL unless cov3D_precomp is given */
+    float* dL_dsh;               /* unused, may be NULL */
+    float* dL_dscale;            /* [P,3] */
+    float* dL_drot;              /* [P,4] */
+    int debug;
+} AsBackwardArgs;
+
+/* ---- the three reference entry points ------------------------------------------------------ */
+
+/* Returns num_rendered (>= 0).  Performs ONE host synchronisation on `stream` to learn
+ * num_rendered before sizing the binning buffer, like rasterizer_impl.cu:283. */
+int as_forward(const AsForwardArgs* args, AsAllocFn geometryBuffer, AsAllocFn binningBuffer,
+               AsAllocFn imageBuffer, void* alloc_ctx, void* cuda_stream);
+
+int as_backward(const AsBackwardArgs* args, void* cuda_stream);
+
+/* present[i] = (w2c * p_i).z > 0.2  (auxiliary.h:154); present is uint8 (bool) [P]. */
+int as_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                    uint8_t* present, void* cuda_stream);
+
+/* ---- scratch sizing / layout (rasterizer_impl.h:21-72 `required<T>` / `fromChunk`) ---------- */
+size_t as_geometry_bytes(int P);
+size_t as_image_bytes(int width, int height);
+size_t as_binning_bytes(int num_rendered, int channels);
+
+/* Byte offsets inside the scratch buffers, for parity tests that compare intermediates.
+ * (The layout is private to the library; offsets are relative to the pointer the allocator returned.) */
+typedef struct AsScratchLayout {
+    /* geometry buffer */
+    size_t depths, means2D, conic_opacity, cov3D, tiles_touched, point_offsets, radii;
+    /* binning buffer */
+    size_t keys_unsorted, values_unsorted, keys_sorted, point_list;
+    /* image buffer */
+    size_t final_T, n_contrib, ranges;
+} AsScratchLayout;
+int as_scratch_layout(int P, int width, int height, int num_rendered, int channels, AsScratchLayout* out);
+
+/* ---- stage-level entry points (used by the fused paths and by parity tests) ----------------- */
+
+/* Stable ascending LSD radix sort (hand-written onesweep) of n (u64 key, u32 value) pairs on key bits
+ * [0, end_bit).  Replaces cub::DeviceRadixSort::SortPairs as called at rasterizer_impl.cu:305-310.
+ * temp must hold as_sort_temp_bytes(n) bytes.  keys_in/values_in are preserved. */
+size_t as_sort_temp_bytes(int n);
+int as_sort_pairs(const uint64_t* keys_in, const uint32_t* values_in, uint64_t* keys_out,
+                  uint32_t* values_out, int n, int end_bit, void* temp, size_t temp_bytes,
+                  void* cuda_stream);
+
+/* Inclusive prefix sum of n u32 (single-pass decoupled look-back).  Replaces cub::DeviceScan::InclusiveSum
+ * (rasterizer_impl.cu:279).  temp must hold as_scan_temp_bytes(n) bytes; total (last element) is also
+ * written to *total_out (device u32) when total_out != NULL. */
+size_t as_scan_temp_bytes(int n);
+int as_inclusive_scan_u32(const uint32_t* in, uint32_t* out, int n, uint32_t* total_out, void* temp,
+                          size_t temp_bytes, void* cuda_stream);
+
+/* getHigherMsb (rasterizer_impl.cu:35-50) */
+uint32_t as_higher_msb(uint32_t n);
+
+const char* as_error_string(int code);
+/* cudaError_t value recorded by the last failing call on this host thread (0 = none). */
+int as_last_cuda_error(void);
+const char* as_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ACTIVESPLAT_B200_H */

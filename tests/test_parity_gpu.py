@@ -1,0 +1,225 @@
+"""GPU: the sm_100a kernels, called through the C ABI, against the CPU oracle and the golden
+vectors of the reference CUDA build.  Bit-exact for every integer / index structure; 1e-4 relative
+(BASELINE.json north_star) for images and gradients."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import helpers
+
+pytestmark = pytest.mark.gpu
+
+INT_KEYS = ["radii", "tiles_touched", "keys_unsorted", "vals_unsorted", "keys", "point_list", "ranges"]
+GRADS = ("means2D", "colors", "opacity", "means3D", "cov3D", "scales", "rotations")
+
+
+def _check_against(out, grads, ref_out, ref_grads, n_contrib_slack):
+    assert out["num_rendered"] == int(ref_out["num_rendered"])
+    for k in INT_KEYS:
+        helpers.compare_exact(k, out[k], ref_out[k])
+    helpers.compare_exact("n_contrib", out["n_contrib"], ref_out["n_contrib"], max_mismatch=n_contrib_slack)
+    vis = np.asarray(ref_out["radii"]) > 0
+    helpers.compare_exact("means2D", out["means2D"][vis], np.asarray(ref_out["means2D"])[vis])
+    helpers.compare_exact("depths", out["depths"][vis], np.asarray(ref_out["depths"])[vis])
+    helpers.compare_float("conic_opacity", out["conic_opacity"][vis], np.asarray(ref_out["conic_opacity"])[vis])
+    for k in ("color", "depth", "opacity", "final_T"):
+        helpers.compare_float(k, out[k], ref_out[k])
+    for k in GRADS:
+        helpers.compare_float("grad_" + k, grads[k], ref_grads[k])
+
+
+@pytest.mark.parametrize("name", helpers.CASES)
+def test_cuda_matches_oracle(name):
+    case = helpers.make_case(name)
+    st, g = helpers.run_oracle(case)
+    out, grads = helpers.run_cuda(case)
+    _check_against(out, grads, st, g, n_contrib_slack=max(1, int(2e-4 * st["n_contrib"].size)))
+    # conic is computed with the same explicit roundings on both sides: must be identical
+    vis = st["radii"] > 0
+    helpers.compare_exact("conic_opacity bits", out["conic_opacity"][vis], st["conic_opacity"][vis])
+
+
+@pytest.mark.parametrize("name", helpers.CASES)
+def test_cuda_matches_reference_golden(name):
+    path = os.path.join(helpers.GOLDEN_DIR, f"ref_{name}.npz")
+    ref = np.load(path)
+    case = helpers.make_case(name)
+    out, grads = helpers.run_cuda(case)
+    # same expf as the reference build => identical alpha decisions => n_contrib identical
+    _check_against(out, grads, ref, {k: ref["grad_" + k] for k in GRADS}, n_contrib_slack=0)
+
+
+@pytest.mark.parametrize("name", ["frustum_small", "lookaround_depthsil"])
+def test_six_channel_bundle_equals_two_passes(name):
+    """C = 6 ([rgb | z,1,z^2] in one sweep) must equal the reference's two 3-channel passes
+    (src/mapper/splatam/splatam.py:208,212): same images, and gradients that are the sum of both passes."""
+    case = helpers.make_case(name)
+    cam_feats = helpers.depth_sil_features(torch.from_numpy(case["means3D"]), np.eye(4)).numpy()
+    rgb = np.random.default_rng(5).uniform(0, 1, case["colors"].shape).astype(np.float32)
+    bg6 = np.array([0.1, 0.2, 0.3, 0.0, 0.0, 0.0], np.float32)
+    dL6 = np.random.default_rng(6).uniform(-1, 1, (6, case["H"], case["W"])).astype(np.float32)
+    out6, g6 = helpers.run_cuda(case, colors=np.concatenate([rgb, cam_feats], 1), bg=bg6, dL=dL6)
+    outa, ga = helpers.run_cuda(case, colors=rgb, bg=bg6[:3], dL=dL6[:3])
+    outb, gb = helpers.run_cuda(case, colors=cam_feats, bg=bg6[3:], dL=dL6[3:])
+    for k in INT_KEYS + ["n_contrib"]:
+        helpers.compare_exact(k, out6[k], outa[k])
+    helpers.compare_exact("color[:3]", out6["color"][:3], outa["color"])
+    helpers.compare_exact("color[3:]", out6["color"][3:], outb["color"])
+    helpers.compare_exact("depth", out6["depth"], outa["depth"])
+    helpers.compare_exact("opacity", out6["opacity"], outa["opacity"])
+    helpers.compare_float("grad_colors[:3]", g6["colors"][:, :3], ga["colors"])
+    helpers.compare_float("grad_colors[3:]", g6["colors"][:, 3:], gb["colors"])
+    for k in ("means2D", "opacity", "means3D", "scales", "rotations"):
+        helpers.compare_float("grad_" + k, g6[k], ga[k] + gb[k])
+    # and against the oracle's 6-channel sweep
+    st, g = helpers.run_oracle(case, colors=np.concatenate([rgb, cam_feats], 1), bg=bg6, dL=dL6)
+    helpers.compare_float("color6 vs oracle", out6["color"], st["color"])
+    for k in GRADS:
+        helpers.compare_float("grad6_" + k, g6[k], g[k])
+
+
+def test_python_surface_autograd_matches_oracle():
+    """GaussianRasterizer through torch autograd (the call the mapper makes, splatam.py:208)."""
+    from activesplat_b200.rasterizer import GaussianRasterizationSettings, GaussianRasterizer
+    from oracle import raster_oracle as ro
+    case = helpers.make_case("frustum_small")
+    outs = {}
+    for dev, R in (("cuda:0", GaussianRasterizer), ("cpu", ro.GaussianRasterizer)):
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+        rs = GaussianRasterizationSettings(case["H"], case["W"], case["tanfovx"], case["tanfovy"], t(case["bg"]), 1.0,
+                                           t(case["view"]).unsqueeze(0), t(case["proj"]).unsqueeze(0), 0,
+                                           t(case["campos"]), False, False)
+        leaves = {k: t(case[k]).requires_grad_(True) for k in ("means3D", "colors", "opacities", "scales", "rotations")}
+        means2D = torch.zeros_like(leaves["means3D"], requires_grad=True)
+        color, radii, depth, opacity = R(rs)(means3D=leaves["means3D"], means2D=means2D, opacities=leaves["opacities"],
+                                             colors_precomp=leaves["colors"], scales=leaves["scales"],
+                                             rotations=leaves["rotations"])
+        assert radii.dtype == torch.int32 and tuple(color.shape) == (3, case["H"], case["W"])
+        assert tuple(depth.shape) == (1, case["H"], case["W"]) and tuple(opacity.shape) == (1, case["H"], case["W"])
+        (color * t(case["dL_dpix"])).sum().backward()
+        outs[dev] = dict(color=color.detach().cpu().numpy(), radii=radii.cpu().numpy(),
+                         means2D=means2D.grad.cpu().numpy(),
+                         **{"g_" + k: v.grad.cpu().numpy() for k, v in leaves.items()})
+    helpers.compare_exact("radii", outs["cuda:0"]["radii"], outs["cpu"]["radii"])
+    for k in outs["cpu"]:
+        if k != "radii":
+            helpers.compare_float(k, outs["cuda:0"][k], outs["cpu"][k])
+
+
+def test_mark_visible_and_edge_cases():
+    from activesplat_b200 import _C
+    from oracle import raster_oracle as ro
+    case = helpers.make_case("room_partial_tiles")
+    dev = "cuda:0"
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    got = _C.mark_visible(t(case["means3D"]), t(case["view"]), t(case["proj"])).cpu().numpy()
+    helpers.compare_exact("mark_visible", got, ro.mark_visible(case["means3D"], case["view"]))
+    e = torch.Tensor([])
+    # P == 0: nothing rendered, zero outputs, empty scratch (rasterize_points.cu:83)
+    R, color, radii, geom, binning, img, depth, opacity = _C.rasterize_gaussians(
+        t(case["bg"]), torch.zeros((0, 3), device=dev), torch.zeros((0, 3), device=dev), torch.zeros((0, 1), device=dev),
+        torch.zeros((0, 3), device=dev), torch.zeros((0, 4), device=dev), 1.0, e, t(case["view"]), t(case["proj"]),
+        case["tanfovx"], case["tanfovy"], 32, 48, e, 0, t(case["campos"]), False, False)
+    assert R == 0 and radii.numel() == 0 and float(color.abs().max()) == 0.0
+    # every Gaussian behind the camera: R == 0, image = background, depth 15, opacity 0
+    m = case["means3D"].copy()
+    m[:, :] = [0, 0, -5]
+    c2 = dict(case, means3D=m, view=np.eye(4, dtype=np.float32))
+    out, grads = helpers.run_cuda(c2)
+    assert out["num_rendered"] == 0 and (out["radii"] == 0).all()
+    np.testing.assert_array_equal(out["color"], np.broadcast_to(case["bg"][:, None, None], out["color"].shape))
+    assert (out["depth"] == 15.0).all() and (out["opacity"] == 0).all()
+    for k in GRADS:
+        assert not grads[k].any()
+    # missing colours -> the reference's error message (rasterizer_impl.cu:244-247)
+    with pytest.raises(RuntimeError, match="For non-RGB, provide precomputed Gaussian colors!"):
+        _C.rasterize_gaussians(t(case["bg"]), t(case["means3D"]), e, t(case["opacities"]), t(case["scales"]),
+                               t(case["rotations"]), 1.0, e, t(case["view"]), t(case["proj"]), case["tanfovx"],
+                               case["tanfovy"], 32, 48, e, 0, t(case["campos"]), False, False)
+    with pytest.raises(RuntimeError, match="means3D must have dimensions"):
+        _C.rasterize_gaussians(t(case["bg"]), torch.zeros((4, 2), device=dev), e, e, e, e, 1.0, e, t(case["view"]),
+                               t(case["proj"]), 1.0, 1.0, 32, 48, e, 0, t(case["campos"]), False, False)
+
+
+@pytest.mark.parametrize("n,end_bit", [(1, 43), (255, 39), (2048, 43), (2049, 43), (100_000, 43), (1_000_003, 64), (50_000, 8)])
+def test_sort_pairs_and_scan(n, end_bit):
+    """as_sort_pairs vs a stable numpy sort (== cub::DeviceRadixSort::SortPairs semantics), and
+    as_inclusive_scan_u32 vs numpy cumsum, through the C ABI with raw device pointers."""
+    from activesplat_b200 import capi
+    L = capi.lib()
+    rng = np.random.default_rng(n)
+    tiles = rng.integers(0, 1 << max(end_bit - 32, 1), n, dtype=np.uint64) if end_bit > 32 else np.zeros(n, np.uint64)
+    depth = rng.uniform(0.2, 10.0, n).astype(np.float32).view(np.uint32).astype(np.uint64)
+    if n > 1000:  # many exact ties to exercise stability
+        depth[rng.integers(0, n, n // 2)] = depth[0]
+    keys = (tiles << np.uint64(32)) | depth
+    if end_bit < 64:
+        keys &= np.uint64((1 << end_bit) - 1)
+    vals = np.arange(n, dtype=np.uint32)
+    dev = "cuda:0"
+    k_in = torch.from_numpy(keys.view(np.int64)).to(dev)
+    v_in = torch.from_numpy(vals.view(np.int32)).to(dev)
+    k_out, v_out = torch.empty_like(k_in), torch.empty_like(v_in)
+    tb = L.as_sort_temp_bytes(n)
+    temp = torch.empty(tb, dtype=torch.uint8, device=dev)
+    s = torch.cuda.current_stream().cuda_stream
+    capi.check(L.as_sort_pairs(k_in.data_ptr(), v_in.data_ptr(), k_out.data_ptr(), v_out.data_ptr(), n, end_bit,
+                               temp.data_ptr(), tb, s))
+    torch.cuda.synchronize()
+    order = np.argsort(keys, kind="stable")
+    helpers.compare_exact("sorted keys", k_out.cpu().numpy().view(np.uint64), keys[order])
+    helpers.compare_exact("sorted values", v_out.cpu().numpy().view(np.uint32), vals[order])
+    helpers.compare_exact("keys_in preserved", k_in.cpu().numpy().view(np.uint64), keys)
+    # scan
+    x = rng.integers(0, 50, n, dtype=np.uint32)
+    x_d = torch.from_numpy(x.view(np.int32)).to(dev)
+    y_d = torch.empty_like(x_d)
+    tot = torch.zeros(1, dtype=torch.int32, device=dev)
+    sb = L.as_scan_temp_bytes(n)
+    stemp = torch.empty(sb, dtype=torch.uint8, device=dev)
+    capi.check(L.as_inclusive_scan_u32(x_d.data_ptr(), y_d.data_ptr(), n, tot.data_ptr(), stemp.data_ptr(), sb, s))
+    torch.cuda.synchronize()
+    ref = np.cumsum(x.astype(np.uint64)).astype(np.uint32)
+    helpers.compare_exact("scan", y_d.cpu().numpy().view(np.uint32), ref)
+    assert int(tot.item()) == int(ref[-1])
+
+
+def test_full_size_properties_cfg1():
+    """BASELINE config 1 size (100k Gaussians, 640x480): size-independent properties.
+    sortedness + stability of the instance list, ranges partition it, offsets are the scan of tiles
+    touched, per-pixel T in [0,1], opacity = 1 - T, 0 <= n_contrib <= tile list length."""
+    from activesplat_b200 import scenes
+    params, cam = scenes.s_frustum(100_000, 640, 480, 0)
+    a = scenes.activated(params)
+    view, proj, campos = cam.matrices()
+    case = dict(means3D=a["means3D"].numpy(), colors=a["colors_precomp"].numpy(), opacities=a["opacities"].numpy(),
+                scales=a["scales"].numpy(), rotations=a["rotations"].numpy(), scale_modifier=1.0, view=view, proj=proj,
+                campos=campos, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, H=480, W=640, bg=np.zeros(3, np.float32),
+                dL_dpix=np.random.default_rng(100).uniform(-1, 1, (3, 480, 640)).astype(np.float32))
+    out, grads = helpers.run_cuda(case)
+    k = out["keys"]
+    assert (k[1:] >= k[:-1]).all()
+    ties = k[1:] == k[:-1]
+    assert (out["point_list"][1:][ties] > out["point_list"][:-1][ties]).all()
+    helpers.compare_exact("offsets == cumsum(tiles_touched)", out["offsets"],
+                          np.cumsum(out["tiles_touched"].astype(np.uint64)).astype(np.uint32))
+    assert int(out["offsets"][-1]) == out["num_rendered"]
+    assert ((out["radii"] > 0) == (out["tiles_touched"] > 0)).all()
+    r = out["ranges"].astype(np.int64)
+    assert int((r[:, 1] - r[:, 0]).sum()) == out["num_rendered"]
+    tile_of_key = (k >> np.uint64(32)).astype(np.int64)
+    nz = np.where(r[:, 1] > r[:, 0])[0]
+    assert (tile_of_key[r[nz, 0]] == nz).all() and (tile_of_key[r[nz, 1] - 1] == nz).all()
+    assert (out["final_T"] >= 0).all() and (out["final_T"] <= 1).all()
+    np.testing.assert_array_equal(out["opacity"][0], np.float32(1) - out["final_T"])
+    tile_len = (r[:, 1] - r[:, 0]).reshape(30, 40)
+    assert (out["n_contrib"].astype(np.int64) <= np.kron(tile_len, np.ones((16, 16), np.int64))).all()
+    for v in grads.values():
+        assert np.isfinite(v).all()
+    # linearity of the backward in dL/dpix: g(2 dL) == 2 g(dL) exactly (power-of-two scaling)
+    _, g2 = helpers.run_cuda(dict(case, dL_dpix=2 * case["dL_dpix"]), want_internals=False)
+    helpers.compare_float("linearity colors", g2["colors"], 2 * grads["colors"], rel=1e-5)
+    helpers.compare_float("linearity means3D", g2["means3D"], 2 * grads["means3D"], rel=1e-5)
