@@ -82,10 +82,16 @@ SYMBOLS = {
     "as_scan_temp_bytes": (_Z, [_I]),
     "as_inclusive_scan_u32": (_I, [_V, _V, _I, _V, _V, _Z, _V]),
     "as_higher_msb": (ctypes.c_uint32, [ctypes.c_uint32]),
+    "as_profile_enable": (None, [_I]),
+    "as_profile_read": (_I, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int), _I]),
+    "as_launch_count": (ctypes.c_longlong, []),
     "as_error_string": (ctypes.c_char_p, [_I]),
     "as_last_cuda_error": (_I, []),
     "as_version": (ctypes.c_char_p, []),
 }
+
+STAGES = ["preprocess", "scan", "duplicate", "sort", "ranges_gather", "blend_fwd", "blend_bwd", "preprocess_bwd",
+          "prologue", "loss", "adam", "other"]
 
 _lib = None
 
@@ -115,3 +121,12 @@ def check(code):
     if code < 0:
         raise AsError(lib().as_error_string(code).decode())
     return code
+
+
+def profile_read():
+    """{stage: (ms, calls)} since the last read (see as_profile_read)."""
+    n = len(STAGES)
+    ms = (ctypes.c_double * n)()
+    calls = (ctypes.c_int * n)()
+    check(lib().as_profile_read(ms, calls, n))
+    return {STAGES[i]: (ms[i], calls[i]) for i in range(n)}

@@ -24,6 +24,7 @@ namespace {
 
 constexpr int BL_THREADS = TILE_PIX;  // 256
 constexpr int BL_BATCH = 128;
+constexpr int FW_UNROLL = 8;  // instances whose alpha is evaluated together (ILP); divides BL_BATCH
 
 __device__ __forceinline__ float eval_power(const float4& co, float dx, float dy) {
     // forward.cu:342: -0.5f*(A*dx*dx + C*dy*dy) - B*dx*dy, contracted as nvcc contracts it
@@ -85,7 +86,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
     bool done = !inside;
     float T = 1.0f;
     float D = 15.0f;  // median depth default (forward.cu:309)
-    uint32_t contributor = 0, last_contributor = 0;
+    uint32_t last_contributor = 0;
     float acc[C];
 #pragma unroll
     for (int ch = 0; ch < C; ch++) acc[ch] = 0.f;
@@ -95,34 +96,57 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
         const int s = b & 1;
         mbar_wait(&sm.bar[s], (uint32_t)((b >> 1) & 1));
         const int cnt = min(BL_BATCH, len - b * BL_BATCH);
-        if (!done) {
-            for (int j = 0; j < cnt; j++) {
-                contributor++;  // forward.cu:335
-                const float4 co = sm.conic[s][j];
-                const float4 ge = sm.geom[s][j];
-                const float dx = __fsub_rn(ge.x, pxf), dy = __fsub_rn(ge.y, pyf);
-                const float power = eval_power(co, dx, dy);
-                if (power > 0.0f) continue;
-                const float alpha = fminf(0.99f, __fmul_rn(co.w, expf(power)));
-                if (alpha < 1.0f / 255.0f) continue;
-                const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
-                if (test_T < 0.0001f) {
-                    done = true;
-                    break;
+        // The per-pixel loop of forward.cu:332-381, restructured so that the warp stays converged:
+        // (1) alpha of FW_UNROLL consecutive instances is evaluated branch-free for all lanes
+        //     (independent chains: the exp latency of one instance hides behind the others),
+        // (2) the order-dependent part (T, colour, median depth, termination) is then applied in list
+        //     order, only for the instances that passed the skip rules.  Same arithmetic per pixel.
+        if (!__all_sync(0xffffffffu, done)) {
+            for (int j0 = 0; j0 < cnt; j0 += FW_UNROLL) {
+                float al[FW_UNROLL];
+                uint32_t hit = 0;
+#pragma unroll
+                for (int u = 0; u < FW_UNROLL; u++) {
+                    const int j = j0 + u;  // < BL_BATCH; entries >= cnt are stale and masked below
+                    const float4 co = sm.conic[s][j];
+                    const float4 ge = sm.geom[s][j];
+                    const float dx = __fsub_rn(ge.x, pxf), dy = __fsub_rn(ge.y, pyf);
+                    const float power = eval_power(co, dx, dy);
+                    const float alpha = fminf(0.99f, __fmul_rn(co.w, expf(power)));
+                    al[u] = alpha;
+                    // skip rules of forward.cu:343-353 (written so that NaN behaves as in the reference)
+                    if (j < cnt && !(power > 0.0f) && !(alpha < 1.0f / 255.0f)) hit |= 1u << u;
                 }
-                const float4 f0 = sm.feat[s][j * FV];
-                acc[0] = __fmaf_rn(__fmul_rn(f0.x, alpha), T, acc[0]);
-                acc[1] = __fmaf_rn(__fmul_rn(f0.y, alpha), T, acc[1]);
-                acc[2] = __fmaf_rn(__fmul_rn(f0.z, alpha), T, acc[2]);
-                if (C == 6) {
-                    const float4 f1 = sm.feat[s][j * FV + FV - 1];
-                    acc[3 % C] = __fmaf_rn(__fmul_rn(f0.w, alpha), T, acc[3 % C]);
-                    acc[4 % C] = __fmaf_rn(__fmul_rn(f1.x, alpha), T, acc[4 % C]);
-                    acc[5 % C] = __fmaf_rn(__fmul_rn(f1.y, alpha), T, acc[5 % C]);
+                if (done) hit = 0;
+                if (__any_sync(0xffffffffu, hit != 0)) {
+#pragma unroll
+                    for (int u = 0; u < FW_UNROLL; u++) {
+                        if (hit & (1u << u)) {
+                            const int j = j0 + u;
+                            const float alpha = al[u];
+                            const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
+                            if (test_T < 0.0001f) {
+                                done = true;  // forward.cu:355-359: nothing further is blended
+                                hit = 0;
+                            } else {
+                                const float4 f0 = sm.feat[s][j * FV];
+                                acc[0] = __fmaf_rn(__fmul_rn(f0.x, alpha), T, acc[0]);
+                                acc[1] = __fmaf_rn(__fmul_rn(f0.y, alpha), T, acc[1]);
+                                acc[2] = __fmaf_rn(__fmul_rn(f0.z, alpha), T, acc[2]);
+                                if (C == 6) {
+                                    const float4 f1 = sm.feat[s][j * FV + FV - 1];
+                                    acc[3 % C] = __fmaf_rn(__fmul_rn(f0.w, alpha), T, acc[3 % C]);
+                                    acc[4 % C] = __fmaf_rn(__fmul_rn(f1.x, alpha), T, acc[4 % C]);
+                                    acc[5 % C] = __fmaf_rn(__fmul_rn(f1.y, alpha), T, acc[5 % C]);
+                                }
+                                if (T > 0.5f && test_T < 0.5f) D = sm.geom[s][j].z;  // forward.cu:370-374
+                                T = test_T;
+                                last_contributor = (uint32_t)(b * BL_BATCH + j + 1);  // forward.cu:335,380
+                            }
+                        }
+                    }
+                    if (__all_sync(0xffffffffu, done)) break;
                 }
-                if (T > 0.5f && test_T < 0.5f) D = ge.z;  // forward.cu:370-374
-                T = test_T;
-                last_contributor = contributor;
             }
         }
         consumed = b + 1;

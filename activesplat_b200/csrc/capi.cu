@@ -6,6 +6,7 @@
 //                rasterizer_impl.cu:155-194, rasterizer_impl.h:21-72
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -79,6 +80,43 @@ static int stage_check(cudaStream_t st, int debug) {
 }
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+// ---- optional per-stage timing (bench.py's roofline attribution) and launch counting ----------
+// Off by default.  When on, every stage is bracketed by two CUDA events recorded on the launching
+// stream; as_profile_read() synchronises and sums elapsed times per stage.  Process-wide (torch runs
+// backward passes on its own thread), guarded by a mutex; one device at a time.
+struct Profiler {
+    std::mutex mu;
+    bool on = false;
+    static constexpr int MAX_EV = 8192;
+    cudaEvent_t ev[MAX_EV];
+    int n_created = 0;
+    int n_used = 0;                   // events used since the last read (pairs: 2k, 2k+1)
+    int stage_of[MAX_EV / 2];
+    long long launches = 0;           // kernels launched by this library on this thread (always counted)
+};
+static Profiler g_prof;
+
+struct StageScope {
+    cudaStream_t st;
+    int slot = -1;
+    StageScope(int stage, cudaStream_t s, int kernels) : st(s) {
+        std::lock_guard<std::mutex> lock(g_prof.mu);
+        g_prof.launches += kernels;
+        if (!g_prof.on || g_prof.n_used + 2 > Profiler::MAX_EV) return;
+        while (g_prof.n_created < g_prof.n_used + 2) {
+            if (cudaEventCreate(&g_prof.ev[g_prof.n_created]) != cudaSuccess) return;
+            g_prof.n_created++;
+        }
+        slot = g_prof.n_used;
+        g_prof.n_used += 2;
+        g_prof.stage_of[slot / 2] = stage;
+        cudaEventRecord(g_prof.ev[slot], st);
+    }
+    ~StageScope() {
+        if (slot >= 0) cudaEventRecord(g_prof.ev[slot + 1], st);
+    }
+};
 
 }  // namespace asb
 
@@ -167,10 +205,16 @@ int as_forward(const AsForwardArgs* a, AsAllocFn geometryBuffer, AsAllocFn binni
     ImageState img = ImageState::fromChunk(ichunk, N, (size_t)tiles);
 
     int r;
+    {
+    StageScope _s(AS_STAGE_PREPROCESS, st, 1);
     launch_preprocess_forward(P, a->means3D, a->scales, a->rotations, a->opacities, a->cov3D_precomp, a->viewmatrix,
                               a->projmatrix, W, H, a->tan_fovx, a->tan_fovy, a->scale_modifier, a->radii, g, st);
+    }
     if ((r = stage_check(st, a->debug))) return r;
+    {
+    StageScope _s(AS_STAGE_SCAN, st, 1);
     launch_inclusive_scan(g.tiles_touched, g.point_offsets, P, g.num_rendered, g.scan_temp, st);
+    }
     if ((r = stage_check(st, a->debug))) return r;
 
     // The one host round trip of the reference (rasterizer_impl.cu:283): R sizes the binning buffer.
@@ -184,16 +228,28 @@ int as_forward(const AsForwardArgs* a, AsAllocFn geometryBuffer, AsAllocFn binni
     BinningState b = BinningState::fromChunk(bchunk, (size_t)R, C);
 
     if (R > 0) {
+        {
+        StageScope _s(AS_STAGE_DUPLICATE, st, 1);
         launch_duplicate_with_keys(P, g, g.radii, W, H, b.keys_unsorted, b.values_unsorted, st);
+        }
         if ((r = stage_check(st, a->debug))) return r;
         const int bit = (int)as_higher_msb((uint32_t)tiles);
+        {
+        StageScope _s(AS_STAGE_SORT, st, 4 + (32 + bit + 7) / 8);
         launch_sort_pairs(b.keys_unsorted, b.values_unsorted, b.keys_sorted, b.point_list, R, 32 + bit, b.sort_temp, st);
+        }
         if ((r = stage_check(st, a->debug))) return r;
     }
+    {
+    StageScope _s(AS_STAGE_RANGES_GATHER, st, R > 0 ? 1 : 0);
     launch_ranges_and_gather(R, tiles, C, b.keys_sorted, b.point_list, g, a->colors_precomp, b, img.ranges, st);
+    }
     if ((r = stage_check(st, a->debug))) return r;
+    {
+    StageScope _s(AS_STAGE_BLEND_FWD, st, 1);
     launch_blend_forward(C, W, H, img.ranges, b, a->background, a->out_color, a->out_depth, a->out_opacity,
                          img.final_T, img.n_contrib, st);
+    }
     if ((r = stage_check(st, a->debug))) return r;
     return R;
 }
@@ -226,7 +282,10 @@ int as_backward(const AsBackwardArgs* a, void* cuda_stream) {
     if (R > 0) {
         char* bchunk = a->binning_buffer;
         BinningState b = BinningState::fromChunk(bchunk, (size_t)R, C);
+        {
+        StageScope _s(AS_STAGE_BLEND_BWD, st, 1);
         launch_blend_backward(C, W, H, img.ranges, b, a->background, img.final_T, img.n_contrib, a->dL_dpix, g.gacc, st);
+        }
         if ((r = stage_check(st, a->debug))) return r;
     }
     PreprocessBackwardOut o;
@@ -238,8 +297,11 @@ int as_backward(const AsBackwardArgs* a, void* cuda_stream) {
     o.dL_dcov3D = a->dL_dcov3D;
     o.dL_dscale = a->dL_dscale;
     o.dL_drot = a->dL_drot;
+    {
+    StageScope _s(AS_STAGE_PREPROCESS_BWD, st, 1);
     launch_preprocess_backward(P, C, a->means3D, radii, a->scales, a->rotations, a->cov3D_precomp, a->scale_modifier,
                                a->viewmatrix, a->projmatrix, W, H, a->tan_fovx, a->tan_fovy, nullptr, g.gacc, o, st);
+    }
     return stage_check(st, a->debug);
 }
 
@@ -276,6 +338,34 @@ int as_inclusive_scan_u32(const uint32_t* in, uint32_t* out, int n, uint32_t* to
     cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
     launch_inclusive_scan(in, out, n, total_out, reinterpret_cast<uint32_t*>(temp), st);
     return check(cudaGetLastError());
+}
+
+void as_profile_enable(int on) {
+    std::lock_guard<std::mutex> lock(g_prof.mu);
+    g_prof.on = on != 0;
+}
+
+int as_profile_read(double* ms_per_stage, int* calls_per_stage, int n_stages) {
+    if (!ms_per_stage || !calls_per_stage || n_stages < AS_NUM_STAGES) return AS_ERR_INVALID_ARG;
+    for (int i = 0; i < n_stages; i++) { ms_per_stage[i] = 0.0; calls_per_stage[i] = 0; }
+    std::lock_guard<std::mutex> lock(g_prof.mu);
+    int r = AS_OK;
+    for (int s = 0; s + 1 < g_prof.n_used; s += 2) {
+        if (cudaEventSynchronize(g_prof.ev[s + 1]) != cudaSuccess) { r = AS_ERR_CUDA; break; }
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, g_prof.ev[s], g_prof.ev[s + 1]) != cudaSuccess) { r = AS_ERR_CUDA; break; }
+        const int stage = g_prof.stage_of[s / 2];
+        ms_per_stage[stage] += ms;
+        calls_per_stage[stage] += 1;
+    }
+    g_prof.n_used = 0;
+    if (r) g_last_cuda_error = (int)cudaGetLastError();
+    return r;
+}
+
+long long as_launch_count(void) {
+    std::lock_guard<std::mutex> lock(g_prof.mu);
+    return g_prof.launches;
 }
 
 const char* as_error_string(int code) {

@@ -48,31 +48,50 @@ def _call_with_debug_dump(fn, args, debug, dump_name, note):
         raise
 
 
-class _RasterizeGaussians(torch.autograd.Function):
-    @staticmethod
-    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-                raster_settings):
-        rs = raster_settings
-        args = (rs.bg, means3D, colors_precomp, opacities, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
-                rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, sh,
-                rs.sh_degree, rs.campos, rs.prefiltered, rs.debug)
-        num_rendered, color, radii, geom, binning, img, depth, opacity = _call_with_debug_dump(
-            _C.rasterize_gaussians, args, rs.debug, "snapshot_fw.dump", "forward")
-        ctx.raster_settings = rs
-        ctx.num_rendered = num_rendered
-        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom, binning, img)
-        return color, radii, depth, opacity
+def make_rasterize_function(backend):
+    """The autograd.Function of the reference (__init__.py:44-155) bound to a `_C`-shaped backend:
+    any object with rasterize_gaussians / rasterize_gaussians_backward in the reference's signature."""
 
-    @staticmethod
-    def backward(ctx, grad_out_color, _grad_radii, _grad_depth, _grad_opacity):
-        rs = ctx.raster_settings
-        colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom, binning, img = ctx.saved_tensors
-        args = (rs.bg, means3D, radii, colors_precomp, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
-                rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_out_color, sh, rs.sh_degree, rs.campos,
-                geom, ctx.num_rendered, binning, img, rs.debug)
-        (g_means2D, g_colors, g_opacities, g_means3D, g_cov3D, g_sh, g_scales, g_rotations) = _call_with_debug_dump(
-            _C.rasterize_gaussians_backward, args, rs.debug, "snapshot_bw.dump", "backward")
-        return (g_means3D, g_means2D, g_sh, g_colors, g_opacities, g_scales, g_rotations, g_cov3D, None)
+    class _Fn(torch.autograd.Function):
+        @staticmethod
+        def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, rs):
+            return _forward_impl(backend, ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
+                                 cov3Ds_precomp, rs)
+
+        @staticmethod
+        def backward(ctx, grad_out_color, _grad_radii, _grad_depth, _grad_opacity):
+            return _backward_impl(backend, ctx, grad_out_color)
+
+    return _Fn
+
+
+def _forward_impl(backend, ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                  raster_settings):
+    rs = raster_settings
+    args = (rs.bg, means3D, colors_precomp, opacities, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
+            rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, sh,
+            rs.sh_degree, rs.campos, rs.prefiltered, rs.debug)
+    num_rendered, color, radii, geom, binning, img, depth, opacity = _call_with_debug_dump(
+        backend.rasterize_gaussians, args, rs.debug, "snapshot_fw.dump", "forward")
+    ctx.raster_settings = rs
+    ctx.num_rendered = num_rendered
+    ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom, binning, img)
+    ctx.mark_non_differentiable(radii)
+    return color, radii, depth, opacity
+
+
+def _backward_impl(backend, ctx, grad_out_color):
+    rs = ctx.raster_settings
+    colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom, binning, img = ctx.saved_tensors
+    args = (rs.bg, means3D, radii, colors_precomp, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
+            rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_out_color, sh, rs.sh_degree, rs.campos,
+            geom, ctx.num_rendered, binning, img, rs.debug)
+    (g_means2D, g_colors, g_opacities, g_means3D, g_cov3D, g_sh, g_scales, g_rotations) = _call_with_debug_dump(
+        backend.rasterize_gaussians_backward, args, rs.debug, "snapshot_bw.dump", "backward")
+    return (g_means3D, g_means2D, g_sh, g_colors, g_opacities, g_scales, g_rotations, g_cov3D, None)
+
+
+_RasterizeGaussians = make_rasterize_function(_C)
 
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,

@@ -182,3 +182,35 @@ def activated(params):
         "scales": torch.exp(params["log_scales"] if params["log_scales"].shape[1] == 3
                             else torch.tile(params["log_scales"], (1, 3))),
     }
+
+
+def rotmat_to_quat(Rm):
+    """(r, x, y, z) unit quaternion of a 3x3 rotation (numpy, float64)."""
+    Rm = np.asarray(Rm, dtype=np.float64)
+    t = np.trace(Rm)
+    if t > 0:
+        s = math.sqrt(t + 1.0) * 2
+        q = [0.25 * s, (Rm[2, 1] - Rm[1, 2]) / s, (Rm[0, 2] - Rm[2, 0]) / s, (Rm[1, 0] - Rm[0, 1]) / s]
+    else:
+        i = int(np.argmax(np.diag(Rm)))
+        j, k = (i + 1) % 3, (i + 2) % 3
+        s = math.sqrt(1.0 + Rm[i, i] - Rm[j, j] - Rm[k, k]) * 2
+        q = [0.0, 0.0, 0.0, 0.0]
+        q[0] = (Rm[k, j] - Rm[j, k]) / s
+        q[1 + i] = 0.25 * s
+        q[1 + j] = (Rm[j, i] + Rm[i, j]) / s
+        q[1 + k] = (Rm[k, i] + Rm[i, k]) / s
+    q = np.array(q)
+    return q / np.linalg.norm(q)
+
+
+def camera_track(cams):
+    """SplaTAM camera parameters for a list of CameraSpec: cam_unnorm_rots [1,4,T], cam_trans [1,3,T]
+    (world == first-frame convention of splatam.py:97-103: w2c_t = [R(q_t) | t_t])."""
+    T = len(cams)
+    rots = np.zeros((1, 4, T), np.float32)
+    trans = np.zeros((1, 3, T), np.float32)
+    for t, c in enumerate(cams):
+        rots[0, :, t] = rotmat_to_quat(c.w2c[:3, :3])
+        trans[0, :, t] = c.w2c[:3, 3]
+    return torch.from_numpy(rots), torch.from_numpy(trans)

@@ -1,0 +1,245 @@
+"""Host-side mirror of the SplaTAM functions that wrap the rasterizer in ActiveSplat.
+
+Same names, arguments and return values as the reference, so the mapper's call sites read the same:
+  setup_camera                 src/mapper/splatam/utils/recon_helpers.py:4-28
+  build_rotation               src/mapper/splatam/utils/slam_external.py:25-42
+  quat_mult                    src/mapper/splatam/utils/slam_helpers.py:21-28
+  transform_to_frame           src/mapper/splatam/utils/slam_helpers.py:252-304
+  get_depth_and_silhouette     src/mapper/splatam/utils/slam_helpers.py:196-213
+  transformed_params2rendervar / transformed_params2depthplussilhouette   slam_helpers.py:124-139, 234-249
+  get_rendervars, render       src/mapper/splatam/splatam.py:436-468, 413-434
+  get_loss                     src/mapper/splatam/splatam.py:172-301
+  calc_ssim                    src/mapper/splatam/utils/slam_external.py:54-97
+  initialize_optimizer         src/mapper/splatam/splatam.py:118-124
+
+What is different underneath: the reference renders every frame twice (RGB pass, then a [z,1,z^2]
+pass over identical geometry, splatam.py:208,212); here both feature sets go through ONE 6-channel
+rasterizer call (preprocess, sort and alpha evaluation shared), which is arithmetically identical.
+All tensors live on the device of `params`; nothing here touches the CPU oracle.
+"""
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+from .rasterizer import GaussianRasterizationSettings as Camera
+from .rasterizer import GaussianRasterizer as Renderer
+
+
+def setup_camera(w, h, k, w2c, near=0.01, far=100, scale_modifier=1.0, device="cuda", bg=(0.0, 0.0, 0.0)):
+    fx, fy, cx, cy = k[0][0], k[1][1], k[0][2], k[1][2]
+    w2c = torch.as_tensor(np.asarray(w2c)).to(device).float()
+    cam_center = torch.inverse(w2c)[:3, 3]
+    w2c = w2c.unsqueeze(0).transpose(1, 2)
+    opengl_proj = torch.tensor([[2 * fx / w, 0.0, -(w - 2 * cx) / w, 0.0],
+                                [0.0, 2 * fy / h, -(h - 2 * cy) / h, 0.0],
+                                [0.0, 0.0, far / (far - near), -(far * near) / (far - near)],
+                                [0.0, 0.0, 1.0, 0.0]]).to(device).float().unsqueeze(0).transpose(1, 2)
+    full_proj = w2c.bmm(opengl_proj)
+    return Camera(image_height=h, image_width=w, tanfovx=w / (2 * fx), tanfovy=h / (2 * fy),
+                  bg=torch.tensor(bg, dtype=torch.float32, device=device), scale_modifier=scale_modifier,
+                  viewmatrix=w2c, projmatrix=full_proj, sh_degree=0, campos=cam_center, prefiltered=False,
+                  debug=False)
+
+
+def with_background(cam, bg):
+    """A copy of `cam` with another background (the white-bg camera of splatam.py:416-429)."""
+    return cam._replace(bg=torch.as_tensor(bg, dtype=torch.float32, device=cam.bg.device))
+
+
+def build_rotation(q):
+    norm = torch.sqrt(q[:, 0] * q[:, 0] + q[:, 1] * q[:, 1] + q[:, 2] * q[:, 2] + q[:, 3] * q[:, 3])
+    q = q / norm[:, None]
+    r, x, y, z = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    rot = torch.stack([
+        1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y),
+        2 * (x * y + r * z), 1 - 2 * (x * x + z * z), 2 * (y * z - r * x),
+        2 * (x * z - r * y), 2 * (y * z + r * x), 1 - 2 * (x * x + y * y)], dim=-1)
+    return rot.reshape(-1, 3, 3)
+
+
+def quat_mult(q1, q2):
+    w1, x1, y1, z1 = q1.T
+    w2, x2, y2, z2 = q2.T
+    w = w1 * w2 - x1 * x2 - y1 * y2 - z1 * z2
+    x = w1 * x2 + x1 * w2 + y1 * z2 - z1 * y2
+    y = w1 * y2 - x1 * z2 + y1 * w2 + z1 * x2
+    z = w1 * z2 + x1 * y2 - y1 * x2 + z1 * w2
+    return torch.stack([w, x, y, z]).T
+
+
+def l1_loss_v1(x, y):
+    return torch.abs((x - y)).mean()
+
+
+def transform_to_frame(params, time_idx, gaussians_grad, camera_grad):
+    if camera_grad:
+        cam_rot = F.normalize(params['cam_unnorm_rots'][..., time_idx])
+        cam_tran = params['cam_trans'][..., time_idx]
+    else:
+        cam_rot = F.normalize(params['cam_unnorm_rots'][..., time_idx].detach())
+        cam_tran = params['cam_trans'][..., time_idx].detach()
+    dev = params['means3D'].device
+    rot = build_rotation(cam_rot)[0]
+    top = torch.cat([rot, cam_tran.reshape(3, 1)], dim=1)
+    rel_w2c = torch.cat([top, torch.tensor([[0.0, 0.0, 0.0, 1.0]], device=dev)], dim=0)
+    transform_rots = params['log_scales'].shape[1] != 1  # anisotropic Gaussians carry their own rotation
+    if gaussians_grad:
+        pts, unnorm_rots = params['means3D'], params['unnorm_rotations']
+    else:
+        pts, unnorm_rots = params['means3D'].detach(), params['unnorm_rotations'].detach()
+    pts4 = torch.cat((pts, torch.ones(pts.shape[0], 1, device=dev)), dim=1)
+    out = {'means3D': (rel_w2c @ pts4.T).T[:, :3]}
+    if transform_rots:
+        out['unnorm_rotations'] = quat_mult(cam_rot, F.normalize(unnorm_rots))
+    else:
+        out['unnorm_rotations'] = unnorm_rots
+    return out
+
+
+def get_depth_and_silhouette(pts_3D, w2c):
+    pts4 = torch.cat((pts_3D, torch.ones_like(pts_3D[:, :1])), dim=-1)
+    pts_in_cam = (w2c @ pts4.transpose(0, 1)).transpose(0, 1)
+    depth_z = pts_in_cam[:, 2].unsqueeze(-1)
+    return torch.cat((depth_z, torch.ones_like(depth_z), torch.square(depth_z)), dim=-1)
+
+
+def _log_scales3(params):
+    ls = params['log_scales']
+    return torch.tile(ls, (1, 3)) if ls.shape[1] == 1 else ls
+
+
+def transformed_params2rendervar(params, transformed_gaussians):
+    return {
+        'means3D': transformed_gaussians['means3D'],
+        'colors_precomp': params['rgb_colors'],
+        'rotations': F.normalize(transformed_gaussians['unnorm_rotations']),
+        'opacities': torch.sigmoid(params['logit_opacities']),
+        'scales': torch.exp(_log_scales3(params)),
+        'means2D': torch.zeros_like(params['means3D'], requires_grad=True) + 0,
+    }
+
+
+def transformed_params2depthplussilhouette(params, w2c, transformed_gaussians):
+    rv = transformed_params2rendervar(params, transformed_gaussians)
+    rv['colors_precomp'] = get_depth_and_silhouette(transformed_gaussians['means3D'], w2c)
+    return rv
+
+
+def get_rendervars(params, w2c, curr_timestep=None):
+    dev = params['means3D'].device
+    w2c = torch.as_tensor(np.asarray(w2c)).to(dev).float()
+    base = {
+        'means3D': params['means3D'],
+        'rotations': F.normalize(params['unnorm_rotations']),
+        'opacities': torch.sigmoid(params['logit_opacities']),
+        'scales': torch.exp(_log_scales3(params)),
+    }
+    rendervar = dict(base, colors_precomp=params['rgb_colors'], means2D=torch.zeros_like(params['means3D']))
+    depth_rendervar = dict(base, colors_precomp=get_depth_and_silhouette(params['means3D'], w2c),
+                           means2D=torch.zeros_like(params['means3D']))
+    return rendervar, depth_rendervar
+
+
+def render_bundle(cam, rendervar, depth_sil_colors, bg_rgb=None):
+    """ONE 6-channel rasterizer call in place of the reference's two passes.
+    Returns (im[3,H,W], radii, median_depth[1,H,W], opacity[1,H,W], depth_sil[3,H,W])."""
+    bg6 = torch.cat([cam.bg if bg_rgb is None else torch.as_tensor(bg_rgb, dtype=torch.float32, device=cam.bg.device),
+                     torch.zeros(3, device=cam.bg.device)])
+    cam6 = cam._replace(bg=bg6)
+    colors6 = torch.cat([rendervar['colors_precomp'], depth_sil_colors], dim=1)
+    out, radii, depth, opacity = Renderer(raster_settings=cam6)(
+        means3D=rendervar['means3D'], means2D=rendervar['means2D'], opacities=rendervar['opacities'],
+        colors_precomp=colors6, scales=rendervar['scales'], rotations=rendervar['rotations'])
+    return out[:3], radii, depth, opacity, out[3:]
+
+
+def render(w2c, k, timestep_data, timestep_depth_data, cfg, scale_modifier=1.0):
+    """splatam.py:413-434: white-background RGB + median depth + opacity, and the silhouette."""
+    with torch.no_grad():
+        dev = timestep_data['means3D'].device
+        cam = setup_camera(cfg['viz_w'], cfg['viz_h'], k, w2c, cfg['viz_near'], cfg['viz_far'],
+                           scale_modifier=scale_modifier, device=dev)
+        im, _, depth, opacity, depth_sil = render_bundle(cam, timestep_data, timestep_depth_data['colors_precomp'],
+                                                         bg_rgb=[1.0, 1.0, 1.0])
+        return im, depth, opacity, depth_sil[1, :, :].unsqueeze(0)
+
+
+def _gaussian_window(window_size, sigma, channel, like):
+    x = torch.arange(window_size, dtype=torch.float32)
+    g = torch.exp(-(x - window_size // 2) ** 2 / float(2 * sigma ** 2))
+    g = (g / g.sum()).unsqueeze(1)
+    w2d = g.mm(g.t()).float().unsqueeze(0).unsqueeze(0)
+    return w2d.expand(channel, 1, window_size, window_size).contiguous().to(like.device).type_as(like)
+
+
+def calc_ssim(img1, img2, window_size=11, size_average=True):
+    channel = img1.size(-3)
+    window = _gaussian_window(window_size, 1.5, channel, img1)
+    pad = window_size // 2
+    mu1 = F.conv2d(img1, window, padding=pad, groups=channel)
+    mu2 = F.conv2d(img2, window, padding=pad, groups=channel)
+    mu1_sq, mu2_sq, mu1_mu2 = mu1.pow(2), mu2.pow(2), mu1 * mu2
+    sigma1_sq = F.conv2d(img1 * img1, window, padding=pad, groups=channel) - mu1_sq
+    sigma2_sq = F.conv2d(img2 * img2, window, padding=pad, groups=channel) - mu2_sq
+    sigma12 = F.conv2d(img1 * img2, window, padding=pad, groups=channel) - mu1_mu2
+    c1, c2 = 0.01 ** 2, 0.03 ** 2
+    ssim_map = ((2 * mu1_mu2 + c1) * (2 * sigma12 + c2)) / ((mu1_sq + mu2_sq + c1) * (sigma1_sq + sigma2_sq + c2))
+    return ssim_map.mean() if size_average else ssim_map.mean(1).mean(1).mean(1)
+
+
+def get_loss(params, curr_data, variables, iter_time_idx, loss_weights, use_sil_for_loss, sil_thres, use_l1,
+             ignore_outlier_depth_loss, tracking=False, mapping=False, do_ba=False, plot_dir=None,
+             visualize_tracking_loss=False, tracking_iteration=None):
+    losses = {}
+    if tracking:
+        tg = transform_to_frame(params, iter_time_idx, gaussians_grad=False, camera_grad=True)
+    elif mapping and do_ba:
+        tg = transform_to_frame(params, iter_time_idx, gaussians_grad=True, camera_grad=True)
+    else:
+        tg = transform_to_frame(params, iter_time_idx, gaussians_grad=True, camera_grad=False)
+    rendervar = transformed_params2rendervar(params, tg)
+    depth_sil_colors = get_depth_and_silhouette(tg['means3D'], curr_data['w2c'])
+    rendervar['means2D'].retain_grad()
+    im, radius, _, _, depth_sil = render_bundle(curr_data['cam'], rendervar, depth_sil_colors)
+    variables['means2D'] = rendervar['means2D']
+    depth = depth_sil[0, :, :].unsqueeze(0)
+    silhouette = depth_sil[1, :, :]
+    presence_sil_mask = (silhouette > sil_thres)
+    depth_sq = depth_sil[2, :, :].unsqueeze(0)
+    invisibility = (depth_sq - depth ** 2).detach()
+    nan_mask = (~torch.isnan(depth)) & (~torch.isnan(invisibility))
+    if ignore_outlier_depth_loss:
+        depth_error = torch.abs(curr_data['depth'] - depth) * (curr_data['depth'] > 0)
+        mask = (depth_error < 10 * depth_error.median()) & (curr_data['depth'] > 0)
+    else:
+        mask = (curr_data['depth'] > 0)
+    mask = mask & nan_mask
+    if tracking and use_sil_for_loss:
+        mask = mask & presence_sil_mask
+    if use_l1:
+        mask = mask.detach()
+        if tracking:
+            losses['depth'] = torch.abs(curr_data['depth'] - depth)[mask].sum()
+        else:
+            losses['depth'] = torch.abs(curr_data['depth'] - depth)[mask].mean()
+    if tracking and (use_sil_for_loss or ignore_outlier_depth_loss):
+        color_mask = torch.tile(mask, (3, 1, 1)).detach()
+        losses['im'] = torch.abs(curr_data['im'] - im)[color_mask].sum()
+    elif tracking:
+        losses['im'] = torch.abs(curr_data['im'] - im).sum()
+    else:
+        losses['im'] = 0.8 * l1_loss_v1(im, curr_data['im']) + 0.2 * (1.0 - calc_ssim(im, curr_data['im']))
+    weighted_losses = {k: v * loss_weights[k] for k, v in losses.items()}
+    loss = sum(weighted_losses.values())
+    seen = radius > 0
+    variables['max_2D_radius'][seen] = torch.max(radius[seen], variables['max_2D_radius'][seen])
+    variables['seen'] = seen
+    weighted_losses['loss'] = loss
+    return loss, variables, weighted_losses
+
+
+def initialize_optimizer(params, lrs_dict, tracking):
+    param_groups = [{'params': [v], 'name': k, 'lr': lrs_dict[k]} for k, v in params.items()]
+    if tracking:
+        return torch.optim.Adam(param_groups)
+    return torch.optim.Adam(param_groups, lr=0.0, eps=1e-15)

@@ -1,0 +1,431 @@
+#!/usr/bin/env python
+"""bench.py -- RGB-D + silhouette render fwd+bwd throughput (Mpix/s) of the rasterizer hot path.
+
+Workload (BASELINE.json configs[1], "cfg2"): SplaTAM camera-tracking iteration on a 500k-Gaussian
+synthetic room map at 640x480.  One step = one get_loss(tracking=True) + backward
+(reference: src/mapper/splatam/splatam.py:172-301): transform to the frame, activations, ONE
+RGB-D+silhouette bundle render (colour[3] + [z,1,z^2][3] + median depth + opacity), masked L1 losses,
+and the full backward down to the camera pose.  Every step uses the next keyframe pose; N > 1 ranks
+render disjoint keyframes of the same (replicated) map -- weak scaling, no data-path collective.
+
+  python bench.py --gpus N --steps K --warmup W             our arm (sm_100a kernels through the C ABI)
+  python bench.py --impl reference ...                      reference arm: the CPU port of the reference
+                                                            algorithm (oracle/) on the host cores
+One JSON line on stdout (rank 0).
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+L2_BYTES = 126e6
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--gaussians", type=int, default=500_000)
+    ap.add_argument("--width", type=int, default=640)
+    ap.add_argument("--height", type=int, default=480)
+    ap.add_argument("--keyframes", type=int, default=8, help="keyframe poses per rank")
+    ap.add_argument("--no-ref-cuda", action="store_true", help="skip the reference-CUDA comparison leg")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# --------------------------------------------------------------------------------------------------
+# workload
+# --------------------------------------------------------------------------------------------------
+LOSS_WEIGHTS = dict(im=0.5, depth=1.0)  # config/splatam/online_habitat_sim.py:33-36
+SIL_THRES = 0.99                        # online_habitat_sim.py:25
+
+
+def make_scene(args, rank, world):
+    from activesplat_b200 import scenes
+    K = args.keyframes
+    params, cams = scenes.s_room(args.gaussians, K * world, seed=1, W=args.width, H=args.height)
+    cams = cams[rank::world]
+    rots, trans = scenes.camera_track(cams)
+    gt_params = scenes.perturbed(params, seed=11)
+    return params, gt_params, cams, rots, trans
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons while the timed region runs (nvidia_ml_py)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.stop_flag, self.max_mhz = index, [], set(), False, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {"hw_slowdown": getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8),
+                 "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+                 "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
+                 "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4)}
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            time.sleep(0.02)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+def algorithmic_bytes(P, V, R, N, tiles, sort_passes):
+    """algorithmic bytes of one RGB-D+sil bundle fwd+bwd, per stage (the reference's
+    two-pass accounting; a fused implementation moves fewer, the figure is kept for comparability)."""
+    b = {}
+    b["preprocess"] = P * 52 + V * 52
+    b["scan"] = P * 8
+    b["duplicate"] = V * 20 + R * 12
+    b["sort"] = R * 8 + R * 24 * sort_passes
+    b["ranges_gather"] = R * 8 + tiles * 8
+    b["blend_fwd"] = 2 * (R * (32 + 12) + N * (12 + 16))
+    b["blend_bwd"] = 2 * (R * (28 + 12) + N * (12 + 8) + 2 * V * 44)
+    b["preprocess_bwd"] = 2 * V * 224
+    b["loss"] = N * 64
+    return b
+
+
+# --------------------------------------------------------------------------------------------------
+# our arm
+# --------------------------------------------------------------------------------------------------
+def run_ours(args, rank, world, local_rank):
+    import torch.distributed as dist
+    from activesplat_b200 import capi, splatam
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    L = capi.lib()
+    params_cpu, gt_cpu, cams, rots, trans = make_scene(args, rank, world)
+    W, H, K = args.width, args.height, len(cams)
+    N = W * H
+    params = {k: v.to(dev).requires_grad_(False) for k, v in params_cpu.items()}
+    params["cam_unnorm_rots"] = rots.to(dev).requires_grad_(True)
+    params["cam_trans"] = trans.to(dev).requires_grad_(True)
+    k_mat = cams[0].k()
+    cam = splatam.setup_camera(W, H, k_mat, np.eye(4), device=dev)  # identity camera
+    first_w2c = torch.eye(4, device=dev)
+    variables = {"max_2D_radius": torch.zeros(args.gaussians, device=dev)}
+
+    # ground truth: the perturbed map rendered at every keyframe pose (set-up, not timed)
+    gt_host = []
+    with torch.no_grad():
+        gtp = {k: v.to(dev) for k, v in gt_cpu.items()}
+        for t in range(K):
+            rv, drv = splatam.get_rendervars(gtp, cams[t].w2c)
+            c = splatam.setup_camera(W, H, k_mat, cams[t].w2c, device=dev)
+            im, _, depth, opacity, _ = splatam.render_bundle(c, rv, drv["colors_precomp"])
+            depth = torch.where(opacity > 0.5, depth, torch.zeros_like(depth))
+            gt_host.append(torch.cat([im, depth], 0).cpu().pin_memory())
+        del gtp
+    gt_dev = [g.to(dev) for g in gt_host]
+    gt_stage = torch.empty_like(gt_dev[0])
+
+    def one_step(i, e2e):
+        t = i % K
+        if e2e:
+            gt_stage.copy_(gt_host[t], non_blocking=True)
+            g = gt_stage
+        else:
+            g = gt_dev[t]
+        curr = {"cam": cam, "im": g[:3], "depth": g[3:4], "w2c": first_w2c}
+        loss, _, _ = splatam.get_loss(params, curr, variables, t, LOSS_WEIGHTS, True, SIL_THRES, True, False,
+                                      tracking=True)
+        loss.backward()
+        out = float(loss.item()) if e2e else None
+        params["cam_unnorm_rots"].grad = None
+        params["cam_trans"].grad = None
+        return out
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def timed(n, e2e, profile):
+        barrier()
+        L.as_profile_enable(1 if profile else 0)
+        capi.profile_read()
+        l0 = L.as_launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(n):
+            one_step(i, e2e)
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            tms = torch.tensor([ms], device=dev)
+            dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+            ms = float(tms.item())
+        stages = capi.profile_read() if profile else None
+        L.as_profile_enable(0)
+        return ms, stages, L.as_launch_count() - l0
+
+    for i in range(args.warmup):
+        one_step(i, False)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ms, stages, launches = timed(args.steps, False, True)
+    sampler.stop_flag = True
+    sampler.join()
+    for i in range(min(args.warmup, 3)):
+        one_step(i, True)
+    ms_e2e, _, _ = timed(args.steps, True, False)
+
+    # workload statistics for the algorithmic-byte figure (one extra forward per keyframe, untimed)
+    stats = []
+    with torch.no_grad():
+        from activesplat_b200 import _C
+        e = torch.Tensor([])
+        for t in range(K):
+            tg = splatam.transform_to_frame(params, t, False, False)
+            rv = splatam.transformed_params2rendervar(params, tg)
+            R, _, radii, *_ = _C.rasterize_gaussians(cam.bg, rv["means3D"], rv["colors_precomp"], rv["opacities"],
+                                                    rv["scales"], rv["rotations"], 1.0, e, cam.viewmatrix, cam.projmatrix,
+                                                    cam.tanfovx, cam.tanfovy, H, W, e, 0, cam.campos, False, False)
+            stats.append((R, int((radii > 0).sum())))
+    R_mean = float(np.mean([s[0] for s in stats]))
+    V_mean = float(np.mean([s[1] for s in stats]))
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    sp = (32 + int(L.as_higher_msb(tiles)) + 7) // 8
+    ab = algorithmic_bytes(args.gaussians, V_mean, R_mean, N, tiles, sp)
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+    dom = max((s for s in stages if stages[s][1] > 0), key=lambda s: stages[s][0])
+    dom_ms = stages[dom][0] / max(stages[dom][1], 1)
+    achieved = ab.get(dom, 0) / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
+    stage_ms = {s: round(v[0] / args.steps, 4) for s, v in stages.items() if v[1] > 0}
+    total_bytes = sum(ab.values())
+
+    result = {
+        "metric": "RGB-D+sil render fwd+bwd Mpix/s",
+        "value": N * args.steps * world / (ms * 1e-3) / 1e6,
+        "unit": "Mpix/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "cfg2: SplaTAM tracking iteration (get_loss(tracking=True) fwd+bwd), "
+                               f"S-room {args.gaussians} Gaussians, {W}x{H}, {K} keyframe poses per rank, "
+                               "one RGB-D+sil bundle per step",
+                   "gaussians": args.gaussians, "width": W, "height": H, "instances_per_step": R_mean,
+                   "visible_per_step": V_mean,
+                   "l2": f"no flush: per-step working set (params+scratch+images) "
+                         f"{(args.gaussians * 150 + R_mean * 110 + N * 80) / 1e6:.0f} MB > L2 126 MB, pose changes every step",
+                   "parallelism": f"keyframes sharded over {world} rank(s), map replicated"},
+        "e2e": {"value": N * args.steps * world / (ms_e2e * 1e-3) / 1e6, "unit": "Mpix/s",
+                "h2d_bytes_per_step": int(gt_host[0].numel() * 4), "d2h_bytes_per_step": 4,
+                "api": "activesplat_b200.splatam.get_loss + backward, GT frame from pinned host memory, loss read back"},
+        "gpu_launches": int(launches),
+        "clocks": sampler.summary(),
+        "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak if peak else None, "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": ab.get(dom, 0),
+                     "whole_step": {"algorithmic_bytes": total_bytes,
+                                    "achieved": total_bytes / (ms / args.steps * 1e-3) / 1e9,
+                                    "frac": total_bytes / (ms / args.steps * 1e-3) / 1e9 / peak}},
+        "stage_ms_per_step": stage_ms,
+    }
+
+    if rank == 0 and not args.no_ref_cuda:
+        try:
+            result["ref_cuda"] = run_ref_cuda(args, dev, params, cams, cam, first_w2c, gt_dev, K)
+        except Exception as ex:  # the reference build may be absent on a box
+            result["ref_cuda"] = {"unavailable": f"{type(ex).__name__}: {ex}"[:200]}
+    if rank == 0 and not args.no_cpu_baseline:
+        result["cpu_baseline"] = cpu_baseline(args, budget_s=25.0)
+    return result
+
+
+# --------------------------------------------------------------------------------------------------
+# comparison leg: the UNMODIFIED reference CUDA rasterizer (oracle/_ref), same step, two passes
+# --------------------------------------------------------------------------------------------------
+def run_ref_cuda(args, dev, params, cams, cam, first_w2c, gt_dev, K):
+    import importlib.util
+    from activesplat_b200 import splatam
+    from activesplat_b200.rasterizer import make_rasterize_function
+    path = os.path.join(ROOT, "oracle", "_ref", "ref_dgr_C.so")
+    spec = importlib.util.spec_from_file_location("ref_dgr_C", path)
+    ref = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ref)
+    fn = make_rasterize_function(ref)
+    e = torch.Tensor([])
+    W, H = args.width, args.height
+
+    def raster(rv):
+        return fn.apply(rv["means3D"], rv["means2D"], e, rv["colors_precomp"], rv["opacities"], rv["scales"],
+                        rv["rotations"], e, cam)
+
+    def one_step(i):
+        t = i % K
+        g = gt_dev[t]
+        tg = splatam.transform_to_frame(params, t, gaussians_grad=False, camera_grad=True)
+        rv = splatam.transformed_params2rendervar(params, tg)
+        drv = splatam.transformed_params2depthplussilhouette(params, first_w2c, tg)
+        im, radius, _, _ = raster(rv)           # splatam.py:208
+        depth_sil, _, _, _ = raster(drv)        # splatam.py:212
+        depth = depth_sil[0:1]
+        mask = (g[3:4] > 0) & (~torch.isnan(depth)) & (depth_sil[1] > SIL_THRES)
+        mask = mask.detach()
+        l_depth = torch.abs(g[3:4] - depth)[mask].sum()
+        l_im = torch.abs(g[:3] - im)[torch.tile(mask, (3, 1, 1))].sum()
+        (LOSS_WEIGHTS["im"] * l_im + LOSS_WEIGHTS["depth"] * l_depth).backward()
+        params["cam_unnorm_rots"].grad = None
+        params["cam_trans"].grad = None
+
+    for i in range(args.warmup):
+        one_step(i)
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        one_step(i)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1)
+    return {"value": W * H * args.steps / (ms * 1e-3) / 1e6, "unit": "Mpix/s", "ms_per_step": ms / args.steps,
+            "what": "unmodified reference diff-gaussian-rasterization compiled for sm_100a (oracle/_ref), "
+                    "same step with its two 3-channel passes, 1 GPU"}
+
+
+# --------------------------------------------------------------------------------------------------
+# CPU legs: the oracle port of the reference algorithm on the host cores
+# --------------------------------------------------------------------------------------------------
+def cpu_step_factory(args, gaussians=None, width=None, height=None):
+    from activesplat_b200 import scenes
+    from oracle import raster_oracle as ro
+    P = gaussians or args.gaussians
+    W, H = width or args.width, height or args.height
+    params, cams = scenes.s_room(P, args.keyframes, seed=1, W=W, H=H)
+    a = {k: v.numpy() for k, v in scenes.activated(params).items()}
+    rng = np.random.default_rng(100)
+    dL = rng.uniform(-1, 1, (6, H, W)).astype(np.float32)
+    bg = np.zeros(3, np.float32)
+    mats = [c.matrices() for c in cams]
+    feats = []
+    for c in cams:
+        z = (params["means3D"].numpy() @ c.w2c[:3, :3].T.astype(np.float32) + c.w2c[:3, 3].astype(np.float32))[:, 2:3]
+        feats.append(np.concatenate([z, np.ones_like(z), z * z], 1).astype(np.float32))
+
+    def step(i):
+        t = i % len(cams)
+        view, proj, _ = mats[t]
+        c = cams[t]
+        for colors, d in ((a["colors_precomp"], dL[:3]), (feats[t], dL[3:])):  # the reference's two passes
+            st = ro.forward(a["means3D"], colors, a["opacities"], a["scales"], a["rotations"], 1.0, None, view, proj,
+                            c.tanfovx, c.tanfovy, H, W, bg)
+            ro.backward(st, d)
+    return step, ro.num_threads(), W, H, P
+
+
+def cpu_baseline(args, budget_s):
+    step, threads, W, H, P = cpu_step_factory(args)
+    t0 = time.time()
+    step(0)
+    first = time.time() - t0
+    n = int(max(1, min(5, budget_s // max(first, 1e-3))))
+    t0 = time.time()
+    for i in range(n):
+        step(i + 1)
+    dt = (time.time() - t0) / n
+    return {"value": W * H / dt / 1e6, "unit": "Mpix/s", "cores": threads, "kind": "port",
+            "sample": f"{n} bundle(s) (two 3-channel passes fwd+bwd) of the full workload: {P} Gaussians, {W}x{H}; "
+                      f"{dt:.2f} s per bundle"}
+
+
+def run_reference_arm(args):
+    """--impl reference: the reference has no CPU implementation of this path and its CUDA build is a
+    GPU program, so the timed reference arm is the C port of its algorithm (oracle/) on the host cores."""
+    step, threads, W, H, P = cpu_step_factory(args)
+    t0 = time.time()
+    step(0)
+    first = time.time() - t0
+    sample = f"full workload per step: {P} Gaussians, {W}x{H}"
+    if first * (args.steps + args.warmup) > 240:  # keep the whole run within a few minutes
+        step, threads, W, H, P = cpu_step_factory(args, gaussians=args.gaussians // 4, width=args.width // 2,
+                                                  height=args.height // 2)
+        sample = f"reduced sample per step: {P} Gaussians, {W}x{H} (full workload would exceed the time budget)"
+    for i in range(args.warmup):
+        step(i)
+    t0 = time.time()
+    for i in range(args.steps):
+        step(i)
+    dt = time.time() - t0
+    v = W * H * args.steps / dt / 1e6
+    return {
+        "impl": "reference", "metric": "RGB-D+sil render fwd+bwd Mpix/s", "value": v, "unit": "Mpix/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "cfg2 bundle (two 3-channel passes fwd+bwd) on the CPU port of the reference algorithm; " + sample,
+                   "gaussians": P, "width": W, "height": H},
+        "cpu_baseline": {"value": v, "unit": "Mpix/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        if rank == 0:
+            print(json.dumps(run_reference_arm(args)), flush=True)
+        return
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    res = run_ours(args, rank, world, local_rank)
+    if rank == 0:
+        print(json.dumps(res), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -153,6 +153,20 @@ int as_inclusive_scan_u32(const uint32_t* in, uint32_t* out, int n, uint32_t* to
 /* getHigherMsb (rasterizer_impl.cu:35-50) */
 uint32_t as_higher_msb(uint32_t n);
 
+/* ---- instrumentation (no counterpart in the reference; used by bench.py) ---------------------- */
+enum {
+    AS_STAGE_PREPROCESS = 0, AS_STAGE_SCAN, AS_STAGE_DUPLICATE, AS_STAGE_SORT, AS_STAGE_RANGES_GATHER,
+    AS_STAGE_BLEND_FWD, AS_STAGE_BLEND_BWD, AS_STAGE_PREPROCESS_BWD, AS_STAGE_PROLOGUE, AS_STAGE_LOSS,
+    AS_STAGE_ADAM, AS_STAGE_OTHER, AS_NUM_STAGES
+};
+/* Per-stage CUDA-event timing on the launching stream, process-wide.  Off by default. */
+void as_profile_enable(int on);
+/* Synchronises the recorded events, writes summed milliseconds and call counts per stage
+ * (arrays of n_stages >= AS_NUM_STAGES entries) and clears the record. */
+int as_profile_read(double* ms_per_stage, int* calls_per_stage, int n_stages);
+/* Number of kernels this library has launched in this process so far. */
+long long as_launch_count(void);
+
 const char* as_error_string(int code);
 /* cudaError_t value recorded by the last failing call on this host thread (0 = none). */
 int as_last_cuda_error(void);
