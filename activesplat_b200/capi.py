@@ -15,6 +15,7 @@ AS_ERR_NO_COLORS = -2
 AS_ERR_ALLOC = -3
 AS_ERR_CUDA = -4
 AS_ERR_CAPACITY = -5
+AS_ERR_STATIC_LIMIT = -6
 
 c_float_p = ctypes.c_void_p  # device pointers travel as integers
 AllocFn = ctypes.CFUNCTYPE(ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t)
@@ -81,6 +82,8 @@ SYMBOLS = {
     "as_sort_pairs": (_I, [_V, _V, _V, _V, _I, _I, _V, _Z, _V]),
     "as_scan_temp_bytes": (_Z, [_I]),
     "as_inclusive_scan_u32": (_I, [_V, _V, _I, _V, _V, _Z, _V]),
+    "as_static_scan_max_n": (_I, []),
+    "as_inclusive_scan_u32_static": (_I, [_V, _V, _I, _V, _V]),
     "as_higher_msb": (ctypes.c_uint32, [ctypes.c_uint32]),
     "as_profile_enable": (None, [_I]),
     "as_profile_read": (_I, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int), _I]),

@@ -368,8 +368,27 @@ long long as_launch_count(void) {
     return g_prof.launches;
 }
 
+int as_static_scan_max_n(void) { return static_scan_max_n(); }
+
+int as_inclusive_scan_u32_static(const uint32_t* in, uint32_t* out, int n, uint32_t* total_out, void* cuda_stream) {
+    if (n < 0) return AS_ERR_INVALID_ARG;
+    if (n > static_scan_max_n()) return AS_ERR_STATIC_LIMIT;
+    if (n > 0 && (!in || !out)) return AS_ERR_INVALID_ARG;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
+    void* scratch = nullptr;
+    int r = check(static_scan_scratch(&scratch));  // first call on a device: symbol lookup, then cached
+    if (r) return r;
+    // The array still holds the previous call's ticket and tile states; launch_inclusive_scan clears
+    // the part this call uses (cudaMemsetAsync on `st`) before the kernel reads it.
+    launch_inclusive_scan(in, out, n, total_out, reinterpret_cast<uint32_t*>(scratch), st);
+    return check(cudaGetLastError());
+}
+
 const char* as_error_string(int code) {
     switch (code) {
+        case AS_ERR_STATIC_LIMIT:
+            return "input larger than the built-in scratch allows: as_inclusive_scan_u32_static handles at most "
+                   "4194304 elements (see as_static_scan_max_n); use as_inclusive_scan_u32 with caller scratch";
         case AS_OK: return "ok";
         case AS_ERR_INVALID_ARG: return "invalid argument";
         case AS_ERR_NO_COLORS: return "For non-RGB, provide precomputed Gaussian colors!";

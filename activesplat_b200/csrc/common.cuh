@@ -65,6 +65,8 @@ struct BinningState {  // per instance (Gaussian x tile)
 
 size_t scan_temp_bytes(int n);
 size_t sort_temp_bytes(int n);
+int static_scan_max_n();
+cudaError_t static_scan_scratch(void** out);  // device address of the built-in scan scratch (current device)
 
 // ---------------------------------------------------------------------------------------------
 // Stage launchers (definitions in the .cu files).  All asynchronous on `st`.

@@ -11,6 +11,8 @@
 // Passes whose digit is identical for all keys (one histogram bin holds everything) are detected
 // on the device and skipped by a pointer swap that is also resolved on the device, so no host
 // synchronisation is needed anywhere.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace asb {
@@ -384,6 +386,49 @@ void launch_sort_pairs(const uint64_t* keys_in, const uint32_t* values_in, uint6
     int cblocks = (n + 255) / 256;
     if (cblocks > NUM_SMS * 4) cblocks = NUM_SMS * 4;
     radix_copy_if_all_skipped<<<cblocks, 256, 0, st>>>(keys_in, values_in, keys_out, values_out, n, t.skip);
+}
+
+
+// ------------------------------------------------------------------------------------------------
+// Prefix sum without any caller- or library-side allocation (as_inclusive_scan_u32_static).
+//
+// Some users of this library cannot hand it scratch memory: a mapping process on a robot that
+// carved up all of its device memory into fixed arenas at start-up has nothing left to allocate
+// from, and a control loop with a latency budget cannot afford cudaMalloc/cudaFree, which may
+// synchronise the whole device.  For them the look-back state of the scan lives in the array below,
+// which is part of the library image: every GPU that loads the library carries these 16 KiB until
+// the process exits.
+//
+// In host code `g_static_scan_scratch` is only a handle for the symbol, not an address the GPU can
+// use; the device address is looked up once per device with cudaGetSymbolAddress and cached.
+// ------------------------------------------------------------------------------------------------
+constexpr int STATIC_SCAN_MAX_TILES = 2048;
+constexpr int STATIC_SCAN_MAX_N = STATIC_SCAN_MAX_TILES * SCAN_TILE;  // 4,194,304 elements
+// [0..1]: ticket word + padding (16 bytes), [2..]: one status word per tile -- the layout of scan_temp
+static __device__ __align__(256) unsigned long long g_static_scan_scratch[2 + STATIC_SCAN_MAX_TILES];
+
+constexpr int MAX_DEVICES = 64;
+static std::mutex g_static_scan_mu;
+static void* g_static_scan_ptr[MAX_DEVICES] = {nullptr};
+
+int static_scan_max_n() { return STATIC_SCAN_MAX_N; }
+
+// Returns cudaSuccess and the device address of the built-in scratch for the CURRENT device.
+// The first call on a device performs the symbol lookup (a host-side runtime query, no allocation).
+cudaError_t static_scan_scratch(void** out) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_static_scan_mu);
+    if (!g_static_scan_ptr[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_static_scan_scratch);
+        if (e != cudaSuccess) return e;
+        g_static_scan_ptr[dev] = p;
+    }
+    *out = g_static_scan_ptr[dev];
+    return cudaSuccess;
 }
 
 }  // namespace asb

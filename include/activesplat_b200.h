@@ -33,6 +33,7 @@ extern "C" {
 #define AS_ERR_ALLOC (-3)         /* an allocator callback returned NULL */
 #define AS_ERR_CUDA (-4)          /* a CUDA runtime call or (debug mode) a kernel failed; see as_last_cuda_error() */
 #define AS_ERR_CAPACITY (-5)      /* a caller-sized buffer is too small (fused / no-sync entries) */
+#define AS_ERR_STATIC_LIMIT (-6)  /* input exceeds the fixed size of the library's built-in scratch */
 
 /* Scratch allocator: returns a DEVICE pointer to at least `bytes` bytes (128-byte aligned or better),
  * valid until the matching as_backward has run.  Mirrors the resize lambdas of rasterize_points.cu:27-33. */
@@ -149,6 +150,27 @@ int as_sort_pairs(const uint64_t* keys_in, const uint32_t* values_in, uint64_t* 
 size_t as_scan_temp_bytes(int n);
 int as_inclusive_scan_u32(const uint32_t* in, uint32_t* out, int n, uint32_t* total_out, void* temp,
                           size_t temp_bytes, void* cuda_stream);
+
+/* Prefix sum for callers that cannot allocate.  (No counterpart in the reference: there every caller
+ * owns a torch allocator and CUB temp storage is carved out of it, rasterizer_impl.cu:166,279.)
+ *
+ * Same result as as_inclusive_scan_u32, but it takes no scratch argument and neither this function
+ * nor anything it calls allocates device or host memory.  It is meant for hosts that have no
+ * allocator to lend us: e.g. a robot's mapping process that split all of its device memory into
+ * fixed arenas at start-up, or a loop with a latency budget in which cudaMalloc / cudaFree (which may
+ * synchronise the device) are off limits.  The look-back state lives in a fixed array inside the
+ * library image instead (about 16 KiB per GPU that loads the library, held until the process exits).
+ *
+ *   - n may be at most as_static_scan_max_n() = 4,194,304 elements; larger inputs are refused with
+ *     AS_ERR_STATIC_LIMIT and nothing is launched.
+ *   - The first call on each device looks up the array's device address (a host-side query) with that
+ *     device current; make that first call before starting any stream capture.
+ *   - All calls on a device share the one array.  Each call clears the part it needs on `cuda_stream`
+ *     before use, so back-to-back calls on one stream are fine; calls that can overlap on the GPU
+ *     (different streams, different host threads) race on it and must be serialised by the caller. */
+int as_static_scan_max_n(void);
+int as_inclusive_scan_u32_static(const uint32_t* in, uint32_t* out, int n, uint32_t* total_out,
+                                 void* cuda_stream);
 
 /* getHigherMsb (rasterizer_impl.cu:35-50) */
 uint32_t as_higher_msb(uint32_t n);
