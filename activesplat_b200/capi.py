@@ -61,6 +61,35 @@ class AsBackwardArgs(ctypes.Structure):
     ]
 
 
+class AsFrameArgs(ctypes.Structure):
+    _fields_ = [
+        ("P", ctypes.c_int), ("width", ctypes.c_int), ("height", ctypes.c_int), ("isotropic", ctypes.c_int),
+        ("means3D", ctypes.c_void_p), ("rgb_colors", ctypes.c_void_p), ("unnorm_rotations", ctypes.c_void_p),
+        ("logit_opacities", ctypes.c_void_p), ("log_scales", ctypes.c_void_p),
+        ("cam_unnorm_rot", ctypes.c_void_p), ("cam_rot_stride", ctypes.c_int),
+        ("cam_trans", ctypes.c_void_p), ("cam_trans_stride", ctypes.c_int),
+        ("sil_w2c", ctypes.c_void_p), ("viewmatrix", ctypes.c_void_p), ("projmatrix", ctypes.c_void_p),
+        ("background", ctypes.c_void_p),
+        ("tan_fovx", ctypes.c_float), ("tan_fovy", ctypes.c_float), ("scale_modifier", ctypes.c_float),
+        ("geom_buffer", ctypes.c_void_p), ("image_buffer", ctypes.c_void_p), ("binning_buffer", ctypes.c_void_p),
+        ("binning_capacity", ctypes.c_int),
+        ("status", ctypes.c_void_p),
+        ("out_color", ctypes.c_void_p), ("out_depth", ctypes.c_void_p), ("out_opacity", ctypes.c_void_p),
+        ("radii", ctypes.c_void_p),
+        ("debug", ctypes.c_int),
+    ]
+
+
+class AsFrameBackwardArgs(ctypes.Structure):
+    _fields_ = [
+        ("frame", ctypes.POINTER(AsFrameArgs)),
+        ("dL_dpix", ctypes.c_void_p), ("grad_scale", ctypes.c_void_p),
+        ("gaussians_grad", ctypes.c_int), ("camera_grad", ctypes.c_int),
+        ("grad_params", ctypes.c_void_p), ("grad_means2D", ctypes.c_void_p), ("grad_cam", ctypes.c_void_p),
+        ("pose_scratch", ctypes.c_void_p),
+    ]
+
+
 class AsScratchLayout(ctypes.Structure):
     _fields_ = [(n, ctypes.c_size_t) for n in (
         "depths", "means2D", "conic_opacity", "cov3D", "tiles_touched", "point_offsets", "radii",
@@ -78,6 +107,11 @@ SYMBOLS = {
     "as_image_bytes": (_Z, [_I, _I]),
     "as_binning_bytes": (_Z, [_I, _I]),
     "as_scratch_layout": (_I, [_I, _I, _I, _I, _I, ctypes.POINTER(AsScratchLayout)]),
+    "as_frame_forward": (_I, [ctypes.POINTER(AsFrameArgs), _V]),
+    "as_frame_backward": (_I, [ctypes.POINTER(AsFrameBackwardArgs), _V]),
+    "as_loss_scratch_floats": (_Z, [_I, _I]),
+    "as_tracking_loss": (_I, [_I, _I, _V, _V, _V, _F, _F, _F, _I, _I, _V, _V, _V, _V, _V]),
+    "as_adam_step": (_I, [_I, _I, _V, _V, _V, _V, _V, _V, _V, _V, ctypes.POINTER(ctypes.c_float), _F, _F, _F, _I, _V]),
     "as_sort_temp_bytes": (_Z, [_I]),
     "as_sort_pairs": (_I, [_V, _V, _V, _V, _I, _I, _V, _Z, _V]),
     "as_scan_temp_bytes": (_Z, [_I]),

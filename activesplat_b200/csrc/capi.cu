@@ -24,6 +24,7 @@ GeometryState GeometryState::fromChunk(char*& chunk, size_t P) {
     g.point_offsets = b.take<uint32_t>(P);
     g.radii = b.take<int>(P);
     g.gacc = b.take<float>(P * GACC_STRIDE);
+    g.zsil = b.take<float>(P);
     g.scan_temp = b.take<uint32_t>((scan_temp_bytes((int)P) + 3) / 4);
     g.num_rendered = b.take<uint32_t>(64);
     chunk = b.p;
@@ -303,6 +304,123 @@ int as_backward(const AsBackwardArgs* a, void* cuda_stream) {
                                a->viewmatrix, a->projmatrix, W, H, a->tan_fovx, a->tan_fovy, nullptr, g.gacc, o, st);
     }
     return stage_check(st, a->debug);
+}
+
+// ---- fused frame path: no host synchronisation, caller-sized binning buffer ---------------------
+int as_frame_forward(const AsFrameArgs* a, void* cuda_stream) {
+    if (!a || a->P <= 0 || a->width <= 0 || a->height <= 0 || a->binning_capacity < 0) return AS_ERR_INVALID_ARG;
+    if (!a->means3D || !a->rgb_colors || !a->unnorm_rotations || !a->logit_opacities || !a->log_scales ||
+        !a->cam_unnorm_rot || !a->cam_trans || !a->viewmatrix || !a->projmatrix || !a->background ||
+        !a->geom_buffer || !a->image_buffer || !a->binning_buffer || !a->status || !a->out_color || !a->out_depth ||
+        !a->out_opacity)
+        return AS_ERR_INVALID_ARG;
+    if (!aligned16(a->unnorm_rotations)) return AS_ERR_INVALID_ARG;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
+    const int P = a->P, W = a->width, H = a->height;
+    const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y, tiles = gx * gy;
+    char* gchunk = a->geom_buffer;
+    GeometryState g = GeometryState::fromChunk(gchunk, (size_t)P);
+    char* ichunk = a->image_buffer;
+    ImageState img = ImageState::fromChunk(ichunk, (size_t)W * H, (size_t)tiles);
+    char* bchunk = a->binning_buffer;
+    const int cap = a->binning_capacity;
+    BinningState b = BinningState::fromChunk(bchunk, (size_t)cap, 6);
+    int r;
+    {
+        StageScope _s(AS_STAGE_PREPROCESS, st, 1);
+        launch_frame_preprocess(*a, g, a->status, st);
+    }
+    if ((r = stage_check(st, a->debug))) return r;
+    {
+        StageScope _s(AS_STAGE_SCAN, st, 1);
+        launch_inclusive_scan(g.tiles_touched, g.point_offsets, P, a->status, g.scan_temp, st);  // status[0] = R
+    }
+    if ((r = stage_check(st, a->debug))) return r;
+    if (cap > 0) {
+        {
+            StageScope _s(AS_STAGE_DUPLICATE, st, 1);
+            launch_frame_duplicate(P, g, W, H, (uint32_t)cap, b.keys_unsorted, b.values_unsorted, a->status, st);
+        }
+        if ((r = stage_check(st, a->debug))) return r;
+        const int bit = (int)as_higher_msb((uint32_t)tiles);
+        {
+            StageScope _s(AS_STAGE_SORT, st, 4 + (32 + bit + 7) / 8);
+            launch_sort_pairs(b.keys_unsorted, b.values_unsorted, b.keys_sorted, b.point_list, cap, 32 + bit, b.sort_temp,
+                              st, a->status);
+        }
+        if ((r = stage_check(st, a->debug))) return r;
+    }
+    {
+        StageScope _s(AS_STAGE_RANGES_GATHER, st, 1);
+        launch_frame_ranges_gather(a->status, (uint32_t)cap, tiles, g, a->rgb_colors, b, img.ranges, st);
+    }
+    if ((r = stage_check(st, a->debug))) return r;
+    {
+        StageScope _s(AS_STAGE_BLEND_FWD, st, 1);
+        launch_blend_forward(6, W, H, img.ranges, b, a->background, a->out_color, a->out_depth, a->out_opacity,
+                             img.final_T, img.n_contrib, st);
+    }
+    return stage_check(st, a->debug);
+}
+
+int as_frame_backward(const AsFrameBackwardArgs* ba, void* cuda_stream) {
+    if (!ba || !ba->frame || !ba->dL_dpix) return AS_ERR_INVALID_ARG;
+    const AsFrameArgs* a = ba->frame;
+    if (a->P <= 0 || !a->geom_buffer || !a->image_buffer || !a->binning_buffer) return AS_ERR_INVALID_ARG;
+    if (ba->camera_grad && (!ba->grad_cam || !ba->pose_scratch)) return AS_ERR_INVALID_ARG;
+    if (ba->gaussians_grad && !ba->grad_params) return AS_ERR_INVALID_ARG;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
+    const int P = a->P, W = a->width, H = a->height;
+    const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y, tiles = gx * gy;
+    char* gchunk = a->geom_buffer;
+    GeometryState g = GeometryState::fromChunk(gchunk, (size_t)P);
+    char* ichunk = a->image_buffer;
+    ImageState img = ImageState::fromChunk(ichunk, (size_t)W * H, (size_t)tiles);
+    char* bchunk = a->binning_buffer;
+    BinningState b = BinningState::fromChunk(bchunk, (size_t)a->binning_capacity, 6);
+    int r;
+    {
+        StageScope _s(AS_STAGE_BLEND_BWD, st, 1);
+        launch_blend_backward(6, W, H, img.ranges, b, a->background, img.final_T, img.n_contrib, ba->dL_dpix, g.gacc, st);
+    }
+    if ((r = stage_check(st, a->debug))) return r;
+    {
+        StageScope _s(AS_STAGE_PREPROCESS_BWD, st, ba->camera_grad ? 2 : 1);
+        launch_frame_preprocess_backward(*a, g, ba->grad_scale, ba->gaussians_grad, ba->camera_grad, ba->grad_params,
+                                         ba->grad_means2D, ba->pose_scratch, ba->grad_cam, st);
+    }
+    return stage_check(st, a->debug);
+}
+
+size_t as_loss_scratch_floats(int width, int height) { return (size_t)loss_partial_blocks(width * height) * 4 + 16; }
+
+int as_tracking_loss(int width, int height, const float* color6, const float* gt_rgb, const float* gt_depth,
+                     float w_im, float w_depth, float sil_thres, int use_sil_for_loss, int mask_color,
+                     float* dL_dcolor6, float* losses, float* scratch, const uint32_t* frame_status,
+                     void* cuda_stream) {
+    if (width <= 0 || height <= 0 || !color6 || !gt_rgb || !gt_depth || !dL_dcolor6 || !losses || !scratch)
+        return AS_ERR_INVALID_ARG;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
+    StageScope _s(AS_STAGE_LOSS, st, 2);
+    launch_tracking_loss(width * height, color6, gt_rgb, gt_depth, w_im, w_depth, sil_thres, use_sil_for_loss,
+                         mask_color, dL_dcolor6, scratch, losses, frame_status, st);
+    return check(cudaGetLastError());
+}
+
+int as_adam_step(int P, int isotropic, float* means3D, float* rgb_colors, float* unnorm_rotations,
+                 float* logit_opacities, float* log_scales, const float* grad_params, float* exp_avg,
+                 float* exp_avg_sq, const float* lrs, float beta1, float beta2, float eps, int step,
+                 void* cuda_stream) {
+    if (P < 0 || step < 1 || !lrs) return AS_ERR_INVALID_ARG;
+    if (P == 0) return AS_OK;
+    if (!means3D || !rgb_colors || !unnorm_rotations || !logit_opacities || !log_scales || !grad_params || !exp_avg ||
+        !exp_avg_sq)
+        return AS_ERR_INVALID_ARG;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
+    float* params[5] = {means3D, rgb_colors, unnorm_rotations, logit_opacities, log_scales};
+    StageScope _s(AS_STAGE_ADAM, st, 1);
+    launch_adam(P, isotropic, params, lrs, grad_params, exp_avg, exp_avg_sq, beta1, beta2, eps, step, st);
+    return check(cudaGetLastError());
 }
 
 int as_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* /*projmatrix*/,

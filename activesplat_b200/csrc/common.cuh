@@ -38,6 +38,7 @@ struct GeometryState {  // per Gaussian
     uint32_t* point_offsets;  // [P] inclusive scan of tiles_touched
     int* radii;               // [P] internal copy (used when the caller passes radii == NULL)
     float* gacc;              // [P,12] backward accumulators (conic x,y,w | opacity | mean2D x,y | colour[<=6])
+    float* zsil;              // [P] depth in the silhouette frame (frame path: feature z of [z,1,z^2])
     uint32_t* scan_temp;      // look-back state of the scan
     uint32_t* num_rendered;   // [1] device copy of R
     static GeometryState fromChunk(char*& chunk, size_t P);
@@ -92,8 +93,11 @@ void launch_inclusive_scan(const uint32_t* in, uint32_t* out, int n, uint32_t* t
 void launch_duplicate_with_keys(int P, const GeometryState& g, const int* radii, int W, int H,
                                 uint64_t* keys, uint32_t* values, cudaStream_t st);
 
+// n_dev != NULL: the element count is read on the device (min(n, *n_dev)); n is then the capacity the
+// grids are sized for, so no host synchronisation is needed to learn it.
 void launch_sort_pairs(const uint64_t* keys_in, const uint32_t* values_in, uint64_t* keys_out,
-                       uint32_t* values_out, int n, int end_bit, char* temp, cudaStream_t st);
+                       uint32_t* values_out, int n, int end_bit, char* temp, cudaStream_t st,
+                       const uint32_t* n_dev = nullptr);
 
 void launch_ranges_and_gather(int R, int tiles, int channels, const uint64_t* keys_sorted,
                               const uint32_t* point_list, const GeometryState& g, const float* features,
@@ -125,6 +129,22 @@ void launch_preprocess_backward(int P, int channels, const float* means3D, const
                                 const PreprocessBackwardOut& o, cudaStream_t st);
 
 constexpr int GACC_STRIDE = 12;
+
+// ---- fused frame path (fused.cu) ----
+void launch_frame_preprocess(const AsFrameArgs& a, const GeometryState& g, uint32_t* status, cudaStream_t st);
+void launch_frame_duplicate(int P, const GeometryState& g, int W, int H, uint32_t capacity, uint64_t* keys,
+                            uint32_t* values, uint32_t* status, cudaStream_t st);
+void launch_frame_ranges_gather(const uint32_t* n_dev, uint32_t capacity, int tiles, const GeometryState& g,
+                                const float* rgb, const BinningState& b, uint2* ranges, cudaStream_t st);
+void launch_frame_preprocess_backward(const AsFrameArgs& a, const GeometryState& g, const float* gscale,
+                                      int gaussians_grad, int camera_grad, float* grad_params, float* grad_means2D,
+                                      float* pose_acc, float* grad_cam, cudaStream_t st);
+int loss_partial_blocks(int N);
+void launch_tracking_loss(int N, const float* c6, const float* gt_rgb, const float* gt_depth, float w_im,
+                          float w_depth, float sil_thres, int use_sil, int mask_color, float* dL, float* partials,
+                          float* losses, const uint32_t* status, cudaStream_t st);
+void launch_adam(int P, int iso, float* const params[5], const float lr[5], const float* grad, float* m, float* v,
+                 float beta1, float beta2, float eps, int step, cudaStream_t st);
 
 // ---------------------------------------------------------------------------------------------
 // device helpers

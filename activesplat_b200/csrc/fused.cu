@@ -1,0 +1,631 @@
+// fused.cu -- the SplaTAM frame step around the rasterizer, fused (sm_100a).
+//
+// The reference runs these as dozens of torch-eager kernels per iteration (SURVEY 2.2 "F1-F5"):
+//   F1 transform_to_frame                    src/mapper/splatam/utils/slam_helpers.py:252-304
+//   F2 activations (sigmoid/exp/normalize)   slam_helpers.py:124-139
+//   F3 [z, 1, z^2] features                  slam_helpers.py:196-213
+//   F4 loss (masked L1, SSIM)                src/mapper/splatam/splatam.py:213-249, utils/slam_external.py:54-97
+//   F5 Adam                                  splatam.py:118-124 (torch.optim.Adam, eps 1e-15)
+// Here: frame_preprocess_kernel = F1+F2+F3+preprocessCUDA in one pass over the raw parameters;
+// frame_preprocess_backward_kernel = computeCov2D/preprocess backward + the backward of F1-F3 down to the
+// raw parameters and the camera pose (block-reduced); tracking_loss_kernel / mapping loss kernels = F4
+// forward and backward in one or two sweeps over the image; adam_kernel = F5 over all five tensors.
+// None of the frame path synchronises with the host: the instance count stays on the device and the
+// binning buffer has a caller-chosen capacity (overflow is flagged, never written past).
+#include "raster_math.cuh"
+
+namespace asb {
+
+namespace {
+
+constexpr int FP_THREADS = 256;
+
+struct Pose {        // shared-memory copy of the frame pose
+    float q[4];      // normalised camera quaternion (r,x,y,z)
+    float R[9];      // rotation of q (row-major, textbook)
+    float t[3];
+    float qnorm;     // |cam_unnorm_rot|
+    float sil[4];    // row 2 of the silhouette w2c
+};
+
+__device__ __forceinline__ void quat_to_rot(const float q[4], float R[9]) {
+    // build_rotation (slam_external.py:25-42) normalises once more
+    const float n = sqrtf(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+    const float r = q[0] / n, x = q[1] / n, y = q[2] / n, z = q[3] / n;
+    R[0] = 1.f - 2.f * (y * y + z * z); R[1] = 2.f * (x * y - r * z); R[2] = 2.f * (x * z + r * y);
+    R[3] = 2.f * (x * y + r * z); R[4] = 1.f - 2.f * (x * x + z * z); R[5] = 2.f * (y * z - r * x);
+    R[6] = 2.f * (x * z - r * y); R[7] = 2.f * (y * z + r * x); R[8] = 1.f - 2.f * (x * x + y * y);
+}
+
+__device__ __forceinline__ void load_pose(Pose& ps, const float* cam_rot, int rs, const float* cam_trans, int ts,
+                                          const float* sil_w2c) {
+    float q[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) q[k] = __ldg(cam_rot + (size_t)k * rs);
+    const float n = fmaxf(sqrtf(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]), 1e-12f);  // F.normalize
+    ps.qnorm = n;
+#pragma unroll
+    for (int k = 0; k < 4; k++) ps.q[k] = q[k] / n;
+    quat_to_rot(ps.q, ps.R);
+#pragma unroll
+    for (int k = 0; k < 3; k++) ps.t[k] = __ldg(cam_trans + (size_t)k * ts);
+    if (sil_w2c) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) ps.sil[k] = __ldg(sil_w2c + 8 + k);
+    } else {
+        ps.sil[0] = 0.f; ps.sil[1] = 0.f; ps.sil[2] = 1.f; ps.sil[3] = 0.f;
+    }
+}
+
+// quat_mult (slam_helpers.py:21-28)
+__device__ __forceinline__ void quat_mul(const float a[4], const float b[4], float o[4]) {
+    o[0] = a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3];
+    o[1] = a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2];
+    o[2] = a[0] * b[2] - a[1] * b[3] + a[2] * b[0] + a[3] * b[1];
+    o[3] = a[0] * b[3] + a[1] * b[2] - a[2] * b[1] + a[3] * b[0];
+}
+
+// Activations + frame transform of one Gaussian (F1+F2).  rot_t is the un-normalised transformed rotation.
+struct Activated {
+    float mc[3];     // mean in the frame
+    float qn[4];     // normalised own rotation (anisotropic only)
+    float qn_norm;   // |unnorm_rotation|
+    float rot_t[4];  // quat_mult(q_cam, qn)  (anisotropic)  or the raw rotation (isotropic)
+    float rot_t_norm;
+    float rot[4];    // normalised rotation fed to the rasterizer
+    float scale[3];
+    float opacity;
+};
+
+template <bool ISO>
+__device__ __forceinline__ void activate(const Pose& ps, float px, float py, float pz, float4 qraw, const float* ls,
+                                         float lo, Activated& a) {
+    a.mc[0] = fmaf(ps.R[2], pz, fmaf(ps.R[1], py, ps.R[0] * px)) + ps.t[0];
+    a.mc[1] = fmaf(ps.R[5], pz, fmaf(ps.R[4], py, ps.R[3] * px)) + ps.t[1];
+    a.mc[2] = fmaf(ps.R[8], pz, fmaf(ps.R[7], py, ps.R[6] * px)) + ps.t[2];
+    const float q[4] = {qraw.x, qraw.y, qraw.z, qraw.w};
+    if (ISO) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) a.rot_t[k] = q[k];
+        a.qn_norm = 1.f;
+    } else {
+        a.qn_norm = fmaxf(sqrtf(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]), 1e-12f);
+#pragma unroll
+        for (int k = 0; k < 4; k++) a.qn[k] = q[k] / a.qn_norm;
+        quat_mul(ps.q, a.qn, a.rot_t);
+    }
+    a.rot_t_norm = fmaxf(sqrtf(a.rot_t[0] * a.rot_t[0] + a.rot_t[1] * a.rot_t[1] + a.rot_t[2] * a.rot_t[2] +
+                               a.rot_t[3] * a.rot_t[3]), 1e-12f);
+#pragma unroll
+    for (int k = 0; k < 4; k++) a.rot[k] = a.rot_t[k] / a.rot_t_norm;
+    a.scale[0] = expf(ls[0]);
+    a.scale[1] = ISO ? a.scale[0] : expf(ls[1]);
+    a.scale[2] = ISO ? a.scale[0] : expf(ls[2]);
+    a.opacity = 1.f / (1.f + expf(-lo));
+}
+
+__device__ __forceinline__ void load_rows(const float* __restrict__ src, int row0, int nrows, int width, float* sm) {
+    const float* p = src + (size_t)row0 * width;
+    const int nfl = nrows * width;
+    if ((reinterpret_cast<uintptr_t>(p) & 15) == 0) {
+        const int nv = nfl >> 2;
+        const float4* p4 = reinterpret_cast<const float4*>(p);
+        for (int i = threadIdx.x; i < nv; i += FP_THREADS) reinterpret_cast<float4*>(sm)[i] = __ldg(p4 + i);
+        for (int i = (nv << 2) + threadIdx.x; i < nfl; i += FP_THREADS) sm[i] = __ldg(p + i);
+    } else {
+        for (int i = threadIdx.x; i < nfl; i += FP_THREADS) sm[i] = __ldg(p + i);
+    }
+}
+
+template <bool ISO>
+__global__ void __launch_bounds__(FP_THREADS)
+frame_preprocess_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ unnorm_rot,
+                        const float* __restrict__ logit_op, const float* __restrict__ log_scales,
+                        const float* __restrict__ cam_rot, int rs, const float* __restrict__ cam_trans, int ts,
+                        const float* __restrict__ sil_w2c, const float* __restrict__ viewmatrix,
+                        const float* __restrict__ projmatrix, int W, int H, int gx, int gy, float tanfovx,
+                        float tanfovy, float focal_x, float focal_y, float scale_modifier, int* __restrict__ radii,
+                        int* __restrict__ radii_internal, float2* __restrict__ means2D_out,
+                        float* __restrict__ depths, float4* __restrict__ conic_opacity,
+                        uint32_t* __restrict__ tiles_touched, float* __restrict__ zsil, uint32_t* status) {
+    __shared__ __align__(16) float s_means[FP_THREADS * 3];
+    __shared__ __align__(16) float s_ls[FP_THREADS * 3];
+    __shared__ float s_view[16], s_proj[16];
+    __shared__ Pose ps;
+    const int row0 = blockIdx.x * FP_THREADS;
+    const int nrows = min(FP_THREADS, P - row0);
+    load_rows(means3D, row0, nrows, 3, s_means);
+    load_rows(log_scales, row0, nrows, ISO ? 1 : 3, s_ls);
+    if (threadIdx.x < 16) s_view[threadIdx.x] = __ldg(viewmatrix + threadIdx.x);
+    else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = __ldg(projmatrix + threadIdx.x - 16);
+    else if (threadIdx.x == 32) load_pose(ps, cam_rot, rs, cam_trans, ts, sil_w2c);
+    if (blockIdx.x == 0 && threadIdx.x == 0) status[1] = 0;  // overflow flag of this frame
+    __syncthreads();
+    const int idx = row0 + threadIdx.x;
+    if (idx >= P) return;
+    Activated a;
+    activate<ISO>(ps, s_means[3 * threadIdx.x], s_means[3 * threadIdx.x + 1], s_means[3 * threadIdx.x + 2],
+                  __ldg(reinterpret_cast<const float4*>(unnorm_rot) + idx), s_ls + (ISO ? 1 : 3) * threadIdx.x,
+                  __ldg(logit_op + idx), a);
+    int my_radii = 0;
+    uint32_t my_tiles = 0;
+    if (xform_row(s_view, 2, a.mc[0], a.mc[1], a.mc[2]) > 0.2f) {
+        float cov3D[6];
+        cov3d_from_scale_rot(a.scale[0], a.scale[1], a.scale[2], scale_modifier,
+                             make_float4(a.rot[0], a.rot[1], a.rot[2], a.rot[3]), cov3D);
+        const PreprocessResult r = preprocess_one(a.mc[0], a.mc[1], a.mc[2], cov3D, a.opacity, s_view, s_proj, W, H, gx,
+                                                  gy, tanfovx, tanfovy, focal_x, focal_y);
+        if (r.radius > 0) {
+            my_radii = r.radius;
+            my_tiles = r.tiles;
+            depths[idx] = r.depth;
+            means2D_out[idx] = r.mean2D;
+            conic_opacity[idx] = r.conic_opacity;
+            zsil[idx] = ps.sil[0] * a.mc[0] + ps.sil[1] * a.mc[1] + ps.sil[2] * a.mc[2] + ps.sil[3];
+        }
+    }
+    if (radii) radii[idx] = my_radii;
+    radii_internal[idx] = my_radii;
+    tiles_touched[idx] = my_tiles;
+}
+
+// duplicateWithKeys (rasterizer_impl.cu:70-111) with a capacity guard instead of a host-sized buffer
+__global__ void __launch_bounds__(256)
+frame_duplicate_kernel(int P, const float2* __restrict__ means2D, const float* __restrict__ depths,
+                       const uint32_t* __restrict__ offsets, const int* __restrict__ radii, int gx, int gy,
+                       uint32_t capacity, uint64_t* __restrict__ keys, uint32_t* __restrict__ values,
+                       uint32_t* status) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P) return;
+    const int r = radii[idx];
+    if (r <= 0) return;
+    if (offsets[idx] > capacity) {  // this Gaussian's slots end past the buffer: flag, write nothing
+        status[1] = 1;
+        return;
+    }
+    uint32_t off = idx == 0 ? 0u : offsets[idx - 1];
+    const float2 p = means2D[idx];
+    int x0, y0, x1, y1;
+    get_rect(p.x, p.y, r, gx, gy, x0, y0, x1, y1);
+    const uint64_t dbits = (uint64_t)__float_as_uint(depths[idx]);
+    for (int y = y0; y < y1; y++)
+        for (int x = x0; x < x1; x++) {
+            keys[off] = ((uint64_t)(uint32_t)(y * gx + x) << 32) | dbits;
+            values[off] = (uint32_t)idx;
+            off++;
+        }
+}
+
+// identifyTileRanges + record gather for the frame path: features are (rgb | z, 1, z^2) built on the fly
+__global__ void __launch_bounds__(256)
+frame_ranges_gather_kernel(const uint32_t* __restrict__ n_dev, uint32_t capacity, const uint64_t* __restrict__ keys,
+                           const uint32_t* __restrict__ point_list, const float2* __restrict__ means2D,
+                           const float4* __restrict__ conic_opacity, const float* __restrict__ rgb,
+                           const float* __restrict__ zsil, float4* __restrict__ inst_conic,
+                           float4* __restrict__ inst_geom, float4* __restrict__ inst_feat, uint2* __restrict__ ranges,
+                           uint32_t tiles) {
+    if (n_dev[1]) return;  // overflow: the key buffer is incomplete; leave every range empty
+    const uint32_t R = min(*n_dev, capacity);
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= R) return;
+    const uint64_t key = keys[i];
+    const uint32_t cur = (uint32_t)(key >> 32);
+    if (cur >= tiles) return;
+    if (i == 0) ranges[cur].x = 0;
+    else {
+        const uint32_t prev = (uint32_t)(keys[i - 1] >> 32);
+        if (cur != prev) {
+            ranges[prev].y = i;
+            ranges[cur].x = i;
+        }
+    }
+    if (i == R - 1) ranges[cur].y = R;
+    const uint32_t id = point_list[i];
+    const float2 m = __ldg(means2D + id);
+    inst_conic[i] = __ldg(conic_opacity + id);
+    inst_geom[i] = make_float4(m.x, m.y, __uint_as_float((uint32_t)key), __uint_as_float(id));
+    const float z = __ldg(zsil + id);
+    const float* c = rgb + 3 * (size_t)id;
+    inst_feat[2 * (size_t)i] = make_float4(__ldg(c), __ldg(c + 1), __ldg(c + 2), z);
+    inst_feat[2 * (size_t)i + 1] = make_float4(1.f, z * z, 0.f, 0.f);
+}
+
+// Block-wide sum of NV per-thread values -> atomicAdd into out[NV] (one atomic per value per block).
+template <int NV>
+__device__ __forceinline__ void block_reduce_add(float (&v)[NV], float* s_red /*[NV * 8]*/, float* out) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < NV; k++) {
+        float x = v[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+        if (lane == 0) s_red[k * 8 + warp] = x;
+    }
+    __syncthreads();
+    if (threadIdx.x < NV) {
+        float x = 0.f;
+#pragma unroll
+        for (int w = 0; w < FP_THREADS / 32; w++) x += s_red[threadIdx.x * 8 + w];
+        if (x != 0.f) atomicAdd(out + threadIdx.x, x);
+    }
+}
+
+// Backward of frame_preprocess_kernel.  grad_params rows: means 3 | rgb 3 | rot 4 | logit 1 | log_scales 3.
+// pose_acc (16 floats): dL/dt (3) | dL/dR (9, row-major) | dL/dq_cam through quat_mult (4).
+template <bool ISO>
+__global__ void __launch_bounds__(FP_THREADS)
+frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ unnorm_rot,
+                                 const float* __restrict__ logit_op, const float* __restrict__ log_scales,
+                                 const float* __restrict__ cam_rot, int rs, const float* __restrict__ cam_trans, int ts,
+                                 const float* __restrict__ sil_w2c, const float* __restrict__ viewmatrix,
+                                 const float* __restrict__ projmatrix, float h_x, float h_y, float tanfovx,
+                                 float tanfovy, float scale_modifier, const int* __restrict__ radii,
+                                 const float* __restrict__ zsil, float* __restrict__ gacc,
+                                 const float* __restrict__ gscale, int gaussians_grad, int camera_grad,
+                                 float* __restrict__ grad_params, float* __restrict__ grad_means2D,
+                                 float* __restrict__ pose_acc) {
+    __shared__ float view[16], proj[16];
+    __shared__ Pose ps;
+    __shared__ float s_red[16 * 8];
+    if (threadIdx.x < 16) view[threadIdx.x] = __ldg(viewmatrix + threadIdx.x);
+    else if (threadIdx.x < 32) proj[threadIdx.x - 16] = __ldg(projmatrix + threadIdx.x - 16);
+    else if (threadIdx.x == 32) load_pose(ps, cam_rot, rs, cam_trans, ts, sil_w2c);
+    __syncthreads();
+    const int idx = blockIdx.x * FP_THREADS + threadIdx.x;
+    const float gs = gscale ? __ldg(gscale) : 1.f;
+    float pacc[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) pacc[k] = 0.f;
+    float out[14];
+#pragma unroll
+    for (int k = 0; k < 14; k++) out[k] = 0.f;
+    float gm2x = 0.f, gm2y = 0.f;
+    if (idx < P && radii[idx] > 0) {
+        float4* ga = reinterpret_cast<float4*>(gacc) + 3 * (size_t)idx;
+        const float4 g0 = ga[0], g1 = ga[1], g2 = ga[2];  // conic x,y,w | op ; mean2D x,y | c0 c1 ; c2 c3 c4 c5
+        const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+        ga[0] = zero; ga[1] = zero; ga[2] = zero;  // leave the accumulators clean for the next frame
+        const float px = __ldg(means3D + 3 * (size_t)idx), py = __ldg(means3D + 3 * (size_t)idx + 1),
+                    pz = __ldg(means3D + 3 * (size_t)idx + 2);
+        float ls[3];
+        ls[0] = __ldg(log_scales + (ISO ? 1 : 3) * (size_t)idx);
+        ls[1] = ISO ? ls[0] : __ldg(log_scales + 3 * (size_t)idx + 1);
+        ls[2] = ISO ? ls[0] : __ldg(log_scales + 3 * (size_t)idx + 2);
+        Activated a;
+        activate<ISO>(ps, px, py, pz, __ldg(reinterpret_cast<const float4*>(unnorm_rot) + idx), ls,
+                      __ldg(logit_op + idx), a);
+        float c3[6];
+        const float4 rot4 = make_float4(a.rot[0], a.rot[1], a.rot[2], a.rot[3]);
+        cov3d_from_scale_rot(a.scale[0], a.scale[1], a.scale[2], scale_modifier, rot4, c3);
+        float dmean[3], dcov[6], dscale[3], drot[4];
+        preprocess_backward_one(a.mc[0], a.mc[1], a.mc[2], c3, true, rot4, a.scale, scale_modifier, view, proj, h_x, h_y,
+                                tanfovx, tanfovy, g0.x, g0.y, g0.z, g1.x, g1.y, dmean, dcov, dscale, drot);
+        gm2x = g1.x; gm2y = g1.y;
+        // [z,1,z^2] features (T20): colour-channel gradients 3 and 5 reach the mean through z
+        const float z = __ldg(zsil + idx);
+        const float gz = g2.y + 2.f * z * g2.w;
+        dmean[0] += ps.sil[0] * gz; dmean[1] += ps.sil[1] * gz; dmean[2] += ps.sil[2] * gz;
+        // rotation chain: rot = normalize(rot_t)
+        float dot = 0.f;
+#pragma unroll
+        for (int k = 0; k < 4; k++) dot += a.rot[k] * drot[k];
+        float g_rt[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) g_rt[k] = (drot[k] - a.rot[k] * dot) / a.rot_t_norm;
+        float g_qraw[4];
+        if (ISO) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) g_qraw[k] = g_rt[k];
+        } else {
+            const float* q1 = ps.q;
+            const float* q2 = a.qn;
+            float g_qn[4];
+            g_qn[0] = q1[0] * g_rt[0] + q1[1] * g_rt[1] + q1[2] * g_rt[2] + q1[3] * g_rt[3];
+            g_qn[1] = -q1[1] * g_rt[0] + q1[0] * g_rt[1] + q1[3] * g_rt[2] - q1[2] * g_rt[3];
+            g_qn[2] = -q1[2] * g_rt[0] - q1[3] * g_rt[1] + q1[0] * g_rt[2] + q1[1] * g_rt[3];
+            g_qn[3] = -q1[3] * g_rt[0] + q1[2] * g_rt[1] - q1[1] * g_rt[2] + q1[0] * g_rt[3];
+            float d2 = 0.f;
+#pragma unroll
+            for (int k = 0; k < 4; k++) d2 += q2[k] * g_qn[k];
+#pragma unroll
+            for (int k = 0; k < 4; k++) g_qraw[k] = (g_qn[k] - q2[k] * d2) / a.qn_norm;
+            if (camera_grad) {
+                pacc[12] = q2[0] * g_rt[0] + q2[1] * g_rt[1] + q2[2] * g_rt[2] + q2[3] * g_rt[3];
+                pacc[13] = -q2[1] * g_rt[0] + q2[0] * g_rt[1] - q2[3] * g_rt[2] + q2[2] * g_rt[3];
+                pacc[14] = -q2[2] * g_rt[0] + q2[3] * g_rt[1] + q2[0] * g_rt[2] - q2[1] * g_rt[3];
+                pacc[15] = -q2[3] * g_rt[0] - q2[2] * g_rt[1] + q2[1] * g_rt[2] + q2[0] * g_rt[3];
+            }
+        }
+        if (camera_grad) {
+            pacc[0] = dmean[0]; pacc[1] = dmean[1]; pacc[2] = dmean[2];
+#pragma unroll
+            for (int i = 0; i < 3; i++) {
+                pacc[3 + 3 * i + 0] = dmean[i] * px;
+                pacc[3 + 3 * i + 1] = dmean[i] * py;
+                pacc[3 + 3 * i + 2] = dmean[i] * pz;
+            }
+        }
+        if (gaussians_grad) {
+            // means: world-frame gradient = R^T dL/dmeans_cam
+            out[0] = ps.R[0] * dmean[0] + ps.R[3] * dmean[1] + ps.R[6] * dmean[2];
+            out[1] = ps.R[1] * dmean[0] + ps.R[4] * dmean[1] + ps.R[7] * dmean[2];
+            out[2] = ps.R[2] * dmean[0] + ps.R[5] * dmean[1] + ps.R[8] * dmean[2];
+            out[3] = g1.z; out[4] = g1.w; out[5] = g2.x;  // rgb
+#pragma unroll
+            for (int k = 0; k < 4; k++) out[6 + k] = g_qraw[k];
+            out[10] = g0.w * a.opacity * (1.f - a.opacity);  // sigmoid'
+            if (ISO) {
+                out[11] = (dscale[0] + dscale[1] + dscale[2]) * a.scale[0];
+            } else {
+                out[11] = dscale[0] * a.scale[0]; out[12] = dscale[1] * a.scale[1]; out[13] = dscale[2] * a.scale[2];
+            }
+        }
+    }
+    if (idx < P) {
+        if (gaussians_grad && grad_params) {
+            float* o = grad_params + 14 * (size_t)idx;  // 56-byte rows: 8-byte aligned
+#pragma unroll
+            for (int k = 0; k < 14; k += 2) *reinterpret_cast<float2*>(o + k) = make_float2(out[k] * gs, out[k + 1] * gs);
+        }
+        if (grad_means2D) {
+            grad_means2D[3 * (size_t)idx] = gm2x * gs;
+            grad_means2D[3 * (size_t)idx + 1] = gm2y * gs;
+            grad_means2D[3 * (size_t)idx + 2] = 0.f;
+        }
+    }
+    if (camera_grad) {
+#pragma unroll
+        for (int k = 0; k < 16; k++) pacc[k] *= gs;
+        block_reduce_add<16>(pacc, s_red, pose_acc);
+    }
+}
+
+// pose_acc -> gradients of cam_unnorm_rot (4) and cam_trans (3); clears pose_acc for the next frame.
+__global__ void pose_finalize_kernel(const float* __restrict__ cam_rot, int rs, float* pose_acc, float* grad_cam) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    float qr[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) qr[k] = cam_rot[(size_t)k * rs];
+    const float n = fmaxf(sqrtf(qr[0] * qr[0] + qr[1] * qr[1] + qr[2] * qr[2] + qr[3] * qr[3]), 1e-12f);
+    float qc[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) qc[k] = qr[k] / n;
+    // build_rotation normalises qc once more: qh = qc / |qc|
+    const float n2 = sqrtf(qc[0] * qc[0] + qc[1] * qc[1] + qc[2] * qc[2] + qc[3] * qc[3]);
+    const float r = qc[0] / n2, x = qc[1] / n2, y = qc[2] / n2, z = qc[3] / n2;
+    const float* G = pose_acc + 3;  // dL/dR row-major
+    float gh[4];
+    gh[0] = 2.f * (-z * G[1] + y * G[2] + z * G[3] - x * G[5] - y * G[6] + x * G[7]);
+    gh[1] = 2.f * (y * G[1] + z * G[2] + y * G[3] - 2.f * x * G[4] - r * G[5] + z * G[6] + r * G[7] - 2.f * x * G[8]);
+    gh[2] = 2.f * (-2.f * y * G[0] + x * G[1] + r * G[2] + x * G[3] + z * G[5] - r * G[6] + z * G[7] - 2.f * y * G[8]);
+    gh[3] = 2.f * (-2.f * z * G[0] - r * G[1] + x * G[2] + r * G[3] - 2.f * z * G[4] + y * G[5] + x * G[6] + y * G[7]);
+    const float qh[4] = {r, x, y, z};
+    float d = 0.f;
+#pragma unroll
+    for (int k = 0; k < 4; k++) d += qh[k] * gh[k];
+    float gq[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) gq[k] = (gh[k] - qh[k] * d) / n2 + pose_acc[12 + k];
+    float d2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < 4; k++) d2 += qc[k] * gq[k];
+#pragma unroll
+    for (int k = 0; k < 4; k++) grad_cam[k] = (gq[k] - qc[k] * d2) / n;
+#pragma unroll
+    for (int k = 0; k < 3; k++) grad_cam[4 + k] = pose_acc[k];
+    grad_cam[7] = 0.f;
+#pragma unroll
+    for (int k = 0; k < 16; k++) pose_acc[k] = 0.f;
+}
+
+// ------------------------------------------------------------------------------------------------
+// F4 tracking loss (splatam.py:213-247, tracking branch with use_l1):
+//   mask = gt_depth > 0 & !nan(depth) & !nan(depth_sq - depth^2) [& sil > sil_thres]
+//   loss = w_im * sum_mask |gt_rgb - im| + w_depth * sum_mask |gt_depth - depth|
+// One sweep: per-block partial sums + dL/d(colour6).  A second tiny kernel adds the partials.
+// ------------------------------------------------------------------------------------------------
+constexpr int LOSS_THREADS = 256;
+
+__device__ __forceinline__ float sgn(float x) { return (x > 0.f) ? 1.f : ((x < 0.f) ? -1.f : 0.f); }
+
+__global__ void __launch_bounds__(LOSS_THREADS)
+tracking_loss_kernel(int N, const float* __restrict__ c6, const float* __restrict__ gt_rgb,
+                     const float* __restrict__ gt_depth, float w_im, float w_depth, float sil_thres, int use_sil,
+                     int mask_color, float* __restrict__ dL, float* __restrict__ partials) {
+    float s_im = 0.f, s_d = 0.f, s_cnt = 0.f;
+    for (int i = blockIdx.x * LOSS_THREADS + threadIdx.x; i < N; i += gridDim.x * LOSS_THREADS) {
+        const float depth = c6[3 * (size_t)N + i], sil = c6[4 * (size_t)N + i], dsq = c6[5 * (size_t)N + i];
+        const float gd = gt_depth[i];
+        const float inv = dsq - depth * depth;
+        bool m = (gd > 0.f) && !isnan(depth) && !isnan(inv);
+        if (use_sil) m = m && (sil > sil_thres);
+        const bool mc = mask_color ? m : true;
+        float g_d = 0.f;
+        if (m) {
+            const float e = gd - depth;
+            s_d += fabsf(e);
+            g_d = -w_depth * sgn(e);
+            s_cnt += 1.f;
+        }
+#pragma unroll
+        for (int ch = 0; ch < 3; ch++) {
+            float g = 0.f;
+            if (mc) {
+                const float e = gt_rgb[ch * (size_t)N + i] - c6[ch * (size_t)N + i];
+                s_im += fabsf(e);
+                g = -w_im * sgn(e);
+            }
+            dL[ch * (size_t)N + i] = g;
+        }
+        dL[3 * (size_t)N + i] = g_d;
+        dL[4 * (size_t)N + i] = 0.f;
+        dL[5 * (size_t)N + i] = 0.f;
+    }
+    __shared__ float s_red[3 * 8];
+    float v[3] = {s_im, s_d, s_cnt};
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        float x = v[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+        if (lane == 0) s_red[k * 8 + warp] = x;
+    }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        float x = 0.f;
+#pragma unroll
+        for (int w = 0; w < LOSS_THREADS / 32; w++) x += s_red[threadIdx.x * 8 + w];
+        partials[blockIdx.x * 4 + threadIdx.x] = x;
+    }
+}
+
+// losses[0] = weighted total, [1] = weighted im, [2] = weighted depth, [3] = mask count
+__global__ void tracking_loss_finalize_kernel(int nblocks, const float* __restrict__ partials, float w_im,
+                                              float w_depth, float* __restrict__ losses,
+                                              const uint32_t* __restrict__ status) {
+    __shared__ float s[3][32];
+    float v[3] = {0.f, 0.f, 0.f};
+    for (int b = threadIdx.x; b < nblocks; b += 32)
+#pragma unroll
+        for (int k = 0; k < 3; k++) v[k] += partials[b * 4 + k];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        float x = v[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+        s[k][0] = x;
+    }
+    if (threadIdx.x == 0) {
+        const float li = w_im * s[0][0], ld = w_depth * s[1][0];
+        losses[0] = li + ld;
+        losses[1] = li;
+        losses[2] = ld;
+        losses[3] = s[2][0];
+        if (status) {  // frame status rides along so that one read-back tells the host everything
+            losses[4] = (float)status[0];
+            losses[5] = (float)status[1];
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// F5 Adam (torch.optim.Adam semantics: no amsgrad, no weight decay), all five tensors in one pass.
+// grad/exp_avg/exp_avg_sq are [P,14] flat (means 3 | rgb 3 | rot 4 | logit 1 | log_scales 3).
+// ------------------------------------------------------------------------------------------------
+struct AdamPtrs {
+    float* p[5];
+    float lr[5];
+};
+
+__global__ void __launch_bounds__(256)
+adam_kernel(int P, int iso, AdamPtrs ap, const float* __restrict__ grad, float* __restrict__ m, float* __restrict__ v,
+            float beta1, float beta2, float eps, float bc1, float bc2_sqrt) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P) return;
+    const int width[5] = {3, 3, 4, 1, iso ? 1 : 3};
+    const int slot[5] = {0, 3, 6, 10, 11};
+#pragma unroll
+    for (int t = 0; t < 5; t++) {
+        const float step_size = ap.lr[t] / bc1;
+        for (int k = 0; k < width[t]; k++) {
+            const size_t f = 14 * (size_t)idx + slot[t] + k;
+            const float g = grad[f];
+            const float mm = m[f] + (g - m[f]) * (1.f - beta1);        // exp_avg.lerp_(grad, 1 - beta1)
+            const float vv = v[f] * beta2 + (1.f - beta2) * g * g;     // mul_(beta2).addcmul_(g, g, 1 - beta2)
+            m[f] = mm;
+            v[f] = vv;
+            const float denom = sqrtf(vv) / bc2_sqrt + eps;
+            float* p = ap.p[t] + (size_t)width[t] * idx + k;
+            *p = *p - step_size * (mm / denom);                         // addcdiv_(exp_avg, denom, -step_size)
+        }
+    }
+}
+
+}  // namespace
+
+// ---- host launchers --------------------------------------------------------------------------------
+void launch_frame_preprocess(const AsFrameArgs& a, const GeometryState& g, uint32_t* status, cudaStream_t st) {
+    const int P = a.P, W = a.width, H = a.height;
+    const float focal_y = H / (2.0f * a.tan_fovy), focal_x = W / (2.0f * a.tan_fovx);
+    const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
+    const int blocks = (P + FP_THREADS - 1) / FP_THREADS;
+    if (a.isotropic)
+        frame_preprocess_kernel<true><<<blocks, FP_THREADS, 0, st>>>(
+            P, a.means3D, a.unnorm_rotations, a.logit_opacities, a.log_scales, a.cam_unnorm_rot, a.cam_rot_stride,
+            a.cam_trans, a.cam_trans_stride, a.sil_w2c, a.viewmatrix, a.projmatrix, W, H, gx, gy, a.tan_fovx, a.tan_fovy,
+            focal_x, focal_y, a.scale_modifier, a.radii, g.radii, g.means2D, g.depths, g.conic_opacity, g.tiles_touched,
+            g.zsil, status);
+    else
+        frame_preprocess_kernel<false><<<blocks, FP_THREADS, 0, st>>>(
+            P, a.means3D, a.unnorm_rotations, a.logit_opacities, a.log_scales, a.cam_unnorm_rot, a.cam_rot_stride,
+            a.cam_trans, a.cam_trans_stride, a.sil_w2c, a.viewmatrix, a.projmatrix, W, H, gx, gy, a.tan_fovx, a.tan_fovy,
+            focal_x, focal_y, a.scale_modifier, a.radii, g.radii, g.means2D, g.depths, g.conic_opacity, g.tiles_touched,
+            g.zsil, status);
+}
+
+void launch_frame_duplicate(int P, const GeometryState& g, int W, int H, uint32_t capacity, uint64_t* keys,
+                            uint32_t* values, uint32_t* status, cudaStream_t st) {
+    const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
+    frame_duplicate_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, g.means2D, g.depths, g.point_offsets, g.radii, gx, gy,
+                                                            capacity, keys, values, status);
+}
+
+void launch_frame_ranges_gather(const uint32_t* n_dev, uint32_t capacity, int tiles, const GeometryState& g,
+                                const float* rgb, const BinningState& b, uint2* ranges, cudaStream_t st) {
+    cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)tiles, st);
+    if (capacity == 0) return;
+    frame_ranges_gather_kernel<<<(capacity + 255) / 256, 256, 0, st>>>(n_dev, capacity, b.keys_sorted, b.point_list,
+                                                                      g.means2D, g.conic_opacity, rgb, g.zsil,
+                                                                      b.inst_conic, b.inst_geom, b.inst_feat, ranges,
+                                                                      (uint32_t)tiles);
+}
+
+void launch_frame_preprocess_backward(const AsFrameArgs& a, const GeometryState& g, const float* gscale,
+                                      int gaussians_grad, int camera_grad, float* grad_params, float* grad_means2D,
+                                      float* pose_acc, float* grad_cam, cudaStream_t st) {
+    const int P = a.P, W = a.width, H = a.height;
+    const float h_y = H / (2.0f * a.tan_fovy), h_x = W / (2.0f * a.tan_fovx);
+    const int blocks = (P + FP_THREADS - 1) / FP_THREADS;
+    if (a.isotropic)
+        frame_preprocess_backward_kernel<true><<<blocks, FP_THREADS, 0, st>>>(
+            P, a.means3D, a.unnorm_rotations, a.logit_opacities, a.log_scales, a.cam_unnorm_rot, a.cam_rot_stride,
+            a.cam_trans, a.cam_trans_stride, a.sil_w2c, a.viewmatrix, a.projmatrix, h_x, h_y, a.tan_fovx, a.tan_fovy,
+            a.scale_modifier, g.radii, g.zsil, g.gacc, gscale, gaussians_grad, camera_grad, grad_params, grad_means2D,
+            pose_acc);
+    else
+        frame_preprocess_backward_kernel<false><<<blocks, FP_THREADS, 0, st>>>(
+            P, a.means3D, a.unnorm_rotations, a.logit_opacities, a.log_scales, a.cam_unnorm_rot, a.cam_rot_stride,
+            a.cam_trans, a.cam_trans_stride, a.sil_w2c, a.viewmatrix, a.projmatrix, h_x, h_y, a.tan_fovx, a.tan_fovy,
+            a.scale_modifier, g.radii, g.zsil, g.gacc, gscale, gaussians_grad, camera_grad, grad_params, grad_means2D,
+            pose_acc);
+    if (camera_grad) pose_finalize_kernel<<<1, 32, 0, st>>>(a.cam_unnorm_rot, a.cam_rot_stride, pose_acc, grad_cam);
+}
+
+int loss_partial_blocks(int N) {
+    int b = (N + LOSS_THREADS - 1) / LOSS_THREADS;
+    return b > NUM_SMS * 4 ? NUM_SMS * 4 : b;
+}
+
+void launch_tracking_loss(int N, const float* c6, const float* gt_rgb, const float* gt_depth, float w_im,
+                          float w_depth, float sil_thres, int use_sil, int mask_color, float* dL, float* partials,
+                          float* losses, const uint32_t* status, cudaStream_t st) {
+    const int blocks = loss_partial_blocks(N);
+    tracking_loss_kernel<<<blocks, LOSS_THREADS, 0, st>>>(N, c6, gt_rgb, gt_depth, w_im, w_depth, sil_thres, use_sil,
+                                                          mask_color, dL, partials);
+    tracking_loss_finalize_kernel<<<1, 32, 0, st>>>(blocks, partials, w_im, w_depth, losses, status);
+}
+
+void launch_adam(int P, int iso, float* const params[5], const float lr[5], const float* grad, float* m, float* v,
+                 float beta1, float beta2, float eps, int step, cudaStream_t st) {
+    AdamPtrs ap;
+    for (int t = 0; t < 5; t++) {
+        ap.p[t] = params[t];
+        ap.lr[t] = lr[t];
+    }
+    const float bc1 = 1.f - powf(beta1, (float)step);
+    const float bc2_sqrt = sqrtf(1.f - powf(beta2, (float)step));
+    adam_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, iso, ap, grad, m, v, beta1, beta2, eps, bc1, bc2_sqrt);
+}
+
+}  // namespace asb

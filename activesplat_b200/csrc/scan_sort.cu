@@ -127,8 +127,10 @@ struct SortTemp {
 __host__ __device__ inline size_t sort_header_words() { return RS_MAX_PASSES * RS_BINS + 2 * RS_MAX_PASSES; }
 
 __global__ void __launch_bounds__(RS_THREADS)
-radix_hist_kernel(const uint64_t* __restrict__ keys, int n, int passes, uint32_t* __restrict__ hist) {
+radix_hist_kernel(const uint64_t* __restrict__ keys, int n, const uint32_t* __restrict__ n_dev, int passes,
+                  uint32_t* __restrict__ hist) {
     __shared__ uint32_t sh[RS_MAX_PASSES * RS_BINS];
+    if (n_dev) n = min(n, (int)*n_dev);  // device-side count (no-sync path); n is then the capacity
     for (int i = threadIdx.x; i < passes * RS_BINS; i += RS_THREADS) sh[i] = 0;
     __syncthreads();
     const int stride = gridDim.x * RS_THREADS;
@@ -144,8 +146,10 @@ radix_hist_kernel(const uint64_t* __restrict__ keys, int n, int passes, uint32_t
 }
 
 // one block per pass: counts -> exclusive offsets; flag passes that do not move anything
-__global__ void __launch_bounds__(RS_BINS) radix_scan_kernel(uint32_t* hist, uint32_t* skip, int n) {
+__global__ void __launch_bounds__(RS_BINS)
+radix_scan_kernel(uint32_t* hist, uint32_t* skip, int n, const uint32_t* __restrict__ n_dev) {
     __shared__ uint32_t s_warp[RS_BINS / 32];
+    if (n_dev) n = min(n, (int)*n_dev);
     const int p = blockIdx.x;
     const uint32_t c = hist[p * RS_BINS + threadIdx.x];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -188,8 +192,9 @@ __device__ __forceinline__ PingPong resolve_buffers(const uint32_t* __restrict__
 
 __global__ void __launch_bounds__(RS_THREADS)
 radix_onesweep_kernel(const uint64_t* k_src, const uint32_t* v_src, uint64_t* k_a, uint32_t* v_a, uint64_t* k_b,
-                      uint32_t* v_b, int n, int pass, const uint32_t* __restrict__ hist,
-                      const uint32_t* __restrict__ skip, uint32_t* ticket, uint32_t* status) {
+                      uint32_t* v_b, int n, const uint32_t* __restrict__ n_dev, int pass,
+                      const uint32_t* __restrict__ hist, const uint32_t* __restrict__ skip, uint32_t* ticket,
+                      uint32_t* status) {
     __shared__ uint32_t s_warp_hist[RS_WARPS][RS_BINS];  // per-warp digit counts -> per-warp exclusive offsets
     __shared__ uint32_t s_loc_off[RS_BINS];              // start of the digit's run inside the reordered tile
     __shared__ uint32_t s_dst_base[RS_BINS];             // global index of the run's first element minus s_loc_off
@@ -199,6 +204,7 @@ radix_onesweep_kernel(const uint64_t* k_src, const uint32_t* v_src, uint64_t* k_
     __shared__ uint32_t s_tile;
 
     if (skip[pass]) return;  // uniform: this pass would be the identity permutation
+    if (n_dev) n = min(n, (int)*n_dev);
     const PingPong pp = resolve_buffers(skip, pass, k_src, v_src, k_a, v_a, k_b, v_b);
 
     if (threadIdx.x == 0) s_tile = atomicAdd(ticket + pass, 1u);
@@ -208,6 +214,7 @@ radix_onesweep_kernel(const uint64_t* k_src, const uint32_t* v_src, uint64_t* k_
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int shift = 8 * pass;
     const int tile_base = tile * RS_TILE;
+    if (tile_base >= n) return;  // launched for the capacity; nobody looks back at tiles past the end
     const int valid = min(RS_TILE, n - tile_base);
 
     // warp-striped load: item i of lane l of warp w is element w*32*KPT + i*32 + l of the tile
@@ -304,9 +311,11 @@ radix_onesweep_kernel(const uint64_t* k_src, const uint32_t* v_src, uint64_t* k_
 
 // All passes skipped (n <= 1 or all keys equal): the output is the input.
 __global__ void radix_copy_if_all_skipped(const uint64_t* k_src, const uint32_t* v_src, uint64_t* k_a, uint32_t* v_a,
-                                          int n, const uint32_t* __restrict__ skip) {
+                                          int n, const uint32_t* __restrict__ n_dev,
+                                          const uint32_t* __restrict__ skip) {
     for (int q = 0; q < RS_MAX_PASSES; q++)
         if (!skip[q]) return;
+    if (n_dev) n = min(n, (int)*n_dev);
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         k_a[i] = k_src[i];
         v_a[i] = v_src[i];
@@ -355,7 +364,8 @@ size_t sort_temp_bytes(int n) {
 }
 
 void launch_sort_pairs(const uint64_t* keys_in, const uint32_t* values_in, uint64_t* keys_out,
-                       uint32_t* values_out, int n, int end_bit, char* temp, cudaStream_t st) {
+                       uint32_t* values_out, int n, int end_bit, char* temp, cudaStream_t st,
+                       const uint32_t* n_dev) {
     if (n <= 0) return;
     int passes = (end_bit + 7) / 8;
     if (passes < 1) passes = 1;
@@ -377,15 +387,15 @@ void launch_sort_pairs(const uint64_t* keys_in, const uint32_t* values_in, uint6
     radix_init_kernel<<<(int)iblocks, 1024, 0, st>>>(words, nwords, passes);
     int hblocks = (n + RS_THREADS * 16 - 1) / (RS_THREADS * 16);
     if (hblocks > NUM_SMS * 8) hblocks = NUM_SMS * 8;
-    radix_hist_kernel<<<hblocks, RS_THREADS, 0, st>>>(keys_in, n, passes, t.hist);
-    radix_scan_kernel<<<passes, RS_BINS, 0, st>>>(t.hist, t.skip, n);
+    radix_hist_kernel<<<hblocks, RS_THREADS, 0, st>>>(keys_in, n, n_dev, passes, t.hist);
+    radix_scan_kernel<<<passes, RS_BINS, 0, st>>>(t.hist, t.skip, n, n_dev);
     for (int pass = 0; pass < passes; pass++)
         radix_onesweep_kernel<<<(int)tiles, RS_THREADS, 0, st>>>(keys_in, values_in, keys_out, values_out, k_b, v_b, n,
-                                                                 pass, t.hist, t.skip, t.ticket,
+                                                                 n_dev, pass, t.hist, t.skip, t.ticket,
                                                                  t.status + (size_t)pass * tiles * RS_BINS);
     int cblocks = (n + 255) / 256;
     if (cblocks > NUM_SMS * 4) cblocks = NUM_SMS * 4;
-    radix_copy_if_all_skipped<<<cblocks, 256, 0, st>>>(keys_in, values_in, keys_out, values_out, n, t.skip);
+    radix_copy_if_all_skipped<<<cblocks, 256, 0, st>>>(keys_in, values_in, keys_out, values_out, n, n_dev, t.skip);
 }
 
 

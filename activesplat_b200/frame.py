@@ -1,0 +1,247 @@
+"""Fused SplaTAM frame step on top of the C ABI (as_frame_forward / as_frame_backward /
+as_tracking_loss / as_adam_step).
+
+`FrameWorkspace` owns the persistent device buffers of one (P, W, H) configuration so that a step
+allocates nothing and never synchronises with the host; `fused_tracking_loss` is the autograd entry
+that `splatam.get_loss(tracking=True)` uses; `FusedAdam` mirrors `torch.optim.Adam` as configured
+by `initialize_optimizer` (src/mapper/splatam/splatam.py:118-124) over the five Gaussian tensors.
+"""
+import ctypes
+
+import torch
+
+from . import capi
+
+PARAM_ORDER = ("means3D", "rgb_colors", "unnorm_rotations", "logit_opacities", "log_scales")
+SLOTS = {"means3D": (0, 3), "rgb_colors": (3, 6), "unnorm_rotations": (6, 10), "logit_opacities": (10, 11),
+         "log_scales": (11, 14)}
+
+
+class FrameWorkspace:
+    """Persistent scratch + outputs for the fused frame path.
+
+    The binning buffer holds `capacity` instances.  The number actually needed is only known on the
+    device; it comes back with the losses (`last_status()` reads it).  If a frame overflowed, its
+    outputs are invalid: `ensure_capacity()` grows the buffer and the caller re-runs the frame.
+    One workspace supports one forward/backward pair in flight.
+    """
+
+    def __init__(self, P, width, height, device, capacity=None, want_means2D_grad=False):
+        L = capi.lib()
+        self.P, self.W, self.H, self.device = int(P), int(width), int(height), torch.device(device)
+        self.capacity = int(capacity) if capacity else max(4 * self.P, 1 << 16)
+        with torch.cuda.device(self.device):
+            u8 = dict(dtype=torch.uint8, device=self.device)
+            f32 = dict(dtype=torch.float32, device=self.device)
+            self.geom = torch.zeros(L.as_geometry_bytes(self.P), **u8)   # accumulators must start at zero
+            self.img = torch.empty(L.as_image_bytes(self.W, self.H), **u8)
+            self.binning = torch.empty(L.as_binning_bytes(self.capacity, 6), **u8)
+            self.status = torch.zeros(2, dtype=torch.int32, device=self.device)
+            self.color6 = torch.empty((6, self.H, self.W), **f32)
+            self.depth = torch.empty((1, self.H, self.W), **f32)
+            self.opacity = torch.empty((1, self.H, self.W), **f32)
+            self.radii = torch.empty((self.P,), dtype=torch.int32, device=self.device)
+            self.dL = torch.empty((6, self.H, self.W), **f32)
+            self.losses = torch.zeros(8, **f32)
+            self.loss_scratch = torch.empty(L.as_loss_scratch_floats(self.W, self.H), **f32)
+            self.grad_params = torch.zeros((self.P, 14), **f32)
+            self.grad_means2D = torch.zeros((self.P, 3), **f32) if want_means2D_grad else None
+            self.grad_cam = torch.zeros(8, **f32)
+            self.pose_scratch = torch.zeros(16, **f32)
+            self.bg6 = torch.zeros(6, **f32)
+        self._args = None
+        self._keep = None
+        self._bg_src = None
+
+    # -- buffer management ---------------------------------------------------------------------
+    def ensure_capacity(self, needed):
+        if needed <= self.capacity:
+            return False
+        self.capacity = int(needed * 1.25) + 1024
+        with torch.cuda.device(self.device):
+            self.binning = torch.empty(capi.lib().as_binning_bytes(self.capacity, 6), dtype=torch.uint8,
+                                       device=self.device)
+        return True
+
+    def last_status(self):
+        """(num_rendered, overflowed) of the last frame -- synchronises."""
+        s = self.status.tolist()
+        return int(s[0]), bool(s[1])
+
+    # -- forward / backward --------------------------------------------------------------------
+    def forward(self, params, cam, time_idx, sil_w2c=None, bg_rgb=None, debug=False):
+        """as_frame_forward.  params: dict with the five Gaussian tensors + cam_unnorm_rots [1,4,T] +
+        cam_trans [1,3,T]; cam: GaussianRasterizationSettings.  Results land in color6/depth/opacity/radii."""
+        L = capi.lib()
+        a = capi.AsFrameArgs()
+        keep = []
+
+        def ptr(t):
+            if t.dtype != torch.float32 or not t.is_contiguous():
+                t = t.contiguous().float()
+            keep.append(t)
+            return t.data_ptr()
+
+        a.P, a.width, a.height = self.P, self.W, self.H
+        a.isotropic = 1 if params["log_scales"].shape[1] == 1 else 0
+        a.means3D = ptr(params["means3D"].detach())
+        a.rgb_colors = ptr(params["rgb_colors"].detach())
+        a.unnorm_rotations = ptr(params["unnorm_rotations"].detach())
+        a.logit_opacities = ptr(params["logit_opacities"].detach())
+        a.log_scales = ptr(params["log_scales"].detach())
+        rots, trans = params["cam_unnorm_rots"].detach(), params["cam_trans"].detach()
+        T = rots.shape[-1]
+        assert rots.is_contiguous() and trans.is_contiguous() and rots.dtype == torch.float32
+        a.cam_unnorm_rot = rots.data_ptr() + 4 * int(time_idx)
+        a.cam_rot_stride = T
+        a.cam_trans = trans.data_ptr() + 4 * int(time_idx)
+        a.cam_trans_stride = T
+        keep += [rots, trans]
+        a.sil_w2c = ptr(sil_w2c) if sil_w2c is not None else None
+        a.viewmatrix = ptr(cam.viewmatrix)
+        a.projmatrix = ptr(cam.projmatrix)
+        bg = cam.bg if bg_rgb is None else bg_rgb
+        if bg is not self._bg_src:  # refresh the 6-channel background only when the caller's object changes
+            self.bg6[:3].copy_(torch.as_tensor(bg, dtype=torch.float32, device=self.device))
+            self._bg_src = bg
+        a.background = self.bg6.data_ptr()
+        a.tan_fovx, a.tan_fovy, a.scale_modifier = float(cam.tanfovx), float(cam.tanfovy), float(cam.scale_modifier)
+        a.geom_buffer, a.image_buffer, a.binning_buffer = self.geom.data_ptr(), self.img.data_ptr(), self.binning.data_ptr()
+        a.binning_capacity = self.capacity
+        a.status = self.status.data_ptr()
+        a.out_color, a.out_depth, a.out_opacity = self.color6.data_ptr(), self.depth.data_ptr(), self.opacity.data_ptr()
+        a.radii = self.radii.data_ptr()
+        a.debug = int(bool(debug))
+        with torch.cuda.device(self.device):
+            capi.check(L.as_frame_forward(ctypes.byref(a), torch.cuda.current_stream(self.device).cuda_stream))
+        self._args, self._keep = a, keep
+        return self.color6, self.radii, self.depth, self.opacity
+
+    def tracking_loss(self, gt_rgb, gt_depth, w_im, w_depth, sil_thres, use_sil_for_loss, mask_color):
+        L = capi.lib()
+        keep = self._keep
+
+        def ptr(t):
+            if t.dtype != torch.float32 or not t.is_contiguous():
+                t = t.contiguous().float()
+            keep.append(t)
+            return t.data_ptr()
+
+        with torch.cuda.device(self.device):
+            capi.check(L.as_tracking_loss(self.W, self.H, self.color6.data_ptr(), ptr(gt_rgb), ptr(gt_depth),
+                                          float(w_im), float(w_depth), float(sil_thres), int(bool(use_sil_for_loss)),
+                                          int(bool(mask_color)), self.dL.data_ptr(), self.losses.data_ptr(),
+                                          self.loss_scratch.data_ptr(), self.status.data_ptr(),
+                                          torch.cuda.current_stream(self.device).cuda_stream))
+        return self.losses
+
+    def backward(self, dL_dpix=None, grad_scale=None, gaussians_grad=True, camera_grad=False):
+        """as_frame_backward for the last forward.  Returns (grad_params [P,14], grad_cam [8])."""
+        L = capi.lib()
+        b = capi.AsFrameBackwardArgs()
+        b.frame = ctypes.pointer(self._args)
+        dL = self.dL if dL_dpix is None else dL_dpix.contiguous()
+        b.dL_dpix = dL.data_ptr()
+        b.grad_scale = grad_scale.data_ptr() if grad_scale is not None else None
+        b.gaussians_grad, b.camera_grad = int(bool(gaussians_grad)), int(bool(camera_grad))
+        b.grad_params = self.grad_params.data_ptr()
+        b.grad_means2D = self.grad_means2D.data_ptr() if self.grad_means2D is not None else None
+        b.grad_cam = self.grad_cam.data_ptr()
+        b.pose_scratch = self.pose_scratch.data_ptr()
+        with torch.cuda.device(self.device):
+            capi.check(L.as_frame_backward(ctypes.byref(b), torch.cuda.current_stream(self.device).cuda_stream))
+        return self.grad_params, self.grad_cam
+
+
+_WORKSPACES = {}
+
+
+def workspace_for(params, cam):
+    """One cached workspace per (P, W, H, device)."""
+    key = (int(params["means3D"].shape[0]), int(cam.image_width), int(cam.image_height),
+           params["means3D"].device.index)
+    ws = _WORKSPACES.get(key)
+    if ws is None:
+        ws = FrameWorkspace(key[0], key[1], key[2], params["means3D"].device)
+        _WORKSPACES[key] = ws
+    return ws
+
+
+class _FusedTrackingLoss(torch.autograd.Function):
+    """loss = w_im * sum_mask|gt_rgb - im| + w_depth * sum_mask|gt_depth - depth|  (splatam.py:230-247)
+    of the frame rendered from the raw parameters, as ONE autograd node."""
+
+    @staticmethod
+    def forward(ctx, means3D, rgb, rots, logit_op, log_scales, cam_rots, cam_trans, ws, cam, time_idx, sil_w2c,
+                gt_rgb, gt_depth, w_im, w_depth, sil_thres, use_sil, mask_color):
+        params = {"means3D": means3D, "rgb_colors": rgb, "unnorm_rotations": rots, "logit_opacities": logit_op,
+                  "log_scales": log_scales, "cam_unnorm_rots": cam_rots, "cam_trans": cam_trans}
+        ws.forward(params, cam, time_idx, sil_w2c=sil_w2c)
+        ws.tracking_loss(gt_rgb, gt_depth, w_im, w_depth, sil_thres, use_sil, mask_color)
+        ctx.ws, ctx.time_idx = ws, int(time_idx)
+        ctx.shapes = (cam_rots.shape, cam_trans.shape, log_scales.shape[1])
+        ctx.gaussians_grad = any(ctx.needs_input_grad[:5])
+        ctx.camera_grad = any(ctx.needs_input_grad[5:7])
+        ctx.need = tuple(ctx.needs_input_grad[:7])
+        return ws.losses[:3].clone()
+
+    @staticmethod
+    def backward(ctx, g):
+        ws = ctx.ws
+        # d(total)/d... ; the im/depth components are returned for logging only
+        scale = g[0:1].contiguous()
+        gp, gc = ws.backward(grad_scale=scale, gaussians_grad=ctx.gaussians_grad, camera_grad=ctx.camera_grad)
+        outs = [None] * 18
+        if ctx.gaussians_grad:
+            ls_w = ctx.shapes[2]
+            views = (gp[:, 0:3], gp[:, 3:6], gp[:, 6:10], gp[:, 10:11], gp[:, 11:11 + ls_w])
+            for i in range(5):
+                if ctx.need[i]:
+                    outs[i] = views[i]
+        if ctx.camera_grad:
+            g_rot = torch.zeros(ctx.shapes[0], dtype=torch.float32, device=gc.device)
+            g_tr = torch.zeros(ctx.shapes[1], dtype=torch.float32, device=gc.device)
+            g_rot[0, :, ctx.time_idx] = gc[0:4]
+            g_tr[0, :, ctx.time_idx] = gc[4:7]
+            outs[5], outs[6] = g_rot, g_tr
+        return tuple(outs)
+
+
+def fused_tracking_loss(params, cam, time_idx, sil_w2c, gt_rgb, gt_depth, w_im, w_depth, sil_thres,
+                        use_sil_for_loss, mask_color, ws=None):
+    """Returns (losses[3] = weighted total / im / depth as a device tensor, workspace)."""
+    ws = ws or workspace_for(params, cam)
+    out = _FusedTrackingLoss.apply(params["means3D"], params["rgb_colors"], params["unnorm_rotations"],
+                                   params["logit_opacities"], params["log_scales"], params["cam_unnorm_rots"],
+                                   params["cam_trans"], ws, cam, time_idx, sil_w2c, gt_rgb, gt_depth, w_im, w_depth,
+                                   sil_thres, use_sil_for_loss, mask_color)
+    return out, ws
+
+
+class FusedAdam:
+    """torch.optim.Adam(lr per tensor, betas (0.9, 0.999), eps) over the five Gaussian tensors in one kernel.
+    State is flat [P,14]; `step(grad_flat)` consumes the flat gradient buffer of the frame backward."""
+
+    def __init__(self, params, lrs, betas=(0.9, 0.999), eps=1e-15):
+        self.params = params
+        self.lrs = (ctypes.c_float * 5)(*[float(lrs[k]) for k in PARAM_ORDER])
+        self.betas, self.eps, self.t = betas, eps, 0
+        P, dev = params["means3D"].shape[0], params["means3D"].device
+        self.exp_avg = torch.zeros((P, 14), dtype=torch.float32, device=dev)
+        self.exp_avg_sq = torch.zeros((P, 14), dtype=torch.float32, device=dev)
+
+    @torch.no_grad()
+    def step(self, grad_flat):
+        L = capi.lib()
+        self.t += 1
+        p = self.params
+        dev = p["means3D"].device
+        for k in PARAM_ORDER:
+            assert p[k].is_contiguous() and p[k].dtype == torch.float32
+        with torch.cuda.device(dev):
+            capi.check(L.as_adam_step(int(p["means3D"].shape[0]), 1 if p["log_scales"].shape[1] == 1 else 0,
+                                      p["means3D"].data_ptr(), p["rgb_colors"].data_ptr(),
+                                      p["unnorm_rotations"].data_ptr(), p["logit_opacities"].data_ptr(),
+                                      p["log_scales"].data_ptr(), grad_flat.data_ptr(), self.exp_avg.data_ptr(),
+                                      self.exp_avg_sq.data_ptr(), self.lrs, self.betas[0], self.betas[1], self.eps,
+                                      self.t, torch.cuda.current_stream(dev).cuda_stream))

@@ -190,6 +190,10 @@ def calc_ssim(img1, img2, window_size=11, size_average=True):
 def get_loss(params, curr_data, variables, iter_time_idx, loss_weights, use_sil_for_loss, sil_thres, use_l1,
              ignore_outlier_depth_loss, tracking=False, mapping=False, do_ba=False, plot_dir=None,
              visualize_tracking_loss=False, tracking_iteration=None):
+    if (tracking and use_l1 and not ignore_outlier_depth_loss and not visualize_tracking_loss
+            and params['means3D'].is_cuda):
+        return _get_loss_tracking_fused(params, curr_data, variables, iter_time_idx, loss_weights, use_sil_for_loss,
+                                        sil_thres)
     losses = {}
     if tracking:
         tg = transform_to_frame(params, iter_time_idx, gaussians_grad=False, camera_grad=True)
@@ -235,6 +239,27 @@ def get_loss(params, curr_data, variables, iter_time_idx, loss_weights, use_sil_
     variables['max_2D_radius'][seen] = torch.max(radius[seen], variables['max_2D_radius'][seen])
     variables['seen'] = seen
     weighted_losses['loss'] = loss
+    return loss, variables, weighted_losses
+
+
+def _get_loss_tracking_fused(params, curr_data, variables, iter_time_idx, loss_weights, use_sil_for_loss, sil_thres):
+    """get_loss(tracking=True) (splatam.py:178-182, 230-247) as one fused autograd node: frame transform,
+    activations, the 6-channel bundle render, the masked L1 sums and the whole backward run as a dozen
+    kernels on the current stream with no host synchronisation."""
+    from .frame import fused_tracking_loss
+    # transform_to_frame(gaussians_grad=False, camera_grad=True): means and rotations are detached,
+    # colours / opacities / scales are not (slam_helpers.py:124-139 reads them from `params` directly)
+    params = dict(params, means3D=params['means3D'].detach(), unnorm_rotations=params['unnorm_rotations'].detach())
+    out, ws = fused_tracking_loss(params, curr_data['cam'], int(iter_time_idx), curr_data['w2c'], curr_data['im'],
+                                  curr_data['depth'], loss_weights['im'], loss_weights['depth'], sil_thres,
+                                  use_sil_for_loss, use_sil_for_loss)
+    loss = out[0]
+    weighted_losses = {'depth': out[2], 'im': out[1], 'loss': loss}
+    radius = ws.radii
+    # radius == 0 exactly where the Gaussian was not seen, so this equals the indexed update of splatam.py:296-298
+    variables['max_2D_radius'] = torch.maximum(variables['max_2D_radius'], radius.to(variables['max_2D_radius'].dtype))
+    variables['seen'] = radius > 0
+    variables['means2D'] = None  # screen-space gradient: FrameWorkspace(want_means2D_grad=True).grad_means2D
     return loss, variables, weighted_losses
 
 

@@ -205,6 +205,10 @@ def run_ours(args, rank, world, local_rank):
     for i in range(min(args.warmup, 3)):
         one_step(i, True)
     ms_e2e, _, _ = timed(args.steps, True, False)
+    from activesplat_b200.frame import workspace_for
+    n_inst, overflowed = workspace_for(params, cam).last_status()
+    if overflowed:
+        raise RuntimeError(f"binning buffer overflow ({n_inst} instances): the timed frames are invalid")
 
     # workload statistics for the algorithmic-byte figure (one extra forward per keyframe, untimed)
     stats = []

@@ -134,6 +134,79 @@ typedef struct AsScratchLayout {
 } AsScratchLayout;
 int as_scratch_layout(int P, int width, int height, int num_rendered, int channels, AsScratchLayout* out);
 
+/* ---- fused SplaTAM frame step (additive; the three entry points above are unchanged) --------
+ *
+ * One call = transform_to_frame + activations + [z,1,z^2] features + the 6-channel bundle render
+ * (reference: src/mapper/splatam/utils/slam_helpers.py:124-139,196-213,252-304 feeding two
+ * Renderer calls at src/mapper/splatam/splatam.py:208,212), straight from the RAW parameters.
+ * No host synchronisation: num_rendered stays on the device (status[0]); the binning buffer is sized
+ * by the caller for `binning_capacity` instances (as_binning_bytes(capacity, 6)); if a frame needs more,
+ * status[1] is set to 1, nothing is written out of bounds, and the frame's outputs are invalid
+ * (re-run with a larger buffer).  The three scratch buffers are caller-owned and reused across
+ * frames; geom_buffer must be zero-filled once when it is created (as_geometry_bytes(P) bytes). */
+typedef struct AsFrameArgs {
+    int P, width, height;
+    int isotropic;                 /* log_scales is [P,1] (rotations then pass through un-transformed) */
+    const float* means3D;          /* [P,3] world frame */
+    const float* rgb_colors;       /* [P,3] */
+    const float* unnorm_rotations; /* [P,4] */
+    const float* logit_opacities;  /* [P] */
+    const float* log_scales;       /* [P,3] or [P,1] */
+    const float* cam_unnorm_rot;   /* camera quaternion (r,x,y,z), element k at cam_unnorm_rot[k*cam_rot_stride] */
+    int cam_rot_stride;
+    const float* cam_trans;        /* camera translation, element k at cam_trans[k*cam_trans_stride] */
+    int cam_trans_stride;
+    const float* sil_w2c;          /* [16] row-major w2c of the [z,1,z^2] features (curr_data['w2c']); NULL = identity */
+    const float* viewmatrix;       /* raster settings, as in AsForwardArgs */
+    const float* projmatrix;
+    const float* background;       /* [6] */
+    float tan_fovx, tan_fovy, scale_modifier;
+    char* geom_buffer;
+    char* image_buffer;
+    char* binning_buffer;
+    int binning_capacity;
+    uint32_t* status;              /* [2] device words: [0] num_rendered, [1] overflow flag */
+    float* out_color;              /* [6,H,W]: rgb | depth, silhouette, depth^2 */
+    float* out_depth;              /* [1,H,W] median depth */
+    float* out_opacity;            /* [1,H,W] */
+    int* radii;                    /* [P] or NULL */
+    int debug;
+} AsFrameArgs;
+
+typedef struct AsFrameBackwardArgs {
+    const AsFrameArgs* frame;      /* the arguments of the matching as_frame_forward */
+    const float* dL_dpix;          /* [6,H,W] */
+    const float* grad_scale;       /* device scalar multiplied into every output gradient; NULL = 1 */
+    int gaussians_grad;            /* transform_to_frame(gaussians_grad=...) */
+    int camera_grad;               /* transform_to_frame(camera_grad=...) */
+    float* grad_params;            /* [P,14] flat: means 3 | rgb 3 | rotation 4 | logit opacity 1 | log scales 3 */
+    float* grad_means2D;           /* [P,3] or NULL (NDC-unit screen gradient used by densification) */
+    float* grad_cam;               /* [8]: d/d cam_unnorm_rot (4) | d/d cam_trans (3) | 0 */
+    float* pose_scratch;           /* [16] device floats, zero on first use; left zero on return */
+} AsFrameBackwardArgs;
+
+int as_frame_forward(const AsFrameArgs* args, void* cuda_stream);
+int as_frame_backward(const AsFrameBackwardArgs* args, void* cuda_stream);
+
+/* Tracking loss of get_loss (splatam.py:213-247, use_l1): masked L1 sums and their gradient w.r.t. the
+ * six rendered channels, in one sweep.  losses[8] = {weighted total, weighted im, weighted depth, mask count,
+ * num_rendered, overflow flag, -, -}; the last two are copied from frame_status (AsFrameArgs.status) when it
+ * is not NULL, so one read-back of `losses` tells the host everything about the frame.
+ * scratch: as_loss_scratch_floats(w,h) floats.  mask_color: 1 = colour loss uses the depth mask (splatam.py:243-245). */
+size_t as_loss_scratch_floats(int width, int height);
+int as_tracking_loss(int width, int height, const float* color6, const float* gt_rgb, const float* gt_depth,
+                     float w_im, float w_depth, float sil_thres, int use_sil_for_loss, int mask_color,
+                     float* dL_dcolor6, float* losses, float* scratch, const uint32_t* frame_status,
+                     void* cuda_stream);
+
+/* torch.optim.Adam step (splatam.py:118-124: betas (0.9,0.999), eps 1e-15, no weight decay) over the five
+ * parameter tensors at once; grad/exp_avg/exp_avg_sq are the flat [P,14] layout of AsFrameBackwardArgs.
+ * lrs[5]: means3D, rgb_colors, unnorm_rotations, logit_opacities, log_scales.  step counts from 1. */
+int as_adam_step(int P, int isotropic, float* means3D, float* rgb_colors, float* unnorm_rotations,
+                 float* logit_opacities, float* log_scales, const float* grad_params, float* exp_avg,
+                 float* exp_avg_sq, const float* lrs, float beta1, float beta2, float eps, int step,
+                 void* cuda_stream);
+
 /* ---- stage-level entry points (used by the fused paths and by parity tests) ----------------- */
 
 /* Stable ascending LSD radix sort (hand-written onesweep) of n (u64 key, u32 value) pairs on key bits
