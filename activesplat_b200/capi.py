@@ -87,6 +87,7 @@ class AsFrameBackwardArgs(ctypes.Structure):
         ("gaussians_grad", ctypes.c_int), ("camera_grad", ctypes.c_int),
         ("grad_params", ctypes.c_void_p), ("grad_means2D", ctypes.c_void_p), ("grad_cam", ctypes.c_void_p),
         ("pose_scratch", ctypes.c_void_p),
+        ("accumulate", ctypes.c_int),
     ]
 
 

@@ -262,7 +262,7 @@ frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const
                                  float tanfovy, float scale_modifier, const int* __restrict__ radii,
                                  const float* __restrict__ zsil, float* __restrict__ gacc,
                                  const float* __restrict__ gscale, int gaussians_grad, int camera_grad,
-                                 float* __restrict__ grad_params, float* __restrict__ grad_means2D,
+                                 int accumulate, float* __restrict__ grad_params, float* __restrict__ grad_means2D,
                                  float* __restrict__ pose_acc) {
     __shared__ float view[16], proj[16];
     __shared__ Pose ps;
@@ -365,7 +365,11 @@ frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const
         if (gaussians_grad && grad_params) {
             float* o = grad_params + 14 * (size_t)idx;  // 56-byte rows: 8-byte aligned
 #pragma unroll
-            for (int k = 0; k < 14; k += 2) *reinterpret_cast<float2*>(o + k) = make_float2(out[k] * gs, out[k + 1] * gs);
+            for (int k = 0; k < 14; k += 2) {
+                float2 prev = make_float2(0.f, 0.f);
+                if (accumulate) prev = *reinterpret_cast<const float2*>(o + k);  // keyframe-batch accumulation
+                *reinterpret_cast<float2*>(o + k) = make_float2(prev.x + out[k] * gs, prev.y + out[k + 1] * gs);
+            }
         }
         if (grad_means2D) {
             grad_means2D[3 * (size_t)idx] = gm2x * gs;
@@ -582,8 +586,8 @@ void launch_frame_ranges_gather(const uint32_t* n_dev, uint32_t capacity, int ti
 }
 
 void launch_frame_preprocess_backward(const AsFrameArgs& a, const GeometryState& g, const float* gscale,
-                                      int gaussians_grad, int camera_grad, float* grad_params, float* grad_means2D,
-                                      float* pose_acc, float* grad_cam, cudaStream_t st) {
+                                      int gaussians_grad, int camera_grad, int accumulate, float* grad_params,
+                                      float* grad_means2D, float* pose_acc, float* grad_cam, cudaStream_t st) {
     const int P = a.P, W = a.width, H = a.height;
     const float h_y = H / (2.0f * a.tan_fovy), h_x = W / (2.0f * a.tan_fovx);
     const int blocks = (P + FP_THREADS - 1) / FP_THREADS;
@@ -591,14 +595,14 @@ void launch_frame_preprocess_backward(const AsFrameArgs& a, const GeometryState&
         frame_preprocess_backward_kernel<true><<<blocks, FP_THREADS, 0, st>>>(
             P, a.means3D, a.unnorm_rotations, a.logit_opacities, a.log_scales, a.cam_unnorm_rot, a.cam_rot_stride,
             a.cam_trans, a.cam_trans_stride, a.sil_w2c, a.viewmatrix, a.projmatrix, h_x, h_y, a.tan_fovx, a.tan_fovy,
-            a.scale_modifier, g.radii, g.zsil, g.gacc, gscale, gaussians_grad, camera_grad, grad_params, grad_means2D,
-            pose_acc);
+            a.scale_modifier, g.radii, g.zsil, g.gacc, gscale, gaussians_grad, camera_grad, accumulate, grad_params,
+            grad_means2D, pose_acc);
     else
         frame_preprocess_backward_kernel<false><<<blocks, FP_THREADS, 0, st>>>(
             P, a.means3D, a.unnorm_rotations, a.logit_opacities, a.log_scales, a.cam_unnorm_rot, a.cam_rot_stride,
             a.cam_trans, a.cam_trans_stride, a.sil_w2c, a.viewmatrix, a.projmatrix, h_x, h_y, a.tan_fovx, a.tan_fovy,
-            a.scale_modifier, g.radii, g.zsil, g.gacc, gscale, gaussians_grad, camera_grad, grad_params, grad_means2D,
-            pose_acc);
+            a.scale_modifier, g.radii, g.zsil, g.gacc, gscale, gaussians_grad, camera_grad, accumulate, grad_params,
+            grad_means2D, pose_acc);
     if (camera_grad) pose_finalize_kernel<<<1, 32, 0, st>>>(a.cam_unnorm_rot, a.cam_rot_stride, pose_acc, grad_cam);
 }
 

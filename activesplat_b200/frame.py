@@ -135,7 +135,7 @@ class FrameWorkspace:
                                           torch.cuda.current_stream(self.device).cuda_stream))
         return self.losses
 
-    def backward(self, dL_dpix=None, grad_scale=None, gaussians_grad=True, camera_grad=False):
+    def backward(self, dL_dpix=None, grad_scale=None, gaussians_grad=True, camera_grad=False, accumulate=False):
         """as_frame_backward for the last forward.  Returns (grad_params [P,14], grad_cam [8])."""
         L = capi.lib()
         b = capi.AsFrameBackwardArgs()
@@ -148,6 +148,8 @@ class FrameWorkspace:
         b.grad_means2D = self.grad_means2D.data_ptr() if self.grad_means2D is not None else None
         b.grad_cam = self.grad_cam.data_ptr()
         b.pose_scratch = self.pose_scratch.data_ptr()
+        b.accumulate = int(bool(accumulate))
+        self._keep.append(dL)
         with torch.cuda.device(self.device):
             capi.check(L.as_frame_backward(ctypes.byref(b), torch.cuda.current_stream(self.device).cuda_stream))
         return self.grad_params, self.grad_cam
@@ -205,6 +207,66 @@ class _FusedTrackingLoss(torch.autograd.Function):
             g_tr[0, :, ctx.time_idx] = gc[4:7]
             outs[5], outs[6] = g_rot, g_tr
         return tuple(outs)
+
+
+class _FusedFrameRender(torch.autograd.Function):
+    """The frame render as one differentiable node: raw parameters + pose -> colour6 [6,H,W]
+    (rgb | depth, silhouette, depth^2).  Replaces transform_to_frame + the rendervar builders + the two
+    Renderer calls of get_loss (splatam.py:191-212); median depth / opacity / radii are side outputs."""
+
+    @staticmethod
+    def forward(ctx, means3D, rgb, rots, logit_op, log_scales, cam_rots, cam_trans, ws, cam, time_idx, sil_w2c, bg_rgb):
+        params = {"means3D": means3D, "rgb_colors": rgb, "unnorm_rotations": rots, "logit_opacities": logit_op,
+                  "log_scales": log_scales, "cam_unnorm_rots": cam_rots, "cam_trans": cam_trans}
+        ws.forward(params, cam, time_idx, sil_w2c=sil_w2c, bg_rgb=bg_rgb)
+        ctx.ws, ctx.time_idx = ws, int(time_idx)
+        ctx.shapes = (cam_rots.shape, cam_trans.shape, log_scales.shape[1])
+        ctx.need = tuple(ctx.needs_input_grad[:7])
+        out = (ws.color6.clone(), ws.radii, ws.depth, ws.opacity)
+        ctx.mark_non_differentiable(*out[1:])
+        return out
+
+    @staticmethod
+    def backward(ctx, g_color6, _r, _d, _o):
+        ws = ctx.ws
+        gaussians_grad, camera_grad = any(ctx.need[:5]), any(ctx.need[5:7])
+        gp, gc = ws.backward(dL_dpix=g_color6, gaussians_grad=gaussians_grad, camera_grad=camera_grad)
+        outs = [None] * 12
+        if gaussians_grad:
+            views = (gp[:, 0:3], gp[:, 3:6], gp[:, 6:10], gp[:, 10:11], gp[:, 11:11 + ctx.shapes[2]])
+            for i in range(5):
+                if ctx.need[i]:
+                    outs[i] = views[i]
+        if camera_grad:
+            g_rot = torch.zeros(ctx.shapes[0], dtype=torch.float32, device=gc.device)
+            g_tr = torch.zeros(ctx.shapes[1], dtype=torch.float32, device=gc.device)
+            g_rot[0, :, ctx.time_idx] = gc[0:4]
+            g_tr[0, :, ctx.time_idx] = gc[4:7]
+            outs[5], outs[6] = g_rot, g_tr
+        return tuple(outs)
+
+
+def fused_render(params, cam, time_idx, sil_w2c=None, bg_rgb=None, ws=None):
+    """(colour6 [6,H,W], radii, median depth, opacity, workspace); colour6 is differentiable w.r.t. `params`."""
+    ws = ws or workspace_for(params, cam)
+    c6, radii, depth, opacity = _FusedFrameRender.apply(
+        params["means3D"], params["rgb_colors"], params["unnorm_rotations"], params["logit_opacities"],
+        params["log_scales"], params["cam_unnorm_rots"], params["cam_trans"], ws, cam, time_idx, sil_w2c, bg_rgb)
+    return c6, radii, depth, opacity, ws
+
+
+_IDENTITY_POSE = {}
+
+
+def identity_pose(device):
+    """cam_unnorm_rots [1,4,1] = (1,0,0,0), cam_trans [1,3,1] = 0: Gaussians stay in the world frame and
+    the real w2c lives in the raster settings (render() / GetOpacity)."""
+    key = torch.device(device)
+    if key not in _IDENTITY_POSE:
+        r = torch.zeros((1, 4, 1), device=device)
+        r[0, 0, 0] = 1.0
+        _IDENTITY_POSE[key] = (r, torch.zeros((1, 3, 1), device=device))
+    return _IDENTITY_POSE[key]
 
 
 def fused_tracking_loss(params, cam, time_idx, sil_w2c, gt_rgb, gt_depth, w_im, w_depth, sil_thres,

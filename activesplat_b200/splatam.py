@@ -157,7 +157,7 @@ def render(w2c, k, timestep_data, timestep_depth_data, cfg, scale_modifier=1.0):
     """splatam.py:413-434: white-background RGB + median depth + opacity, and the silhouette."""
     with torch.no_grad():
         dev = timestep_data['means3D'].device
-        cam = setup_camera(cfg['viz_w'], cfg['viz_h'], k, w2c, cfg['viz_near'], cfg['viz_far'],
+        cam = setup_camera(cfg['viz_w'], cfg['viz_h'], k, w2c, cfg.get('viz_near', 0.01), cfg.get('viz_far', 100),
                            scale_modifier=scale_modifier, device=dev)
         im, _, depth, opacity, depth_sil = render_bundle(cam, timestep_data, timestep_depth_data['colors_precomp'],
                                                          bg_rgb=[1.0, 1.0, 1.0])
@@ -195,17 +195,26 @@ def get_loss(params, curr_data, variables, iter_time_idx, loss_weights, use_sil_
         return _get_loss_tracking_fused(params, curr_data, variables, iter_time_idx, loss_weights, use_sil_for_loss,
                                         sil_thres)
     losses = {}
-    if tracking:
-        tg = transform_to_frame(params, iter_time_idx, gaussians_grad=False, camera_grad=True)
-    elif mapping and do_ba:
-        tg = transform_to_frame(params, iter_time_idx, gaussians_grad=True, camera_grad=True)
+    gaussians_grad = not tracking
+    camera_grad = tracking or (mapping and do_ba)
+    if params['means3D'].is_cuda:
+        # fused frame node: transform + activations + features + 6-channel render, backward to raw params
+        from .frame import fused_render
+        p = dict(params)
+        if not gaussians_grad:
+            p['means3D'], p['unnorm_rotations'] = p['means3D'].detach(), p['unnorm_rotations'].detach()
+        if not camera_grad:
+            p['cam_unnorm_rots'], p['cam_trans'] = p['cam_unnorm_rots'].detach(), p['cam_trans'].detach()
+        c6, radius, _, _, _ = fused_render(p, curr_data['cam'], int(iter_time_idx), curr_data['w2c'])
+        im, depth_sil = c6[:3], c6[3:]
+        variables['means2D'] = None
     else:
-        tg = transform_to_frame(params, iter_time_idx, gaussians_grad=True, camera_grad=False)
-    rendervar = transformed_params2rendervar(params, tg)
-    depth_sil_colors = get_depth_and_silhouette(tg['means3D'], curr_data['w2c'])
-    rendervar['means2D'].retain_grad()
-    im, radius, _, _, depth_sil = render_bundle(curr_data['cam'], rendervar, depth_sil_colors)
-    variables['means2D'] = rendervar['means2D']
+        tg = transform_to_frame(params, iter_time_idx, gaussians_grad=gaussians_grad, camera_grad=camera_grad)
+        rendervar = transformed_params2rendervar(params, tg)
+        depth_sil_colors = get_depth_and_silhouette(tg['means3D'], curr_data['w2c'])
+        rendervar['means2D'].retain_grad()
+        im, radius, _, _, depth_sil = render_bundle(curr_data['cam'], rendervar, depth_sil_colors)
+        variables['means2D'] = rendervar['means2D']
     depth = depth_sil[0, :, :].unsqueeze(0)
     silhouette = depth_sil[1, :, :]
     presence_sil_mask = (silhouette > sil_thres)
@@ -236,7 +245,9 @@ def get_loss(params, curr_data, variables, iter_time_idx, loss_weights, use_sil_
     weighted_losses = {k: v * loss_weights[k] for k, v in losses.items()}
     loss = sum(weighted_losses.values())
     seen = radius > 0
-    variables['max_2D_radius'][seen] = torch.max(radius[seen], variables['max_2D_radius'][seen])
+    # == max_2D_radius[seen] = max(radius[seen], max_2D_radius[seen]) (splatam.py:296-298) without the
+    # boolean-index host sync: radius is 0 exactly where the Gaussian was not seen
+    variables['max_2D_radius'] = torch.maximum(variables['max_2D_radius'], radius.to(variables['max_2D_radius'].dtype))
     variables['seen'] = seen
     weighted_losses['loss'] = loss
     return loss, variables, weighted_losses
@@ -268,3 +279,28 @@ def initialize_optimizer(params, lrs_dict, tracking):
     if tracking:
         return torch.optim.Adam(param_groups)
     return torch.optim.Adam(param_groups, lr=0.0, eps=1e-15)
+
+
+def render_view(params, w2c, k, width, height, near=0.01, far=100, scale_modifier=1.0, ws=None):
+    """get_rendervars + render (splatam.py:436-468, 413-434) for one candidate view, straight from the raw
+    parameters: white-background RGB, median depth, opacity and silhouette, one fused forward, no gradients.
+    This is the per-view body of the GetOpacity sweeps (src/mapper/splatam/__init__.py:716-737)."""
+    from .frame import fused_render, identity_pose
+    with torch.no_grad():
+        dev = params['means3D'].device
+        cam = setup_camera(width, height, k, w2c, near, far, scale_modifier=scale_modifier, device=dev)
+        rot, tr = identity_pose(dev)
+        p = dict(params, cam_unnorm_rots=rot, cam_trans=tr)
+        sil_w2c = torch.as_tensor(np.asarray(w2c)).to(dev).float().contiguous()
+        c6, _, depth, opacity, ws = fused_render(p, cam, 0, sil_w2c, bg_rgb=_white_bg(dev), ws=ws)
+        return c6[:3], depth, opacity, c6[4:5]
+
+
+_WHITE = {}
+
+
+def _white_bg(dev):
+    key = torch.device(dev)
+    if key not in _WHITE:
+        _WHITE[key] = torch.ones(3, device=dev)
+    return _WHITE[key]

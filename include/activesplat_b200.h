@@ -183,6 +183,7 @@ typedef struct AsFrameBackwardArgs {
     float* grad_means2D;           /* [P,3] or NULL (NDC-unit screen gradient used by densification) */
     float* grad_cam;               /* [8]: d/d cam_unnorm_rot (4) | d/d cam_trans (3) | 0 */
     float* pose_scratch;           /* [16] device floats, zero on first use; left zero on return */
+    int accumulate;                /* non-zero: grad_params += (keyframe-batch accumulation) instead of = */
 } AsFrameBackwardArgs;
 
 int as_frame_forward(const AsFrameArgs* args, void* cuda_stream);

@@ -1,0 +1,97 @@
+"""CPU, world_size 2, gloo: the host-side sharding logic of activesplat_b200/dist.py
+(view scoring gather and keyframe-batch gradient all-reduce) against the single-process result."""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import helpers  # noqa: F401
+
+
+def _views_worker(rank, world, port, n_views, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from activesplat_b200 import dist as asd
+    calls = []
+
+    def render_fn(v):  # a deterministic stand-in for the per-view opacity image
+        calls.append(v)
+        g = torch.Generator().manual_seed(1000 + v)
+        return torch.rand(1, 15, 12, generator=g)
+
+    full = asd.score_views(render_fn, n_views)
+    q.put((rank, calls, full.clone()))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def _mapping_worker(rank, world, port, n_kf, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from activesplat_b200 import dist as asd
+    P = 50
+    flat = torch.full((P, 14), float("nan"))
+    params = torch.zeros(P, 14)
+
+    def frame_grad_fn(k, accumulate):
+        g = torch.Generator().manual_seed(77 + k)
+        gk = torch.randn(P, 14, generator=g)
+        if accumulate:
+            flat.add_(gk)
+        else:
+            flat.copy_(gk)
+        return gk.abs().sum()
+
+    def opt_step(f):
+        params.sub_(0.1 * f)
+
+    asd.mapping_step_keyframe_batch(frame_grad_fn, n_kf, flat, opt_step)
+    q.put((rank, params.clone()))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def _spawn(fn, world, *args):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=fn, args=(r, world, port) + args + (q,)) for r in range(world)]
+    for p in procs:
+        p.start()
+    out = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    return sorted(out, key=lambda t: t[0])
+
+
+def test_view_scoring_shards_and_gathers():
+    for n_views in (7, 2, 1):
+        res = _spawn(_views_worker, 2, n_views)
+        # each view rendered exactly once, round-robin
+        assert res[0][1] == list(range(0, n_views, 2)) and res[1][1] == list(range(1, n_views, 2))
+        expect = []
+        for v in range(n_views):
+            op = torch.rand(1, 15, 12, generator=torch.Generator().manual_seed(1000 + v))
+            expect.append(torch.stack([(1 - op).sum(), op.mean()]))
+        expect = torch.stack(expect)
+        for r in range(2):
+            torch.testing.assert_close(res[r][2], expect)
+
+
+def test_keyframe_batch_mapping_allreduce_matches_sequential():
+    for n_kf in (5, 1):
+        res = _spawn(_mapping_worker, 2, n_kf)
+        total = sum(torch.randn(50, 14, generator=torch.Generator().manual_seed(77 + k)) for k in range(n_kf))
+        for r in range(2):
+            torch.testing.assert_close(res[r][1], -0.1 * total, rtol=1e-6, atol=1e-6)
+
+
+def test_shard_indices_cover_exactly():
+    from activesplat_b200 import dist as asd
+    for n in (0, 1, 5, 256):
+        for world in (1, 2, 4, 8):
+            got = sorted(sum((asd.shard_indices(n, r, world) for r in range(world)), []))
+            assert got == list(range(n))

@@ -357,3 +357,70 @@ def test_fused_adam_matches_torch_adam():
             fa.step(flat.to(dev))
         for k in PARAM_ORDER:
             helpers.compare_float("adam " + k, mine[k].cpu().numpy(), ref[k].detach().numpy(), rel=1e-5)
+
+
+def test_mapping_get_loss_and_adam_steps_match_oracle():
+    """get_loss(mapping=True) (0.8 L1 + 0.2 (1-SSIM) colour loss, masked mean depth loss, splatam.py:239-249)
+    + Adam, three iterations: losses, gradients of all five tensors, and the parameters after the steps,
+    against the CPU oracle (two-pass oracle rasterizer + torch autograd + torch.optim.Adam)."""
+    from activesplat_b200 import splatam
+    from activesplat_b200.frame import FusedAdam, PARAM_ORDER, workspace_for
+    from oracle import splatam_oracle as so
+    params, cams, gt_rgb, gt_depth = _frame_case(P=2000, W=96, H=80, seed=21)
+    W, H, t_idx = cams[0].width, cams[0].height, 1
+    lw = dict(im=0.5, depth=1.0)
+    lrs = dict(means3D=1e-4, rgb_colors=2.5e-3, unnorm_rotations=1e-3, logit_opacities=5e-2, log_scales=1e-3,
+               cam_unnorm_rots=0.0, cam_trans=0.0)
+    pc = {k: v.clone().requires_grad_(True) for k, v in params.items()}
+    opt_c = torch.optim.Adam([{"params": [v], "name": k, "lr": lrs[k]} for k, v in pc.items()], lr=0.0, eps=1e-15)
+    cam_c = splatam.setup_camera(W, H, cams[0].k(), np.eye(4), device="cpu")
+    cur_c = {"cam": cam_c, "im": gt_rgb, "depth": gt_depth, "w2c": torch.eye(4)}
+    dev = "cuda:0"
+    pg = {k: v.clone().to(dev).requires_grad_(True) for k, v in params.items()}
+    opt_g = FusedAdam(pg, lrs)
+    cam_g = splatam.setup_camera(W, H, cams[0].k(), np.eye(4), device=dev)
+    cur_g = {"cam": cam_g, "im": gt_rgb.to(dev), "depth": gt_depth.to(dev), "w2c": torch.eye(4, device=dev)}
+    variables = {"max_2D_radius": torch.zeros(pg["means3D"].shape[0], device=dev)}
+    for it in range(3):
+        loss_c, wl_c, _ = so.get_loss(pc, cur_c, t_idx, lw, False, 0.98, True, False, mapping=True)
+        opt_c.zero_grad(set_to_none=True)
+        loss_c.backward()
+        loss_g, variables, wl_g = splatam.get_loss(pg, cur_g, variables, t_idx, lw, False, 0.98, True, False, mapping=True)
+        for p in pg.values():
+            p.grad = None
+        loss_g.backward()
+        for k in ("loss", "im", "depth"):
+            helpers.compare_float(f"it{it} loss {k}", wl_g[k].detach().cpu().numpy(), wl_c[k].detach().numpy(), rel=2e-4)
+        if it == 0:
+            for k in PARAM_ORDER:
+                helpers.compare_float("grad " + k, pg[k].grad.cpu().numpy(), pc[k].grad.numpy(), rel=5e-4)
+            assert pg["cam_trans"].grad is None and pc["cam_trans"].grad is None  # camera_grad=False in mapping
+        opt_c.step()
+        opt_g.step(workspace_for(pg, cam_g).grad_params)
+    for k in PARAM_ORDER:
+        d_ref = (pc[k].detach() - params[k]).numpy()
+        d_got = (pg[k].detach().cpu() - params[k]).numpy()
+        # Adam's first steps are sign-like (|update| ~ lr): compare the parameter DRIFT, elementwise
+        helpers.compare_float("drift " + k, d_got, d_ref, rel=2e-3, flip_fraction=5e-3, flip_bound=2.5)
+
+
+def test_render_view_matches_oracle_render():
+    """render_view (GetOpacity per-view body) vs the oracle's get_rendervars + render (two passes, white bg)."""
+    from activesplat_b200 import scenes, splatam
+    from oracle import raster_oracle as ro
+    params, _ = scenes.s_room(4000, 3, 2, scale_mult=12.0)
+    cam = scenes.candidate_views(3, seed=2)[2]
+    dev = "cuda:0"
+    pg = {k: v.to(dev) for k, v in params.items()}
+    im, depth, opacity, sil = splatam.render_view(pg, cam.w2c, cam.k(), cam.width, cam.height)
+    a = scenes.activated(params)
+    view, proj, campos = cam.matrices()
+    feats = helpers.depth_sil_features(a["means3D"], cam.w2c).numpy()
+    common = (a["opacities"].numpy(), a["scales"].numpy(), a["rotations"].numpy(), 1.0, None, view, proj, cam.tanfovx,
+              cam.tanfovy, cam.height, cam.width)
+    st1 = ro.forward(a["means3D"].numpy(), a["colors_precomp"].numpy(), *common, np.ones(3, np.float32))
+    st2 = ro.forward(a["means3D"].numpy(), feats, *common, np.zeros(3, np.float32))
+    helpers.compare_float("im", im.cpu().numpy(), st1["color"])
+    helpers.compare_float("median depth", depth.cpu().numpy(), st1["depth"])
+    helpers.compare_float("opacity", opacity.cpu().numpy(), st1["opacity"])
+    helpers.compare_float("silhouette", sil.cpu().numpy(), st2["color"][1:2])
