@@ -338,6 +338,7 @@ def run_ref_cuda(args, dev, params, cams, cam, first_w2c, gt_dev, K):
 def cpu_step_factory(args, gaussians=None, width=None, height=None):
     from activesplat_b200 import scenes
     from oracle import raster_oracle as ro
+    ro.set_num_threads(os.cpu_count() or 1)  # torchrun exports OMP_NUM_THREADS=1; use every host core
     P = gaussians or args.gaussians
     W, H = width or args.width, height or args.height
     params, cams = scenes.s_room(P, args.keyframes, seed=1, W=W, H=H)

@@ -531,6 +531,15 @@ void orc_preprocess_backward(int P, const float* means3D, const int* radii, cons
     }
 }
 
+void orc_set_num_threads(int n) {
+#ifdef _OPENMP
+    extern void omp_set_num_threads(int);
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 int orc_num_threads(void) {
 #ifdef _OPENMP
     extern int omp_get_max_threads(void);

@@ -47,6 +47,11 @@ def num_threads():
     return int(lib().orc_num_threads())
 
 
+def set_num_threads(n):
+    """Use n OpenMP threads (launchers such as torchrun export OMP_NUM_THREADS=1)."""
+    lib().orc_set_num_threads(ctypes.c_int(int(n)))
+
+
 def higher_msb(n):
     return int(lib().orc_higher_msb(ctypes.c_uint32(n)))
 
