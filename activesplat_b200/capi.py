@@ -111,6 +111,7 @@ SYMBOLS = {
     "as_frame_forward": (_I, [ctypes.POINTER(AsFrameArgs), _V]),
     "as_frame_backward": (_I, [ctypes.POINTER(AsFrameBackwardArgs), _V]),
     "as_loss_scratch_floats": (_Z, [_I, _I]),
+    "as_pose_scratch_floats": (_Z, [_I]),
     "as_tracking_loss": (_I, [_I, _I, _V, _V, _V, _F, _F, _F, _I, _I, _V, _V, _V, _V, _V]),
     "as_adam_step": (_I, [_I, _I, _V, _V, _V, _V, _V, _V, _V, _V, ctypes.POINTER(ctypes.c_float), _F, _F, _F, _I, _V]),
     "as_sort_temp_bytes": (_Z, [_I]),

@@ -16,6 +16,8 @@
 //   * backward skips the tail of the list that no pixel of the warp/tile reached in the forward.
 // Per-pixel arithmetic, skip rules and termination are the reference's (SURVEY 8a' T10-T18) and are
 // spelled with rounding-explicit intrinsics so alpha decisions match the reference build bit for bit.
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace asb {
@@ -53,6 +55,46 @@ __device__ __forceinline__ void issue_batch(BlendSmem<C>& sm, int stage, const f
     bulk_g2s(sm.feat[stage], inst_feat + (size_t)start * FV, bytes * FV, &sm.bar[stage]);
 }
 
+// ---- per-warp culling ---------------------------------------------------------------------------
+// A pair (pixel, Gaussian) can only pass the skip rules (power <= 0, alpha >= 1/255; forward.cu:343-353)
+// inside the ellipse  A dx^2 + 2B dx dy + C dy^2 <= 2 ln(255 * opacity).  ranges_gather stores the
+// ellipse's axis-aligned half-extents (rounded UP, with margin) per instance; a warp whose 16x2-pixel
+// strip lies outside that box skips the instance without evaluating anything.  Skipped pairs would have
+// been skipped by the rules anyway, so images, n_contrib and gradients are unchanged.
+template <int C>
+__device__ __forceinline__ float2 inst_extent(const BlendSmem<C>& sm, int s, int j) {
+    constexpr int FV = BlendSmem<C>::FV;
+    const float4 f = sm.feat[s][j * FV + FV - 1];
+    const uint32_t bits = __float_as_uint(C == 3 ? f.w : f.z);
+    const __half2 h = *reinterpret_cast<const __half2*>(&bits);
+    return __half22float2(h);
+}
+
+// Compacts the indices of the batch's records that can touch this warp's pixel strip into the warp's
+// private list (ascending record order) and returns how many there are.
+template <int C>
+__device__ __forceinline__ int cull_batch(const BlendSmem<C>& sm, int s, int limit, int lane, float strip_x0,
+                                          float strip_yc, uint8_t* list) {
+    int n = 0;
+    const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int k = 0; k < BL_BATCH / 32; k++) {
+        const int j = lane + 32 * k;
+        bool ok = false;
+        if (j < limit) {
+            const float4 ge = sm.geom[s][j];
+            const float2 e = inst_extent<C>(sm, s, j);
+            ok = (fabsf(ge.y - strip_yc) <= e.y + 0.5f) && (ge.x + e.x >= strip_x0) &&
+                 (ge.x - e.x <= strip_x0 + (float)(TILE_X - 1));
+        }
+        const uint32_t bal = __ballot_sync(0xffffffffu, ok);
+        if (ok) list[n + __popc(bal & lt)] = (uint8_t)j;
+        n += __popc(bal);
+    }
+    __syncwarp();
+    return n;
+}
+
 template <int C>
 __global__ void __launch_bounds__(BL_THREADS)
 blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict__ inst_conic,
@@ -62,12 +104,17 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
                      uint32_t* __restrict__ n_contrib) {
     constexpr int FV = BlendSmem<C>::FV;
     __shared__ __align__(128) BlendSmem<C> sm;
+    __shared__ uint8_t s_list[BL_THREADS / 32][BL_BATCH];
     const int tile = blockIdx.x;
     const int tx = tile % gx, ty = tile / gx;
     const int px = tx * TILE_X + (threadIdx.x & (TILE_X - 1));
     const int py = ty * TILE_Y + (threadIdx.x / TILE_X);
     const bool inside = px < W && py < H;
     const float pxf = (float)px, pyf = (float)py;
+    const int lane = threadIdx.x & 31;
+    // this warp's pixels: columns [tile x0, +15], rows 2w and 2w+1
+    const float strip_x0 = (float)(tx * TILE_X);
+    const float strip_yc = (float)(ty * TILE_Y + 2 * (threadIdx.x >> 5)) + 0.5f;
     const uint2 range = ranges[tile];
     const int len = (int)(range.y - range.x);
     const int nb = (len + BL_BATCH - 1) / BL_BATCH;
@@ -97,17 +144,25 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
         mbar_wait(&sm.bar[s], (uint32_t)((b >> 1) & 1));
         const int cnt = min(BL_BATCH, len - b * BL_BATCH);
         // The per-pixel loop of forward.cu:332-381, restructured so that the warp stays converged:
-        // (1) alpha of FW_UNROLL consecutive instances is evaluated branch-free for all lanes
-        //     (independent chains: the exp latency of one instance hides behind the others),
-        // (2) the order-dependent part (T, colour, median depth, termination) is then applied in list
-        //     order, only for the instances that passed the skip rules.  Same arithmetic per pixel.
-        if (!__all_sync(0xffffffffu, done)) {
-            for (int j0 = 0; j0 < cnt; j0 += FW_UNROLL) {
+        // (0) the warp drops the records whose ellipse cannot reach its strip,
+        // (1) alpha of up to FW_UNROLL surviving records is evaluated branch-free for all lanes
+        //     (independent chains: the exp latency of one record hides behind the others),
+        // (2) the order-dependent part (T, colour, median depth, termination) is applied in list order,
+        //     only for the records that passed the skip rules.  Same arithmetic per pixel.
+        bool warp_done = __all_sync(0xffffffffu, done);
+        if (!warp_done) {
+            uint8_t* list = s_list[threadIdx.x >> 5];
+            const int n = cull_batch<C>(sm, s, cnt, lane, strip_x0, strip_yc, list);
+#pragma unroll 1
+            for (int t = 0; t < n && !warp_done; t += FW_UNROLL) {
+                int jj[FW_UNROLL];
+#pragma unroll
+                for (int u = 0; u < FW_UNROLL; u++) jj[u] = (t + u < n) ? (int)list[t + u] : -1;
                 float al[FW_UNROLL];
                 uint32_t hit = 0;
 #pragma unroll
                 for (int u = 0; u < FW_UNROLL; u++) {
-                    const int j = j0 + u;  // < BL_BATCH; entries >= cnt are stale and masked below
+                    const int j = max(jj[u], 0);
                     const float4 co = sm.conic[s][j];
                     const float4 ge = sm.geom[s][j];
                     const float dx = __fsub_rn(ge.x, pxf), dy = __fsub_rn(ge.y, pyf);
@@ -115,14 +170,14 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
                     const float alpha = fminf(0.99f, __fmul_rn(co.w, expf(power)));
                     al[u] = alpha;
                     // skip rules of forward.cu:343-353 (written so that NaN behaves as in the reference)
-                    if (j < cnt && !(power > 0.0f) && !(alpha < 1.0f / 255.0f)) hit |= 1u << u;
+                    if (jj[u] >= 0 && !(power > 0.0f) && !(alpha < 1.0f / 255.0f)) hit |= 1u << u;
                 }
                 if (done) hit = 0;
                 if (__any_sync(0xffffffffu, hit != 0)) {
 #pragma unroll
                     for (int u = 0; u < FW_UNROLL; u++) {
                         if (hit & (1u << u)) {
-                            const int j = j0 + u;
+                            const int j = jj[u];
                             const float alpha = al[u];
                             const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
                             if (test_T < 0.0001f) {
@@ -145,9 +200,10 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
                             }
                         }
                     }
-                    if (__all_sync(0xffffffffu, done)) break;
+                    warp_done = __all_sync(0xffffffffu, done);
                 }
             }
+            __syncwarp();  // the list is rewritten by the next batch
         }
         consumed = b + 1;
         // all 256 pixels finished => stop (forward.cu:315-317); the barrier also frees stage s for reuse
@@ -209,6 +265,8 @@ __device__ __forceinline__ void warp_transpose_reduce16(float (&v)[16], int lane
     v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
 }
 
+constexpr int BW_UNROLL = 4;  // records whose alpha is evaluated together in the backward
+
 template <int C>
 __global__ void __launch_bounds__(BL_THREADS)
 blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict__ inst_conic,
@@ -220,6 +278,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
     constexpr int NV = 6 + C;  // live gradient terms per (pixel, Gaussian)
     __shared__ __align__(128) BlendSmem<C> sm;
     __shared__ __align__(16) float s_acc[BL_BATCH * 16];
+    __shared__ uint8_t s_list[BL_THREADS / 32][BL_BATCH];
     __shared__ int s_max_contrib;
 
     const int tile = blockIdx.x;
@@ -230,6 +289,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
     const float pxf = (float)px, pyf = (float)py;
     const size_t pix_id = (size_t)W * py + px;
     const int lane = threadIdx.x & 31;
+    const float strip_x0 = (float)(tx * TILE_X);
+    const float strip_yc = (float)(ty * TILE_Y + 2 * (threadIdx.x >> 5)) + 0.5f;
     const uint2 range = ranges[tile];
 
     const float T_final = inside ? final_Ts[pix_id] : 0.f;
@@ -286,56 +347,81 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
         mbar_wait(&sm.bar[s], (uint32_t)((b >> 1) & 1));
         __syncthreads();
 
-        // records at list index >= warp_max are skipped by the whole warp
-        const int jstart = min(cnt, warp_max - lo) - 1;
-        for (int j = jstart; j >= 0; j--) {
-            const int idx = lo + j;  // the reference's `contributor` after its decrement
-            float v[16];
+        // records at list index >= warp_max are skipped by the whole warp; so are records whose ellipse
+        // cannot reach this warp's strip (see cull_batch)
+        uint8_t* list = s_list[threadIdx.x >> 5];
+        const int n = cull_batch<C>(sm, s, min(cnt, warp_max - lo), lane, strip_x0, strip_yc, list);
+#pragma unroll 1
+        for (int t = n; t > 0; t -= BW_UNROLL) {
+            {
+                int jj[BW_UNROLL];
 #pragma unroll
-            for (int k = 0; k < 16; k++) v[k] = 0.f;
-            bool active = idx < last_contributor;
-            if (active) {
-                const float4 co = sm.conic[s][j];
-                const float4 ge = sm.geom[s][j];
-                const float dx = __fsub_rn(ge.x, pxf), dy = __fsub_rn(ge.y, pyf);
-                const float power = eval_power(co, dx, dy);
-                const float G = expf(power);
-                const float alpha = fminf(0.99f, __fmul_rn(co.w, G));
-                active = !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-                if (active) {
-                    T = T / (1.f - alpha);
-                    const float dchannel_dcolor = alpha * T;
-                    const float4 f0 = sm.feat[s][j * FV];
-                    const float4 f1 = sm.feat[s][j * FV + FV - 1];
-                    float col[C];
-                    col[0] = f0.x; col[1] = f0.y; col[2] = f0.z;
-                    if (C == 6) { col[3 % C] = f0.w; col[4 % C] = f1.x; col[5 % C] = f1.y; }
-                    float dL_dalpha = 0.f;
+                for (int u = 0; u < BW_UNROLL; u++) jj[u] = (t - 1 - u >= 0) ? (int)list[t - 1 - u] : -1;  // back to front
+                // (1) branch-free alpha for the chunk
+                float al[BW_UNROLL], Gs[BW_UNROLL];
+                uint32_t act = 0;
 #pragma unroll
-                    for (int ch = 0; ch < C; ch++) {
-                        accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
-                        last_color[ch] = col[ch];
-                        dL_dalpha += (col[ch] - accum_rec[ch]) * dL_dpixel[ch];
-                        v[6 + ch] = dchannel_dcolor * dL_dpixel[ch];
+                for (int u = 0; u < BW_UNROLL; u++) {
+                    const int j = max(jj[u], 0);
+                    const float4 co = sm.conic[s][j];
+                    const float4 ge = sm.geom[s][j];
+                    const float dx = __fsub_rn(ge.x, pxf), dy = __fsub_rn(ge.y, pyf);
+                    const float power = eval_power(co, dx, dy);
+                    const float G = expf(power);
+                    const float alpha = fminf(0.99f, __fmul_rn(co.w, G));
+                    al[u] = alpha;
+                    Gs[u] = G;
+                    // the reference's `contributor` after its decrement is lo + j (backward.cu:486-490)
+                    if (jj[u] >= 0 && (lo + j) < last_contributor && !(power > 0.0f) && !(alpha < 1.0f / 255.0f))
+                        act |= 1u << u;
+                }
+                // (2) ordered part + warp reduction, one record at a time
+#pragma unroll
+                for (int u = 0; u < BW_UNROLL; u++) {
+                    const bool active = act & (1u << u);
+                    if (!__any_sync(0xffffffffu, active)) continue;
+                    const int j = jj[u];
+                    float v[16];
+#pragma unroll
+                    for (int q = 0; q < 16; q++) v[q] = 0.f;
+                    if (active) {
+                        const float4 co = sm.conic[s][j];
+                        const float4 ge = sm.geom[s][j];
+                        const float dx = __fsub_rn(ge.x, pxf), dy = __fsub_rn(ge.y, pyf);
+                        const float alpha = al[u], G = Gs[u];
+                        T = T / (1.f - alpha);
+                        const float dchannel_dcolor = alpha * T;
+                        const float4 f0 = sm.feat[s][j * FV];
+                        const float4 f1 = sm.feat[s][j * FV + FV - 1];
+                        float col[C];
+                        col[0] = f0.x; col[1] = f0.y; col[2] = f0.z;
+                        if (C == 6) { col[3 % C] = f0.w; col[4 % C] = f1.x; col[5 % C] = f1.y; }
+                        float dL_dalpha = 0.f;
+#pragma unroll
+                        for (int ch = 0; ch < C; ch++) {
+                            accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
+                            last_color[ch] = col[ch];
+                            dL_dalpha += (col[ch] - accum_rec[ch]) * dL_dpixel[ch];
+                            v[6 + ch] = dchannel_dcolor * dL_dpixel[ch];
+                        }
+                        dL_dalpha *= T;
+                        last_alpha = alpha;
+                        dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;  // backward.cu:531-534
+                        const float dL_dG = co.w * dL_dalpha;                     // straight-through clamp (:538)
+                        const float gdx = G * dx, gdy = G * dy;
+                        const float dG_ddelx = -gdx * co.x - gdy * co.y;
+                        const float dG_ddely = -gdy * co.z - gdx * co.y;
+                        v[0] = -0.5f * gdx * dx * dL_dG;
+                        v[1] = -0.5f * gdx * dy * dL_dG;
+                        v[2] = -0.5f * gdy * dy * dL_dG;
+                        v[3] = G * dL_dalpha;
+                        v[4] = dL_dG * dG_ddelx * ddelx_dx;
+                        v[5] = dL_dG * dG_ddely * ddely_dy;
                     }
-                    dL_dalpha *= T;
-                    last_alpha = alpha;
-                    dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;  // backward.cu:531-534
-                    const float dL_dG = co.w * dL_dalpha;                     // straight-through clamp (:538)
-                    const float gdx = G * dx, gdy = G * dy;
-                    const float dG_ddelx = -gdx * co.x - gdy * co.y;
-                    const float dG_ddely = -gdy * co.z - gdx * co.y;
-                    v[0] = -0.5f * gdx * dx * dL_dG;
-                    v[1] = -0.5f * gdx * dy * dL_dG;
-                    v[2] = -0.5f * gdy * dy * dL_dG;
-                    v[3] = G * dL_dalpha;
-                    v[4] = dL_dG * dG_ddelx * ddelx_dx;
-                    v[5] = dL_dG * dG_ddely * ddely_dy;
+                    warp_transpose_reduce16(v, lane);
+                    if (!(lane & 1) && (lane >> 1) < NV) atomicAdd(&s_acc[j * 16 + (lane >> 1)], v[0]);
                 }
             }
-            if (!__any_sync(0xffffffffu, active)) continue;
-            warp_transpose_reduce16(v, lane);
-            if (!(lane & 1) && (lane >> 1) < NV) atomicAdd(&s_acc[j * 16 + (lane >> 1)], v[0]);
         }
         __syncthreads();
         // flush: two threads per instance; 3 (C=6) or 2.25 (C=3) vector reductions per touched instance

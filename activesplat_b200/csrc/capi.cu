@@ -392,6 +392,8 @@ int as_frame_backward(const AsFrameBackwardArgs* ba, void* cuda_stream) {
     return stage_check(st, a->debug);
 }
 
+size_t as_pose_scratch_floats(int P) { return pose_scratch_floats(P > 0 ? P : 0); }
+
 size_t as_loss_scratch_floats(int width, int height) { return (size_t)loss_partial_blocks(width * height) * 4 + 16; }
 
 int as_tracking_loss(int width, int height, const float* color6, const float* gt_rgb, const float* gt_depth,

@@ -140,6 +140,7 @@ void launch_frame_preprocess_backward(const AsFrameArgs& a, const GeometryState&
                                       int gaussians_grad, int camera_grad, int accumulate, float* grad_params,
                                       float* grad_means2D, float* pose_acc, float* grad_cam, cudaStream_t st);
 int loss_partial_blocks(int N);
+size_t pose_scratch_floats(int P);
 void launch_tracking_loss(int N, const float* c6, const float* gt_rgb, const float* gt_depth, float w_im,
                           float w_depth, float sil_thres, int use_sil, int mask_color, float* dL, float* partials,
                           float* losses, const uint32_t* status, cudaStream_t st);

@@ -222,17 +222,19 @@ frame_ranges_gather_kernel(const uint32_t* __restrict__ n_dev, uint32_t capacity
     if (i == R - 1) ranges[cur].y = R;
     const uint32_t id = point_list[i];
     const float2 m = __ldg(means2D + id);
-    inst_conic[i] = __ldg(conic_opacity + id);
+    const float4 co = __ldg(conic_opacity + id);
+    inst_conic[i] = co;
     inst_geom[i] = make_float4(m.x, m.y, __uint_as_float((uint32_t)key), __uint_as_float(id));
     const float z = __ldg(zsil + id);
     const float* c = rgb + 3 * (size_t)id;
     inst_feat[2 * (size_t)i] = make_float4(__ldg(c), __ldg(c + 1), __ldg(c + 2), z);
-    inst_feat[2 * (size_t)i + 1] = make_float4(1.f, z * z, 0.f, 0.f);
+    inst_feat[2 * (size_t)i + 1] = make_float4(1.f, z * z, pack_cull_extent(co), 0.f);
 }
 
-// Block-wide sum of NV per-thread values -> atomicAdd into out[NV] (one atomic per value per block).
+// Block-wide sum of NV per-thread values -> out[NV] (plain stores: one row of partials per block; a
+// few thousand blocks adding into the same 16 words with atomics serialise in L2).
 template <int NV>
-__device__ __forceinline__ void block_reduce_add(float (&v)[NV], float* s_red /*[NV * 8]*/, float* out) {
+__device__ __forceinline__ void block_reduce_store(float (&v)[NV], float* s_red /*[NV * 8]*/, float* out) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
     for (int k = 0; k < NV; k++) {
@@ -246,12 +248,12 @@ __device__ __forceinline__ void block_reduce_add(float (&v)[NV], float* s_red /*
         float x = 0.f;
 #pragma unroll
         for (int w = 0; w < FP_THREADS / 32; w++) x += s_red[threadIdx.x * 8 + w];
-        if (x != 0.f) atomicAdd(out + threadIdx.x, x);
+        out[threadIdx.x] = x;
     }
 }
 
 // Backward of frame_preprocess_kernel.  grad_params rows: means 3 | rgb 3 | rot 4 | logit 1 | log_scales 3.
-// pose_acc (16 floats): dL/dt (3) | dL/dR (9, row-major) | dL/dq_cam through quat_mult (4).
+// pose_acc ([blocks,16] partial sums): dL/dt (3) | dL/dR (9, row-major) | dL/dq_cam through quat_mult (4).
 template <bool ISO>
 __global__ void __launch_bounds__(FP_THREADS)
 frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ unnorm_rot,
@@ -380,13 +382,31 @@ frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const
     if (camera_grad) {
 #pragma unroll
         for (int k = 0; k < 16; k++) pacc[k] *= gs;
-        block_reduce_add<16>(pacc, s_red, pose_acc);
+        block_reduce_store<16>(pacc, s_red, pose_acc + 16 * (size_t)blockIdx.x);
     }
 }
 
-// pose_acc -> gradients of cam_unnorm_rot (4) and cam_trans (3); clears pose_acc for the next frame.
-__global__ void pose_finalize_kernel(const float* __restrict__ cam_rot, int rs, float* pose_acc, float* grad_cam) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+// per-block pose partials [nblocks,16] -> gradients of cam_unnorm_rot (4) and cam_trans (3).
+__global__ void __launch_bounds__(256)
+pose_finalize_kernel(const float* __restrict__ cam_rot, int rs, const float* __restrict__ partials, int nblocks,
+                     float* grad_cam) {
+    __shared__ float s_part[16][17];
+    __shared__ float pose_acc[16];
+    {
+        const int k = threadIdx.x & 15, g = threadIdx.x >> 4;  // 16 groups stride over the blocks
+        float x = 0.f;
+        for (int b = g; b < nblocks; b += 16) x += partials[16 * (size_t)b + k];
+        s_part[g][k] = x;
+    }
+    __syncthreads();
+    if (threadIdx.x < 16) {
+        float x = 0.f;
+#pragma unroll
+        for (int g = 0; g < 16; g++) x += s_part[g][threadIdx.x];
+        pose_acc[threadIdx.x] = x;
+    }
+    __syncthreads();
+    if (threadIdx.x != 0) return;
     float qr[4];
 #pragma unroll
     for (int k = 0; k < 4; k++) qr[k] = cam_rot[(size_t)k * rs];
@@ -418,8 +438,6 @@ __global__ void pose_finalize_kernel(const float* __restrict__ cam_rot, int rs, 
 #pragma unroll
     for (int k = 0; k < 3; k++) grad_cam[4 + k] = pose_acc[k];
     grad_cam[7] = 0.f;
-#pragma unroll
-    for (int k = 0; k < 16; k++) pose_acc[k] = 0.f;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -603,8 +621,11 @@ void launch_frame_preprocess_backward(const AsFrameArgs& a, const GeometryState&
             a.cam_trans, a.cam_trans_stride, a.sil_w2c, a.viewmatrix, a.projmatrix, h_x, h_y, a.tan_fovx, a.tan_fovy,
             a.scale_modifier, g.radii, g.zsil, g.gacc, gscale, gaussians_grad, camera_grad, accumulate, grad_params,
             grad_means2D, pose_acc);
-    if (camera_grad) pose_finalize_kernel<<<1, 32, 0, st>>>(a.cam_unnorm_rot, a.cam_rot_stride, pose_acc, grad_cam);
+    if (camera_grad)
+        pose_finalize_kernel<<<1, 256, 0, st>>>(a.cam_unnorm_rot, a.cam_rot_stride, pose_acc, blocks, grad_cam);
 }
+
+size_t pose_scratch_floats(int P) { return 16 * (size_t)((P + FP_THREADS - 1) / FP_THREADS) + 16; }
 
 int loss_partial_blocks(int N) {
     int b = (N + LOSS_THREADS - 1) / LOSS_THREADS;

@@ -135,15 +135,17 @@ ranges_gather_kernel(int R, const uint64_t* __restrict__ keys, const uint32_t* _
 
     const uint32_t id = point_list[i];
     const float2 m = __ldg(means2D + id);
-    inst_conic[i] = __ldg(conic_opacity + id);
+    const float4 co = __ldg(conic_opacity + id);
+    inst_conic[i] = co;
     // depth is the low word of the key (rasterizer_impl.cu:101-103)
     inst_geom[i] = make_float4(m.x, m.y, __uint_as_float((uint32_t)key), __uint_as_float(id));
+    const float ext = pack_cull_extent(co);  // spare slot of the feature record: culling box for the blend kernels
     const float* f = features + (size_t)id * C;
     if (C == 3) {
-        inst_feat[i] = make_float4(__ldg(f), __ldg(f + 1), __ldg(f + 2), 0.f);
+        inst_feat[i] = make_float4(__ldg(f), __ldg(f + 1), __ldg(f + 2), ext);
     } else {
         inst_feat[2 * (size_t)i] = make_float4(__ldg(f), __ldg(f + 1), __ldg(f + 2), __ldg(f + 3));
-        inst_feat[2 * (size_t)i + 1] = make_float4(__ldg(f + 4), __ldg(f + 5), 0.f, 0.f);
+        inst_feat[2 * (size_t)i + 1] = make_float4(__ldg(f + 4), __ldg(f + 5), ext, 0.f);
     }
 }
 

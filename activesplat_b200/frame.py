@@ -47,7 +47,7 @@ class FrameWorkspace:
             self.grad_params = torch.zeros((self.P, 14), **f32)
             self.grad_means2D = torch.zeros((self.P, 3), **f32) if want_means2D_grad else None
             self.grad_cam = torch.zeros(8, **f32)
-            self.pose_scratch = torch.zeros(16, **f32)
+            self.pose_scratch = torch.empty(L.as_pose_scratch_floats(self.P), **f32)
             self.bg6 = torch.zeros(6, **f32)
         self._args = None
         self._keep = None

@@ -182,10 +182,11 @@ typedef struct AsFrameBackwardArgs {
     float* grad_params;            /* [P,14] flat: means 3 | rgb 3 | rotation 4 | logit opacity 1 | log scales 3 */
     float* grad_means2D;           /* [P,3] or NULL (NDC-unit screen gradient used by densification) */
     float* grad_cam;               /* [8]: d/d cam_unnorm_rot (4) | d/d cam_trans (3) | 0 */
-    float* pose_scratch;           /* [16] device floats, zero on first use; left zero on return */
+    float* pose_scratch;           /* as_pose_scratch_floats(P) device floats (per-block partial sums; no init needed) */
     int accumulate;                /* non-zero: grad_params += (keyframe-batch accumulation) instead of = */
 } AsFrameBackwardArgs;
 
+size_t as_pose_scratch_floats(int P);
 int as_frame_forward(const AsFrameArgs* args, void* cuda_stream);
 int as_frame_backward(const AsFrameBackwardArgs* args, void* cuda_stream);
 
