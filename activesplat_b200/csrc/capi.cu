@@ -25,7 +25,8 @@ GeometryState GeometryState::fromChunk(char*& chunk, size_t P) {
     g.radii = b.take<int>(P);
     g.gacc = b.take<float>(P * GACC_STRIDE);
     g.zsil = b.take<float>(P);
-    g.scan_temp = b.take<uint32_t>((scan_temp_bytes((int)P) + 3) / 4);
+    g.vis_list = b.take<uint32_t>(P);
+    g.scan_temp = b.take<uint32_t>((scan_temp_bytes((int)P) + 3) / 4 + 2 * ((P + 255) / 256) + 8);
     g.num_rendered = b.take<uint32_t>(64);
     chunk = b.p;
     return g;
@@ -329,11 +330,6 @@ int as_frame_forward(const AsFrameArgs* a, void* cuda_stream) {
     {
         StageScope _s(AS_STAGE_PREPROCESS, st, 1);
         launch_frame_preprocess(*a, g, a->status, st);
-    }
-    if ((r = stage_check(st, a->debug))) return r;
-    {
-        StageScope _s(AS_STAGE_SCAN, st, 1);
-        launch_inclusive_scan(g.tiles_touched, g.point_offsets, P, a->status, g.scan_temp, st);  // status[0] = R
     }
     if ((r = stage_check(st, a->debug))) return r;
     if (cap > 0) {

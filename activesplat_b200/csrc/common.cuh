@@ -39,6 +39,7 @@ struct GeometryState {  // per Gaussian
     int* radii;               // [P] internal copy (used when the caller passes radii == NULL)
     float* gacc;              // [P,12] backward accumulators (conic x,y,w | opacity | mean2D x,y | colour[<=6])
     float* zsil;              // [P] depth in the silhouette frame (frame path: feature z of [z,1,z^2])
+    uint32_t* vis_list;       // [P] compact list of visible Gaussian ids (frame path)
     uint32_t* scan_temp;      // look-back state of the scan
     uint32_t* num_rendered;   // [1] device copy of R
     static GeometryState fromChunk(char*& chunk, size_t P);

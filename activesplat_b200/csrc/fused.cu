@@ -117,6 +117,12 @@ __device__ __forceinline__ void load_rows(const float* __restrict__ src, int row
     }
 }
 
+// Look-back state of the scan fused into frame_preprocess_kernel: one u64 per block,
+// flag (2 bits, 62..63) | visible count (24 bits, 32..55) | tiles touched (32 bits, 0..31).
+constexpr uint64_t FPS_AGG = 1ull << 62;
+constexpr uint64_t FPS_PREFIX = 2ull << 62;
+constexpr uint64_t FPS_VALUE_MASK = (1ull << 56) - 1ull;
+
 template <bool ISO>
 __global__ void __launch_bounds__(FP_THREADS)
 frame_preprocess_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ unnorm_rot,
@@ -127,46 +133,113 @@ frame_preprocess_kernel(int P, const float* __restrict__ means3D, const float* _
                         float tanfovy, float focal_x, float focal_y, float scale_modifier, int* __restrict__ radii,
                         int* __restrict__ radii_internal, float2* __restrict__ means2D_out,
                         float* __restrict__ depths, float4* __restrict__ conic_opacity,
-                        uint32_t* __restrict__ tiles_touched, float* __restrict__ zsil, uint32_t* status) {
+                        uint32_t* __restrict__ point_offsets, float* __restrict__ zsil,
+                        uint32_t* __restrict__ vis_list, uint32_t* ticket, uint64_t* scan_status, uint32_t* status) {
     __shared__ __align__(16) float s_means[FP_THREADS * 3];
     __shared__ __align__(16) float s_ls[FP_THREADS * 3];
     __shared__ float s_view[16], s_proj[16];
     __shared__ Pose ps;
-    const int row0 = blockIdx.x * FP_THREADS;
+    __shared__ uint32_t s_block;
+    __shared__ uint32_t s_wt[FP_THREADS / 32], s_wv[FP_THREADS / 32];
+    __shared__ uint32_t s_pref_t, s_pref_v;
+    // blocks take their slab in the order they start, so the look-back below can never wait on a
+    // block that has not been scheduled yet
+    if (threadIdx.x == 0) s_block = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const uint32_t blk = s_block;
+    const int row0 = blk * FP_THREADS;
     const int nrows = min(FP_THREADS, P - row0);
     load_rows(means3D, row0, nrows, 3, s_means);
     load_rows(log_scales, row0, nrows, ISO ? 1 : 3, s_ls);
     if (threadIdx.x < 16) s_view[threadIdx.x] = __ldg(viewmatrix + threadIdx.x);
     else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = __ldg(projmatrix + threadIdx.x - 16);
     else if (threadIdx.x == 32) load_pose(ps, cam_rot, rs, cam_trans, ts, sil_w2c);
-    if (blockIdx.x == 0 && threadIdx.x == 0) status[1] = 0;  // overflow flag of this frame
+    if (blk == 0 && threadIdx.x == 0) status[1] = 0;  // overflow flag of this frame
     __syncthreads();
     const int idx = row0 + threadIdx.x;
-    if (idx >= P) return;
-    Activated a;
-    activate<ISO>(ps, s_means[3 * threadIdx.x], s_means[3 * threadIdx.x + 1], s_means[3 * threadIdx.x + 2],
-                  __ldg(reinterpret_cast<const float4*>(unnorm_rot) + idx), s_ls + (ISO ? 1 : 3) * threadIdx.x,
-                  __ldg(logit_op + idx), a);
     int my_radii = 0;
     uint32_t my_tiles = 0;
-    if (xform_row(s_view, 2, a.mc[0], a.mc[1], a.mc[2]) > 0.2f) {
-        float cov3D[6];
-        cov3d_from_scale_rot(a.scale[0], a.scale[1], a.scale[2], scale_modifier,
-                             make_float4(a.rot[0], a.rot[1], a.rot[2], a.rot[3]), cov3D);
-        const PreprocessResult r = preprocess_one(a.mc[0], a.mc[1], a.mc[2], cov3D, a.opacity, s_view, s_proj, W, H, gx,
-                                                  gy, tanfovx, tanfovy, focal_x, focal_y);
-        if (r.radius > 0) {
-            my_radii = r.radius;
-            my_tiles = r.tiles;
-            depths[idx] = r.depth;
-            means2D_out[idx] = r.mean2D;
-            conic_opacity[idx] = r.conic_opacity;
-            zsil[idx] = ps.sil[0] * a.mc[0] + ps.sil[1] * a.mc[1] + ps.sil[2] * a.mc[2] + ps.sil[3];
+    if (idx < P) {
+        Activated a;
+        activate<ISO>(ps, s_means[3 * threadIdx.x], s_means[3 * threadIdx.x + 1], s_means[3 * threadIdx.x + 2],
+                      __ldg(reinterpret_cast<const float4*>(unnorm_rot) + idx), s_ls + (ISO ? 1 : 3) * threadIdx.x,
+                      __ldg(logit_op + idx), a);
+        if (xform_row(s_view, 2, a.mc[0], a.mc[1], a.mc[2]) > 0.2f) {
+            float cov3D[6];
+            cov3d_from_scale_rot(a.scale[0], a.scale[1], a.scale[2], scale_modifier,
+                                 make_float4(a.rot[0], a.rot[1], a.rot[2], a.rot[3]), cov3D);
+            const PreprocessResult r = preprocess_one(a.mc[0], a.mc[1], a.mc[2], cov3D, a.opacity, s_view, s_proj, W, H,
+                                                      gx, gy, tanfovx, tanfovy, focal_x, focal_y);
+            if (r.radius > 0) {
+                my_radii = r.radius;
+                my_tiles = r.tiles;
+                depths[idx] = r.depth;
+                means2D_out[idx] = r.mean2D;
+                conic_opacity[idx] = r.conic_opacity;
+                zsil[idx] = ps.sil[0] * a.mc[0] + ps.sil[1] * a.mc[1] + ps.sil[2] * a.mc[2] + ps.sil[3];
+            }
+        }
+        if (radii) radii[idx] = my_radii;
+        radii_internal[idx] = my_radii;
+    }
+    // ---- fused prefix sums (replaces the separate InclusiveSum launch, rasterizer_impl.cu:279):
+    //      tiles touched -> point_offsets, visible count -> compact list of visible Gaussians ----
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool vis = my_radii > 0;
+    uint32_t incl = my_tiles;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    const uint32_t bal = __ballot_sync(0xffffffffu, vis);
+    if (lane == 31) s_wt[warp] = incl;
+    if (lane == 0) s_wv[warp] = __popc(bal);
+    __syncthreads();
+    uint32_t woff_t = 0, woff_v = 0, tot_t = 0, tot_v = 0;
+#pragma unroll
+    for (int w = 0; w < FP_THREADS / 32; w++) {
+        if (w < warp) { woff_t += s_wt[w]; woff_v += s_wv[w]; }
+        tot_t += s_wt[w];
+        tot_v += s_wv[w];
+    }
+    if (warp == 0) {
+        // decoupled look-back, one warp wide: lane l inspects slab blk-1-l, the window slides back by 32
+        const uint64_t mine = ((uint64_t)tot_v << 32) | tot_t;
+        if (lane == 0 && blk > 0) st_volatile_u64(scan_status + blk, FPS_AGG | mine);
+        uint64_t prefix = 0;
+        int base = (int)blk - 1;
+        while (base >= 0) {
+            const int p = base - lane;
+            uint64_t v = FPS_PREFIX;  // slabs before the first one: an empty inclusive prefix
+            if (p >= 0) {
+                do { v = ld_volatile_u64(scan_status + p); } while ((v >> 62) == 0);
+            }
+            const uint32_t is_prefix = __ballot_sync(0xffffffffu, (v >> 62) == 2);
+            const int first = is_prefix ? (__ffs(is_prefix) - 1) : 31;
+            // fields cannot carry into each other: tiles total < 2^32, visible total < 2^24
+            uint64_t c = (lane <= first) ? (v & FPS_VALUE_MASK) : 0ull;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+            prefix += c;
+            if (is_prefix) break;
+            base -= 32;
+        }
+        if (lane == 0) {
+            st_volatile_u64(scan_status + blk, FPS_PREFIX | (prefix + mine));
+            s_pref_t = (uint32_t)prefix;
+            s_pref_v = (uint32_t)(prefix >> 32);
+            if ((int)blk == (P + FP_THREADS - 1) / FP_THREADS - 1) {  // the last slab knows the totals
+                status[0] = (uint32_t)prefix + tot_t;          // num_rendered
+                status[2] = (uint32_t)(prefix >> 32) + tot_v;  // number of visible Gaussians
+            }
         }
     }
-    if (radii) radii[idx] = my_radii;
-    radii_internal[idx] = my_radii;
-    tiles_touched[idx] = my_tiles;
+    __syncthreads();
+    if (idx < P) {
+        point_offsets[idx] = s_pref_t + woff_t + incl;
+        if (vis) vis_list[s_pref_v + woff_v + __popc(bal & ((1u << lane) - 1u))] = (uint32_t)idx;
+    }
 }
 
 // duplicateWithKeys (rasterizer_impl.cu:70-111) with a capacity guard instead of a host-sized buffer
@@ -262,7 +335,8 @@ frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const
                                  const float* __restrict__ sil_w2c, const float* __restrict__ viewmatrix,
                                  const float* __restrict__ projmatrix, float h_x, float h_y, float tanfovx,
                                  float tanfovy, float scale_modifier, const int* __restrict__ radii,
-                                 const float* __restrict__ zsil, float* __restrict__ gacc,
+                                 const float* __restrict__ zsil, const uint32_t* __restrict__ vis_list,
+                                 const uint32_t* __restrict__ status, float* __restrict__ gacc,
                                  const float* __restrict__ gscale, int gaussians_grad, int camera_grad,
                                  int accumulate, float* __restrict__ grad_params, float* __restrict__ grad_means2D,
                                  float* __restrict__ pose_acc) {
@@ -273,16 +347,37 @@ frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const
     else if (threadIdx.x < 32) proj[threadIdx.x - 16] = __ldg(projmatrix + threadIdx.x - 16);
     else if (threadIdx.x == 32) load_pose(ps, cam_rot, rs, cam_trans, ts, sil_w2c);
     __syncthreads();
-    const int idx = blockIdx.x * FP_THREADS + threadIdx.x;
     const float gs = gscale ? __ldg(gscale) : 1.f;
     float pacc[16];
 #pragma unroll
     for (int k = 0; k < 16; k++) pacc[k] = 0.f;
+    // (A) rows of culled Gaussians are zero
+    {
+        const int my = blockIdx.x * FP_THREADS + threadIdx.x;
+        if (my < P && !(radii[my] > 0)) {
+            if (gaussians_grad && grad_params && !accumulate) {
+                float* o = grad_params + 14 * (size_t)my;
+#pragma unroll
+                for (int k = 0; k < 14; k += 2) *reinterpret_cast<float2*>(o + k) = make_float2(0.f, 0.f);
+            }
+            if (grad_means2D) {
+                grad_means2D[3 * (size_t)my] = 0.f;
+                grad_means2D[3 * (size_t)my + 1] = 0.f;
+                grad_means2D[3 * (size_t)my + 2] = 0.f;
+            }
+        }
+    }
+    // (B) the long per-Gaussian path runs densely over the compact list of visible Gaussians that the
+    //     forward wrote (visible ones are usually a scattered minority): the first ceil(V/256) blocks are
+    //     full, the rest are done after (A)
+    const int nvis = (int)status[2];
+    for (int slot = blockIdx.x * FP_THREADS + threadIdx.x; slot < nvis; slot += FP_THREADS * gridDim.x) {
+    const int idx = (int)vis_list[slot];
     float out[14];
 #pragma unroll
     for (int k = 0; k < 14; k++) out[k] = 0.f;
     float gm2x = 0.f, gm2y = 0.f;
-    if (idx < P && radii[idx] > 0) {
+    {
         float4* ga = reinterpret_cast<float4*>(gacc) + 3 * (size_t)idx;
         const float4 g0 = ga[0], g1 = ga[1], g2 = ga[2];  // conic x,y,w | op ; mean2D x,y | c0 c1 ; c2 c3 c4 c5
         const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -332,19 +427,19 @@ frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const
 #pragma unroll
             for (int k = 0; k < 4; k++) g_qraw[k] = (g_qn[k] - q2[k] * d2) / a.qn_norm;
             if (camera_grad) {
-                pacc[12] = q2[0] * g_rt[0] + q2[1] * g_rt[1] + q2[2] * g_rt[2] + q2[3] * g_rt[3];
-                pacc[13] = -q2[1] * g_rt[0] + q2[0] * g_rt[1] - q2[3] * g_rt[2] + q2[2] * g_rt[3];
-                pacc[14] = -q2[2] * g_rt[0] + q2[3] * g_rt[1] + q2[0] * g_rt[2] - q2[1] * g_rt[3];
-                pacc[15] = -q2[3] * g_rt[0] - q2[2] * g_rt[1] + q2[1] * g_rt[2] + q2[0] * g_rt[3];
+                pacc[12] += q2[0] * g_rt[0] + q2[1] * g_rt[1] + q2[2] * g_rt[2] + q2[3] * g_rt[3];
+                pacc[13] += -q2[1] * g_rt[0] + q2[0] * g_rt[1] - q2[3] * g_rt[2] + q2[2] * g_rt[3];
+                pacc[14] += -q2[2] * g_rt[0] + q2[3] * g_rt[1] + q2[0] * g_rt[2] - q2[1] * g_rt[3];
+                pacc[15] += -q2[3] * g_rt[0] - q2[2] * g_rt[1] + q2[1] * g_rt[2] + q2[0] * g_rt[3];
             }
         }
         if (camera_grad) {
-            pacc[0] = dmean[0]; pacc[1] = dmean[1]; pacc[2] = dmean[2];
+            pacc[0] += dmean[0]; pacc[1] += dmean[1]; pacc[2] += dmean[2];
 #pragma unroll
             for (int i = 0; i < 3; i++) {
-                pacc[3 + 3 * i + 0] = dmean[i] * px;
-                pacc[3 + 3 * i + 1] = dmean[i] * py;
-                pacc[3 + 3 * i + 2] = dmean[i] * pz;
+                pacc[3 + 3 * i + 0] += dmean[i] * px;
+                pacc[3 + 3 * i + 1] += dmean[i] * py;
+                pacc[3 + 3 * i + 2] += dmean[i] * pz;
             }
         }
         if (gaussians_grad) {
@@ -363,7 +458,7 @@ frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const
             }
         }
     }
-    if (idx < P) {
+    {
         if (gaussians_grad && grad_params) {
             float* o = grad_params + 14 * (size_t)idx;  // 56-byte rows: 8-byte aligned
 #pragma unroll
@@ -379,6 +474,7 @@ frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const
             grad_means2D[3 * (size_t)idx + 2] = 0.f;
         }
     }
+    }  // slot loop
     if (camera_grad) {
 #pragma unroll
         for (int k = 0; k < 16; k++) pacc[k] *= gs;
@@ -569,6 +665,8 @@ adam_kernel(int P, int iso, AdamPtrs ap, const float* __restrict__ grad, float* 
 // ---- host launchers --------------------------------------------------------------------------------
 void launch_frame_preprocess(const AsFrameArgs& a, const GeometryState& g, uint32_t* status, cudaStream_t st) {
     const int P = a.P, W = a.width, H = a.height;
+    // ticket + one look-back word per 256-Gaussian slab (same footprint as the stand-alone scan's temp)
+    cudaMemsetAsync(g.scan_temp, 0, 16 + sizeof(uint64_t) * (size_t)((P + FP_THREADS - 1) / FP_THREADS), st);
     const float focal_y = H / (2.0f * a.tan_fovy), focal_x = W / (2.0f * a.tan_fovx);
     const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
     const int blocks = (P + FP_THREADS - 1) / FP_THREADS;
@@ -576,14 +674,14 @@ void launch_frame_preprocess(const AsFrameArgs& a, const GeometryState& g, uint3
         frame_preprocess_kernel<true><<<blocks, FP_THREADS, 0, st>>>(
             P, a.means3D, a.unnorm_rotations, a.logit_opacities, a.log_scales, a.cam_unnorm_rot, a.cam_rot_stride,
             a.cam_trans, a.cam_trans_stride, a.sil_w2c, a.viewmatrix, a.projmatrix, W, H, gx, gy, a.tan_fovx, a.tan_fovy,
-            focal_x, focal_y, a.scale_modifier, a.radii, g.radii, g.means2D, g.depths, g.conic_opacity, g.tiles_touched,
-            g.zsil, status);
+            focal_x, focal_y, a.scale_modifier, a.radii, g.radii, g.means2D, g.depths, g.conic_opacity, g.point_offsets,
+            g.zsil, g.vis_list, g.scan_temp, reinterpret_cast<uint64_t*>(g.scan_temp + 4), status);
     else
         frame_preprocess_kernel<false><<<blocks, FP_THREADS, 0, st>>>(
             P, a.means3D, a.unnorm_rotations, a.logit_opacities, a.log_scales, a.cam_unnorm_rot, a.cam_rot_stride,
             a.cam_trans, a.cam_trans_stride, a.sil_w2c, a.viewmatrix, a.projmatrix, W, H, gx, gy, a.tan_fovx, a.tan_fovy,
-            focal_x, focal_y, a.scale_modifier, a.radii, g.radii, g.means2D, g.depths, g.conic_opacity, g.tiles_touched,
-            g.zsil, status);
+            focal_x, focal_y, a.scale_modifier, a.radii, g.radii, g.means2D, g.depths, g.conic_opacity, g.point_offsets,
+            g.zsil, g.vis_list, g.scan_temp, reinterpret_cast<uint64_t*>(g.scan_temp + 4), status);
 }
 
 void launch_frame_duplicate(int P, const GeometryState& g, int W, int H, uint32_t capacity, uint64_t* keys,
@@ -613,14 +711,14 @@ void launch_frame_preprocess_backward(const AsFrameArgs& a, const GeometryState&
         frame_preprocess_backward_kernel<true><<<blocks, FP_THREADS, 0, st>>>(
             P, a.means3D, a.unnorm_rotations, a.logit_opacities, a.log_scales, a.cam_unnorm_rot, a.cam_rot_stride,
             a.cam_trans, a.cam_trans_stride, a.sil_w2c, a.viewmatrix, a.projmatrix, h_x, h_y, a.tan_fovx, a.tan_fovy,
-            a.scale_modifier, g.radii, g.zsil, g.gacc, gscale, gaussians_grad, camera_grad, accumulate, grad_params,
-            grad_means2D, pose_acc);
+            a.scale_modifier, g.radii, g.zsil, g.vis_list, a.status, g.gacc, gscale, gaussians_grad, camera_grad,
+            accumulate, grad_params, grad_means2D, pose_acc);
     else
         frame_preprocess_backward_kernel<false><<<blocks, FP_THREADS, 0, st>>>(
             P, a.means3D, a.unnorm_rotations, a.logit_opacities, a.log_scales, a.cam_unnorm_rot, a.cam_rot_stride,
             a.cam_trans, a.cam_trans_stride, a.sil_w2c, a.viewmatrix, a.projmatrix, h_x, h_y, a.tan_fovx, a.tan_fovy,
-            a.scale_modifier, g.radii, g.zsil, g.gacc, gscale, gaussians_grad, camera_grad, accumulate, grad_params,
-            grad_means2D, pose_acc);
+            a.scale_modifier, g.radii, g.zsil, g.vis_list, a.status, g.gacc, gscale, gaussians_grad, camera_grad,
+            accumulate, grad_params, grad_means2D, pose_acc);
     if (camera_grad)
         pose_finalize_kernel<<<1, 256, 0, st>>>(a.cam_unnorm_rot, a.cam_rot_stride, pose_acc, blocks, grad_cam);
 }

@@ -36,7 +36,7 @@ class FrameWorkspace:
             self.geom = torch.zeros(L.as_geometry_bytes(self.P), **u8)   # accumulators must start at zero
             self.img = torch.empty(L.as_image_bytes(self.W, self.H), **u8)
             self.binning = torch.empty(L.as_binning_bytes(self.capacity, 6), **u8)
-            self.status = torch.zeros(2, dtype=torch.int32, device=self.device)
+            self.status = torch.zeros(4, dtype=torch.int32, device=self.device)
             self.color6 = torch.empty((6, self.H, self.W), **f32)
             self.depth = torch.empty((1, self.H, self.W), **f32)
             self.opacity = torch.empty((1, self.H, self.W), **f32)

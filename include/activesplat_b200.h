@@ -165,7 +165,7 @@ typedef struct AsFrameArgs {
     char* image_buffer;
     char* binning_buffer;
     int binning_capacity;
-    uint32_t* status;              /* [2] device words: [0] num_rendered, [1] overflow flag */
+    uint32_t* status;              /* [4] device words: [0] num_rendered, [1] overflow flag, [2] visible Gaussians */
     float* out_color;              /* [6,H,W]: rgb | depth, silhouette, depth^2 */
     float* out_depth;              /* [1,H,W] median depth */
     float* out_opacity;            /* [1,H,W] */
