@@ -405,6 +405,20 @@ int as_tracking_loss(int width, int height, const float* color6, const float* gt
     return check(cudaGetLastError());
 }
 
+size_t as_mapping_loss_scratch_floats(int width, int height) { return mapping_loss_scratch_floats(width, height); }
+
+int as_mapping_loss(int width, int height, const float* color6, const float* gt_rgb, const float* gt_depth,
+                    float w_im, float w_depth, float* dL_dcolor6, float* losses, float* scratch,
+                    const uint32_t* frame_status, void* cuda_stream) {
+    if (width <= 0 || height <= 0 || !color6 || !gt_rgb || !gt_depth || !dL_dcolor6 || !losses || !scratch)
+        return AS_ERR_INVALID_ARG;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
+    StageScope _s(AS_STAGE_LOSS, st, 3);
+    launch_mapping_loss(width, height, color6, gt_rgb, gt_depth, w_im, w_depth, dL_dcolor6, losses, scratch,
+                        frame_status, st);
+    return check(cudaGetLastError());
+}
+
 int as_adam_step(int P, int isotropic, float* means3D, float* rgb_colors, float* unnorm_rotations,
                  float* logit_opacities, float* log_scales, const float* grad_params, float* exp_avg,
                  float* exp_avg_sq, const float* lrs, float beta1, float beta2, float eps, int step,

@@ -145,6 +145,10 @@ size_t pose_scratch_floats(int P);
 void launch_tracking_loss(int N, const float* c6, const float* gt_rgb, const float* gt_depth, float w_im,
                           float w_depth, float sil_thres, int use_sil, int mask_color, float* dL, float* partials,
                           float* losses, const uint32_t* status, cudaStream_t st);
+size_t mapping_loss_scratch_floats(int W, int H);
+void launch_mapping_loss(int W, int H, const float* c6, const float* gt_rgb, const float* gt_depth, float w_im,
+                         float w_depth, float* dL, float* losses, float* scratch, const uint32_t* status,
+                         cudaStream_t st);
 void launch_adam(int P, int iso, float* const params[5], const float lr[5], const float* grad, float* m, float* v,
                  float beta1, float beta2, float eps, int step, cudaStream_t st);
 

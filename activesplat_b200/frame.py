@@ -52,6 +52,7 @@ class FrameWorkspace:
         self._args = None
         self._keep = None
         self._bg_src = None
+        self.map_scratch = None
 
     # -- buffer management ---------------------------------------------------------------------
     def ensure_capacity(self, needed):
@@ -135,6 +136,27 @@ class FrameWorkspace:
                                           torch.cuda.current_stream(self.device).cuda_stream))
         return self.losses
 
+    def mapping_loss(self, gt_rgb, gt_depth, w_im, w_depth):
+        """as_mapping_loss on the last forward's colour6: fills self.dL and self.losses."""
+        L = capi.lib()
+        keep = self._keep
+
+        def ptr(t):
+            if t.dtype != torch.float32 or not t.is_contiguous():
+                t = t.contiguous().float()
+            keep.append(t)
+            return t.data_ptr()
+
+        with torch.cuda.device(self.device):
+            if self.map_scratch is None:
+                self.map_scratch = torch.empty(L.as_mapping_loss_scratch_floats(self.W, self.H), dtype=torch.float32,
+                                               device=self.device)
+            capi.check(L.as_mapping_loss(self.W, self.H, self.color6.data_ptr(), ptr(gt_rgb), ptr(gt_depth),
+                                         float(w_im), float(w_depth), self.dL.data_ptr(), self.losses.data_ptr(),
+                                         self.map_scratch.data_ptr(), self.status.data_ptr(),
+                                         torch.cuda.current_stream(self.device).cuda_stream))
+        return self.losses
+
     def backward(self, dL_dpix=None, grad_scale=None, gaussians_grad=True, camera_grad=False, accumulate=False):
         """as_frame_backward for the last forward.  Returns (grad_params [P,14], grad_cam [8])."""
         L = capi.lib()
@@ -170,8 +192,11 @@ def workspace_for(params, cam):
 
 
 class _FusedTrackingLoss(torch.autograd.Function):
-    """loss = w_im * sum_mask|gt_rgb - im| + w_depth * sum_mask|gt_depth - depth|  (splatam.py:230-247)
-    of the frame rendered from the raw parameters, as ONE autograd node."""
+    """The frame rendered from the raw parameters and its loss as ONE autograd node.
+    use_sil is a bool  -> tracking loss: w_im * sum_mask|gt_rgb - im| + w_depth * sum_mask|gt_depth - depth|
+                          (splatam.py:230-247);
+    use_sil == "mapping" -> mapping loss: w_im * (0.8 L1 + 0.2 (1 - SSIM)) + w_depth * masked mean depth L1
+                          (splatam.py:239-249)."""
 
     @staticmethod
     def forward(ctx, means3D, rgb, rots, logit_op, log_scales, cam_rots, cam_trans, ws, cam, time_idx, sil_w2c,
@@ -179,7 +204,10 @@ class _FusedTrackingLoss(torch.autograd.Function):
         params = {"means3D": means3D, "rgb_colors": rgb, "unnorm_rotations": rots, "logit_opacities": logit_op,
                   "log_scales": log_scales, "cam_unnorm_rots": cam_rots, "cam_trans": cam_trans}
         ws.forward(params, cam, time_idx, sil_w2c=sil_w2c)
-        ws.tracking_loss(gt_rgb, gt_depth, w_im, w_depth, sil_thres, use_sil, mask_color)
+        if isinstance(use_sil, str):
+            ws.mapping_loss(gt_rgb, gt_depth, w_im, w_depth)
+        else:
+            ws.tracking_loss(gt_rgb, gt_depth, w_im, w_depth, sil_thres, use_sil, mask_color)
         ctx.ws, ctx.time_idx = ws, int(time_idx)
         ctx.shapes = (cam_rots.shape, cam_trans.shape, log_scales.shape[1])
         ctx.gaussians_grad = any(ctx.needs_input_grad[:5])
@@ -277,6 +305,16 @@ def fused_tracking_loss(params, cam, time_idx, sil_w2c, gt_rgb, gt_depth, w_im, 
                                    params["logit_opacities"], params["log_scales"], params["cam_unnorm_rots"],
                                    params["cam_trans"], ws, cam, time_idx, sil_w2c, gt_rgb, gt_depth, w_im, w_depth,
                                    sil_thres, use_sil_for_loss, mask_color)
+    return out, ws
+
+
+def fused_mapping_loss(params, cam, time_idx, sil_w2c, gt_rgb, gt_depth, w_im, w_depth, ws=None):
+    """Mapping-loss twin of fused_tracking_loss: (losses[3] = weighted total / im / depth, workspace)."""
+    ws = ws or workspace_for(params, cam)
+    out = _FusedTrackingLoss.apply(params["means3D"], params["rgb_colors"], params["unnorm_rotations"],
+                                   params["logit_opacities"], params["log_scales"], params["cam_unnorm_rots"],
+                                   params["cam_trans"], ws, cam, time_idx, sil_w2c, gt_rgb, gt_depth, w_im, w_depth,
+                                   0.0, "mapping", False)
     return out, ws
 
 

@@ -194,6 +194,8 @@ def get_loss(params, curr_data, variables, iter_time_idx, loss_weights, use_sil_
             and params['means3D'].is_cuda):
         return _get_loss_tracking_fused(params, curr_data, variables, iter_time_idx, loss_weights, use_sil_for_loss,
                                         sil_thres)
+    if (not tracking and use_l1 and not ignore_outlier_depth_loss and params['means3D'].is_cuda):
+        return _get_loss_mapping_fused(params, curr_data, variables, iter_time_idx, loss_weights, mapping and do_ba)
     losses = {}
     gaussians_grad = not tracking
     camera_grad = tracking or (mapping and do_ba)
@@ -271,6 +273,23 @@ def _get_loss_tracking_fused(params, curr_data, variables, iter_time_idx, loss_w
     variables['max_2D_radius'] = torch.maximum(variables['max_2D_radius'], radius.to(variables['max_2D_radius'].dtype))
     variables['seen'] = radius > 0
     variables['means2D'] = None  # screen-space gradient: FrameWorkspace(want_means2D_grad=True).grad_means2D
+    return loss, variables, weighted_losses
+
+
+def _get_loss_mapping_fused(params, curr_data, variables, iter_time_idx, loss_weights, camera_grad):
+    """get_loss(mapping=True) (splatam.py:183-196, 213-249) as one fused autograd node, SSIM included."""
+    from .frame import fused_mapping_loss
+    p = dict(params)
+    if not camera_grad:
+        p['cam_unnorm_rots'], p['cam_trans'] = p['cam_unnorm_rots'].detach(), p['cam_trans'].detach()
+    out, ws = fused_mapping_loss(p, curr_data['cam'], int(iter_time_idx), curr_data['w2c'], curr_data['im'],
+                                 curr_data['depth'], loss_weights['im'], loss_weights['depth'])
+    loss = out[0]
+    weighted_losses = {'depth': out[2], 'im': out[1], 'loss': loss}
+    radius = ws.radii
+    variables['max_2D_radius'] = torch.maximum(variables['max_2D_radius'], radius.to(variables['max_2D_radius'].dtype))
+    variables['seen'] = radius > 0
+    variables['means2D'] = None
     return loss, variables, weighted_losses
 
 

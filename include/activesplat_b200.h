@@ -201,6 +201,16 @@ int as_tracking_loss(int width, int height, const float* color6, const float* gt
                      float* dL_dcolor6, float* losses, float* scratch, const uint32_t* frame_status,
                      void* cuda_stream);
 
+/* Mapping loss of get_loss (splatam.py:239-249): w_im * (0.8 * mean|im - gt| + 0.2 * (1 - mean SSIM)) +
+ * w_depth * mean over the valid-depth mask of |gt_depth - depth|, SSIM as calc_ssim (slam_external.py:54-97:
+ * 11x11 Gaussian window, sigma 1.5, zero padding, c1 1e-4, c2 9e-4), with its gradient w.r.t. the six
+ * rendered channels.  losses[8] as in as_tracking_loss, plus losses[6] = mean SSIM.
+ * scratch: as_mapping_loss_scratch_floats(w,h) floats. */
+size_t as_mapping_loss_scratch_floats(int width, int height);
+int as_mapping_loss(int width, int height, const float* color6, const float* gt_rgb, const float* gt_depth,
+                    float w_im, float w_depth, float* dL_dcolor6, float* losses, float* scratch,
+                    const uint32_t* frame_status, void* cuda_stream);
+
 /* torch.optim.Adam step (splatam.py:118-124: betas (0.9,0.999), eps 1e-15, no weight decay) over the five
  * parameter tensors at once; grad/exp_avg/exp_avg_sq are the flat [P,14] layout of AsFrameBackwardArgs.
  * lrs[5]: means3D, rgb_colors, unnorm_rotations, logit_opacities, log_scales.  step counts from 1. */
