@@ -307,12 +307,31 @@ def render_view(params, w2c, k, width, height, near=0.01, far=100, scale_modifie
     from .frame import fused_render, identity_pose
     with torch.no_grad():
         dev = params['means3D'].device
-        cam = setup_camera(width, height, k, w2c, near, far, scale_modifier=scale_modifier, device=dev)
+        cam, sil_w2c = _camera_one_upload(width, height, k, w2c, near, far, scale_modifier, dev)
         rot, tr = identity_pose(dev)
         p = dict(params, cam_unnorm_rots=rot, cam_trans=tr)
-        sil_w2c = torch.as_tensor(np.asarray(w2c)).to(dev).float().contiguous()
         c6, _, depth, opacity, ws = fused_render(p, cam, 0, sil_w2c, bg_rgb=_white_bg(dev), ws=ws)
         return c6[:3], depth, opacity, c6[4:5]
+
+
+def _camera_one_upload(w, h, k, w2c, near, far, scale_modifier, dev):
+    """setup_camera's matrices (recon_helpers.py:6-14) computed on the host and sent to the device in ONE
+    copy (the reference builds them with ~8 tiny device ops + a matrix inverse per candidate view)."""
+    fx, fy, cx, cy = k[0][0], k[1][1], k[0][2], k[1][2]
+    w2c_t = torch.as_tensor(np.asarray(w2c)).float()
+    cam_center = torch.inverse(w2c_t)[:3, 3]
+    view = w2c_t.unsqueeze(0).transpose(1, 2)
+    opengl_proj = torch.tensor([[2 * fx / w, 0.0, -(w - 2 * cx) / w, 0.0],
+                                [0.0, 2 * fy / h, -(h - 2 * cy) / h, 0.0],
+                                [0.0, 0.0, far / (far - near), -(far * near) / (far - near)],
+                                [0.0, 0.0, 1.0, 0.0]]).float().unsqueeze(0).transpose(1, 2)
+    full_proj = view.bmm(opengl_proj)
+    packed = torch.cat([view.reshape(-1), full_proj.reshape(-1), w2c_t.reshape(-1), cam_center, torch.zeros(3)])
+    d = packed.to(dev, non_blocking=True)
+    cam = Camera(image_height=h, image_width=w, tanfovx=w / (2 * fx), tanfovy=h / (2 * fy), bg=d[51:54],
+                 scale_modifier=scale_modifier, viewmatrix=d[0:16].view(1, 4, 4), projmatrix=d[16:32].view(1, 4, 4),
+                 sh_degree=0, campos=d[48:51], prefiltered=False, debug=False)
+    return cam, d[32:48].view(4, 4)
 
 
 _WHITE = {}

@@ -17,13 +17,17 @@ from math import exp
 import torch
 import torch.nn.functional as F
 
-from .raster_oracle import GaussianRasterizer as Renderer
+from .raster_oracle import GaussianRasterizer as Renderer  # default: the CPU oracle rasterizer
+
+# Every function creates its temporaries on the device of its inputs, and get_loss / render take the
+# rasterizer class as an argument, so the same restatement also drives the UNMODIFIED reference CUDA
+# rasterizer (oracle/_ref) on a GPU: that combination is the "reference pipeline" timed by the benchmarks.
 
 
 def build_rotation(q):
     norm = torch.sqrt(q[:, 0] * q[:, 0] + q[:, 1] * q[:, 1] + q[:, 2] * q[:, 2] + q[:, 3] * q[:, 3])
     q = q / norm[:, None]
-    rot = torch.zeros((q.size(0), 3, 3))
+    rot = torch.zeros((q.size(0), 3, 3), device=q.device)
     r, x, y, z = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
     rot[:, 0, 0] = 1 - 2 * (y * y + z * z)
     rot[:, 0, 1] = 2 * (x * y - r * z)
@@ -54,7 +58,7 @@ def transform_to_frame(params, time_idx, gaussians_grad, camera_grad):
     else:
         cam_rot = F.normalize(params['cam_unnorm_rots'][..., time_idx].detach())
         cam_tran = params['cam_trans'][..., time_idx].detach()
-    rel_w2c = torch.eye(4)
+    rel_w2c = torch.eye(4, device=params['means3D'].device)
     rel_w2c[:3, :3] = build_rotation(cam_rot)
     rel_w2c[:3, 3] = cam_tran
     transform_rots = params['log_scales'].shape[1] != 1
@@ -62,7 +66,7 @@ def transform_to_frame(params, time_idx, gaussians_grad, camera_grad):
         pts, unnorm_rots = params['means3D'], params['unnorm_rotations']
     else:
         pts, unnorm_rots = params['means3D'].detach(), params['unnorm_rotations'].detach()
-    pts4 = torch.cat((pts, torch.ones(pts.shape[0], 1)), dim=1)
+    pts4 = torch.cat((pts, torch.ones(pts.shape[0], 1, device=pts.device)), dim=1)
     out = {'means3D': (rel_w2c @ pts4.T).T[:, :3]}
     out['unnorm_rotations'] = quat_mult(cam_rot, F.normalize(unnorm_rots)) if transform_rots else unnorm_rots
     return out
@@ -72,8 +76,10 @@ def get_depth_and_silhouette(pts_3D, w2c):
     pts4 = torch.cat((pts_3D, torch.ones_like(pts_3D[:, :1])), dim=-1)
     pts_in_cam = (w2c @ pts4.transpose(0, 1)).transpose(0, 1)
     depth_z = pts_in_cam[:, 2].unsqueeze(-1)
-    ds = torch.zeros((pts_3D.shape[0], 3))
-    ds = torch.cat([depth_z, torch.ones_like(depth_z), torch.square(depth_z)], dim=1) + 0 * ds
+    ds = torch.zeros((pts_3D.shape[0], 3), device=pts_3D.device)
+    ds[:, 0] = depth_z.squeeze(-1)
+    ds[:, 1] = 1.0
+    ds[:, 2] = torch.square(depth_z).squeeze(-1)
     return ds
 
 
@@ -104,6 +110,7 @@ def calc_ssim(img1, img2, window_size=11):
     channel = img1.size(-3)
     w1 = gaussian(window_size, 1.5).unsqueeze(1)
     window = w1.mm(w1.t()).float().unsqueeze(0).unsqueeze(0).expand(channel, 1, window_size, window_size).contiguous()
+    window = window.to(img1.device).type_as(img1)
     pad = window_size // 2
     mu1 = F.conv2d(img1, window, padding=pad, groups=channel)
     mu2 = F.conv2d(img2, window, padding=pad, groups=channel)
@@ -116,8 +123,26 @@ def calc_ssim(img1, img2, window_size=11):
     return ssim_map.mean()
 
 
+def get_rendervars(params, w2c):
+    """splatam.py:436-468 (no timestep filtering)."""
+    base = {'means3D': params['means3D'], 'rotations': F.normalize(params['unnorm_rotations']),
+            'opacities': torch.sigmoid(params['logit_opacities']), 'scales': torch.exp(_log_scales3(params))}
+    rv = dict(base, colors_precomp=params['rgb_colors'], means2D=torch.zeros_like(params['means3D']))
+    drv = dict(base, colors_precomp=get_depth_and_silhouette(params['means3D'], w2c),
+               means2D=torch.zeros_like(params['means3D']))
+    return rv, drv
+
+
+def render(cam, white_bg_cam, timestep_data, timestep_depth_data, Renderer=Renderer):
+    """splatam.py:413-434: white-background RGB pass, then the depth/silhouette pass."""
+    with torch.no_grad():
+        im, _, depth, opacity = Renderer(white_bg_cam)(**timestep_data)
+        depth_sil, _, _, _ = Renderer(cam)(**timestep_depth_data)
+        return im, depth, opacity, depth_sil[1, :, :].unsqueeze(0)
+
+
 def get_loss(params, curr_data, iter_time_idx, loss_weights, use_sil_for_loss, sil_thres, use_l1,
-             ignore_outlier_depth_loss, tracking=False, mapping=False, do_ba=False):
+             ignore_outlier_depth_loss, tracking=False, mapping=False, do_ba=False, Renderer=Renderer):
     losses = {}
     if tracking:
         tg = transform_to_frame(params, iter_time_idx, gaussians_grad=False, camera_grad=True)
