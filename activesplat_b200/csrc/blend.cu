@@ -174,31 +174,32 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
                 }
                 if (done) hit = 0;
                 if (__any_sync(0xffffffffu, hit != 0)) {
+                    // order-dependent part, branch-free: the only serial chain is T -> test_T -> T
+                    // (one multiply, one compare, one select per record); everything else is predicated
+                    // selects, so a warp with many hits is not slowed down by 8 divergent branches.
 #pragma unroll
                     for (int u = 0; u < FW_UNROLL; u++) {
-                        if (hit & (1u << u)) {
-                            const int j = jj[u];
-                            const float alpha = al[u];
-                            const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
-                            if (test_T < 0.0001f) {
-                                done = true;  // forward.cu:355-359: nothing further is blended
-                                hit = 0;
-                            } else {
-                                const float4 f0 = sm.feat[s][j * FV];
-                                acc[0] = __fmaf_rn(__fmul_rn(f0.x, alpha), T, acc[0]);
-                                acc[1] = __fmaf_rn(__fmul_rn(f0.y, alpha), T, acc[1]);
-                                acc[2] = __fmaf_rn(__fmul_rn(f0.z, alpha), T, acc[2]);
-                                if (C == 6) {
-                                    const float4 f1 = sm.feat[s][j * FV + FV - 1];
-                                    acc[3 % C] = __fmaf_rn(__fmul_rn(f0.w, alpha), T, acc[3 % C]);
-                                    acc[4 % C] = __fmaf_rn(__fmul_rn(f1.x, alpha), T, acc[4 % C]);
-                                    acc[5 % C] = __fmaf_rn(__fmul_rn(f1.y, alpha), T, acc[5 % C]);
-                                }
-                                if (T > 0.5f && test_T < 0.5f) D = sm.geom[s][j].z;  // forward.cu:370-374
-                                T = test_T;
-                                last_contributor = (uint32_t)(b * BL_BATCH + j + 1);  // forward.cu:335,380
-                            }
+                        const int j = max(jj[u], 0);
+                        const float alpha = al[u];
+                        const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
+                        const bool h = ((hit >> u) & 1u) && !done;
+                        const bool stop = h && (test_T < 0.0001f);  // forward.cu:355-359: stop BEFORE blending it
+                        const bool blend = h && !stop;
+                        done = done || stop;
+                        const float4 f0 = sm.feat[s][j * FV];
+                        const float4 ge = sm.geom[s][j];
+                        acc[0] = blend ? __fmaf_rn(__fmul_rn(f0.x, alpha), T, acc[0]) : acc[0];
+                        acc[1] = blend ? __fmaf_rn(__fmul_rn(f0.y, alpha), T, acc[1]) : acc[1];
+                        acc[2] = blend ? __fmaf_rn(__fmul_rn(f0.z, alpha), T, acc[2]) : acc[2];
+                        if (C == 6) {
+                            const float4 f1 = sm.feat[s][j * FV + FV - 1];
+                            acc[3 % C] = blend ? __fmaf_rn(__fmul_rn(f0.w, alpha), T, acc[3 % C]) : acc[3 % C];
+                            acc[4 % C] = blend ? __fmaf_rn(__fmul_rn(f1.x, alpha), T, acc[4 % C]) : acc[4 % C];
+                            acc[5 % C] = blend ? __fmaf_rn(__fmul_rn(f1.y, alpha), T, acc[5 % C]) : acc[5 % C];
                         }
+                        D = (blend && T > 0.5f && test_T < 0.5f) ? ge.z : D;  // forward.cu:370-374
+                        last_contributor = blend ? (uint32_t)(b * BL_BATCH + j + 1) : last_contributor;  // :335,380
+                        T = blend ? test_T : T;
                     }
                     warp_done = __all_sync(0xffffffffu, done);
                 }
