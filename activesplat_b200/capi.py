@@ -77,6 +77,7 @@ class AsFrameArgs(ctypes.Structure):
         ("out_color", ctypes.c_void_p), ("out_depth", ctypes.c_void_p), ("out_opacity", ctypes.c_void_p),
         ("radii", ctypes.c_void_p),
         ("debug", ctypes.c_int),
+        ("max_2D_radius", ctypes.c_void_p), ("seen", ctypes.c_void_p),
     ]
 
 
@@ -88,6 +89,7 @@ class AsFrameBackwardArgs(ctypes.Structure):
         ("grad_params", ctypes.c_void_p), ("grad_means2D", ctypes.c_void_p), ("grad_cam", ctypes.c_void_p),
         ("pose_scratch", ctypes.c_void_p),
         ("accumulate", ctypes.c_int),
+        ("grad_cam_stride", ctypes.c_int),
     ]
 
 

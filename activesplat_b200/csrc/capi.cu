@@ -383,7 +383,8 @@ int as_frame_backward(const AsFrameBackwardArgs* ba, void* cuda_stream) {
     {
         StageScope _s(AS_STAGE_PREPROCESS_BWD, st, ba->camera_grad ? 2 : 1);
         launch_frame_preprocess_backward(*a, g, ba->grad_scale, ba->gaussians_grad, ba->camera_grad, ba->accumulate,
-                                         ba->grad_params, ba->grad_means2D, ba->pose_scratch, ba->grad_cam, st);
+                                         ba->grad_params, ba->grad_means2D, ba->pose_scratch, ba->grad_cam,
+                                         ba->grad_cam_stride, st);
     }
     return stage_check(st, a->debug);
 }

@@ -139,7 +139,8 @@ void launch_frame_ranges_gather(const uint32_t* n_dev, uint32_t capacity, int ti
                                 const float* rgb, const BinningState& b, uint2* ranges, cudaStream_t st);
 void launch_frame_preprocess_backward(const AsFrameArgs& a, const GeometryState& g, const float* gscale,
                                       int gaussians_grad, int camera_grad, int accumulate, float* grad_params,
-                                      float* grad_means2D, float* pose_acc, float* grad_cam, cudaStream_t st);
+                                      float* grad_means2D, float* pose_acc, float* grad_cam, int grad_cam_stride,
+                                      cudaStream_t st);
 int loss_partial_blocks(int N);
 size_t pose_scratch_floats(int P);
 void launch_tracking_loss(int N, const float* c6, const float* gt_rgb, const float* gt_depth, float w_im,

@@ -134,7 +134,8 @@ frame_preprocess_kernel(int P, const float* __restrict__ means3D, const float* _
                         int* __restrict__ radii_internal, float2* __restrict__ means2D_out,
                         float* __restrict__ depths, float4* __restrict__ conic_opacity,
                         uint32_t* __restrict__ point_offsets, float* __restrict__ zsil,
-                        uint32_t* __restrict__ vis_list, uint32_t* ticket, uint64_t* scan_status, uint32_t* status) {
+                        uint32_t* __restrict__ vis_list, uint32_t* ticket, uint64_t* scan_status, uint32_t* status,
+                        float* __restrict__ max_2D_radius, uint8_t* __restrict__ seen) {
     __shared__ __align__(16) float s_means[FP_THREADS * 3];
     __shared__ __align__(16) float s_ls[FP_THREADS * 3];
     __shared__ float s_view[16], s_proj[16];
@@ -181,6 +182,9 @@ frame_preprocess_kernel(int P, const float* __restrict__ means3D, const float* _
         }
         if (radii) radii[idx] = my_radii;
         radii_internal[idx] = my_radii;
+        // bookkeeping of get_loss (splatam.py:296-298): max_2D_radius[seen] = max(radius, .), seen = radius > 0
+        if (max_2D_radius && my_radii > 0) max_2D_radius[idx] = fmaxf(max_2D_radius[idx], (float)my_radii);
+        if (seen) seen[idx] = my_radii > 0 ? 1 : 0;
     }
     // ---- fused prefix sums (replaces the separate InclusiveSum launch, rasterizer_impl.cu:279):
     //      tiles touched -> point_offsets, visible count -> compact list of visible Gaussians ----
@@ -485,7 +489,7 @@ frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const
 // per-block pose partials [nblocks,16] -> gradients of cam_unnorm_rot (4) and cam_trans (3).
 __global__ void __launch_bounds__(256)
 pose_finalize_kernel(const float* __restrict__ cam_rot, int rs, const float* __restrict__ partials, int nblocks,
-                     float* grad_cam) {
+                     float* grad_cam, int gstride) {
     __shared__ float s_part[16][17];
     __shared__ float pose_acc[16];
     {
@@ -530,10 +534,9 @@ pose_finalize_kernel(const float* __restrict__ cam_rot, int rs, const float* __r
 #pragma unroll
     for (int k = 0; k < 4; k++) d2 += qc[k] * gq[k];
 #pragma unroll
-    for (int k = 0; k < 4; k++) grad_cam[k] = (gq[k] - qc[k] * d2) / n;
+    for (int k = 0; k < 4; k++) grad_cam[(size_t)k * gstride] = (gq[k] - qc[k] * d2) / n;
 #pragma unroll
-    for (int k = 0; k < 3; k++) grad_cam[4 + k] = pose_acc[k];
-    grad_cam[7] = 0.f;
+    for (int k = 0; k < 3; k++) grad_cam[(size_t)(4 + k) * gstride] = pose_acc[k];
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -675,13 +678,15 @@ void launch_frame_preprocess(const AsFrameArgs& a, const GeometryState& g, uint3
             P, a.means3D, a.unnorm_rotations, a.logit_opacities, a.log_scales, a.cam_unnorm_rot, a.cam_rot_stride,
             a.cam_trans, a.cam_trans_stride, a.sil_w2c, a.viewmatrix, a.projmatrix, W, H, gx, gy, a.tan_fovx, a.tan_fovy,
             focal_x, focal_y, a.scale_modifier, a.radii, g.radii, g.means2D, g.depths, g.conic_opacity, g.point_offsets,
-            g.zsil, g.vis_list, g.scan_temp, reinterpret_cast<uint64_t*>(g.scan_temp + 4), status);
+            g.zsil, g.vis_list, g.scan_temp, reinterpret_cast<uint64_t*>(g.scan_temp + 4), status, a.max_2D_radius,
+            a.seen);
     else
         frame_preprocess_kernel<false><<<blocks, FP_THREADS, 0, st>>>(
             P, a.means3D, a.unnorm_rotations, a.logit_opacities, a.log_scales, a.cam_unnorm_rot, a.cam_rot_stride,
             a.cam_trans, a.cam_trans_stride, a.sil_w2c, a.viewmatrix, a.projmatrix, W, H, gx, gy, a.tan_fovx, a.tan_fovy,
             focal_x, focal_y, a.scale_modifier, a.radii, g.radii, g.means2D, g.depths, g.conic_opacity, g.point_offsets,
-            g.zsil, g.vis_list, g.scan_temp, reinterpret_cast<uint64_t*>(g.scan_temp + 4), status);
+            g.zsil, g.vis_list, g.scan_temp, reinterpret_cast<uint64_t*>(g.scan_temp + 4), status, a.max_2D_radius,
+            a.seen);
 }
 
 void launch_frame_duplicate(int P, const GeometryState& g, int W, int H, uint32_t capacity, uint64_t* keys,
@@ -703,7 +708,8 @@ void launch_frame_ranges_gather(const uint32_t* n_dev, uint32_t capacity, int ti
 
 void launch_frame_preprocess_backward(const AsFrameArgs& a, const GeometryState& g, const float* gscale,
                                       int gaussians_grad, int camera_grad, int accumulate, float* grad_params,
-                                      float* grad_means2D, float* pose_acc, float* grad_cam, cudaStream_t st) {
+                                      float* grad_means2D, float* pose_acc, float* grad_cam, int grad_cam_stride,
+                                      cudaStream_t st) {
     const int P = a.P, W = a.width, H = a.height;
     const float h_y = H / (2.0f * a.tan_fovy), h_x = W / (2.0f * a.tan_fovx);
     const int blocks = (P + FP_THREADS - 1) / FP_THREADS;
@@ -720,7 +726,8 @@ void launch_frame_preprocess_backward(const AsFrameArgs& a, const GeometryState&
             a.scale_modifier, g.radii, g.zsil, g.vis_list, a.status, g.gacc, gscale, gaussians_grad, camera_grad,
             accumulate, grad_params, grad_means2D, pose_acc);
     if (camera_grad)
-        pose_finalize_kernel<<<1, 256, 0, st>>>(a.cam_unnorm_rot, a.cam_rot_stride, pose_acc, blocks, grad_cam);
+        pose_finalize_kernel<<<1, 256, 0, st>>>(a.cam_unnorm_rot, a.cam_rot_stride, pose_acc, blocks, grad_cam,
+                                                grad_cam_stride > 0 ? grad_cam_stride : 1);
 }
 
 size_t pose_scratch_floats(int P) { return 16 * (size_t)((P + FP_THREADS - 1) / FP_THREADS) + 16; }

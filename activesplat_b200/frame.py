@@ -70,7 +70,7 @@ class FrameWorkspace:
         return int(s[0]), bool(s[1])
 
     # -- forward / backward --------------------------------------------------------------------
-    def forward(self, params, cam, time_idx, sil_w2c=None, bg_rgb=None, debug=False):
+    def forward(self, params, cam, time_idx, sil_w2c=None, bg_rgb=None, debug=False, max_2D_radius=None, seen=None):
         """as_frame_forward.  params: dict with the five Gaussian tensors + cam_unnorm_rots [1,4,T] +
         cam_trans [1,3,T]; cam: GaussianRasterizationSettings.  Results land in color6/depth/opacity/radii."""
         L = capi.lib()
@@ -113,6 +113,8 @@ class FrameWorkspace:
         a.out_color, a.out_depth, a.out_opacity = self.color6.data_ptr(), self.depth.data_ptr(), self.opacity.data_ptr()
         a.radii = self.radii.data_ptr()
         a.debug = int(bool(debug))
+        a.max_2D_radius = max_2D_radius.data_ptr() if max_2D_radius is not None else None
+        a.seen = seen.data_ptr() if seen is not None else None
         with torch.cuda.device(self.device):
             capi.check(L.as_frame_forward(ctypes.byref(a), torch.cuda.current_stream(self.device).cuda_stream))
         self._args, self._keep = a, keep
@@ -157,8 +159,10 @@ class FrameWorkspace:
                                          torch.cuda.current_stream(self.device).cuda_stream))
         return self.losses
 
-    def backward(self, dL_dpix=None, grad_scale=None, gaussians_grad=True, camera_grad=False, accumulate=False):
-        """as_frame_backward for the last forward.  Returns (grad_params [P,14], grad_cam [8])."""
+    def backward(self, dL_dpix=None, grad_scale=None, gaussians_grad=True, camera_grad=False, accumulate=False,
+                 grad_cam_out=None, grad_cam_stride=1):
+        """as_frame_backward for the last forward.  Returns (grad_params [P,14], grad_cam).
+        grad_cam_out/grad_cam_stride: write the 7 pose gradients at grad_cam_out[k * stride] instead."""
         L = capi.lib()
         b = capi.AsFrameBackwardArgs()
         b.frame = ctypes.pointer(self._args)
@@ -168,13 +172,15 @@ class FrameWorkspace:
         b.gaussians_grad, b.camera_grad = int(bool(gaussians_grad)), int(bool(camera_grad))
         b.grad_params = self.grad_params.data_ptr()
         b.grad_means2D = self.grad_means2D.data_ptr() if self.grad_means2D is not None else None
-        b.grad_cam = self.grad_cam.data_ptr()
+        gc = self.grad_cam if grad_cam_out is None else grad_cam_out
+        b.grad_cam = gc.data_ptr()
+        b.grad_cam_stride = int(grad_cam_stride)
         b.pose_scratch = self.pose_scratch.data_ptr()
         b.accumulate = int(bool(accumulate))
         self._keep.append(dL)
         with torch.cuda.device(self.device):
             capi.check(L.as_frame_backward(ctypes.byref(b), torch.cuda.current_stream(self.device).cuda_stream))
-        return self.grad_params, self.grad_cam
+        return self.grad_params, gc
 
 
 _WORKSPACES = {}
@@ -200,10 +206,10 @@ class _FusedTrackingLoss(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, means3D, rgb, rots, logit_op, log_scales, cam_rots, cam_trans, ws, cam, time_idx, sil_w2c,
-                gt_rgb, gt_depth, w_im, w_depth, sil_thres, use_sil, mask_color):
+                gt_rgb, gt_depth, w_im, w_depth, sil_thres, use_sil, mask_color, max_2D_radius=None, seen=None):
         params = {"means3D": means3D, "rgb_colors": rgb, "unnorm_rotations": rots, "logit_opacities": logit_op,
                   "log_scales": log_scales, "cam_unnorm_rots": cam_rots, "cam_trans": cam_trans}
-        ws.forward(params, cam, time_idx, sil_w2c=sil_w2c)
+        ws.forward(params, cam, time_idx, sil_w2c=sil_w2c, max_2D_radius=max_2D_radius, seen=seen)
         if isinstance(use_sil, str):
             ws.mapping_loss(gt_rgb, gt_depth, w_im, w_depth)
         else:
@@ -220,8 +226,11 @@ class _FusedTrackingLoss(torch.autograd.Function):
         ws = ctx.ws
         # d(total)/d... ; the im/depth components are returned for logging only
         scale = g[0:1].contiguous()
-        gp, gc = ws.backward(grad_scale=scale, gaussians_grad=ctx.gaussians_grad, camera_grad=ctx.camera_grad)
-        outs = [None] * 18
+        T = ctx.shapes[0][-1]
+        gcam = torch.zeros((7, T), dtype=torch.float32, device=g.device) if ctx.camera_grad else None
+        gp, gc = ws.backward(grad_scale=scale, gaussians_grad=ctx.gaussians_grad, camera_grad=ctx.camera_grad,
+                             grad_cam_out=gcam[:, ctx.time_idx:] if gcam is not None else None, grad_cam_stride=T)
+        outs = [None] * 20
         if ctx.gaussians_grad:
             ls_w = ctx.shapes[2]
             views = (gp[:, 0:3], gp[:, 3:6], gp[:, 6:10], gp[:, 10:11], gp[:, 11:11 + ls_w])
@@ -229,11 +238,7 @@ class _FusedTrackingLoss(torch.autograd.Function):
                 if ctx.need[i]:
                     outs[i] = views[i]
         if ctx.camera_grad:
-            g_rot = torch.zeros(ctx.shapes[0], dtype=torch.float32, device=gc.device)
-            g_tr = torch.zeros(ctx.shapes[1], dtype=torch.float32, device=gc.device)
-            g_rot[0, :, ctx.time_idx] = gc[0:4]
-            g_tr[0, :, ctx.time_idx] = gc[4:7]
-            outs[5], outs[6] = g_rot, g_tr
+            outs[5], outs[6] = gcam[0:4].unsqueeze(0), gcam[4:7].unsqueeze(0)
         return tuple(outs)
 
 
@@ -258,7 +263,10 @@ class _FusedFrameRender(torch.autograd.Function):
     def backward(ctx, g_color6, _r, _d, _o):
         ws = ctx.ws
         gaussians_grad, camera_grad = any(ctx.need[:5]), any(ctx.need[5:7])
-        gp, gc = ws.backward(dL_dpix=g_color6, gaussians_grad=gaussians_grad, camera_grad=camera_grad)
+        T = ctx.shapes[0][-1]
+        gcam = torch.zeros((7, T), dtype=torch.float32, device=g_color6.device) if camera_grad else None
+        gp, gc = ws.backward(dL_dpix=g_color6, gaussians_grad=gaussians_grad, camera_grad=camera_grad,
+                             grad_cam_out=gcam[:, ctx.time_idx:] if gcam is not None else None, grad_cam_stride=T)
         outs = [None] * 12
         if gaussians_grad:
             views = (gp[:, 0:3], gp[:, 3:6], gp[:, 6:10], gp[:, 10:11], gp[:, 11:11 + ctx.shapes[2]])
@@ -266,11 +274,7 @@ class _FusedFrameRender(torch.autograd.Function):
                 if ctx.need[i]:
                     outs[i] = views[i]
         if camera_grad:
-            g_rot = torch.zeros(ctx.shapes[0], dtype=torch.float32, device=gc.device)
-            g_tr = torch.zeros(ctx.shapes[1], dtype=torch.float32, device=gc.device)
-            g_rot[0, :, ctx.time_idx] = gc[0:4]
-            g_tr[0, :, ctx.time_idx] = gc[4:7]
-            outs[5], outs[6] = g_rot, g_tr
+            outs[5], outs[6] = gcam[0:4].unsqueeze(0), gcam[4:7].unsqueeze(0)
         return tuple(outs)
 
 
@@ -298,23 +302,24 @@ def identity_pose(device):
 
 
 def fused_tracking_loss(params, cam, time_idx, sil_w2c, gt_rgb, gt_depth, w_im, w_depth, sil_thres,
-                        use_sil_for_loss, mask_color, ws=None):
+                        use_sil_for_loss, mask_color, ws=None, max_2D_radius=None, seen=None):
     """Returns (losses[3] = weighted total / im / depth as a device tensor, workspace)."""
     ws = ws or workspace_for(params, cam)
     out = _FusedTrackingLoss.apply(params["means3D"], params["rgb_colors"], params["unnorm_rotations"],
                                    params["logit_opacities"], params["log_scales"], params["cam_unnorm_rots"],
                                    params["cam_trans"], ws, cam, time_idx, sil_w2c, gt_rgb, gt_depth, w_im, w_depth,
-                                   sil_thres, use_sil_for_loss, mask_color)
+                                   sil_thres, use_sil_for_loss, mask_color, max_2D_radius, seen)
     return out, ws
 
 
-def fused_mapping_loss(params, cam, time_idx, sil_w2c, gt_rgb, gt_depth, w_im, w_depth, ws=None):
+def fused_mapping_loss(params, cam, time_idx, sil_w2c, gt_rgb, gt_depth, w_im, w_depth, ws=None, max_2D_radius=None,
+                       seen=None):
     """Mapping-loss twin of fused_tracking_loss: (losses[3] = weighted total / im / depth, workspace)."""
     ws = ws or workspace_for(params, cam)
     out = _FusedTrackingLoss.apply(params["means3D"], params["rgb_colors"], params["unnorm_rotations"],
                                    params["logit_opacities"], params["log_scales"], params["cam_unnorm_rots"],
                                    params["cam_trans"], ws, cam, time_idx, sil_w2c, gt_rgb, gt_depth, w_im, w_depth,
-                                   0.0, "mapping", False)
+                                   0.0, "mapping", False, max_2D_radius, seen)
     return out, ws
 
 

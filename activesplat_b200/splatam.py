@@ -263,15 +263,15 @@ def _get_loss_tracking_fused(params, curr_data, variables, iter_time_idx, loss_w
     # transform_to_frame(gaussians_grad=False, camera_grad=True): means and rotations are detached,
     # colours / opacities / scales are not (slam_helpers.py:124-139 reads them from `params` directly)
     params = dict(params, means3D=params['means3D'].detach(), unnorm_rotations=params['unnorm_rotations'].detach())
+    seen = _seen_buffer(variables, params)
     out, ws = fused_tracking_loss(params, curr_data['cam'], int(iter_time_idx), curr_data['w2c'], curr_data['im'],
                                   curr_data['depth'], loss_weights['im'], loss_weights['depth'], sil_thres,
-                                  use_sil_for_loss, use_sil_for_loss)
+                                  use_sil_for_loss, use_sil_for_loss, max_2D_radius=_radius_buffer(variables),
+                                  seen=seen)
     loss = out[0]
     weighted_losses = {'depth': out[2], 'im': out[1], 'loss': loss}
-    radius = ws.radii
-    # radius == 0 exactly where the Gaussian was not seen, so this equals the indexed update of splatam.py:296-298
-    variables['max_2D_radius'] = torch.maximum(variables['max_2D_radius'], radius.to(variables['max_2D_radius'].dtype))
-    variables['seen'] = radius > 0
+    # max_2D_radius / seen (splatam.py:296-298) were updated in place by the preprocess kernel
+    variables['seen'] = seen
     variables['means2D'] = None  # screen-space gradient: FrameWorkspace(want_means2D_grad=True).grad_means2D
     return loss, variables, weighted_losses
 
@@ -282,15 +282,28 @@ def _get_loss_mapping_fused(params, curr_data, variables, iter_time_idx, loss_we
     p = dict(params)
     if not camera_grad:
         p['cam_unnorm_rots'], p['cam_trans'] = p['cam_unnorm_rots'].detach(), p['cam_trans'].detach()
+    seen = _seen_buffer(variables, params)
     out, ws = fused_mapping_loss(p, curr_data['cam'], int(iter_time_idx), curr_data['w2c'], curr_data['im'],
-                                 curr_data['depth'], loss_weights['im'], loss_weights['depth'])
+                                 curr_data['depth'], loss_weights['im'], loss_weights['depth'],
+                                 max_2D_radius=_radius_buffer(variables), seen=seen)
     loss = out[0]
     weighted_losses = {'depth': out[2], 'im': out[1], 'loss': loss}
-    radius = ws.radii
-    variables['max_2D_radius'] = torch.maximum(variables['max_2D_radius'], radius.to(variables['max_2D_radius'].dtype))
-    variables['seen'] = radius > 0
+    variables['seen'] = seen
     variables['means2D'] = None
     return loss, variables, weighted_losses
+
+
+def _radius_buffer(variables):
+    r = variables.get('max_2D_radius')
+    return r if (r is not None and r.dtype == torch.float32 and r.is_contiguous()) else None
+
+
+def _seen_buffer(variables, params):
+    s = variables.get('seen')
+    n = params['means3D'].shape[0]
+    if s is None or s.dtype != torch.bool or s.shape[0] != n or s.device != params['means3D'].device:
+        s = torch.zeros(n, dtype=torch.bool, device=params['means3D'].device)
+    return s
 
 
 def initialize_optimizer(params, lrs_dict, tracking):

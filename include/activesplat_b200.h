@@ -171,6 +171,8 @@ typedef struct AsFrameArgs {
     float* out_opacity;            /* [1,H,W] */
     int* radii;                    /* [P] or NULL */
     int debug;
+    float* max_2D_radius;          /* [P] or NULL: updated in place, max(radius, .) where seen (splatam.py:296-298) */
+    uint8_t* seen;                 /* [P] bool or NULL: radius > 0 */
 } AsFrameArgs;
 
 typedef struct AsFrameBackwardArgs {
@@ -181,9 +183,10 @@ typedef struct AsFrameBackwardArgs {
     int camera_grad;               /* transform_to_frame(camera_grad=...) */
     float* grad_params;            /* [P,14] flat: means 3 | rgb 3 | rotation 4 | logit opacity 1 | log scales 3 */
     float* grad_means2D;           /* [P,3] or NULL (NDC-unit screen gradient used by densification) */
-    float* grad_cam;               /* [8]: d/d cam_unnorm_rot (4) | d/d cam_trans (3) | 0 */
+    float* grad_cam;               /* 7 values, element k at grad_cam[k*grad_cam_stride]: d/d cam_unnorm_rot (4) | d/d cam_trans (3) */
     float* pose_scratch;           /* as_pose_scratch_floats(P) device floats (per-block partial sums; no init needed) */
     int accumulate;                /* non-zero: grad_params += (keyframe-batch accumulation) instead of = */
+    int grad_cam_stride;           /* 0 or 1 = packed */
 } AsFrameBackwardArgs;
 
 size_t as_pose_scratch_floats(int P);
