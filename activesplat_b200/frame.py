@@ -350,3 +350,30 @@ class FusedAdam:
                                       p["log_scales"].data_ptr(), grad_flat.data_ptr(), self.exp_avg.data_ptr(),
                                       self.exp_avg_sq.data_ptr(), self.lrs, self.betas[0], self.betas[1], self.eps,
                                       self.t, torch.cuda.current_stream(dev).cuda_stream))
+
+
+class GraphedStep:
+    """Replays a fixed step (e.g. `get_loss(...)` + `backward()` for one keyframe) as ONE CUDA graph launch.
+
+    The fused frame path never synchronises with the host and allocates nothing of its own, so the ~25
+    kernels of a step can be captured once and replayed; that removes the launch gaps between the many
+    short kernels (scan, sort passes, gather, loss).  `fn` must read its inputs from tensors that stay alive
+    and in place (update them with copy_ before a replay); its outputs are overwritten by every replay.
+    """
+
+    def __init__(self, fn, warmup=2):
+        cur = torch.cuda.current_stream()
+        side = torch.cuda.Stream()
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                fn()
+        cur.wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.out = fn()
+
+    def __call__(self):
+        self.graph.replay()
+        return self.out
