@@ -489,9 +489,11 @@ frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const
 // per-block pose partials [nblocks,16] -> gradients of cam_unnorm_rot (4) and cam_trans (3).
 __global__ void __launch_bounds__(256)
 pose_finalize_kernel(const float* __restrict__ cam_rot, int rs, const float* __restrict__ partials, int nblocks,
-                     float* grad_cam, int gstride) {
+                     const uint32_t* __restrict__ status, float* grad_cam, int gstride) {
     __shared__ float s_part[16][17];
     __shared__ float pose_acc[16];
+    // only the first ceil(V/256) blocks of the backward had visible Gaussians; the others wrote zeros
+    nblocks = min(nblocks, (int)((status[2] + FP_THREADS - 1) / FP_THREADS));
     {
         const int k = threadIdx.x & 15, g = threadIdx.x >> 4;  // 16 groups stride over the blocks
         float x = 0.f;
@@ -726,7 +728,7 @@ void launch_frame_preprocess_backward(const AsFrameArgs& a, const GeometryState&
             a.scale_modifier, g.radii, g.zsil, g.vis_list, a.status, g.gacc, gscale, gaussians_grad, camera_grad,
             accumulate, grad_params, grad_means2D, pose_acc);
     if (camera_grad)
-        pose_finalize_kernel<<<1, 256, 0, st>>>(a.cam_unnorm_rot, a.cam_rot_stride, pose_acc, blocks, grad_cam,
+        pose_finalize_kernel<<<1, 256, 0, st>>>(a.cam_unnorm_rot, a.cam_rot_stride, pose_acc, blocks, a.status, grad_cam,
                                                 grad_cam_stride > 0 ? grad_cam_stride : 1);
 }
 
