@@ -628,6 +628,9 @@ __global__ void tracking_loss_finalize_kernel(int nblocks, const float* __restri
         if (status) {  // frame status rides along so that one read-back tells the host everything
             losses[4] = (float)status[0];
             losses[5] = (float)status[1];
+            if (status[1]) {  // binning buffer overflowed: the frame is invalid -- make that impossible to miss
+                losses[0] = CUDART_NAN_F; losses[1] = CUDART_NAN_F; losses[2] = CUDART_NAN_F;
+            }
         }
     }
 }

@@ -12,6 +12,8 @@
 //       (dS/dmu1, dS/dE[x^2], dS/dE[xy]) and per-block partial sums (|d im|, SSIM, |d depth|, mask count);
 //   mapping_loss_grad_kernel  : the same window applied to the three derivative maps (the adjoint of a
 //       symmetric zero-padded window is the window itself) + the L1 terms -> dL/d(colour6).
+#include <math_constants.h>
+
 #include "common.cuh"
 
 namespace asb {
@@ -156,6 +158,9 @@ __global__ void mapping_loss_finalize_kernel(int nblocks, const float* __restric
         if (status) {
             losses[4] = (float)status[0];
             losses[5] = (float)status[1];
+            if (status[1]) {  // binning buffer overflowed: the frame is invalid -- make that impossible to miss
+                losses[0] = CUDART_NAN_F; losses[1] = CUDART_NAN_F; losses[2] = CUDART_NAN_F;
+            }
         }
         losses[6] = ssim;
     }

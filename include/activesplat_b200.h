@@ -196,7 +196,8 @@ int as_frame_backward(const AsFrameBackwardArgs* args, void* cuda_stream);
 /* Tracking loss of get_loss (splatam.py:213-247, use_l1): masked L1 sums and their gradient w.r.t. the
  * six rendered channels, in one sweep.  losses[8] = {weighted total, weighted im, weighted depth, mask count,
  * num_rendered, overflow flag, -, -}; the last two are copied from frame_status (AsFrameArgs.status) when it
- * is not NULL, so one read-back of `losses` tells the host everything about the frame.
+ * is not NULL, so one read-back of `losses` tells the host everything about the frame; if the frame overflowed
+ * its binning buffer, the three loss values are NaN.
  * scratch: as_loss_scratch_floats(w,h) floats.  mask_color: 1 = colour loss uses the depth mask (splatam.py:243-245). */
 size_t as_loss_scratch_floats(int width, int height);
 int as_tracking_loss(int width, int height, const float* color6, const float* gt_rgb, const float* gt_depth,

@@ -424,3 +424,50 @@ def test_render_view_matches_oracle_render():
     helpers.compare_float("median depth", depth.cpu().numpy(), st1["depth"])
     helpers.compare_float("opacity", opacity.cpu().numpy(), st1["opacity"])
     helpers.compare_float("silhouette", sil.cpu().numpy(), st2["color"][1:2])
+
+
+def test_fused_frame_edge_cases():
+    """Fused frame path: image sizes that are not multiples of 16, P not a multiple of 256, a frame in which
+    every Gaussian is culled, and the NaN-loss signal on binning overflow."""
+    from activesplat_b200 import scenes, splatam
+    from activesplat_b200.frame import FrameWorkspace, fused_tracking_loss
+    from oracle import splatam_oracle as so
+    dev = "cuda:0"
+    params, cams = scenes.s_room(1777, 2, 31, W=150, H=100, scale_mult=5.0)
+    rots, trans = scenes.camera_track(cams)
+    params["cam_unnorm_rots"], params["cam_trans"] = rots, trans
+    g = torch.Generator().manual_seed(3)
+    gt_rgb, gt_depth = torch.rand(3, 100, 150, generator=g), torch.rand(1, 100, 150, generator=g) * 5
+    lw = dict(im=0.5, depth=1.0)
+    pc = {k: v.clone().requires_grad_(True) for k, v in params.items()}
+    cam_c = splatam.setup_camera(150, 100, cams[0].k(), np.eye(4), device="cpu")
+    loss_c, wl_c, aux = so.get_loss(pc, {"cam": cam_c, "im": gt_rgb, "depth": gt_depth, "w2c": torch.eye(4)}, 1, lw,
+                                    True, 0.9, True, False, tracking=True)
+    loss_c.backward()
+    pg = {k: v.clone().to(dev).requires_grad_(True) for k, v in params.items()}
+    cam_g = splatam.setup_camera(150, 100, cams[0].k(), np.eye(4), device=dev)
+    cur_g = {"cam": cam_g, "im": gt_rgb.to(dev), "depth": gt_depth.to(dev), "w2c": torch.eye(4, device=dev)}
+    variables = {"max_2D_radius": torch.zeros(1777, device=dev)}
+    loss_g, variables, _ = splatam.get_loss(pg, cur_g, variables, 1, lw, True, 0.9, True, False, tracking=True)
+    loss_g.backward()
+    helpers.compare_float("loss", loss_g.detach().cpu().numpy(), loss_c.detach().numpy(), rel=2e-4)
+    helpers.compare_float("grad cam_trans", pg["cam_trans"].grad.cpu().numpy(), pc["cam_trans"].grad.numpy(), rel=5e-4)
+    helpers.compare_exact("seen", variables["seen"].cpu().numpy(), (aux["radius"] > 0).numpy())
+    helpers.compare_exact("max_2D_radius", variables["max_2D_radius"].cpu().numpy(), aux["radius"].float().numpy())
+    # every Gaussian behind the camera: background image, zero gradients, loss = the GT sums under the mask
+    far = {k: v.detach().clone() for k, v in pg.items()}
+    far["means3D"] = far["means3D"] * 0 + torch.tensor([0.0, 0.0, -50.0], device=dev)
+    far["cam_unnorm_rots"] = torch.tensor([1.0, 0, 0, 0], device=dev).reshape(1, 4, 1).repeat(1, 1, 2).contiguous()
+    far["cam_trans"] = torch.zeros(1, 3, 2, device=dev)
+    ws = FrameWorkspace(1777, 150, 100, dev, capacity=4096)
+    ws.forward(far, cam_g, 0)
+    assert ws.last_status() == (0, False) and int(ws.radii.max()) == 0
+    assert float(ws.color6.abs().max()) == 0.0 and bool((ws.depth == 15.0).all()) and float(ws.opacity.max()) == 0.0
+    ws.tracking_loss(gt_rgb.to(dev), gt_depth.to(dev), 0.5, 1.0, 0.9, False, False)
+    gp, gc = ws.backward(gaussians_grad=True, camera_grad=True)
+    assert float(gp.abs().max()) == 0.0 and float(gc.abs().max()) == 0.0
+    # overflow: the loss turns NaN instead of silently using a truncated instance list
+    small = FrameWorkspace(1777, 150, 100, dev, capacity=64)
+    out, _ = fused_tracking_loss({k: v.detach() for k, v in pg.items()}, cam_g, 1, None, gt_rgb.to(dev),
+                                 gt_depth.to(dev), 0.5, 1.0, 0.9, True, True, ws=small)
+    assert bool(torch.isnan(out).all()) and small.last_status()[1]
