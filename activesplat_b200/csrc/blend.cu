@@ -95,26 +95,31 @@ __device__ __forceinline__ int cull_batch(const BlendSmem<C>& sm, int s, int lim
     return n;
 }
 
-template <int C>
-__global__ void __launch_bounds__(BL_THREADS)
+// WARPS warps per CTA: a CTA blends 2*WARPS pixel rows of one tile, so 8/WARPS CTAs share a tile (each
+// stages the tile's records for itself).  Small images have few tiles; splitting them keeps all SMs busy
+// and spreads a heavy tile over several SMs.  Per-pixel results do not depend on WARPS.
+template <int C, int WARPS>
+__global__ void __launch_bounds__(32 * WARPS)
 blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict__ inst_conic,
                      const float4* __restrict__ inst_geom, const float4* __restrict__ inst_feat, int W, int H,
                      int gx, const float* __restrict__ bg, float* __restrict__ out_color,
                      float* __restrict__ out_depth, float* __restrict__ out_opacity, float* __restrict__ final_T,
                      uint32_t* __restrict__ n_contrib) {
     constexpr int FV = BlendSmem<C>::FV;
+    constexpr int NT = 32 * WARPS, PARTS = (BL_THREADS / 32) / WARPS;
     __shared__ __align__(128) BlendSmem<C> sm;
-    __shared__ uint8_t s_list[BL_THREADS / 32][BL_BATCH];
-    const int tile = blockIdx.x;
+    __shared__ uint8_t s_list[WARPS][BL_BATCH];
+    const int tile = blockIdx.x / PARTS;
     const int tx = tile % gx, ty = tile / gx;
-    const int px = tx * TILE_X + (threadIdx.x & (TILE_X - 1));
-    const int py = ty * TILE_Y + (threadIdx.x / TILE_X);
+    const int lane = threadIdx.x & 31;
+    const int strip = (blockIdx.x % PARTS) * WARPS + (threadIdx.x >> 5);  // which 16x2 strip of the tile
+    const int px = tx * TILE_X + (lane & (TILE_X - 1));
+    const int py = ty * TILE_Y + 2 * strip + (lane >> 4);
     const bool inside = px < W && py < H;
     const float pxf = (float)px, pyf = (float)py;
-    const int lane = threadIdx.x & 31;
-    // this warp's pixels: columns [tile x0, +15], rows 2w and 2w+1
+    // this warp's pixels: columns [tile x0, +15], rows 2*strip and 2*strip+1
     const float strip_x0 = (float)(tx * TILE_X);
-    const float strip_yc = (float)(ty * TILE_Y + 2 * (threadIdx.x >> 5)) + 0.5f;
+    const float strip_yc = (float)(ty * TILE_Y + 2 * strip) + 0.5f;
     const uint2 range = ranges[tile];
     const int len = (int)(range.y - range.x);
     const int nb = (len + BL_BATCH - 1) / BL_BATCH;
@@ -208,7 +213,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
         }
         consumed = b + 1;
         // all 256 pixels finished => stop (forward.cu:315-317); the barrier also frees stage s for reuse
-        if (__syncthreads_count(done) == BL_THREADS) break;
+        if (__syncthreads_count(done) == NT) break;
         if (threadIdx.x == 0 && b + 2 < nb) {
             const int nstart = (b + 2) * BL_BATCH;
             issue_batch<C>(sm, s, inst_conic, inst_geom, inst_feat, range.x + nstart, min(BL_BATCH, len - nstart));
@@ -268,8 +273,8 @@ __device__ __forceinline__ void warp_transpose_reduce16(float (&v)[16], int lane
 
 constexpr int BW_UNROLL = 4;  // records whose alpha is evaluated together in the backward
 
-template <int C>
-__global__ void __launch_bounds__(BL_THREADS)
+template <int C, int WARPS>
+__global__ void __launch_bounds__(32 * WARPS)
 blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict__ inst_conic,
                       const float4* __restrict__ inst_geom, const float4* __restrict__ inst_feat, int W, int H,
                       int gx, const float* __restrict__ bg, const float* __restrict__ final_Ts,
@@ -277,21 +282,23 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
                       float* __restrict__ gacc) {
     constexpr int FV = BlendSmem<C>::FV;
     constexpr int NV = 6 + C;  // live gradient terms per (pixel, Gaussian)
+    constexpr int NT = 32 * WARPS, PARTS = (BL_THREADS / 32) / WARPS;
     __shared__ __align__(128) BlendSmem<C> sm;
     __shared__ __align__(16) float s_acc[BL_BATCH * 16];
-    __shared__ uint8_t s_list[BL_THREADS / 32][BL_BATCH];
+    __shared__ uint8_t s_list[WARPS][BL_BATCH];
     __shared__ int s_max_contrib;
 
-    const int tile = blockIdx.x;
+    const int tile = blockIdx.x / PARTS;
     const int tx = tile % gx, ty = tile / gx;
-    const int px = tx * TILE_X + (threadIdx.x & (TILE_X - 1));
-    const int py = ty * TILE_Y + (threadIdx.x / TILE_X);
+    const int lane = threadIdx.x & 31;
+    const int strip = (blockIdx.x % PARTS) * WARPS + (threadIdx.x >> 5);
+    const int px = tx * TILE_X + (lane & (TILE_X - 1));
+    const int py = ty * TILE_Y + 2 * strip + (lane >> 4);
     const bool inside = px < W && py < H;
     const float pxf = (float)px, pyf = (float)py;
     const size_t pix_id = (size_t)W * py + px;
-    const int lane = threadIdx.x & 31;
     const float strip_x0 = (float)(tx * TILE_X);
-    const float strip_yc = (float)(ty * TILE_Y + 2 * (threadIdx.x >> 5)) + 0.5f;
+    const float strip_yc = (float)(ty * TILE_Y + 2 * strip) + 0.5f;
     const uint2 range = ranges[tile];
 
     const float T_final = inside ? final_Ts[pix_id] : 0.f;
@@ -343,7 +350,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
         // clear the batch accumulator (16 floats per instance)
         {
             float4* a4 = reinterpret_cast<float4*>(s_acc);
-            for (int i = threadIdx.x; i < cnt * 4; i += BL_THREADS) a4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int i = threadIdx.x; i < cnt * 4; i += NT) a4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         mbar_wait(&sm.bar[s], (uint32_t)((b >> 1) & 1));
         __syncthreads();
@@ -426,9 +433,9 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
         }
         __syncthreads();
         // flush: two threads per instance; 3 (C=6) or 2.25 (C=3) vector reductions per touched instance
-        {
-            const int inst = threadIdx.x >> 1, half = threadIdx.x & 1;
-            if (inst < cnt) {
+        for (int i = threadIdx.x; i < 2 * cnt; i += NT) {
+            const int inst = i >> 1, half = i & 1;
+            {
                 const uint32_t id = __float_as_uint(sm.geom[s][inst].w);
                 float* dst = gacc + (size_t)id * GACC_STRIDE;
                 const float4* a4 = reinterpret_cast<const float4*>(s_acc + inst * 16);
@@ -452,32 +459,67 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
 
 }  // namespace
 
+// Warps per CTA: whole tiles (8 warps) when there are plenty of tiles, finer splits for small images.
+static int pick_warps(int tiles) {
+    if (tiles >= 3 * NUM_SMS) return 8;
+    if (tiles * 2 >= 3 * NUM_SMS) return 4;
+    if (tiles * 4 >= 3 * NUM_SMS) return 2;
+    return 1;
+}
+
+template <int C>
+static void launch_fwd_c(int warps, int tiles, cudaStream_t st, const uint2* ranges, const BinningState& b, int W, int H,
+                         int gx, const float* bg, float* out_color, float* out_depth, float* out_opacity,
+                         float* final_T, uint32_t* n_contrib) {
+#define ASB_FWD(WP)                                                                                              \
+    blend_forward_kernel<C, WP><<<tiles*(8 / WP), 32 * WP, 0, st>>>(ranges, b.inst_conic, b.inst_geom, b.inst_feat, W, \
+                                                                    H, gx, bg, out_color, out_depth, out_opacity,    \
+                                                                    final_T, n_contrib)
+    if (warps == 8) ASB_FWD(8);
+    else if (warps == 4) ASB_FWD(4);
+    else if (warps == 2) ASB_FWD(2);
+    else ASB_FWD(1);
+#undef ASB_FWD
+}
+
+template <int C>
+static void launch_bwd_c(int warps, int tiles, cudaStream_t st, const uint2* ranges, const BinningState& b, int W, int H,
+                         int gx, const float* bg, const float* final_T, const uint32_t* n_contrib,
+                         const float* dL_dpix, float* gacc) {
+#define ASB_BWD(WP)                                                                                               \
+    blend_backward_kernel<C, WP><<<tiles*(8 / WP), 32 * WP, 0, st>>>(ranges, b.inst_conic, b.inst_geom, b.inst_feat, W, \
+                                                                     H, gx, bg, final_T, n_contrib, dL_dpix, gacc)
+    if (warps == 8) ASB_BWD(8);
+    else if (warps == 4) ASB_BWD(4);
+    else if (warps == 2) ASB_BWD(2);
+    else ASB_BWD(1);
+#undef ASB_BWD
+}
+
 void launch_blend_forward(int channels, int W, int H, const uint2* ranges, const BinningState& b, const float* bg,
                           float* out_color, float* out_depth, float* out_opacity, float* final_T,
                           uint32_t* n_contrib, cudaStream_t st) {
     const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
-    if (gx * gy <= 0) return;
+    const int tiles = gx * gy;
+    if (tiles <= 0) return;
+    const int warps = pick_warps(tiles);
     if (channels == 3)
-        blend_forward_kernel<3><<<gx * gy, BL_THREADS, 0, st>>>(ranges, b.inst_conic, b.inst_geom, b.inst_feat, W, H,
-                                                                 gx, bg, out_color, out_depth, out_opacity, final_T,
-                                                                 n_contrib);
+        launch_fwd_c<3>(warps, tiles, st, ranges, b, W, H, gx, bg, out_color, out_depth, out_opacity, final_T, n_contrib);
     else
-        blend_forward_kernel<6><<<gx * gy, BL_THREADS, 0, st>>>(ranges, b.inst_conic, b.inst_geom, b.inst_feat, W, H,
-                                                                 gx, bg, out_color, out_depth, out_opacity, final_T,
-                                                                 n_contrib);
+        launch_fwd_c<6>(warps, tiles, st, ranges, b, W, H, gx, bg, out_color, out_depth, out_opacity, final_T, n_contrib);
 }
 
 void launch_blend_backward(int channels, int W, int H, const uint2* ranges, const BinningState& b, const float* bg,
                            const float* final_T, const uint32_t* n_contrib, const float* dL_dpix, float* gacc,
                            cudaStream_t st) {
     const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
-    if (gx * gy <= 0) return;
+    const int tiles = gx * gy;
+    if (tiles <= 0) return;
+    const int warps = pick_warps(tiles);
     if (channels == 3)
-        blend_backward_kernel<3><<<gx * gy, BL_THREADS, 0, st>>>(ranges, b.inst_conic, b.inst_geom, b.inst_feat, W, H,
-                                                                  gx, bg, final_T, n_contrib, dL_dpix, gacc);
+        launch_bwd_c<3>(warps, tiles, st, ranges, b, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc);
     else
-        blend_backward_kernel<6><<<gx * gy, BL_THREADS, 0, st>>>(ranges, b.inst_conic, b.inst_geom, b.inst_feat, W, H,
-                                                                  gx, bg, final_T, n_contrib, dL_dpix, gacc);
+        launch_bwd_c<6>(warps, tiles, st, ranges, b, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc);
 }
 
 }  // namespace asb
