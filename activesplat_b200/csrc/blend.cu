@@ -26,6 +26,7 @@ namespace {
 
 constexpr int BL_THREADS = TILE_PIX;  // 256
 constexpr int BL_BATCH = 128;
+constexpr int BL_STAGES = 4;  // bulk-copy pipeline depth (power of two): batches b..b+3 are in flight
 constexpr int FW_UNROLL = 8;  // instances whose alpha is evaluated together (ILP); divides BL_BATCH
 
 __device__ __forceinline__ float eval_power(const float4& co, float dx, float dy) {
@@ -37,10 +38,10 @@ __device__ __forceinline__ float eval_power(const float4& co, float dx, float dy
 template <int C>
 struct BlendSmem {
     static constexpr int FV = (C == 3) ? 1 : 2;
-    float4 conic[2][BL_BATCH];
-    float4 geom[2][BL_BATCH];
-    float4 feat[2][BL_BATCH * FV];
-    uint64_t bar[2];
+    float4 conic[BL_STAGES][BL_BATCH];
+    float4 geom[BL_STAGES][BL_BATCH];
+    float4 feat[BL_STAGES][BL_BATCH * FV];
+    uint64_t bar[BL_STAGES];
 };
 
 template <int C>
@@ -125,14 +126,15 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
     const int nb = (len + BL_BATCH - 1) / BL_BATCH;
 
     if (threadIdx.x == 0) {
-        mbar_init(&sm.bar[0], 1);
-        mbar_init(&sm.bar[1], 1);
+#pragma unroll
+        for (int q = 0; q < BL_STAGES; q++) mbar_init(&sm.bar[q], 1);
         mbar_fence_init();
     }
     __syncthreads();
     if (threadIdx.x == 0) {
-        if (nb > 0) issue_batch<C>(sm, 0, inst_conic, inst_geom, inst_feat, range.x, min(BL_BATCH, len));
-        if (nb > 1) issue_batch<C>(sm, 1, inst_conic, inst_geom, inst_feat, range.x + BL_BATCH, min(BL_BATCH, len - BL_BATCH));
+        for (int q = 0; q < BL_STAGES && q < nb; q++)
+            issue_batch<C>(sm, q, inst_conic, inst_geom, inst_feat, range.x + q * BL_BATCH,
+                           min(BL_BATCH, len - q * BL_BATCH));
     }
 
     bool done = !inside;
@@ -145,8 +147,8 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
 
     int consumed = 0;
     for (int b = 0; b < nb; b++) {
-        const int s = b & 1;
-        mbar_wait(&sm.bar[s], (uint32_t)((b >> 1) & 1));
+        const int s = b & (BL_STAGES - 1);
+        mbar_wait(&sm.bar[s], (uint32_t)((b / BL_STAGES) & 1));
         const int cnt = min(BL_BATCH, len - b * BL_BATCH);
         // The per-pixel loop of forward.cu:332-381, restructured so that the warp stays converged:
         // (0) the warp drops the records whose ellipse cannot reach its strip,
@@ -214,13 +216,16 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
         consumed = b + 1;
         // all 256 pixels finished => stop (forward.cu:315-317); the barrier also frees stage s for reuse
         if (__syncthreads_count(done) == NT) break;
-        if (threadIdx.x == 0 && b + 2 < nb) {
-            const int nstart = (b + 2) * BL_BATCH;
+        if (threadIdx.x == 0 && b + BL_STAGES < nb) {
+            const int nstart = (b + BL_STAGES) * BL_BATCH;
             issue_batch<C>(sm, s, inst_conic, inst_geom, inst_feat, range.x + nstart, min(BL_BATCH, len - nstart));
         }
     }
-    // a copy that was issued but never consumed must land before this CTA's shared memory is released
-    if (consumed < nb && consumed >= 1) mbar_wait(&sm.bar[consumed & 1], (uint32_t)((consumed >> 1) & 1));
+    // copies that were issued but never consumed must land before this CTA's shared memory is released:
+    // after an early exit at batch consumed-1, batches consumed .. consumed+BL_STAGES-2 are still in flight
+    if (consumed >= 1)
+        for (int q = consumed; q < nb && q < consumed - 1 + BL_STAGES; q++)
+            mbar_wait(&sm.bar[q & (BL_STAGES - 1)], (uint32_t)((q / BL_STAGES) & 1));
 
     if (inside) {
         const size_t pix_id = (size_t)W * py + px;
@@ -307,8 +312,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
 
     if (threadIdx.x == 0) {
         s_max_contrib = 0;
-        mbar_init(&sm.bar[0], 1);
-        mbar_init(&sm.bar[1], 1);
+#pragma unroll
+        for (int q = 0; q < BL_STAGES; q++) mbar_init(&sm.bar[q], 1);
         mbar_fence_init();
     }
     __syncthreads();
@@ -320,13 +325,9 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
     const int nb = (len + BL_BATCH - 1) / BL_BATCH;
     // batch k covers list indices [hi_k - cnt_k, hi_k), hi_k = len - k*BATCH, walked back to front
     if (threadIdx.x == 0) {
-        if (nb > 0) {
-            const int cnt = min(BL_BATCH, len);
-            issue_batch<C>(sm, 0, inst_conic, inst_geom, inst_feat, range.x + (uint32_t)(len - cnt), cnt);
-        }
-        if (nb > 1) {
-            const int hi = len - BL_BATCH, cnt = min(BL_BATCH, hi);
-            issue_batch<C>(sm, 1, inst_conic, inst_geom, inst_feat, range.x + (uint32_t)(hi - cnt), cnt);
+        for (int q = 0; q < BL_STAGES && q < nb; q++) {
+            const int hi = len - q * BL_BATCH, cnt = min(BL_BATCH, hi);
+            issue_batch<C>(sm, q, inst_conic, inst_geom, inst_feat, range.x + (uint32_t)(hi - cnt), cnt);
         }
     }
 
@@ -343,7 +344,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
     const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;  // backward.cu:460-461
 
     for (int b = 0; b < nb; b++) {
-        const int s = b & 1;
+        const int s = b & (BL_STAGES - 1);
         const int hi = len - b * BL_BATCH;
         const int cnt = min(BL_BATCH, hi);
         const int lo = hi - cnt;  // list index of record 0 of this batch
@@ -352,7 +353,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
             float4* a4 = reinterpret_cast<float4*>(s_acc);
             for (int i = threadIdx.x; i < cnt * 4; i += NT) a4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        mbar_wait(&sm.bar[s], (uint32_t)((b >> 1) & 1));
+        mbar_wait(&sm.bar[s], (uint32_t)((b / BL_STAGES) & 1));
         __syncthreads();
 
         // records at list index >= warp_max are skipped by the whole warp; so are records whose ellipse
@@ -450,8 +451,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
             }
         }
         __syncthreads();
-        if (threadIdx.x == 0 && b + 2 < nb) {
-            const int nhi = len - (b + 2) * BL_BATCH, ncnt = min(BL_BATCH, nhi);
+        if (threadIdx.x == 0 && b + BL_STAGES < nb) {
+            const int nhi = len - (b + BL_STAGES) * BL_BATCH, ncnt = min(BL_BATCH, nhi);
             issue_batch<C>(sm, s, inst_conic, inst_geom, inst_feat, range.x + (uint32_t)(nhi - ncnt), ncnt);
         }
     }
