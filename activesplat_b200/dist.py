@@ -42,20 +42,38 @@ def gather_scores(local_scores, n_total, rank, world, group=None):
     return full
 
 
-def score_views(render_fn, n_views, device="cpu", group=None):
-    """GetOpacity scoring, sharded.  render_fn(view_index) -> opacity image [1,H,W] (or any tensor whose
+def score_views(render_fn, n_views, device="cpu", group=None, n_streams=1):
+    """GetOpacity scoring, sharded.  render_fn(view_index, slot) -> opacity image [1,H,W] (or any tensor whose
     `1 - x` summed is the view's invisibility, src/mapper/splatam/__init__.py:738).  Every rank renders
-    its shard and all ranks receive [n_views, 2] = (sum of invisibility, mean opacity)."""
+    its shard and all ranks receive [n_views, 2] = (sum of invisibility, mean opacity).
+
+    n_streams > 1 (CUDA only): views are issued round-robin on that many streams, `slot` telling render_fn
+    which of its per-stream workspaces to use.  A low-resolution candidate view has few tiles and ends in a
+    long tail on a handful of SMs; with several views in flight the tails overlap instead of idling the GPU.
+    """
     rank, world = world_info(group)
     mine = shard_indices(n_views, rank, world)
-    rows = []
-    for v in mine:
-        op = render_fn(v)
-        rows.append(torch.stack([(1.0 - op).sum(), op.mean()]))
-    if rows:
-        local = torch.stack(rows)
-    else:
-        local = torch.zeros((0, 2), device=device)
+    local = torch.zeros((len(mine), 2), dtype=torch.float32, device=device)
+    use_streams = n_streams > 1 and torch.device(device).type == "cuda"
+    if use_streams:
+        cur = torch.cuda.current_stream(device)
+        streams = [torch.cuda.Stream(device=device) for _ in range(n_streams)]
+        for st in streams:
+            st.wait_stream(cur)
+    for j, v in enumerate(mine):
+        slot = j % n_streams if use_streams else 0
+        if use_streams:
+            with torch.cuda.stream(streams[slot]):
+                op = render_fn(v, slot)
+                local[j, 0] = (1.0 - op).sum()
+                local[j, 1] = op.mean()
+        else:
+            op = render_fn(v, slot)
+            local[j, 0] = (1.0 - op).sum()
+            local[j, 1] = op.mean()
+    if use_streams:
+        for st in streams:
+            cur.wait_stream(st)
     return gather_scores(local, n_views, rank, world, group)
 
 

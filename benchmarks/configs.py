@@ -184,15 +184,17 @@ def cfg4(dev, RefRenderer, args, rank, world):
         if mk:
             fx, fy, cx, cy = scenes.compute_intrinsics(w, h, math.radians(90.0))
             views = [scenes.CameraSpec(w, h, fx, fy, cx, cy, v.w2c) for v in views]
-        ws_holder = {}
+        n_streams = 8
+        from activesplat_b200.frame import FrameWorkspace
+        wss = [FrameWorkspace(P, w, h, dev) for _ in range(n_streams)]
 
-        def render_fn(v):
+        def render_fn(v, slot):
             c = views[v]
-            _, _, opacity, _ = splatam.render_view(params, c.w2c, c.k(), c.width, c.height, ws=ws_holder.get("ws"))
+            _, _, opacity, _ = splatam.render_view(params, c.w2c, c.k(), c.width, c.height, ws=wss[slot])
             return opacity
 
         def run_once(_i):
-            return asd.score_views(render_fn, n_views, device=dev)
+            return asd.score_views(render_fn, n_views, device=dev, n_streams=n_streams)
 
         run_once(0)
         torch.cuda.synchronize(dev)
@@ -209,7 +211,8 @@ def cfg4(dev, RefRenderer, args, rank, world):
             torch.distributed.all_reduce(tt, op=torch.distributed.ReduceOp.MAX)
             dt = float(tt.item())
         res[tag] = {"ours": {"views_per_s": n_views / dt, "mpix_s": n_views * w * h / dt / 1e6,
-                             "mean_invisibility": float(scores[:, 0].mean())}}
+                             "mean_invisibility": float(scores[:, 0].mean()), "streams": n_streams}}
+        del wss
         if RefRenderer and rank == 0 and world == 1:
             def ref_view(v):
                 c = views[v]

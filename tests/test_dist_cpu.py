@@ -16,7 +16,7 @@ def _views_worker(rank, world, port, n_views, q):
     from activesplat_b200 import dist as asd
     calls = []
 
-    def render_fn(v):  # a deterministic stand-in for the per-view opacity image
+    def render_fn(v, slot=0):  # a deterministic stand-in for the per-view opacity image
         calls.append(v)
         g = torch.Generator().manual_seed(1000 + v)
         return torch.rand(1, 15, 12, generator=g)
