@@ -388,7 +388,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
 #pragma unroll
                 for (int u = 0; u < BW_UNROLL; u++) {
                     const bool active = act & (1u << u);
-                    if (!__any_sync(0xffffffffu, active)) continue;
+                    const uint32_t active_lanes = __ballot_sync(0xffffffffu, active);
+                    if (active_lanes == 0) continue;
                     const int j = jj[u];
                     float v[16];
 #pragma unroll
@@ -398,7 +399,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
                         const float4 ge = sm.geom[s][j];
                         const float dx = __fsub_rn(ge.x, pxf), dy = __fsub_rn(ge.y, pyf);
                         const float alpha = al[u], G = Gs[u];
-                        T = T / (1.f - alpha);
+                        const float inv_1ma = 1.f / (1.f - alpha);  // shared by T / (1 - alpha) and the background term
+                        T = T * inv_1ma;
                         const float dchannel_dcolor = alpha * T;
                         const float4 f0 = sm.feat[s][j * FV];
                         const float4 f1 = sm.feat[s][j * FV + FV - 1];
@@ -415,7 +417,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
                         }
                         dL_dalpha *= T;
                         last_alpha = alpha;
-                        dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;  // backward.cu:531-534
+                        dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;  // backward.cu:531-534
                         const float dL_dG = co.w * dL_dalpha;                     // straight-through clamp (:538)
                         const float gdx = G * dx, gdy = G * dy;
                         const float dG_ddelx = -gdx * co.x - gdy * co.y;
