@@ -11,6 +11,7 @@ Same names, arguments and return values as the reference, so the mapper's call s
   get_loss                     src/mapper/splatam/splatam.py:172-301
   calc_ssim                    src/mapper/splatam/utils/slam_external.py:54-97
   initialize_optimizer         src/mapper/splatam/splatam.py:118-124
+  get_pointcloud, initialize_new_params, add_new_gaussians   src/mapper/splatam/splatam.py:25-75, 304-379
 
 What is different underneath: the reference renders every frame twice (RGB pass, then a [z,1,z^2]
 pass over identical geometry, splatam.py:208,212); here both feature sets go through ONE 6-channel
@@ -291,6 +292,95 @@ def _get_loss_mapping_fused(params, curr_data, variables, iter_time_idx, loss_we
     variables['seen'] = seen
     variables['means2D'] = None
     return loss, variables, weighted_losses
+
+
+def get_pointcloud(color, depth, intrinsics, w2c, transform_pts=True, mask=None, compute_mean_sq_dist=False,
+                   mean_sq_dist_method="projective"):
+    """Back-projection of an RGB-D frame (src/mapper/splatam/splatam.py:25-75)."""
+    dev = color.device
+    width, height = color.shape[2], color.shape[1]
+    CX, CY, FX, FY = intrinsics[0][2], intrinsics[1][2], intrinsics[0][0], intrinsics[1][1]
+    x_grid, y_grid = torch.meshgrid(torch.arange(width, device=dev).float(), torch.arange(height, device=dev).float(),
+                                    indexing='xy')
+    xx = ((x_grid - CX) / FX).reshape(-1)
+    yy = ((y_grid - CY) / FY).reshape(-1)
+    depth_z = depth[0].reshape(-1)
+    pts_cam = torch.stack((xx * depth_z, yy * depth_z, depth_z), dim=-1)
+    if transform_pts:
+        pts4 = torch.cat((pts_cam, torch.ones(height * width, 1, device=dev)), dim=1)
+        pts = (torch.inverse(w2c) @ pts4.T).T[:, :3]
+    else:
+        pts = pts_cam
+    if compute_mean_sq_dist:
+        if mean_sq_dist_method != "projective":
+            raise ValueError(f"Unknown mean_sq_dist_method {mean_sq_dist_method}")
+        mean3_sq_dist = (depth_z / ((FX + FY) / 2)) ** 2
+    cols = torch.permute(color, (1, 2, 0)).reshape(-1, 3)
+    point_cld = torch.cat((pts, cols), -1)
+    if mask is not None:
+        point_cld = point_cld[mask]
+        if compute_mean_sq_dist:
+            mean3_sq_dist = mean3_sq_dist[mask]
+    return (point_cld, mean3_sq_dist) if compute_mean_sq_dist else point_cld
+
+
+def initialize_new_params(new_pt_cld, mean3_sq_dist, gaussian_distribution):
+    """splatam.py:304-329."""
+    num_pts, dev = new_pt_cld.shape[0], new_pt_cld.device
+    unnorm_rots = torch.zeros((num_pts, 4), device=dev)
+    unnorm_rots[:, 0] = 1.0
+    if gaussian_distribution == "isotropic":
+        log_scales = torch.tile(torch.log(torch.sqrt(mean3_sq_dist))[..., None], (1, 1))
+    elif gaussian_distribution == "anisotropic":
+        log_scales = torch.tile(torch.log(torch.sqrt(mean3_sq_dist))[..., None], (1, 3))
+    else:
+        raise ValueError(f"Unknown gaussian_distribution {gaussian_distribution}")
+    params = {'means3D': new_pt_cld[:, :3], 'rgb_colors': new_pt_cld[:, 3:6], 'unnorm_rotations': unnorm_rots,
+              'logit_opacities': torch.zeros((num_pts, 1), dtype=torch.float, device=dev), 'log_scales': log_scales}
+    return {k: torch.nn.Parameter(v.float().contiguous().requires_grad_(True)) for k, v in params.items()}
+
+
+def add_new_gaussians(params, variables, curr_data, sil_thres, time_idx, mean_sq_dist_method, gaussian_distribution):
+    """Silhouette-driven densification (splatam.py:332-379): render the depth/silhouette of the current map
+    at the frame's pose, find pixels the map does not explain, back-project them as new Gaussians.
+    The render is one fused forward from the raw parameters (no gradients)."""
+    from .frame import fused_render
+    dev = params['means3D'].device
+    with torch.no_grad():
+        p = {k: v.detach() for k, v in params.items()}
+        c6, _, _, _, _ = fused_render(p, curr_data['cam'], int(time_idx), curr_data['w2c'])
+    depth_sil = c6[3:]
+    silhouette = depth_sil[1, :, :]
+    non_presence_sil_mask = (silhouette < sil_thres)
+    gt_depth = curr_data['depth'][0, :, :]
+    render_depth = depth_sil[0, :, :]
+    depth_error = torch.abs(gt_depth - render_depth) * (gt_depth > 0)
+    non_presence_depth_mask = (render_depth > gt_depth) * (depth_error > 2 * depth_error.median())
+    presence_sil_mask = (silhouette > sil_thres)
+    good_depth_mask = presence_sil_mask * (gt_depth < 5)
+    non_presence_depth_mask = non_presence_depth_mask & good_depth_mask
+    non_presence_mask = (non_presence_sil_mask | non_presence_depth_mask).reshape(-1)
+    if torch.sum(non_presence_mask) > 0:
+        curr_cam_rot = F.normalize(params['cam_unnorm_rots'][..., time_idx].detach())
+        curr_cam_tran = params['cam_trans'][..., time_idx].detach()
+        curr_w2c = torch.eye(4, device=dev)
+        curr_w2c[:3, :3] = build_rotation(curr_cam_rot)
+        curr_w2c[:3, 3] = curr_cam_tran
+        valid_depth_mask = (curr_data['depth'][0, :, :] > 0)
+        non_presence_mask = non_presence_mask & valid_depth_mask.reshape(-1)
+        new_pt_cld, mean3_sq_dist = get_pointcloud(curr_data['im'], curr_data['depth'], curr_data['intrinsics'], curr_w2c,
+                                                   mask=non_presence_mask, compute_mean_sq_dist=True,
+                                                   mean_sq_dist_method=mean_sq_dist_method)
+        new_params = initialize_new_params(new_pt_cld, mean3_sq_dist, gaussian_distribution)
+        for k, v in new_params.items():
+            params[k] = torch.nn.Parameter(torch.cat((params[k], v), dim=0).requires_grad_(True))
+        num_pts = params['means3D'].shape[0]
+        variables['means2D_gradient_accum'] = torch.zeros(num_pts, device=dev).float()
+        variables['denom'] = torch.zeros(num_pts, device=dev).float()
+        variables['max_2D_radius'] = torch.zeros(num_pts, device=dev).float()
+        new_timestep = time_idx * torch.ones(new_pt_cld.shape[0], device=dev).float()
+        variables['timestep'] = torch.cat((variables['timestep'], new_timestep), dim=0)
+    return params, variables
 
 
 def _radius_buffer(variables):

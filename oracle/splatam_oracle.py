@@ -185,3 +185,51 @@ def get_loss(params, curr_data, iter_time_idx, loss_weights, use_sil_for_loss, s
     loss = sum(weighted.values())
     weighted['loss'] = loss
     return loss, weighted, dict(im=im, depth_sil=depth_sil, radius=radius)
+
+
+def get_pointcloud(color, depth, intrinsics, w2c, mask=None):
+    """splatam.py:25-75 (transform_pts=True, projective mean-squared distance)."""
+    width, height = color.shape[2], color.shape[1]
+    CX, CY, FX, FY = intrinsics[0][2], intrinsics[1][2], intrinsics[0][0], intrinsics[1][1]
+    x_grid, y_grid = torch.meshgrid(torch.arange(width).float(), torch.arange(height).float(), indexing='xy')
+    xx = ((x_grid - CX) / FX).reshape(-1)
+    yy = ((y_grid - CY) / FY).reshape(-1)
+    depth_z = depth[0].reshape(-1)
+    pts_cam = torch.stack((xx * depth_z, yy * depth_z, depth_z), dim=-1)
+    pts4 = torch.cat((pts_cam, torch.ones(height * width, 1)), dim=1)
+    pts = (torch.inverse(w2c) @ pts4.T).T[:, :3]
+    mean3_sq_dist = (depth_z / ((FX + FY) / 2)) ** 2
+    point_cld = torch.cat((pts, torch.permute(color, (1, 2, 0)).reshape(-1, 3)), -1)
+    if mask is not None:
+        point_cld, mean3_sq_dist = point_cld[mask], mean3_sq_dist[mask]
+    return point_cld, mean3_sq_dist
+
+
+def add_new_gaussians(params, curr_data, sil_thres, time_idx, gaussian_distribution, Renderer=Renderer):
+    """splatam.py:332-379.  Returns (non_presence_mask [H*W] bool, new parameter dict or None)."""
+    tg = transform_to_frame(params, time_idx, gaussians_grad=False, camera_grad=False)
+    drv = transformed_params2depthplussilhouette(params, curr_data['w2c'], tg)
+    with torch.no_grad():
+        depth_sil, _, _, _ = Renderer(curr_data['cam'])(**{k: v.detach() for k, v in drv.items()})
+    silhouette = depth_sil[1, :, :]
+    gt_depth = curr_data['depth'][0, :, :]
+    render_depth = depth_sil[0, :, :]
+    depth_error = torch.abs(gt_depth - render_depth) * (gt_depth > 0)
+    non_presence_depth_mask = (render_depth > gt_depth) * (depth_error > 2 * depth_error.median())
+    good_depth_mask = (silhouette > sil_thres) * (gt_depth < 5)
+    non_presence_mask = ((silhouette < sil_thres) | (non_presence_depth_mask & good_depth_mask)).reshape(-1)
+    if torch.sum(non_presence_mask) == 0:
+        return non_presence_mask, None
+    cam_rot = F.normalize(params['cam_unnorm_rots'][..., time_idx].detach())
+    w2c = torch.eye(4)
+    w2c[:3, :3] = build_rotation(cam_rot)
+    w2c[:3, 3] = params['cam_trans'][..., time_idx].detach()
+    non_presence_mask = non_presence_mask & (gt_depth > 0).reshape(-1)
+    pt, msd = get_pointcloud(curr_data['im'], curr_data['depth'], curr_data['intrinsics'], w2c, mask=non_presence_mask)
+    n = pt.shape[0]
+    rots = torch.zeros(n, 4)
+    rots[:, 0] = 1.0
+    reps = 1 if gaussian_distribution == "isotropic" else 3
+    new = {'means3D': pt[:, :3], 'rgb_colors': pt[:, 3:6], 'unnorm_rotations': rots,
+           'logit_opacities': torch.zeros(n, 1), 'log_scales': torch.tile(torch.log(torch.sqrt(msd))[..., None], (1, reps))}
+    return non_presence_mask, new

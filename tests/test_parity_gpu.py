@@ -228,9 +228,9 @@ def test_full_size_properties_cfg1():
 # ------------------------------------------------------------------------------------------------
 # fused SplaTAM frame step vs the CPU oracle of the reference's torch code (two passes, autograd)
 # ------------------------------------------------------------------------------------------------
-def _frame_case(P=3000, W=128, H=96, K=3, seed=7, iso=False):
+def _frame_case(P=3000, W=128, H=96, K=3, seed=7, iso=False, scale_mult=6.0):
     from activesplat_b200 import scenes
-    params, cams = scenes.s_room(P, K, seed, W=W, H=H, scale_mult=6.0)
+    params, cams = scenes.s_room(P, K, seed, W=W, H=H, scale_mult=scale_mult)
     if iso:
         params["log_scales"] = params["log_scales"][:, :1].contiguous()
     rots, trans = scenes.camera_track(cams)
@@ -522,3 +522,36 @@ def test_full_size_matches_reference_build_live(size):
         # the reference sums ~10^2-10^4 atomics per Gaussian in arbitrary order: compare at 1e-4 of the scale,
         # allowing a small fraction of large-cancellation entries
         helpers.compare_float("grad_" + k, grads[k], r["grad_" + k], rel=1e-4, flip_fraction=2e-3, flip_bound=5e-2)
+
+
+def test_add_new_gaussians_matches_oracle():
+    """Silhouette-driven densification (splatam.py:332-379), SURVEY 8f rank 1: same new Gaussians as the oracle."""
+    from activesplat_b200 import splatam
+    from oracle import splatam_oracle as so
+    params, cams, gt_rgb, gt_depth = _frame_case(P=1500, W=96, H=80, seed=41, scale_mult=2.0)  # map with holes
+    gt_depth = gt_depth * 0.6 + 0.4
+    gt_depth[0, 30:50, 20:60] = 0.5   # a new foreground object in front of the mapped surface
+    gt_depth[0, :5, :] = 0.0          # invalid depth
+    W, H, t_idx = cams[0].width, cams[0].height, 1
+    k = torch.tensor(cams[0].k()).float()
+    cam_c = splatam.setup_camera(W, H, cams[0].k(), np.eye(4), device="cpu")
+    cur_c = {"cam": cam_c, "im": gt_rgb, "depth": gt_depth, "w2c": torch.eye(4), "intrinsics": k}
+    mask_c, new_c = so.add_new_gaussians({k_: v.clone() for k_, v in params.items()}, cur_c, 0.5, t_idx, "anisotropic")
+    dev = "cuda:0"
+    pg = {k_: torch.nn.Parameter(v.clone().to(dev)) for k_, v in params.items()}
+    cam_g = splatam.setup_camera(W, H, cams[0].k(), np.eye(4), device=dev)
+    cur_g = {"cam": cam_g, "im": gt_rgb.to(dev), "depth": gt_depth.to(dev), "w2c": torch.eye(4, device=dev),
+             "intrinsics": k.to(dev)}
+    variables = {"timestep": torch.zeros(1500, device=dev), "max_2D_radius": torch.zeros(1500, device=dev)}
+    P0 = 1500
+    pg, variables = splatam.add_new_gaussians(pg, variables, cur_g, 0.5, t_idx, "projective", "anisotropic")
+    n_new = pg["means3D"].shape[0] - P0
+    assert new_c is not None and n_new > 100
+    # a pixel whose silhouette sits within rounding of the threshold may flip; everything else must agree
+    assert abs(n_new - new_c["means3D"].shape[0]) <= max(2, int(1e-3 * n_new))
+    if n_new == new_c["means3D"].shape[0]:
+        for k_ in ("means3D", "rgb_colors", "unnorm_rotations", "logit_opacities", "log_scales"):
+            helpers.compare_float("new " + k_, pg[k_][P0:].detach().cpu().numpy(), new_c[k_].numpy(), rel=1e-5)
+            helpers.compare_exact("old " + k_, pg[k_][:P0].detach().cpu().numpy(), params[k_].numpy())
+    assert variables["timestep"].shape[0] == P0 + n_new and float(variables["timestep"][P0:].min()) == t_idx
+    assert variables["max_2D_radius"].shape[0] == P0 + n_new and pg["means3D"].requires_grad
