@@ -150,7 +150,15 @@ def cfg3(dev, RefRenderer, args):
     ms = timeit(ours, iters, 5, dev)
     n_inst, over = ws.last_status()
     assert not over
-    res["ours"] = {"ms_per_iter": ms, "mpix_s": W * H / ms / 1e3, "instances": n_inst}
+    from activesplat_b200 import capi
+    capi.lib().as_profile_enable(1)
+    capi.profile_read()
+    for i in range(10):
+        ours(i)
+    st = capi.profile_read()
+    capi.lib().as_profile_enable(0)
+    res["ours"] = {"ms_per_iter": ms, "mpix_s": W * H / ms / 1e3, "instances": n_inst,
+                   "stage_ms": {k: round(v[0] / 10, 4) for k, v in st.items() if v[1]}}
     if RefRenderer:
         p2 = fresh()
         opt2 = torch.optim.Adam([{"params": [v], "name": k, "lr": MAP_LRS[k]} for k, v in p2.items()], lr=0.0, eps=1e-15)
@@ -167,8 +175,9 @@ def cfg3(dev, RefRenderer, args):
         drift = {}
         for k in PARAM_ORDER:
             a_, b_ = p[k].detach(), p2[k].detach()
-            drift[k] = float((a_ - b_).abs().max() / ((b_ - params_cpu[k].to(dev)).abs().max() + 1e-12))
-        res["max_param_diff_over_max_update"] = drift
+            upd = b_ - params_cpu[k].to(dev)
+            drift[k] = float((a_ - b_).norm() / (upd.norm() + 1e-12))
+        res["rel_l2_param_diff_over_update"] = drift
     return res
 
 
