@@ -17,6 +17,13 @@ import torch
 
 from . import capi
 
+# Note on non-contiguous inputs: the reference's backward reads `scales` and `rotations` through a bare data_ptr()
+# (dgr/rasterize_points.cu:173,175) although its forward used .contiguous() (:102,:104).  SplaTAM's anisotropic path
+# passes rotations whose memory is column-major (F.normalize of quat_mult's torch.stack([...]).T, slam_helpers.py:28,135),
+# so the stock reference differentiates w.r.t. scrambled quaternions there.  This shim always hands the kernels the
+# values the forward used (what the math says, what the oracle does, and what the reference does for contiguous
+# inputs); see DESIGN.md section 2.1 and tests/test_parity_gpu.py::test_noncontiguous_rotations_*.
+
 
 def _dev_ptr(t, name, keep):
     """Device pointer of an optional tensor; empty tensors mean 'not provided' (rasterizer __init__.py:197-207)."""

@@ -644,28 +644,30 @@ struct AdamPtrs {
     float lr[5];
 };
 
+// One thread per flat element e of the [P,14] gradient / state arrays: those are read and written fully
+// coalesced; the five parameter tensors are touched at neighbouring addresses by neighbouring threads.
 __global__ void __launch_bounds__(256)
 adam_kernel(int P, int iso, AdamPtrs ap, const float* __restrict__ grad, float* __restrict__ m, float* __restrict__ v,
             float beta1, float beta2, float eps, float bc1, float bc2_sqrt) {
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= P) return;
-    const int width[5] = {3, 3, 4, 1, iso ? 1 : 3};
-    const int slot[5] = {0, 3, 6, 10, 11};
-#pragma unroll
-    for (int t = 0; t < 5; t++) {
-        const float step_size = ap.lr[t] / bc1;
-        for (int k = 0; k < width[t]; k++) {
-            const size_t f = 14 * (size_t)idx + slot[t] + k;
-            const float g = grad[f];
-            const float mm = m[f] + (g - m[f]) * (1.f - beta1);        // exp_avg.lerp_(grad, 1 - beta1)
-            const float vv = v[f] * beta2 + (1.f - beta2) * g * g;     // mul_(beta2).addcmul_(g, g, 1 - beta2)
-            m[f] = mm;
-            v[f] = vv;
-            const float denom = sqrtf(vv) / bc2_sqrt + eps;
-            float* p = ap.p[t] + (size_t)width[t] * idx + k;
-            *p = *p - step_size * (mm / denom);                         // addcdiv_(exp_avg, denom, -step_size)
-        }
-    }
+    const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= (size_t)P * 14) return;
+    const int idx = (int)(e / 14), slot = (int)(e - (size_t)idx * 14);
+    // slot -> (tensor, component): means 0-2 | rgb 3-5 | rotation 6-9 | logit opacity 10 | log scales 11-13
+    int t, k, width;
+    if (slot < 3) { t = 0; k = slot; width = 3; }
+    else if (slot < 6) { t = 1; k = slot - 3; width = 3; }
+    else if (slot < 10) { t = 2; k = slot - 6; width = 4; }
+    else if (slot < 11) { t = 3; k = 0; width = 1; }
+    else { t = 4; k = slot - 11; width = iso ? 1 : 3; if (k >= width) return; }  // isotropic: slots 12,13 unused
+    const float g = grad[e];
+    const float mm = m[e] + (g - m[e]) * (1.f - beta1);      // exp_avg.lerp_(grad, 1 - beta1)
+    const float vv = v[e] * beta2 + (1.f - beta2) * g * g;   // mul_(beta2).addcmul_(g, g, 1 - beta2)
+    m[e] = mm;
+    v[e] = vv;
+    const float denom = sqrtf(vv) / bc2_sqrt + eps;
+    const float step_size = ap.lr[t] / bc1;
+    float* p = ap.p[t] + (size_t)width * idx + k;
+    *p = *p - step_size * (mm / denom);                       // addcdiv_(exp_avg, denom, -step_size)
 }
 
 }  // namespace
@@ -760,7 +762,8 @@ void launch_adam(int P, int iso, float* const params[5], const float lr[5], cons
     }
     const float bc1 = 1.f - powf(beta1, (float)step);
     const float bc2_sqrt = sqrtf(1.f - powf(beta2, (float)step));
-    adam_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, iso, ap, grad, m, v, beta1, beta2, eps, bc1, bc2_sqrt);
+    const size_t n = (size_t)P * 14;
+    adam_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(P, iso, ap, grad, m, v, beta1, beta2, eps, bc1, bc2_sqrt);
 }
 
 }  // namespace asb

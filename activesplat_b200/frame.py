@@ -53,12 +53,13 @@ class FrameWorkspace:
         self._keep = None
         self._bg_src = None
         self.map_scratch = None
+        self.calibrated = capacity is not None  # an explicit capacity is taken as is
 
     # -- buffer management ---------------------------------------------------------------------
     def ensure_capacity(self, needed):
         if needed <= self.capacity:
             return False
-        self.capacity = int(needed * 1.25) + 1024
+        self.capacity = int(needed) + 1024
         with torch.cuda.device(self.device):
             self.binning = torch.empty(capi.lib().as_binning_bytes(self.capacity, 6), dtype=torch.uint8,
                                        device=self.device)
@@ -116,7 +117,17 @@ class FrameWorkspace:
         a.max_2D_radius = max_2D_radius.data_ptr() if max_2D_radius is not None else None
         a.seen = seen.data_ptr() if seen is not None else None
         with torch.cuda.device(self.device):
-            capi.check(L.as_frame_forward(ctypes.byref(a), torch.cuda.current_stream(self.device).cuda_stream))
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+            capi.check(L.as_frame_forward(ctypes.byref(a), stream))
+            if not self.calibrated and not torch.cuda.is_current_stream_capturing():
+                # first frame of this workspace: ONE synchronising look at the instance count sizes the binning
+                # buffer with head-room (2x); after that the path never synchronises and an overflow shows up as
+                # a NaN loss / last_status()
+                self.calibrated = True
+                n, _ = self.last_status()
+                if self.ensure_capacity(2 * n):
+                    a.binning_buffer, a.binning_capacity = self.binning.data_ptr(), self.capacity
+                    capi.check(L.as_frame_forward(ctypes.byref(a), stream))
         self._args, self._keep = a, keep
         return self.color6, self.radii, self.depth, self.opacity
 

@@ -32,8 +32,14 @@ MAP_LRS = dict(means3D=1e-4, rgb_colors=2.5e-3, unnorm_rotations=1e-3, logit_opa
                cam_unnorm_rots=0.0, cam_trans=0.0)  # config/splatam/online_habitat_sim.py:61-69
 
 
-def load_ref_renderer():
-    """GaussianRasterizer-shaped class bound to the reference's _C (None if the build is absent)."""
+def load_ref_renderer(contiguous_inputs=False):
+    """GaussianRasterizer-shaped class bound to the reference's _C (None if the build is absent).
+
+    contiguous_inputs=True makes scales/rotations contiguous before the call.  The stock reference reads them
+    with .contiguous() in its forward (dgr/rasterize_points.cu:102,104) but with a bare data_ptr() in its backward
+    (:173,:175); SplaTAM's anisotropic path hands it rotations = F.normalize(quat_mult(...)) whose memory is
+    column-major (quat_mult ends in torch.stack([...]).T, slam_helpers.py:28), so the stock backward computes
+    dL/dscale and dL/drot from scrambled quaternions.  Our kernels (and the oracle) use the values the forward used."""
     path = os.path.join(ROOT, "oracle", "_ref", "ref_dgr_C.so")
     if not os.path.exists(path):
         return None
@@ -49,6 +55,8 @@ def load_ref_renderer():
             self.rs = raster_settings
 
         def __call__(self, means3D, means2D, opacities, colors_precomp, scales, rotations):
+            if contiguous_inputs:
+                scales, rotations = scales.contiguous(), rotations.contiguous()
             return fn.apply(means3D, means2D, e, colors_precomp, opacities, scales, rotations, e, self.rs)
 
     return RefRenderer
@@ -171,6 +179,20 @@ def cfg3(dev, RefRenderer, args):
 
         ms = timeit(ref, iters, 5, dev)
         res["ref_cuda"] = {"ms_per_iter": ms, "mpix_s": W * H / ms / 1e3}
+        # a second, identical run of the reference: its float atomics are unordered, and Adam with eps 1e-15
+        # turns every noise-level gradient into a full-size step, so the reference does not reproduce itself
+        p3 = fresh()
+        opt3 = torch.optim.Adam([{"params": [v], "name": k, "lr": MAP_LRS[k]} for k, v in p3.items()], lr=0.0, eps=1e-15)
+
+        def ref_again(i):
+            loss, _, _ = so.get_loss(p3, cur, 0, LW, False, 0.98, True, False, mapping=True, Renderer=RefRenderer)
+            loss.backward()
+            opt3.step()
+            opt3.zero_grad(set_to_none=True)
+
+        timeit(ref_again, iters, 5, dev)
+        res["ref_vs_ref_rel_l2"] = {k: float((p3[k].detach() - p2[k].detach()).norm() /
+                                             ((p2[k].detach() - params_cpu[k].to(dev)).norm() + 1e-12)) for k in PARAM_ORDER}
         # parameter drift between the two after the same number of steps (both started from the same map)
         drift = {}
         for k in PARAM_ORDER:
