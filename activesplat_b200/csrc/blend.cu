@@ -27,7 +27,10 @@ namespace {
 constexpr int BL_THREADS = TILE_PIX;  // 256
 constexpr int BL_BATCH = 128;
 constexpr int BL_STAGES = 4;  // bulk-copy pipeline depth (power of two): batches b..b+3 are in flight
-constexpr int FW_UNROLL = 8;  // instances whose alpha is evaluated together (ILP); divides BL_BATCH
+#ifndef ASB_FW_UNROLL
+#define ASB_FW_UNROLL 4
+#endif
+constexpr int FW_UNROLL = ASB_FW_UNROLL;  // records a lane evaluates together in the forward (ILP)
 
 __device__ __forceinline__ float eval_power(const float4& co, float dx, float dy) {
     // forward.cu:342: -0.5f*(A*dx*dx + C*dy*dy) - B*dx*dy, contracted as nvcc contracts it
@@ -35,20 +38,20 @@ __device__ __forceinline__ float eval_power(const float4& co, float dx, float dy
     return __fmaf_rn(q, -0.5f, -__fmul_rn(__fmul_rn(co.y, dx), dy));
 }
 
-template <int C>
+template <int C, int STAGES = BL_STAGES>
 struct BlendSmem {
     static constexpr int FV = (C == 3) ? 1 : 2;
-    float4 conic[BL_STAGES][BL_BATCH];
-    float4 geom[BL_STAGES][BL_BATCH];
-    float4 feat[BL_STAGES][BL_BATCH * FV];
-    uint64_t bar[BL_STAGES];
+    float4 conic[STAGES][BL_BATCH];
+    float4 geom[STAGES][BL_BATCH];
+    float4 feat[STAGES][BL_BATCH * FV];
+    uint64_t bar[STAGES];
 };
 
-template <int C>
-__device__ __forceinline__ void issue_batch(BlendSmem<C>& sm, int stage, const float4* __restrict__ inst_conic,
+template <class SM>
+__device__ __forceinline__ void issue_batch(SM& sm, int stage, const float4* __restrict__ inst_conic,
                                             const float4* __restrict__ inst_geom,
                                             const float4* __restrict__ inst_feat, uint32_t start, int cnt) {
-    constexpr int FV = BlendSmem<C>::FV;
+    constexpr int FV = SM::FV;
     const uint32_t bytes = (uint32_t)cnt * 16u;
     mbar_expect_tx(&sm.bar[stage], bytes * (2 + FV));
     bulk_g2s(sm.conic[stage], inst_conic + start, bytes, &sm.bar[stage]);
@@ -62,38 +65,64 @@ __device__ __forceinline__ void issue_batch(BlendSmem<C>& sm, int stage, const f
 // ellipse's axis-aligned half-extents (rounded UP, with margin) per instance; a warp whose 16x2-pixel
 // strip lies outside that box skips the instance without evaluating anything.  Skipped pairs would have
 // been skipped by the rules anyway, so images, n_contrib and gradients are unchanged.
-template <int C>
-__device__ __forceinline__ float2 inst_extent(const BlendSmem<C>& sm, int s, int j) {
-    constexpr int FV = BlendSmem<C>::FV;
+template <class SM>
+__device__ __forceinline__ float2 inst_extent(const SM& sm, int s, int j) {
+    constexpr int FV = SM::FV;
     const float4 f = sm.feat[s][j * FV + FV - 1];
-    const uint32_t bits = __float_as_uint(C == 3 ? f.w : f.z);
+    const uint32_t bits = __float_as_uint(FV == 1 ? f.w : f.z);
     const __half2 h = *reinterpret_cast<const __half2*>(&bits);
     return __half22float2(h);
 }
 
-// Compacts the indices of the batch's records that can touch this warp's pixel strip into the warp's
-// private list (ascending record order) and returns how many there are.
-template <int C>
-__device__ __forceinline__ int cull_batch(const BlendSmem<C>& sm, int s, int limit, int lane, float strip_x0,
-                                          float strip_yc, uint8_t* list) {
+// Compacts the batch's records that can touch this warp's pixel strip into the warp's private list
+// (ascending record order) and returns how many there are.  For every kept record it also stores the
+// LANE MASK of the strip's pixels that lie inside the record's box (bit l = pixel of lane l: column l & 15,
+// row l >> 4).  The box is a superset of the pixels that pass the skip rules, so a pixel outside it never
+// needs to look at the record.
+template <class SM>
+__device__ __forceinline__ int cull_batch(const SM& sm, int s, int limit, int lane, float strip_x0,
+                                          float strip_y0, uint8_t* list, uint32_t* masks) {
     int n = 0;
     const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll
     for (int k = 0; k < BL_BATCH / 32; k++) {
         const int j = lane + 32 * k;
-        bool ok = false;
+        uint32_t m = 0;
         if (j < limit) {
             const float4 ge = sm.geom[s][j];
-            const float2 e = inst_extent<C>(sm, s, j);
-            ok = (fabsf(ge.y - strip_yc) <= e.y + 0.5f) && (ge.x + e.x >= strip_x0) &&
-                 (ge.x - e.x <= strip_x0 + (float)(TILE_X - 1));
+            const float2 e = inst_extent(sm, s, j);
+            const bool r0 = fabsf(ge.y - strip_y0) <= e.y;
+            const bool r1 = fabsf(ge.y - (strip_y0 + 1.0f)) <= e.y;
+            const float rel = ge.x - strip_x0;
+            const int lo = max(0, __float2int_ru(rel - e.x));             // -inf saturates to INT_MIN
+            const int hi = min(TILE_X - 1, __float2int_rd(rel + e.x));    // +inf saturates to INT_MAX
+            const uint32_t xb = (hi >= lo) ? ((2u << hi) - (1u << lo)) : 0u;
+            m = (r0 ? xb : 0u) | (r1 ? (xb << 16) : 0u);
         }
-        const uint32_t bal = __ballot_sync(0xffffffffu, ok);
-        if (ok) list[n + __popc(bal & lt)] = (uint8_t)j;
+        const uint32_t bal = __ballot_sync(0xffffffffu, m != 0u);
+        if (m != 0u) {
+            const int slot = n + __popc(bal & lt);
+            list[slot] = (uint8_t)j;
+            masks[slot] = m;
+        }
         n += __popc(bal);
     }
     __syncwarp();
     return n;
+}
+
+// 32x32 bit-matrix transpose across the warp: lane r passes row r, lane p receives column p
+// (bit r of the result = bit p of lane r's input).  Five butterfly stages.
+__device__ __forceinline__ uint32_t warp_bit_transpose(uint32_t x, int lane) {
+#pragma unroll
+    for (int st = 0; st < 5; st++) {
+        const int j = 16 >> st;
+        const uint32_t m = (st == 0) ? 0x0000ffffu : (st == 1) ? 0x00ff00ffu : (st == 2) ? 0x0f0f0f0fu
+                         : (st == 3) ? 0x33333333u : 0x55555555u;
+        const uint32_t t = __shfl_xor_sync(0xffffffffu, x, j);
+        x = (lane & j) ? (((t >> j) & m) | (x & ~m)) : ((x & m) | ((t & m) << j));
+    }
+    return x;
 }
 
 // WARPS warps per CTA: a CTA blends 2*WARPS pixel rows of one tile, so 8/WARPS CTAs share a tile (each
@@ -110,6 +139,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
     constexpr int NT = 32 * WARPS, PARTS = (BL_THREADS / 32) / WARPS;
     __shared__ __align__(128) BlendSmem<C> sm;
     __shared__ uint8_t s_list[WARPS][BL_BATCH];
+    __shared__ uint32_t s_mask[WARPS][BL_BATCH];
     const int tile = blockIdx.x / PARTS;
     const int tx = tile % gx, ty = tile / gx;
     const int lane = threadIdx.x & 31;
@@ -120,7 +150,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
     const float pxf = (float)px, pyf = (float)py;
     // this warp's pixels: columns [tile x0, +15], rows 2*strip and 2*strip+1
     const float strip_x0 = (float)(tx * TILE_X);
-    const float strip_yc = (float)(ty * TILE_Y + 2 * strip) + 0.5f;
+    const float strip_y0 = (float)(ty * TILE_Y + 2 * strip);
     const uint2 range = ranges[tile];
     const int len = (int)(range.y - range.x);
     const int nb = (len + BL_BATCH - 1) / BL_BATCH;
@@ -133,7 +163,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
     __syncthreads();
     if (threadIdx.x == 0) {
         for (int q = 0; q < BL_STAGES && q < nb; q++)
-            issue_batch<C>(sm, q, inst_conic, inst_geom, inst_feat, range.x + q * BL_BATCH,
+            issue_batch(sm, q, inst_conic, inst_geom, inst_feat, range.x + q * BL_BATCH,
                            min(BL_BATCH, len - q * BL_BATCH));
     }
 
@@ -150,43 +180,57 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
         const int s = b & (BL_STAGES - 1);
         mbar_wait(&sm.bar[s], (uint32_t)((b / BL_STAGES) & 1));
         const int cnt = min(BL_BATCH, len - b * BL_BATCH);
-        // The per-pixel loop of forward.cu:332-381, restructured so that the warp stays converged:
-        // (0) the warp drops the records whose ellipse cannot reach its strip,
-        // (1) alpha of up to FW_UNROLL surviving records is evaluated branch-free for all lanes
-        //     (independent chains: the exp latency of one record hides behind the others),
-        // (2) the order-dependent part (T, colour, median depth, termination) is applied in list order,
-        //     only for the records that passed the skip rules.  Same arithmetic per pixel.
+        // The per-pixel loop of forward.cu:332-381, restructured so that every lane works on a record that can
+        // actually reach ITS pixel:
+        // (0) the warp drops the records whose box cannot reach its strip and keeps, per surviving record, the
+        //     mask of the strip's pixels inside the box (lane = record);
+        // (1) 32 surviving records at a time, the 32x32 bit matrix (record x pixel) is transposed with five
+        //     shuffles, so each lane holds the set of records that can touch its own pixel;
+        // (2) each lane walks ITS OWN set in list order with the reference's arithmetic and skip rules.  Lanes are
+        //     on different records at the same time; nothing in the forward needs them to agree.
         bool warp_done = __all_sync(0xffffffffu, done);
         if (!warp_done) {
-            uint8_t* list = s_list[threadIdx.x >> 5];
-            const int n = cull_batch<C>(sm, s, cnt, lane, strip_x0, strip_yc, list);
+            const int w = threadIdx.x >> 5;
+            uint8_t* list = s_list[w];
+            uint32_t* masks = s_mask[w];
+            const int n = cull_batch(sm, s, cnt, lane, strip_x0, strip_y0, list, masks);
 #pragma unroll 1
-            for (int t = 0; t < n && !warp_done; t += FW_UNROLL) {
-                int jj[FW_UNROLL];
-#pragma unroll
-                for (int u = 0; u < FW_UNROLL; u++) jj[u] = (t + u < n) ? (int)list[t + u] : -1;
-                float al[FW_UNROLL];
-                uint32_t hit = 0;
-#pragma unroll
-                for (int u = 0; u < FW_UNROLL; u++) {
-                    const int j = max(jj[u], 0);
-                    const float4 co = sm.conic[s][j];
-                    const float4 ge = sm.geom[s][j];
-                    const float dx = __fsub_rn(ge.x, pxf), dy = __fsub_rn(ge.y, pyf);
-                    const float power = eval_power(co, dx, dy);
-                    const float alpha = fminf(0.99f, __fmul_rn(co.w, expf(power)));
-                    al[u] = alpha;
-                    // skip rules of forward.cu:343-353 (written so that NaN behaves as in the reference)
-                    if (jj[u] >= 0 && !(power > 0.0f) && !(alpha < 1.0f / 255.0f)) hit |= 1u << u;
-                }
-                if (done) hit = 0;
-                if (__any_sync(0xffffffffu, hit != 0)) {
-                    // order-dependent part, branch-free: the only serial chain is T -> test_T -> T
-                    // (one multiply, one compare, one select per record); everything else is predicated
-                    // selects, so a warp with many hits is not slowed down by 8 divergent branches.
+            for (int g0 = 0; g0 < n && !warp_done; g0 += 32) {
+                const bool have = g0 + lane < n;
+                const int jmine = have ? (int)list[g0 + lane] : 0;
+                uint32_t hits = warp_bit_transpose(have ? masks[g0 + lane] : 0u, lane);
+                if (done) hits = 0u;
+#pragma unroll 1
+                while (__any_sync(0xffffffffu, hits != 0u)) {
+                    // pop up to FW_UNROLL of this lane's records (ascending = list order); their alphas are
+                    // independent chains, so the exp latency of one hides behind the others
+                    int jj[FW_UNROLL];
+                    uint32_t valid = 0u;
 #pragma unroll
                     for (int u = 0; u < FW_UNROLL; u++) {
-                        const int j = max(jj[u], 0);
+                        const bool has = hits != 0u;
+                        const int r = has ? (__ffs((int)hits) - 1) : 0;
+                        hits &= hits - 1u;  // 0 stays 0
+                        jj[u] = __shfl_sync(0xffffffffu, jmine, r);
+                        if (has) valid |= 1u << u;
+                    }
+                    float al[FW_UNROLL];
+                    uint32_t hit = 0u;
+#pragma unroll
+                    for (int u = 0; u < FW_UNROLL; u++) {
+                        const float4 co = sm.conic[s][jj[u]];
+                        const float4 ge = sm.geom[s][jj[u]];
+                        const float dx = __fsub_rn(ge.x, pxf), dy = __fsub_rn(ge.y, pyf);
+                        const float power = eval_power(co, dx, dy);
+                        const float alpha = fminf(0.99f, __fmul_rn(co.w, expf(power)));
+                        al[u] = alpha;
+                        // skip rules of forward.cu:343-353 (written so that NaN behaves as in the reference)
+                        if (((valid >> u) & 1u) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f)) hit |= 1u << u;
+                    }
+                    // order-dependent part, branch-free: the only serial chain is T -> test_T -> T
+#pragma unroll
+                    for (int u = 0; u < FW_UNROLL; u++) {
+                        const int j = jj[u];
                         const float alpha = al[u];
                         const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
                         const bool h = ((hit >> u) & 1u) && !done;
@@ -194,7 +238,6 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
                         const bool blend = h && !stop;
                         done = done || stop;
                         const float4 f0 = sm.feat[s][j * FV];
-                        const float4 ge = sm.geom[s][j];
                         acc[0] = blend ? __fmaf_rn(__fmul_rn(f0.x, alpha), T, acc[0]) : acc[0];
                         acc[1] = blend ? __fmaf_rn(__fmul_rn(f0.y, alpha), T, acc[1]) : acc[1];
                         acc[2] = blend ? __fmaf_rn(__fmul_rn(f0.z, alpha), T, acc[2]) : acc[2];
@@ -204,12 +247,13 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
                             acc[4 % C] = blend ? __fmaf_rn(__fmul_rn(f1.x, alpha), T, acc[4 % C]) : acc[4 % C];
                             acc[5 % C] = blend ? __fmaf_rn(__fmul_rn(f1.y, alpha), T, acc[5 % C]) : acc[5 % C];
                         }
-                        D = (blend && T > 0.5f && test_T < 0.5f) ? ge.z : D;  // forward.cu:370-374
+                        if (blend && T > 0.5f && test_T < 0.5f) D = sm.geom[s][j].z;                  // forward.cu:370-374
                         last_contributor = blend ? (uint32_t)(b * BL_BATCH + j + 1) : last_contributor;  // :335,380
                         T = blend ? test_T : T;
                     }
-                    warp_done = __all_sync(0xffffffffu, done);
+                    if (done) hits = 0u;
                 }
+                warp_done = __all_sync(0xffffffffu, done);
             }
             __syncwarp();  // the list is rewritten by the next batch
         }
@@ -218,7 +262,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
         if (__syncthreads_count(done) == NT) break;
         if (threadIdx.x == 0 && b + BL_STAGES < nb) {
             const int nstart = (b + BL_STAGES) * BL_BATCH;
-            issue_batch<C>(sm, s, inst_conic, inst_geom, inst_feat, range.x + nstart, min(BL_BATCH, len - nstart));
+            issue_batch(sm, s, inst_conic, inst_geom, inst_feat, range.x + nstart, min(BL_BATCH, len - nstart));
         }
     }
     // copies that were issued but never consumed must land before this CTA's shared memory is released:
@@ -238,45 +282,53 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
     }
 }
 
-// Sum 16 per-lane values over the warp.  On return lane l holds in v[0] the warp total of value (l >> 1).
-__device__ __forceinline__ void warp_transpose_reduce16(float (&v)[16], int lane) {
-    {
-        const bool up = lane & 16;
+// ---- backward -----------------------------------------------------------------------------------
+// The reference walks every pixel back to front and issues 9 global atomics per (pixel, Gaussian)
+// (backward.cu:486-554).  Here a warp handles its 16x2 strip in groups of BW_GROUP surviving records:
+//   phase 1 (lane = pixel): each lane walks, back to front, only the records whose box contains ITS pixel
+//     (same bit-matrix transpose as the forward), replays T / accum_rec / dL_dalpha with the reference's
+//     arithmetic, and leaves two numbers per (record, pixel) in a per-warp staging tile:
+//       q = G * dL_dalpha   and   w = alpha * T.
+//     Every geometric term of backward.cu:505-554 is q times a polynomial in (dx, dy) and the record's own
+//     conic/opacity, and the colour terms are w * dL_dpixel, so nothing else has to cross lanes.
+//   phase 2 (lane = record x pixel row): each lane sums ITS record's q, q*dx, q*dx^2 and w*dL_dpixel over the
+//     pixels of one row serially in registers -- no butterfly, every lane busy on its own record -- forms the
+//     12 gradient terms, and adds them to the CTA's per-batch accumulator.
+// The CTA flushes the accumulator once per (tile, instance) with 128-bit vector reductions (REDG.ADD.F32x4).
+constexpr int BW_GROUP = 16;   // records per group: 16 x 32 staging slots per warp
+constexpr int BW_STAGES = 2;   // bulk-copy pipeline depth of the backward (a batch takes long enough to hide one copy)
+#ifndef ASB_BW_UNROLL
+#define ASB_BW_UNROLL 2
+#endif
+constexpr int BW_UNROLL = ASB_BW_UNROLL;  // records a lane evaluates together in phase 1 (ILP)
+
+// 16x16 bit-matrix transposes in both half-warps at once (lane r of a half passes row r, lane k receives column k).
+__device__ __forceinline__ uint32_t half_warp_bit_transpose(uint32_t x, int lane) {
 #pragma unroll
-        for (int k = 0; k < 8; k++) {
-            const float send = up ? v[k] : v[k + 8];
-            const float keep = up ? v[k + 8] : v[k];
-            v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-        }
+    for (int st = 0; st < 4; st++) {
+        const int j = 8 >> st;
+        const uint32_t m = (st == 0) ? 0x00ffu : (st == 1) ? 0x0f0fu : (st == 2) ? 0x3333u : 0x5555u;
+        const uint32_t t = __shfl_xor_sync(0xffffffffu, x, j);
+        x = (lane & j) ? (((t >> j) & m) | (x & ~m & 0xffffu)) : ((x & m) | ((t & m) << j));
     }
-    {
-        const bool up = lane & 8;
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const float send = up ? v[k] : v[k + 4];
-            const float keep = up ? v[k + 4] : v[k];
-            v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-        }
-    }
-    {
-        const bool up = lane & 4;
-#pragma unroll
-        for (int k = 0; k < 2; k++) {
-            const float send = up ? v[k] : v[k + 2];
-            const float keep = up ? v[k + 2] : v[k];
-            v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-        }
-    }
-    {
-        const bool up = lane & 2;
-        const float send = up ? v[0] : v[1];
-        const float keep = up ? v[1] : v[0];
-        v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
-    }
-    v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
+    return x;
 }
 
-constexpr int BW_UNROLL = 4;  // records whose alpha is evaluated together in the backward
+// staging slot of (record r of the group, pixel lane p): rotated by r inside the row so that lanes reading the
+// same column of different records (phase 2) and lanes writing the same record (phase 1) hit distinct banks
+__device__ __forceinline__ int stage_slot(int r, int p) { return r * 32 + (p & 16) + ((p + r) & 15); }
+
+template <int C, int WARPS>
+struct BwdLayout {
+    using SM = BlendSmem<C, BW_STAGES>;
+    static constexpr size_t off_acc = (sizeof(SM) + 127) / 128 * 128;
+    static constexpr size_t off_q = off_acc + sizeof(float) * BL_BATCH * 12;
+    static constexpr size_t off_w = off_q + sizeof(float) * WARPS * BW_GROUP * 32;
+    static constexpr size_t off_dpx = off_w + sizeof(float) * WARPS * BW_GROUP * 32;
+    static constexpr size_t off_mask = off_dpx + sizeof(float) * WARPS * C * 32;
+    static constexpr size_t off_list = off_mask + sizeof(uint32_t) * WARPS * BL_BATCH;
+    static constexpr size_t bytes = off_list + WARPS * BL_BATCH;
+};
 
 template <int C, int WARPS>
 __global__ void __launch_bounds__(32 * WARPS)
@@ -285,25 +337,32 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
                       int gx, const float* __restrict__ bg, const float* __restrict__ final_Ts,
                       const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
                       float* __restrict__ gacc) {
-    constexpr int FV = BlendSmem<C>::FV;
-    constexpr int NV = 6 + C;  // live gradient terms per (pixel, Gaussian)
+    using LY = BwdLayout<C, WARPS>;
+    using SM = typename LY::SM;
+    constexpr int FV = SM::FV;
     constexpr int NT = 32 * WARPS, PARTS = (BL_THREADS / 32) / WARPS;
-    __shared__ __align__(128) BlendSmem<C> sm;
-    __shared__ __align__(16) float s_acc[BL_BATCH * 16];
-    __shared__ uint8_t s_list[WARPS][BL_BATCH];
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    SM& sm = *reinterpret_cast<SM*>(smem_raw);
+    float* s_acc = reinterpret_cast<float*>(smem_raw + LY::off_acc);
+    const int wid = threadIdx.x >> 5;
+    float* stg_q = reinterpret_cast<float*>(smem_raw + LY::off_q) + wid * BW_GROUP * 32;
+    float* stg_w = reinterpret_cast<float*>(smem_raw + LY::off_w) + wid * BW_GROUP * 32;
+    float* dpx = reinterpret_cast<float*>(smem_raw + LY::off_dpx) + wid * C * 32;   // [C][32]
+    uint32_t* masks = reinterpret_cast<uint32_t*>(smem_raw + LY::off_mask) + wid * BL_BATCH;
+    uint8_t* list = reinterpret_cast<uint8_t*>(smem_raw + LY::off_list) + wid * BL_BATCH;
     __shared__ int s_max_contrib;
 
     const int tile = blockIdx.x / PARTS;
     const int tx = tile % gx, ty = tile / gx;
     const int lane = threadIdx.x & 31;
-    const int strip = (blockIdx.x % PARTS) * WARPS + (threadIdx.x >> 5);
+    const int strip = (blockIdx.x % PARTS) * WARPS + wid;
     const int px = tx * TILE_X + (lane & (TILE_X - 1));
     const int py = ty * TILE_Y + 2 * strip + (lane >> 4);
     const bool inside = px < W && py < H;
     const float pxf = (float)px, pyf = (float)py;
     const size_t pix_id = (size_t)W * py + px;
     const float strip_x0 = (float)(tx * TILE_X);
-    const float strip_yc = (float)(ty * TILE_Y + 2 * strip) + 0.5f;
+    const float strip_y0 = (float)(ty * TILE_Y + 2 * strip);
     const uint2 range = ranges[tile];
 
     const float T_final = inside ? final_Ts[pix_id] : 0.f;
@@ -313,7 +372,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
     if (threadIdx.x == 0) {
         s_max_contrib = 0;
 #pragma unroll
-        for (int q = 0; q < BL_STAGES; q++) mbar_init(&sm.bar[q], 1);
+        for (int q = 0; q < BW_STAGES; q++) mbar_init(&sm.bar[q], 1);
         mbar_fence_init();
     }
     __syncthreads();
@@ -325,9 +384,9 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
     const int nb = (len + BL_BATCH - 1) / BL_BATCH;
     // batch k covers list indices [hi_k - cnt_k, hi_k), hi_k = len - k*BATCH, walked back to front
     if (threadIdx.x == 0) {
-        for (int q = 0; q < BL_STAGES && q < nb; q++) {
+        for (int q = 0; q < BW_STAGES && q < nb; q++) {
             const int hi = len - q * BL_BATCH, cnt = min(BL_BATCH, hi);
-            issue_batch<C>(sm, q, inst_conic, inst_geom, inst_feat, range.x + (uint32_t)(hi - cnt), cnt);
+            issue_batch(sm, q, inst_conic, inst_geom, inst_feat, range.x + (uint32_t)(hi - cnt), cnt);
         }
     }
 
@@ -339,39 +398,56 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
         last_color[ch] = 0.f;
         dL_dpixel[ch] = inside ? __ldg(dL_dpixels + (size_t)ch * H * W + pix_id) : 0.f;
         bg_dot_dpixel += __ldg(bg + ch) * dL_dpixel[ch];
+        dpx[ch * 32 + lane] = dL_dpixel[ch];
     }
     float last_alpha = 0.f;
     const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;  // backward.cu:460-461
+    const int rl = lane & (BW_GROUP - 1), row = lane >> 4;   // phase-2 identity of this lane: (record, pixel row)
+    const float row_y = strip_y0 + (float)row;
 
     for (int b = 0; b < nb; b++) {
-        const int s = b & (BL_STAGES - 1);
+        const int s = b & (BW_STAGES - 1);
         const int hi = len - b * BL_BATCH;
         const int cnt = min(BL_BATCH, hi);
         const int lo = hi - cnt;  // list index of record 0 of this batch
-        // clear the batch accumulator (16 floats per instance)
+        // clear the batch accumulator ([12 terms][BL_BATCH instances])
         {
             float4* a4 = reinterpret_cast<float4*>(s_acc);
-            for (int i = threadIdx.x; i < cnt * 4; i += NT) a4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int i = threadIdx.x; i < BL_BATCH * 12 / 4; i += NT) a4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        mbar_wait(&sm.bar[s], (uint32_t)((b / BL_STAGES) & 1));
+        mbar_wait(&sm.bar[s], (uint32_t)((b / BW_STAGES) & 1));
         __syncthreads();
 
-        // records at list index >= warp_max are skipped by the whole warp; so are records whose ellipse
-        // cannot reach this warp's strip (see cull_batch)
-        uint8_t* list = s_list[threadIdx.x >> 5];
-        const int n = cull_batch<C>(sm, s, min(cnt, warp_max - lo), lane, strip_x0, strip_yc, list);
+        // records at list index >= warp_max are skipped by the whole warp; so are records whose box cannot
+        // reach this warp's strip (see cull_batch)
+        const int n = cull_batch(sm, s, min(cnt, warp_max - lo), lane, strip_x0, strip_y0, list, masks);
 #pragma unroll 1
-        for (int t = n; t > 0; t -= BW_UNROLL) {
-            {
-                int jj[BW_UNROLL];
-#pragma unroll
-                for (int u = 0; u < BW_UNROLL; u++) jj[u] = (t - 1 - u >= 0) ? (int)list[t - 1 - u] : -1;  // back to front
-                // (1) branch-free alpha for the chunk
-                float al[BW_UNROLL], Gs[BW_UNROLL];
-                uint32_t act = 0;
+        for (int t = n; t > 0; t -= BW_GROUP) {
+            const int gbase = max(t - BW_GROUP, 0), gs = t - gbase;
+            const bool have = rl < gs;
+            const int jr = have ? (int)list[gbase + rl] : 0;           // both half-warps hold the group's records
+            const uint32_t mrow = have ? ((masks[gbase + rl] >> (16 * row)) & 0xffffu) : 0u;  // my record, my row
+            uint32_t hits = half_warp_bit_transpose(mrow, lane);       // records of the group that reach MY pixel
+
+            // ---- phase 1: lane = pixel, back to front ----
+#pragma unroll 1
+            while (__any_sync(0xffffffffu, hits != 0u)) {
+                int jj[BW_UNROLL], rr[BW_UNROLL];
+                uint32_t valid = 0u;
 #pragma unroll
                 for (int u = 0; u < BW_UNROLL; u++) {
-                    const int j = max(jj[u], 0);
+                    const bool has = hits != 0u;
+                    const int r = has ? (31 - __clz((int)hits)) : 0;
+                    hits &= ~(1u << r);      // no-op when hits == 0 (bit 0 is clear then)
+                    rr[u] = r;
+                    jj[u] = __shfl_sync(0xffffffffu, jr, r);
+                    if (has) valid |= 1u << u;
+                }
+                float al[BW_UNROLL], Gs[BW_UNROLL];
+                uint32_t act = 0u;
+#pragma unroll
+                for (int u = 0; u < BW_UNROLL; u++) {
+                    const int j = jj[u];
                     const float4 co = sm.conic[s][j];
                     const float4 ge = sm.geom[s][j];
                     const float dx = __fsub_rn(ge.x, pxf), dy = __fsub_rn(ge.y, pyf);
@@ -381,27 +457,18 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
                     al[u] = alpha;
                     Gs[u] = G;
                     // the reference's `contributor` after its decrement is lo + j (backward.cu:486-490)
-                    if (jj[u] >= 0 && (lo + j) < last_contributor && !(power > 0.0f) && !(alpha < 1.0f / 255.0f))
+                    if (((valid >> u) & 1u) && (lo + j) < last_contributor && !(power > 0.0f) &&
+                        !(alpha < 1.0f / 255.0f))
                         act |= 1u << u;
                 }
-                // (2) ordered part + warp reduction, one record at a time
 #pragma unroll
                 for (int u = 0; u < BW_UNROLL; u++) {
-                    const bool active = act & (1u << u);
-                    const uint32_t active_lanes = __ballot_sync(0xffffffffu, active);
-                    if (active_lanes == 0) continue;
-                    const int j = jj[u];
-                    float v[16];
-#pragma unroll
-                    for (int q = 0; q < 16; q++) v[q] = 0.f;
-                    if (active) {
-                        const float4 co = sm.conic[s][j];
-                        const float4 ge = sm.geom[s][j];
-                        const float dx = __fsub_rn(ge.x, pxf), dy = __fsub_rn(ge.y, pyf);
-                        const float alpha = al[u], G = Gs[u];
+                    float q = 0.f, w = 0.f;
+                    if ((act >> u) & 1u) {
+                        const int j = jj[u];
+                        const float alpha = al[u];
                         const float inv_1ma = 1.f / (1.f - alpha);  // shared by T / (1 - alpha) and the background term
                         T = T * inv_1ma;
-                        const float dchannel_dcolor = alpha * T;
                         const float4 f0 = sm.feat[s][j * FV];
                         const float4 f1 = sm.feat[s][j * FV + FV - 1];
                         float col[C];
@@ -413,26 +480,71 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
                             accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
                             last_color[ch] = col[ch];
                             dL_dalpha += (col[ch] - accum_rec[ch]) * dL_dpixel[ch];
-                            v[6 + ch] = dchannel_dcolor * dL_dpixel[ch];
                         }
                         dL_dalpha *= T;
                         last_alpha = alpha;
                         dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;  // backward.cu:531-534
-                        const float dL_dG = co.w * dL_dalpha;                     // straight-through clamp (:538)
-                        const float gdx = G * dx, gdy = G * dy;
-                        const float dG_ddelx = -gdx * co.x - gdy * co.y;
-                        const float dG_ddely = -gdy * co.z - gdx * co.y;
-                        v[0] = -0.5f * gdx * dx * dL_dG;
-                        v[1] = -0.5f * gdx * dy * dL_dG;
-                        v[2] = -0.5f * gdy * dy * dL_dG;
-                        v[3] = G * dL_dalpha;
-                        v[4] = dL_dG * dG_ddelx * ddelx_dx;
-                        v[5] = dL_dG * dG_ddely * ddely_dy;
+                        q = Gs[u] * dL_dalpha;
+                        w = alpha * T;                                      // dchannel_dcolor (:513)
                     }
-                    warp_transpose_reduce16(v, lane);
-                    if (!(lane & 1) && (lane >> 1) < NV) atomicAdd(&s_acc[j * 16 + (lane >> 1)], v[0]);
+                    if ((valid >> u) & 1u) {
+                        const int slot = stage_slot(rr[u], lane);
+                        stg_q[slot] = q;
+                        stg_w[slot] = w;
+                    }
                 }
             }
+            __syncwarp();
+
+            // ---- phase 2: lane = (record rl, pixel row): serial sums over the row's pixels inside the box ----
+            {
+                float Sq = 0.f, Sx = 0.f, Sxx = 0.f, cc[C];
+#pragma unroll
+                for (int ch = 0; ch < C; ch++) cc[ch] = 0.f;
+                const float4 ge = sm.geom[s][jr];
+                uint32_t bits = mrow;
+                while (bits) {
+                    const int k = __ffs((int)bits) - 1;
+                    bits &= bits - 1u;
+                    const int p = 16 * row + k;
+                    const int slot = stage_slot(rl, p);
+                    const float q = stg_q[slot], w = stg_w[slot];
+                    const float dx = __fsub_rn(ge.x, strip_x0 + (float)k);   // same dx the pixel lane used
+                    const float qdx = q * dx;
+                    Sq += q;
+                    Sx += qdx;
+                    Sxx = fmaf(qdx, dx, Sxx);
+#pragma unroll
+                    for (int ch = 0; ch < C; ch++) cc[ch] = fmaf(w, dpx[ch * 32 + p], cc[ch]);
+                }
+                // the 12 gradient terms of backward.cu:505-554 for (record, row); dy is constant along the row
+                const float4 co = sm.conic[s][jr];
+                const float dy = __fsub_rn(ge.y, row_y);
+                const float Sy = dy * Sq, Sxy = dy * Sx, Syy = dy * Sy;
+                float v[6 + C];
+                v[0] = -0.5f * co.w * Sxx;                                  // dL_dconic.x : -0.5 gdx dx dL_dG
+                v[1] = -0.5f * co.w * Sxy;                                  // dL_dconic.y
+                v[2] = -0.5f * co.w * Syy;                                  // dL_dconic.w
+                v[3] = Sq;                                                  // dL_dopacity : G dL_dalpha
+                v[4] = -co.w * ddelx_dx * (co.x * Sx + co.y * Sy);          // dL_dmean2D.x : dL_dG dG_ddelx ddelx_dx
+                v[5] = -co.w * ddely_dy * (co.z * Sy + co.y * Sx);          // dL_dmean2D.y
+#pragma unroll
+                for (int ch = 0; ch < C; ch++) v[6 + ch] = cc[ch];
+                // add the two rows of the strip, then each row-lane commits half of the terms
+#pragma unroll
+                for (int i = 0; i < 6 + C; i++) v[i] += __shfl_xor_sync(0xffffffffu, v[i], 16);
+                if (have) {
+                    float* dst = s_acc + jr;  // term-major accumulator: lanes (= records) land in distinct banks
+                    if (row == 0) {
+#pragma unroll
+                        for (int i = 0; i < 6; i++) atomicAdd(dst + i * BL_BATCH, v[i]);
+                    } else {
+#pragma unroll
+                        for (int i = 6; i < 6 + C; i++) atomicAdd(dst + i * BL_BATCH, v[i]);
+                    }
+                }
+            }
+            __syncwarp();  // the staging tile is rewritten by the next group
         }
         __syncthreads();
         // flush: two threads per instance; 3 (C=6) or 2.25 (C=3) vector reductions per touched instance
@@ -441,21 +553,22 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
             {
                 const uint32_t id = __float_as_uint(sm.geom[s][inst].w);
                 float* dst = gacc + (size_t)id * GACC_STRIDE;
-                const float4* a4 = reinterpret_cast<const float4*>(s_acc + inst * 16);
+                const float* a = s_acc + inst;
                 if (half == 0) {
-                    const float4 x = a4[0], y = a4[1];
+                    const float4 x = make_float4(a[0], a[BL_BATCH], a[2 * BL_BATCH], a[3 * BL_BATCH]);
+                    const float4 y = make_float4(a[4 * BL_BATCH], a[5 * BL_BATCH], a[6 * BL_BATCH], a[7 * BL_BATCH]);
                     if (x.x != 0.f || x.y != 0.f || x.z != 0.f || x.w != 0.f) red_add_v4(dst, x.x, x.y, x.z, x.w);
                     if (y.x != 0.f || y.y != 0.f || y.z != 0.f || y.w != 0.f) red_add_v4(dst + 4, y.x, y.y, y.z, y.w);
                 } else {
-                    const float4 z = a4[2];
+                    const float4 z = make_float4(a[8 * BL_BATCH], a[9 * BL_BATCH], a[10 * BL_BATCH], a[11 * BL_BATCH]);
                     if (z.x != 0.f || z.y != 0.f || z.z != 0.f || z.w != 0.f) red_add_v4(dst + 8, z.x, z.y, z.z, z.w);
                 }
             }
         }
         __syncthreads();
-        if (threadIdx.x == 0 && b + BL_STAGES < nb) {
-            const int nhi = len - (b + BL_STAGES) * BL_BATCH, ncnt = min(BL_BATCH, nhi);
-            issue_batch<C>(sm, s, inst_conic, inst_geom, inst_feat, range.x + (uint32_t)(nhi - ncnt), ncnt);
+        if (threadIdx.x == 0 && b + BW_STAGES < nb) {
+            const int nhi = len - (b + BW_STAGES) * BL_BATCH, ncnt = min(BL_BATCH, nhi);
+            issue_batch(sm, s, inst_conic, inst_geom, inst_feat, range.x + (uint32_t)(nhi - ncnt), ncnt);
         }
     }
 }
@@ -489,9 +602,13 @@ template <int C>
 static void launch_bwd_c(int warps, int tiles, cudaStream_t st, const uint2* ranges, const BinningState& b, int W, int H,
                          int gx, const float* bg, const float* final_T, const uint32_t* n_contrib,
                          const float* dL_dpix, float* gacc) {
-#define ASB_BWD(WP)                                                                                               \
-    blend_backward_kernel<C, WP><<<tiles*(8 / WP), 32 * WP, 0, st>>>(ranges, b.inst_conic, b.inst_geom, b.inst_feat, W, \
-                                                                     H, gx, bg, final_T, n_contrib, dL_dpix, gacc)
+#define ASB_BWD(WP)                                                                                                \
+    do {                                                                                                           \
+        constexpr size_t smem = BwdLayout<C, WP>::bytes;                                                           \
+        cudaFuncSetAttribute(blend_backward_kernel<C, WP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        blend_backward_kernel<C, WP><<<tiles*(8 / WP), 32 * WP, smem, st>>>(                                       \
+            ranges, b.inst_conic, b.inst_geom, b.inst_feat, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc);      \
+    } while (0)
     if (warps == 8) ASB_BWD(8);
     else if (warps == 4) ASB_BWD(4);
     else if (warps == 2) ASB_BWD(2);

@@ -13,7 +13,8 @@ FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std
 
 def build(force=False, verbose=False):
     srcs = [os.path.join(HERE, s) for s in SOURCES if os.path.exists(os.path.join(HERE, s))]
-    deps = srcs + [os.path.join(HERE, "common.cuh"), os.path.join(HERE, "..", "..", "include", "activesplat_b200.h")]
+    deps = srcs + [os.path.join(HERE, "common.cuh"), os.path.join(HERE, "raster_math.cuh"),
+                   os.path.join(HERE, "..", "..", "include", "activesplat_b200.h")]
     if not force and os.path.exists(OUT) and all(os.path.getmtime(OUT) >= os.path.getmtime(d) for d in deps):
         return OUT
     objs = []
@@ -21,7 +22,8 @@ def build(force=False, verbose=False):
     for s in srcs:
         o = s[:-3] + ".o"
         objs.append(o)
-        cmd = [NVCC, *[f for f in FLAGS if f != "--use_fast_math=false"], "-c", s, "-o", o]
+        extra = os.environ.get("ASB_NVCC_EXTRA", "").split()  # experiments only (e.g. -DASB_FW_UNROLL=4)
+        cmd = [NVCC, *[f for f in FLAGS if f != "--use_fast_math=false"], *extra, "-c", s, "-o", o]
         procs.append((s, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     log = []
     for s, p in procs:
