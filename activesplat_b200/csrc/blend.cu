@@ -314,23 +314,31 @@ __device__ __forceinline__ uint32_t half_warp_bit_transpose(uint32_t x, int lane
     return x;
 }
 
-// staging slot of (record r of the group, pixel lane p): rotated by r inside the row so that lanes reading the
+// staging slot of (record r of the group, pixel lane p): the column is XOR-swizzled by r so that lanes reading the
 // same column of different records (phase 2) and lanes writing the same record (phase 1) hit distinct banks
-__device__ __forceinline__ int stage_slot(int r, int p) { return r * 32 + (p & 16) + ((p + r) & 15); }
+__device__ __forceinline__ int stage_slot(int r, int p) { return r * 32 + (p ^ r); }  // r < 16: the row bit survives
+
+// Which of the 12 per-Gaussian terms the caller consumes (conic x,y,w | opacity | mean2D x,y | colour 0..5):
+//   BWD_ALL       everything (rasterizer API)
+//   BWD_MAPPING   fused frame path with Gaussian gradients: colour 4 is the constant 1 of [z,1,z^2], never read
+//   BWD_TRACKING  fused frame path, pose only: conic, mean2D and the z / z^2 colour terms (T20)
+enum BwdMode { BWD_ALL = 0, BWD_MAPPING = 1, BWD_TRACKING = 2 };
+template <int C, int MODE>
+__device__ __forceinline__ constexpr bool need_colour(int ch) {
+    return MODE == BWD_ALL ? true : MODE == BWD_MAPPING ? (ch != 4) : (ch == 3 || ch == 5);
+}
 
 template <int C, int WARPS>
 struct BwdLayout {
     using SM = BlendSmem<C, BW_STAGES>;
-    static constexpr size_t off_acc = (sizeof(SM) + 127) / 128 * 128;
-    static constexpr size_t off_q = off_acc + sizeof(float) * BL_BATCH * 12;
-    static constexpr size_t off_w = off_q + sizeof(float) * WARPS * BW_GROUP * 32;
-    static constexpr size_t off_dpx = off_w + sizeof(float) * WARPS * BW_GROUP * 32;
+    static constexpr size_t off_qw = (sizeof(SM) + 127) / 128 * 128;
+    static constexpr size_t off_dpx = off_qw + sizeof(float2) * WARPS * BW_GROUP * 32;
     static constexpr size_t off_mask = off_dpx + sizeof(float) * WARPS * C * 32;
     static constexpr size_t off_list = off_mask + sizeof(uint32_t) * WARPS * BL_BATCH;
     static constexpr size_t bytes = off_list + WARPS * BL_BATCH;
 };
 
-template <int C, int WARPS>
+template <int C, int WARPS, int MODE>
 __global__ void __launch_bounds__(32 * WARPS)
 blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict__ inst_conic,
                       const float4* __restrict__ inst_geom, const float4* __restrict__ inst_feat, int W, int H,
@@ -340,13 +348,11 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
     using LY = BwdLayout<C, WARPS>;
     using SM = typename LY::SM;
     constexpr int FV = SM::FV;
-    constexpr int NT = 32 * WARPS, PARTS = (BL_THREADS / 32) / WARPS;
+    constexpr int PARTS = (BL_THREADS / 32) / WARPS;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     SM& sm = *reinterpret_cast<SM*>(smem_raw);
-    float* s_acc = reinterpret_cast<float*>(smem_raw + LY::off_acc);
     const int wid = threadIdx.x >> 5;
-    float* stg_q = reinterpret_cast<float*>(smem_raw + LY::off_q) + wid * BW_GROUP * 32;
-    float* stg_w = reinterpret_cast<float*>(smem_raw + LY::off_w) + wid * BW_GROUP * 32;
+    float2* stg = reinterpret_cast<float2*>(smem_raw + LY::off_qw) + wid * BW_GROUP * 32;
     float* dpx = reinterpret_cast<float*>(smem_raw + LY::off_dpx) + wid * C * 32;   // [C][32]
     uint32_t* masks = reinterpret_cast<uint32_t*>(smem_raw + LY::off_mask) + wid * BL_BATCH;
     uint8_t* list = reinterpret_cast<uint8_t*>(smem_raw + LY::off_list) + wid * BL_BATCH;
@@ -410,13 +416,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
         const int hi = len - b * BL_BATCH;
         const int cnt = min(BL_BATCH, hi);
         const int lo = hi - cnt;  // list index of record 0 of this batch
-        // clear the batch accumulator ([12 terms][BL_BATCH instances])
-        {
-            float4* a4 = reinterpret_cast<float4*>(s_acc);
-            for (int i = threadIdx.x; i < BL_BATCH * 12 / 4; i += NT) a4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        }
         mbar_wait(&sm.bar[s], (uint32_t)((b / BW_STAGES) & 1));
-        __syncthreads();
 
         // records at list index >= warp_max are skipped by the whole warp; so are records whose box cannot
         // reach this warp's strip (see cull_batch)
@@ -467,7 +467,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
                     if ((act >> u) & 1u) {
                         const int j = jj[u];
                         const float alpha = al[u];
-                        const float inv_1ma = 1.f / (1.f - alpha);  // shared by T / (1 - alpha) and the background term
+                        const float inv_1ma = __frcp_rn(1.f - alpha);  // 1 - alpha is in [0.01, 1]; shared by T / (1 - alpha) and the background term
                         T = T * inv_1ma;
                         const float4 f0 = sm.feat[s][j * FV];
                         const float4 f1 = sm.feat[s][j * FV + FV - 1];
@@ -487,11 +487,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
                         q = Gs[u] * dL_dalpha;
                         w = alpha * T;                                      // dchannel_dcolor (:513)
                     }
-                    if ((valid >> u) & 1u) {
-                        const int slot = stage_slot(rr[u], lane);
-                        stg_q[slot] = q;
-                        stg_w[slot] = w;
-                    }
+                    if ((valid >> u) & 1u) stg[stage_slot(rr[u], lane)] = make_float2(q, w);
                 }
             }
             __syncwarp();
@@ -502,26 +498,27 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
 #pragma unroll
                 for (int ch = 0; ch < C; ch++) cc[ch] = 0.f;
                 const float4 ge = sm.geom[s][jr];
+                const float2* my_stg = stg + rl * 32 + 16 * row;
+                const float* my_dpx = dpx + 16 * row;
                 uint32_t bits = mrow;
                 while (bits) {
                     const int k = __ffs((int)bits) - 1;
                     bits &= bits - 1u;
-                    const int p = 16 * row + k;
-                    const int slot = stage_slot(rl, p);
-                    const float q = stg_q[slot], w = stg_w[slot];
+                    const float2 qw = my_stg[k ^ rl];
                     const float dx = __fsub_rn(ge.x, strip_x0 + (float)k);   // same dx the pixel lane used
-                    const float qdx = q * dx;
-                    Sq += q;
+                    const float qdx = qw.x * dx;
+                    Sq += qw.x;
                     Sx += qdx;
                     Sxx = fmaf(qdx, dx, Sxx);
 #pragma unroll
-                    for (int ch = 0; ch < C; ch++) cc[ch] = fmaf(w, dpx[ch * 32 + p], cc[ch]);
+                    for (int ch = 0; ch < C; ch++)
+                        if (need_colour<C, MODE>(ch)) cc[ch] = fmaf(qw.y, my_dpx[ch * 32 + k], cc[ch]);
                 }
                 // the 12 gradient terms of backward.cu:505-554 for (record, row); dy is constant along the row
                 const float4 co = sm.conic[s][jr];
                 const float dy = __fsub_rn(ge.y, row_y);
                 const float Sy = dy * Sq, Sxy = dy * Sx, Syy = dy * Sy;
-                float v[6 + C];
+                float v[12];
                 v[0] = -0.5f * co.w * Sxx;                                  // dL_dconic.x : -0.5 gdx dx dL_dG
                 v[1] = -0.5f * co.w * Sxy;                                  // dL_dconic.y
                 v[2] = -0.5f * co.w * Syy;                                  // dL_dconic.w
@@ -529,43 +526,28 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
                 v[4] = -co.w * ddelx_dx * (co.x * Sx + co.y * Sy);          // dL_dmean2D.x : dL_dG dG_ddelx ddelx_dx
                 v[5] = -co.w * ddely_dy * (co.z * Sy + co.y * Sx);          // dL_dmean2D.y
 #pragma unroll
-                for (int ch = 0; ch < C; ch++) v[6 + ch] = cc[ch];
-                // add the two rows of the strip, then each row-lane commits half of the terms
+                for (int ch = 0; ch < 6; ch++) v[6 + ch] = (ch < C && need_colour<C, MODE>(ch)) ? cc[ch % C] : 0.f;
+                // add the two rows of the strip; then each row-lane commits half of the accumulator row
+                // (conic x,y,w | opacity | mean2D x,y || colour 0..5) with vector reductions to global memory
 #pragma unroll
-                for (int i = 0; i < 6 + C; i++) v[i] += __shfl_xor_sync(0xffffffffu, v[i], 16);
+                for (int i = 0; i < 12; i++) {
+                    const bool used = i < 6 ? (i != 3 || MODE != BWD_TRACKING) : (i - 6 < C && need_colour<C, MODE>(i - 6));
+                    if (used) v[i] += __shfl_xor_sync(0xffffffffu, v[i], 16);
+                }
                 if (have) {
-                    float* dst = s_acc + jr;  // term-major accumulator: lanes (= records) land in distinct banks
+                    float* dst = gacc + (size_t)__float_as_uint(ge.w) * GACC_STRIDE;
                     if (row == 0) {
-#pragma unroll
-                        for (int i = 0; i < 6; i++) atomicAdd(dst + i * BL_BATCH, v[i]);
+                        red_add_v4(dst, v[0], v[1], v[2], v[3]);
+                        red_add_v2(dst + 4, v[4], v[5]);
                     } else {
-#pragma unroll
-                        for (int i = 6; i < 6 + C; i++) atomicAdd(dst + i * BL_BATCH, v[i]);
+                        if (MODE != BWD_TRACKING) red_add_v2(dst + 6, v[6], v[7]);
+                        if (C == 6 || MODE == BWD_ALL) red_add_v4(dst + 8, v[8], v[9], v[10], v[11]);
                     }
                 }
             }
             __syncwarp();  // the staging tile is rewritten by the next group
         }
-        __syncthreads();
-        // flush: two threads per instance; 3 (C=6) or 2.25 (C=3) vector reductions per touched instance
-        for (int i = threadIdx.x; i < 2 * cnt; i += NT) {
-            const int inst = i >> 1, half = i & 1;
-            {
-                const uint32_t id = __float_as_uint(sm.geom[s][inst].w);
-                float* dst = gacc + (size_t)id * GACC_STRIDE;
-                const float* a = s_acc + inst;
-                if (half == 0) {
-                    const float4 x = make_float4(a[0], a[BL_BATCH], a[2 * BL_BATCH], a[3 * BL_BATCH]);
-                    const float4 y = make_float4(a[4 * BL_BATCH], a[5 * BL_BATCH], a[6 * BL_BATCH], a[7 * BL_BATCH]);
-                    if (x.x != 0.f || x.y != 0.f || x.z != 0.f || x.w != 0.f) red_add_v4(dst, x.x, x.y, x.z, x.w);
-                    if (y.x != 0.f || y.y != 0.f || y.z != 0.f || y.w != 0.f) red_add_v4(dst + 4, y.x, y.y, y.z, y.w);
-                } else {
-                    const float4 z = make_float4(a[8 * BL_BATCH], a[9 * BL_BATCH], a[10 * BL_BATCH], a[11 * BL_BATCH]);
-                    if (z.x != 0.f || z.y != 0.f || z.z != 0.f || z.w != 0.f) red_add_v4(dst + 8, z.x, z.y, z.z, z.w);
-                }
-            }
-        }
-        __syncthreads();
+        __syncthreads();  // every warp is done with stage s
         if (threadIdx.x == 0 && b + BW_STAGES < nb) {
             const int nhi = len - (b + BW_STAGES) * BL_BATCH, ncnt = min(BL_BATCH, nhi);
             issue_batch(sm, s, inst_conic, inst_geom, inst_feat, range.x + (uint32_t)(nhi - ncnt), ncnt);
@@ -598,15 +580,17 @@ static void launch_fwd_c(int warps, int tiles, cudaStream_t st, const uint2* ran
 #undef ASB_FWD
 }
 
-template <int C>
+template <int C, int MODE>
 static void launch_bwd_c(int warps, int tiles, cudaStream_t st, const uint2* ranges, const BinningState& b, int W, int H,
                          int gx, const float* bg, const float* final_T, const uint32_t* n_contrib,
                          const float* dL_dpix, float* gacc) {
 #define ASB_BWD(WP)                                                                                                \
     do {                                                                                                           \
         constexpr size_t smem = BwdLayout<C, WP>::bytes;                                                           \
-        cudaFuncSetAttribute(blend_backward_kernel<C, WP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-        blend_backward_kernel<C, WP><<<tiles*(8 / WP), 32 * WP, smem, st>>>(                                       \
+        if (smem > 48 * 1024)                                                                                      \
+            cudaFuncSetAttribute(blend_backward_kernel<C, WP, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
+                                 (int)smem);                                                                       \
+        blend_backward_kernel<C, WP, MODE><<<tiles*(8 / WP), 32 * WP, smem, st>>>(                                 \
             ranges, b.inst_conic, b.inst_geom, b.inst_feat, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc);      \
     } while (0)
     if (warps == 8) ASB_BWD(8);
@@ -631,15 +615,19 @@ void launch_blend_forward(int channels, int W, int H, const uint2* ranges, const
 
 void launch_blend_backward(int channels, int W, int H, const uint2* ranges, const BinningState& b, const float* bg,
                            const float* final_T, const uint32_t* n_contrib, const float* dL_dpix, float* gacc,
-                           cudaStream_t st) {
+                           cudaStream_t st, int mode) {
     const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
     const int tiles = gx * gy;
     if (tiles <= 0) return;
     const int warps = pick_warps(tiles);
     if (channels == 3)
-        launch_bwd_c<3>(warps, tiles, st, ranges, b, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc);
+        launch_bwd_c<3, BWD_ALL>(warps, tiles, st, ranges, b, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc);
+    else if (mode == BWD_MAPPING)
+        launch_bwd_c<6, BWD_MAPPING>(warps, tiles, st, ranges, b, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc);
+    else if (mode == BWD_TRACKING)
+        launch_bwd_c<6, BWD_TRACKING>(warps, tiles, st, ranges, b, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc);
     else
-        launch_bwd_c<6>(warps, tiles, st, ranges, b, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc);
+        launch_bwd_c<6, BWD_ALL>(warps, tiles, st, ranges, b, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc);
 }
 
 }  // namespace asb

@@ -377,7 +377,8 @@ int as_frame_backward(const AsFrameBackwardArgs* ba, void* cuda_stream) {
     int r;
     {
         StageScope _s(AS_STAGE_BLEND_BWD, st, 1);
-        launch_blend_backward(6, W, H, img.ranges, b, a->background, img.final_T, img.n_contrib, ba->dL_dpix, g.gacc, st);
+        launch_blend_backward(6, W, H, img.ranges, b, a->background, img.final_T, img.n_contrib, ba->dL_dpix, g.gacc, st,
+                              ba->gaussians_grad ? 1 : 2);
     }
     if ((r = stage_check(st, a->debug))) return r;
     {

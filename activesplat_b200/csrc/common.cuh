@@ -109,9 +109,11 @@ void launch_blend_forward(int channels, int W, int H, const uint2* ranges, const
                           float* final_T, uint32_t* n_contrib, cudaStream_t st);
 
 // gacc: [P,12] accumulators (conic x,y,w | opacity | mean2D x,y | colour[<=6]); must be zero on entry.
+// mode (6 channels only): 0 = all 12 terms, 1 = the frame path with Gaussian gradients (the constant-1 channel of
+// [z,1,z^2] is skipped), 2 = pose-only frame path (conic, mean2D and the z / z^2 terms; the rest is left undefined).
 void launch_blend_backward(int channels, int W, int H, const uint2* ranges, const BinningState& b,
                            const float* bg, const float* final_T, const uint32_t* n_contrib,
-                           const float* dL_dpix, float* gacc, cudaStream_t st);
+                           const float* dL_dpix, float* gacc, cudaStream_t st, int mode = 0);
 
 struct PreprocessBackwardOut {
     float* dL_dmean2D;   // [P,3] or NULL
