@@ -16,7 +16,7 @@
 //   * backward skips the tail of the list that no pixel of the warp/tile reached in the forward.
 // Per-pixel arithmetic, skip rules and termination are the reference's (SURVEY 8a' T10-T18) and are
 // spelled with rounding-explicit intrinsics so alpha decisions match the reference build bit for bit.
-#include <cuda_fp16.h>
+#include <math_constants.h>
 
 #include "common.cuh"
 
@@ -61,24 +61,30 @@ __device__ __forceinline__ void issue_batch(SM& sm, int stage, const float4* __r
 
 // ---- per-warp culling ---------------------------------------------------------------------------
 // A pair (pixel, Gaussian) can only pass the skip rules (power <= 0, alpha >= 1/255; forward.cu:343-353)
-// inside the ellipse  A dx^2 + 2B dx dy + C dy^2 <= 2 ln(255 * opacity).  ranges_gather stores the
-// ellipse's axis-aligned half-extents (rounded UP, with margin) per instance; a warp whose 16x2-pixel
-// strip lies outside that box skips the instance without evaluating anything.  Skipped pairs would have
-// been skipped by the rules anyway, so images, n_contrib and gradients are unchanged.
+// inside the ellipse  A dx^2 + 2B dx dy + C dy^2 <= L,  L = 2 ln(255 * opacity); ranges_gather stores L (with
+// margin) per instance.  For one pixel row (dy fixed) that is an interval of columns: a warp computes, per record,
+// the columns of its two rows inside the ellipse, skips the record when there are none, and otherwise keeps the
+// 32-bit lane mask.  Pairs outside the mask would have been skipped by the rules anyway, so images, n_contrib and
+// gradients are unchanged.
 template <class SM>
-__device__ __forceinline__ float2 inst_extent(const SM& sm, int s, int j) {
+__device__ __forceinline__ float inst_level(const SM& sm, int s, int j) {
     constexpr int FV = SM::FV;
     const float4 f = sm.feat[s][j * FV + FV - 1];
-    const uint32_t bits = __float_as_uint(FV == 1 ? f.w : f.z);
-    const __half2 h = *reinterpret_cast<const __half2*>(&bits);
-    return __half22float2(h);
+    return FV == 1 ? f.w : f.z;
+}
+
+// columns (bit k = column k of the tile) with |column - c| <= hw
+__device__ __forceinline__ uint32_t column_bits(float c, float hw) {
+    const int lo = max(0, __float2int_ru(c - hw));             // -inf saturates to INT_MIN
+    const int hi = min(TILE_X - 1, __float2int_rd(c + hw));    // +inf saturates to INT_MAX
+    return (hi >= lo) ? ((2u << hi) - (1u << lo)) : 0u;
 }
 
 // Compacts the batch's records that can touch this warp's pixel strip into the warp's private list
 // (ascending record order) and returns how many there are.  For every kept record it also stores the
-// LANE MASK of the strip's pixels that lie inside the record's box (bit l = pixel of lane l: column l & 15,
-// row l >> 4).  The box is a superset of the pixels that pass the skip rules, so a pixel outside it never
-// needs to look at the record.
+// LANE MASK of the strip's pixels inside the record's ellipse (bit l = pixel of lane l: column l & 15,
+// row l >> 4).  Two steps: a cheap row test over all records (does the ellipse reach either row at all?),
+// then the column intervals for the survivors only.
 template <class SM>
 __device__ __forceinline__ int cull_batch(const SM& sm, int s, int limit, int lane, float strip_x0,
                                           float strip_y0, uint8_t* list, uint32_t* masks) {
@@ -87,28 +93,57 @@ __device__ __forceinline__ int cull_batch(const SM& sm, int s, int limit, int la
 #pragma unroll
     for (int k = 0; k < BL_BATCH / 32; k++) {
         const int j = lane + 32 * k;
-        uint32_t m = 0;
+        bool ok = false;
         if (j < limit) {
-            const float4 ge = sm.geom[s][j];
-            const float2 e = inst_extent(sm, s, j);
-            const bool r0 = fabsf(ge.y - strip_y0) <= e.y;
-            const bool r1 = fabsf(ge.y - (strip_y0 + 1.0f)) <= e.y;
-            const float rel = ge.x - strip_x0;
-            const int lo = max(0, __float2int_ru(rel - e.x));             // -inf saturates to INT_MIN
-            const int hi = min(TILE_X - 1, __float2int_rd(rel + e.x));    // +inf saturates to INT_MAX
-            const uint32_t xb = (hi >= lo) ? ((2u << hi) - (1u << lo)) : 0u;
-            m = (r0 ? xb : 0u) | (r1 ? (xb << 16) : 0u);
+            const float4 co = sm.conic[s][j];
+            const float gy = sm.geom[s][j].y;
+            const float L = inst_level(sm, s, j);
+            // row r is reached iff D_r = A L - det dy_r^2 >= 0; anything not finite is kept (never cull the unknown)
+            const float det = co.x * co.z - co.y * co.y, al = co.x * L;
+            const float dy0 = gy - strip_y0, dy1 = dy0 - 1.0f;
+            const float D0 = al - det * dy0 * dy0, D1 = al - det * dy1 * dy1;
+            ok = (L >= 0.f) && !(D0 < 0.f && D1 < 0.f);
         }
-        const uint32_t bal = __ballot_sync(0xffffffffu, m != 0u);
-        if (m != 0u) {
-            const int slot = n + __popc(bal & lt);
-            list[slot] = (uint8_t)j;
-            masks[slot] = m;
-        }
+        const uint32_t bal = __ballot_sync(0xffffffffu, ok);
+        if (ok) list[n + __popc(bal & lt)] = (uint8_t)j;
         n += __popc(bal);
     }
     __syncwarp();
-    return n;
+    // column intervals of the survivors; records whose interval misses the tile's columns drop out here
+    int n2 = 0;
+#pragma unroll 1
+    for (int i0 = 0; i0 < n; i0 += 32) {
+        uint32_t m = 0;
+        int j = 0;
+        if (i0 + lane < n) {
+            j = list[i0 + lane];
+            const float4 co = sm.conic[s][j];
+            const float4 ge = sm.geom[s][j];
+            const float L = inst_level(sm, s, j);
+            const float det = co.x * co.z - co.y * co.y;
+            const float inv_a = 1.0f / co.x;
+            const float rel = ge.x - strip_x0;
+            const float dy0 = ge.y - strip_y0, dy1 = dy0 - 1.0f;
+            // row r: A dx^2 + 2 B dy dx + (C dy^2 - L) <= 0  =>  pixel column in  rel + (B dy -+ sqrt(D)) / A
+            const float D0 = co.x * L - det * dy0 * dy0, D1 = co.x * L - det * dy1 * dy1;
+            const float c0 = rel + co.y * dy0 * inv_a, c1 = rel + co.y * dy1 * inv_a;
+            const float h0 = sqrtf(D0) * inv_a + 0.02f, h1 = sqrtf(D1) * inv_a + 0.02f;  // NaN when D < 0
+            uint32_t b0 = (D0 >= 0.f) ? column_bits(c0, h0) : 0u;
+            uint32_t b1 = (D1 >= 0.f) ? column_bits(c1, h1) : 0u;
+            if (!(L < CUDART_INF_F) || !(c0 == c0) || !(D0 == D0) || !(h0 == h0 || D0 < 0.f)) b0 = 0xffffu;
+            if (!(L < CUDART_INF_F) || !(c1 == c1) || !(D1 == D1) || !(h1 == h1 || D1 < 0.f)) b1 = 0xffffu;
+            m = b0 | (b1 << 16);
+        }
+        const uint32_t bal = __ballot_sync(0xffffffffu, m != 0u);  // also orders this round's reads before its writes
+        if (m != 0u) {
+            const int slot = n2 + __popc(bal & lt);  // slot <= i0 + lane: in-place compaction never overtakes the reads
+            list[slot] = (uint8_t)j;
+            masks[slot] = m;
+        }
+        n2 += __popc(bal);
+        __syncwarp();
+    }
+    return n2;
 }
 
 // 32x32 bit-matrix transpose across the warp: lane r passes row r, lane p receives column p
@@ -396,12 +431,11 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
         }
     }
 
-    float accum_rec[C], last_color[C], dL_dpixel[C];
+    float dL_dpixel[C];
+    float adot = 0.f, last_cdot = 0.f;
     float bg_dot_dpixel = 0.f;
 #pragma unroll
     for (int ch = 0; ch < C; ch++) {
-        accum_rec[ch] = 0.f;
-        last_color[ch] = 0.f;
         dL_dpixel[ch] = inside ? __ldg(dL_dpixels + (size_t)ch * H * W + pix_id) : 0.f;
         bg_dot_dpixel += __ldg(bg + ch) * dL_dpixel[ch];
         dpx[ch * 32 + lane] = dL_dpixel[ch];
@@ -474,14 +508,15 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
                         float col[C];
                         col[0] = f0.x; col[1] = f0.y; col[2] = f0.z;
                         if (C == 6) { col[3 % C] = f0.w; col[4 % C] = f1.x; col[5 % C] = f1.y; }
-                        float dL_dalpha = 0.f;
+                        // backward.cu:516-528 keeps accum_rec[ch] and sums (col[ch] - accum_rec[ch]) * dL_dpixel[ch];
+                        // only that sum is ever used, so the recurrence is carried on the two dot products
+                        //   cdot = sum col[ch] dL_dpixel[ch]   and   adot = sum accum_rec[ch] dL_dpixel[ch]
+                        float cdot = 0.f;
 #pragma unroll
-                        for (int ch = 0; ch < C; ch++) {
-                            accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
-                            last_color[ch] = col[ch];
-                            dL_dalpha += (col[ch] - accum_rec[ch]) * dL_dpixel[ch];
-                        }
-                        dL_dalpha *= T;
+                        for (int ch = 0; ch < C; ch++) cdot = fmaf(col[ch], dL_dpixel[ch], cdot);
+                        adot = last_alpha * last_cdot + (1.f - last_alpha) * adot;
+                        last_cdot = cdot;
+                        float dL_dalpha = (cdot - adot) * T;
                         last_alpha = alpha;
                         dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;  // backward.cu:531-534
                         q = Gs[u] * dL_dalpha;

@@ -95,25 +95,16 @@ __device__ __forceinline__ void cov2d_from_T(const float Tm[2][3], const float* 
 }
 
 
-// Axis-aligned half-extents (in pixels, rounded up, with margin) of the region where a Gaussian can pass
-// the blend kernels' skip rules:  A dx^2 + 2B dx dy + C dy^2 <= 2 ln(255 opacity).  Packed as two halves.
-// Negative extents = can never contribute; +inf = unknown, never culled.
+// Culling level L of a Gaussian for the blend kernels: a pixel can pass their skip rules (power <= 0 and
+// opacity * exp(power) >= 1/255; forward.cu:343-353) only if  A dx^2 + 2B dx dy + C dy^2 <= 2 ln(255 opacity) =: L.
+// Stored with a small margin.  Negative = can never contribute; +inf = unknown, never culled.
 __device__ __forceinline__ float pack_cull_extent(float4 co) {
-    float ex, ey;
-    const float t2 = 2.f * logf(255.f * co.w);
+    if (!(co.w >= 1.0f / 255.0f))  // alpha = min(0.99, op * G) < 1/255 for every G <= 1 (NaN opacity: keep)
+        return (co.w == co.w) ? -1.f : CUDART_INF_F;
     const float det = co.x * co.z - co.y * co.y;
-    if (!(co.w >= 1.0f / 255.0f)) {  // alpha = min(0.99, op * G) < 1/255 for every G <= 1 (NaN opacity: keep)
-        ex = ey = (co.w == co.w) ? -1.f : CUDART_INF_F;
-    } else if (!(det > 0.f) || !(t2 >= 0.f) || !isfinite(det)) {
-        ex = ey = CUDART_INF_F;
-    } else {
-        ex = sqrtf(fmaxf(t2 * co.z / det, 0.f)) * 1.002f + 0.05f;
-        ey = sqrtf(fmaxf(t2 * co.x / det, 0.f)) * 1.002f + 0.05f;
-        if (!(ex == ex)) ex = CUDART_INF_F;
-        if (!(ey == ey)) ey = CUDART_INF_F;
-    }
-    const __half2 h = __halves2half2(__float2half_ru(ex), __float2half_ru(ey));
-    return __uint_as_float(*reinterpret_cast<const uint32_t*>(&h));
+    const float L = 2.f * logf(255.f * co.w);
+    if (!(det > 0.f) || !(co.x > 0.f) || !isfinite(det) || !(L >= 0.f) || !isfinite(L)) return CUDART_INF_F;
+    return L * 1.001f + 1e-4f;
 }
 
 // Result of the forward per-Gaussian computation (forward.cu:155-256, colors_precomp path).
