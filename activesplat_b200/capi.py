@@ -78,6 +78,7 @@ class AsFrameArgs(ctypes.Structure):
         ("radii", ctypes.c_void_p),
         ("debug", ctypes.c_int),
         ("max_2D_radius", ctypes.c_void_p), ("seen", ctypes.c_void_p),
+        ("binning_mode", ctypes.c_int),
     ]
 
 
@@ -114,6 +115,7 @@ SYMBOLS = {
     "as_frame_backward": (_I, [ctypes.POINTER(AsFrameBackwardArgs), _V]),
     "as_loss_scratch_floats": (_Z, [_I, _I]),
     "as_pose_scratch_floats": (_Z, [_I]),
+    "as_tile_sort_capacity": (_I, []),
     "as_tracking_loss": (_I, [_I, _I, _V, _V, _V, _F, _F, _F, _I, _I, _V, _V, _V, _V, _V]),
     "as_mapping_loss_scratch_floats": (_Z, [_I, _I]),
     "as_mapping_loss": (_I, [_I, _I, _V, _V, _V, _F, _F, _V, _V, _V, _V, _V]),

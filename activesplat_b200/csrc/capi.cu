@@ -38,6 +38,8 @@ ImageState ImageState::fromChunk(char*& chunk, size_t N, size_t tiles) {
     img.final_T = b.take<float>(N);
     img.n_contrib = b.take<uint32_t>(N);
     img.ranges = b.take<uint2>(tiles);
+    img.tile_count = b.take<uint32_t>(tiles * 8);   // TB_SUB sub-counters per tile (fused.cu)
+    img.tile_cursor = b.take<uint32_t>(tiles * 8);
     chunk = b.p;
     return img;
 }
@@ -327,28 +329,36 @@ int as_frame_forward(const AsFrameArgs* a, void* cuda_stream) {
     const int cap = a->binning_capacity;
     BinningState b = BinningState::fromChunk(bchunk, (size_t)cap, 6);
     int r;
+    const bool buckets = a->binning_mode == AS_BINNING_TILE_BUCKETS;
+    if (buckets) cudaMemsetAsync(img.tile_count, 0, sizeof(uint32_t) * (size_t)tiles * 8, st);
     {
         StageScope _s(AS_STAGE_PREPROCESS, st, 1);
-        launch_frame_preprocess(*a, g, a->status, st);
+        launch_frame_preprocess(*a, g, a->status, buckets ? img.tile_count : nullptr, st);
     }
     if ((r = stage_check(st, a->debug))) return r;
-    if (cap > 0) {
-        {
-            StageScope _s(AS_STAGE_DUPLICATE, st, 1);
-            launch_frame_duplicate(P, g, W, H, (uint32_t)cap, b.keys_unsorted, b.values_unsorted, a->status, st);
+    if (buckets) {
+        // tile-bucket binning: scan of per-tile counts, scatter, per-tile sort fused with the record gather
+        StageScope _s(AS_STAGE_SORT, st, cap > 0 ? 3 : 1);
+        launch_frame_tile_binning(P, g, W, H, (uint32_t)cap, a->rgb_colors, b, img, a->status, st);
+    } else {
+        if (cap > 0) {
+            {
+                StageScope _s(AS_STAGE_DUPLICATE, st, 1);
+                launch_frame_duplicate(P, g, W, H, (uint32_t)cap, b.keys_unsorted, b.values_unsorted, a->status, st);
+            }
+            if ((r = stage_check(st, a->debug))) return r;
+            const int bit = (int)as_higher_msb((uint32_t)tiles);
+            {
+                StageScope _s(AS_STAGE_SORT, st, 4 + (32 + bit + 7) / 8);
+                launch_sort_pairs(b.keys_unsorted, b.values_unsorted, b.keys_sorted, b.point_list, cap, 32 + bit,
+                                  b.sort_temp, st, a->status);
+            }
+            if ((r = stage_check(st, a->debug))) return r;
         }
-        if ((r = stage_check(st, a->debug))) return r;
-        const int bit = (int)as_higher_msb((uint32_t)tiles);
         {
-            StageScope _s(AS_STAGE_SORT, st, 4 + (32 + bit + 7) / 8);
-            launch_sort_pairs(b.keys_unsorted, b.values_unsorted, b.keys_sorted, b.point_list, cap, 32 + bit, b.sort_temp,
-                              st, a->status);
+            StageScope _s(AS_STAGE_RANGES_GATHER, st, 1);
+            launch_frame_ranges_gather(a->status, (uint32_t)cap, tiles, g, a->rgb_colors, b, img.ranges, st);
         }
-        if ((r = stage_check(st, a->debug))) return r;
-    }
-    {
-        StageScope _s(AS_STAGE_RANGES_GATHER, st, 1);
-        launch_frame_ranges_gather(a->status, (uint32_t)cap, tiles, g, a->rgb_colors, b, img.ranges, st);
     }
     if ((r = stage_check(st, a->debug))) return r;
     {
@@ -391,6 +401,7 @@ int as_frame_backward(const AsFrameBackwardArgs* ba, void* cuda_stream) {
 }
 
 size_t as_pose_scratch_floats(int P) { return pose_scratch_floats(P > 0 ? P : 0); }
+int as_tile_sort_capacity(void) { return tile_sort_capacity(); }
 
 size_t as_loss_scratch_floats(int width, int height) { return (size_t)loss_partial_blocks(width * height) * 4 + 16; }
 

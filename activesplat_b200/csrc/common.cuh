@@ -49,6 +49,8 @@ struct ImageState {  // per pixel / per tile
     float* final_T;       // [N]
     uint32_t* n_contrib;  // [N]
     uint2* ranges;        // [tiles]
+    uint32_t* tile_count;   // [tiles] instances per tile (frame path, tile-bucket binning)
+    uint32_t* tile_cursor;  // [tiles] next free slot of each tile's bucket
     static ImageState fromChunk(char*& chunk, size_t N, size_t tiles);
 };
 
@@ -134,7 +136,12 @@ void launch_preprocess_backward(int P, int channels, const float* means3D, const
 constexpr int GACC_STRIDE = 12;
 
 // ---- fused frame path (fused.cu) ----
-void launch_frame_preprocess(const AsFrameArgs& a, const GeometryState& g, uint32_t* status, cudaStream_t st);
+// tile_count != NULL (zeroed by the caller): also counts the instances every tile will receive
+void launch_frame_preprocess(const AsFrameArgs& a, const GeometryState& g, uint32_t* status, uint32_t* tile_count,
+                             cudaStream_t st);
+// tile-bucket binning: scan of the tile counts -> ranges, scatter into buckets, per-tile sort + record gather
+void launch_frame_tile_binning(int P, const GeometryState& g, int W, int H, uint32_t capacity, const float* rgb,
+                               const BinningState& b, const ImageState& img, uint32_t* status, cudaStream_t st);
 void launch_frame_duplicate(int P, const GeometryState& g, int W, int H, uint32_t capacity, uint64_t* keys,
                             uint32_t* values, uint32_t* status, cudaStream_t st);
 void launch_frame_ranges_gather(const uint32_t* n_dev, uint32_t capacity, int tiles, const GeometryState& g,
@@ -143,6 +150,7 @@ void launch_frame_preprocess_backward(const AsFrameArgs& a, const GeometryState&
                                       int gaussians_grad, int camera_grad, int accumulate, float* grad_params,
                                       float* grad_means2D, float* pose_acc, float* grad_cam, int grad_cam_stride,
                                       cudaStream_t st);
+int tile_sort_capacity();
 int loss_partial_blocks(int N);
 size_t pose_scratch_floats(int P);
 void launch_tracking_loss(int N, const float* c6, const float* gt_rgb, const float* gt_depth, float w_im,

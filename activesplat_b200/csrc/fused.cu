@@ -119,6 +119,10 @@ __device__ __forceinline__ void load_rows(const float* __restrict__ src, int row
 
 // Look-back state of the scan fused into frame_preprocess_kernel: one u64 per block,
 // flag (2 bits, 62..63) | visible count (24 bits, 32..55) | tiles touched (32 bits, 0..31).
+// tile-bucket binning: every tile's counter is split TB_SUB ways (by Gaussian id) so that the atomics of a
+// crowded tile do not all serialise on one address; a tile's bucket is its TB_SUB sub-buckets back to back
+constexpr int TB_SUB = 8;
+
 constexpr uint64_t FPS_AGG = 1ull << 62;
 constexpr uint64_t FPS_PREFIX = 2ull << 62;
 constexpr uint64_t FPS_VALUE_MASK = (1ull << 56) - 1ull;
@@ -135,7 +139,8 @@ frame_preprocess_kernel(int P, const float* __restrict__ means3D, const float* _
                         float* __restrict__ depths, float4* __restrict__ conic_opacity,
                         uint32_t* __restrict__ point_offsets, float* __restrict__ zsil,
                         uint32_t* __restrict__ vis_list, uint32_t* ticket, uint64_t* scan_status, uint32_t* status,
-                        float* __restrict__ max_2D_radius, uint8_t* __restrict__ seen) {
+                        float* __restrict__ max_2D_radius, uint8_t* __restrict__ seen,
+                        uint32_t* __restrict__ tile_count) {
     __shared__ __align__(16) float s_means[FP_THREADS * 3];
     __shared__ __align__(16) float s_ls[FP_THREADS * 3];
     __shared__ float s_view[16], s_proj[16];
@@ -178,6 +183,13 @@ frame_preprocess_kernel(int P, const float* __restrict__ means3D, const float* _
                 means2D_out[idx] = r.mean2D;
                 conic_opacity[idx] = r.conic_opacity;
                 zsil[idx] = ps.sil[0] * a.mc[0] + ps.sil[1] * a.mc[1] + ps.sil[2] * a.mc[2] + ps.sil[3];
+                if (tile_count) {  // tile-bucket binning: how many instances each tile will receive
+                    int x0, y0, x1, y1;
+                    get_rect(r.mean2D.x, r.mean2D.y, r.radius, gx, gy, x0, y0, x1, y1);
+                    const uint32_t sub = (uint32_t)idx & (TB_SUB - 1);
+                    for (int y = y0; y < y1; y++)
+                        for (int x = x0; x < x1; x++) atomicAdd(tile_count + ((y * gx + x) * TB_SUB + sub), 1u);
+                }
             }
         }
         if (radii) radii[idx] = my_radii;
@@ -306,6 +318,192 @@ frame_ranges_gather_kernel(const uint32_t* __restrict__ n_dev, uint32_t capacity
     const float* c = rgb + 3 * (size_t)id;
     inst_feat[2 * (size_t)i] = make_float4(__ldg(c), __ldg(c + 1), __ldg(c + 2), z);
     inst_feat[2 * (size_t)i + 1] = make_float4(1.f, z * z, pack_cull_extent(co), 0.f);
+}
+
+// ---- tile-bucket binning (AsFrameArgs.binning_mode = 1) -------------------------------------------------
+// The reference sorts all R (tile, depth) keys globally (rasterizer_impl.cu:305-310).  The tile part of the key is
+// known before any sorting, so here every tile gets its own bucket: the preprocess counts instances per tile, one
+// block scans the counts into tile ranges, the scatter drops (depth bits << 32 | Gaussian id) into the tile's
+// bucket in arrival order, and one CTA per tile sorts its bucket in shared memory and gathers the records.
+// Sorting by (depth, id) reproduces the stable radix sort exactly: the reference emits instances in ascending
+// Gaussian id, so equal (tile, depth) keys stay in id order.
+constexpr int TS_THREADS = 256;
+constexpr int TS_CAP = 4096;  // instances per tile sorted in shared memory; larger buckets are sorted in place (slow)
+
+__global__ void __launch_bounds__(1024)
+frame_tile_scan_kernel(const uint32_t* __restrict__ tile_count, int tiles, uint32_t capacity, uint2* __restrict__ ranges,
+                       uint32_t* __restrict__ cursor, uint32_t* status) {
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_max;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_max = 0;
+    __syncthreads();
+    const bool overflow = status[0] > capacity;  // num_rendered (written by the preprocess) exceeds the buffer
+    // every thread owns `per` consecutive tiles (TB_SUB sub-counters each): local sums, one block scan, write-out
+    const int per = (tiles + 1023) / 1024;
+    const int t0 = threadIdx.x * per, t1 = min(tiles, t0 + per);
+    uint32_t mine = 0, biggest = 0;
+    for (int t = t0; t < t1; t++) {
+        const uint4* p = reinterpret_cast<const uint4*>(tile_count + (size_t)t * TB_SUB);
+        uint32_t c = 0;
+#pragma unroll
+        for (int q = 0; q < TB_SUB / 4; q++) {
+            const uint4 v = p[q];
+            c += v.x + v.y + v.z + v.w;
+        }
+        mine += c;
+        biggest = max(biggest, c);
+    }
+    uint32_t incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    const uint32_t wmax = __reduce_max_sync(0xffffffffu, biggest);
+    if (lane == 0) atomicMax(&s_max, wmax);
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t w = s_warp[lane], wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += v;
+        }
+        s_warp[lane] = wi - w;  // exclusive offset of each warp
+    }
+    __syncthreads();
+    uint32_t run = s_warp[warp] + incl - mine;
+    for (int t = t0; t < t1; t++) {
+        const uint4* p = reinterpret_cast<const uint4*>(tile_count + (size_t)t * TB_SUB);
+        const uint32_t start = run;
+#pragma unroll
+        for (int q = 0; q < TB_SUB / 4; q++) {
+            const uint4 v = p[q];
+            uint4 cur;
+            cur.x = run; run += v.x;
+            cur.y = run; run += v.y;
+            cur.z = run; run += v.z;
+            cur.w = run; run += v.w;
+            reinterpret_cast<uint4*>(cursor + (size_t)t * TB_SUB)[q] = cur;
+        }
+        // untouched tiles keep {0,0} like identifyTileRanges leaves them (rasterizer_impl.cu:116-138)
+        ranges[t] = (run > start && !overflow) ? make_uint2(start, run) : make_uint2(0u, 0u);
+    }
+    if (threadIdx.x == 0) {
+        status[3] = s_max;
+        if (overflow) status[1] = 1;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+frame_scatter_kernel(const uint32_t* __restrict__ vis_list, const float2* __restrict__ means2D,
+                     const float* __restrict__ depths, const int* __restrict__ radii, int gx, int gy,
+                     uint32_t* __restrict__ cursor, uint64_t* __restrict__ entries, const uint32_t* __restrict__ status) {
+    if (status[1]) return;  // overflow: nothing may be written
+    const uint32_t nvis = status[2];
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= nvis) return;
+    const uint32_t idx = vis_list[slot];
+    const float2 p = means2D[idx];
+    int x0, y0, x1, y1;
+    get_rect(p.x, p.y, radii[idx], gx, gy, x0, y0, x1, y1);
+    const uint64_t e = ((uint64_t)__float_as_uint(depths[idx]) << 32) | idx;
+    const uint32_t sub = idx & (TB_SUB - 1);
+    // the slot of a tile comes back from an atomic: keep eight of them in flight before the dependent stores
+    const int w = x1 - x0, total = w * (y1 - y0);
+    int x = x0, y = y0;
+    for (int base = 0; base < total; base += 8) {
+        uint32_t pos[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            if (base + u < total) {
+                pos[u] = atomicAdd(cursor + ((y * gx + x) * TB_SUB + sub), 1u);
+                if (++x == x1) { x = x0; y++; }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 8; u++)
+            if (base + u < total) entries[pos[u]] = e;
+    }
+}
+
+// compare-exchange network, ascending only (first step of every merge mirrors the upper half), so the
+// missing tail of a bucket whose size is not a power of two behaves like +infinity and never moves.
+// Compare-exchange t of a stage touches only the aligned 64-element block 2*32*(t/32).. when the stage's span is
+// at most 64, and each warp always takes the same t's: those stages need only a warp-level barrier.
+__device__ __forceinline__ void stage_barrier(bool block_wide) {
+    if (block_wide) __syncthreads();
+    else __syncwarp();
+}
+
+template <class Ptr>
+__device__ __forceinline__ void bitonic_sort_ascending(Ptr a, int n, int nthreads) {
+    int npow2 = 1;
+    while (npow2 < n) npow2 <<= 1;
+    for (int k = 2, lk = 1; k <= npow2; k <<= 1, lk++) {  // k = 1 << lk
+        for (int t = threadIdx.x; t < npow2 / 2; t += nthreads) {
+            const int blk = t >> (lk - 1), off = t & ((k >> 1) - 1);
+            const int i = (blk << lk) + off, j = (blk << lk) + k - 1 - off;
+            if (j < n) {
+                const uint64_t x = a[i], y = a[j];
+                if (x > y) { a[i] = y; a[j] = x; }
+            }
+        }
+        stage_barrier(k > 64);  // what follows has a smaller span (or, for k == 2, span 4)
+        for (int js = k >> 2, ljs = lk - 2; js > 0; js >>= 1, ljs--) {  // js = 1 << ljs
+            for (int t = threadIdx.x; t < npow2 / 2; t += nthreads) {
+                const int i = ((t >> ljs) << (ljs + 1)) + (t & (js - 1)), j = i + js;
+                if (j < n) {
+                    const uint64_t x = a[i], y = a[j];
+                    if (x > y) { a[i] = y; a[j] = x; }
+                }
+            }
+            // the next stage is either js/2 of this merge or, after js == 1, the span-2k flip of the next merge
+            const int next_span = js > 1 ? js : 2 * k;
+            stage_barrier(2 * js > 64 || next_span > 64);
+        }
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(TS_THREADS)
+frame_tile_sort_gather_kernel(const uint2* __restrict__ ranges, uint64_t* __restrict__ entries,
+                              uint32_t* __restrict__ point_list, const float2* __restrict__ means2D,
+                              const float4* __restrict__ conic_opacity, const float* __restrict__ rgb,
+                              const float* __restrict__ zsil, float4* __restrict__ inst_conic,
+                              float4* __restrict__ inst_geom, float4* __restrict__ inst_feat,
+                              const uint32_t* __restrict__ status) {
+    __shared__ uint64_t s_e[TS_CAP];
+    if (status[1]) return;
+    const uint2 range = ranges[blockIdx.x];
+    const int n = (int)(range.y - range.x);
+    if (n <= 0) return;
+    uint64_t* ge = entries + range.x;
+    const bool in_smem = n <= TS_CAP;
+    if (in_smem) {
+        for (int i = threadIdx.x; i < n; i += TS_THREADS) s_e[i] = ge[i];
+        __syncthreads();
+        bitonic_sort_ascending(s_e, n, TS_THREADS);
+    } else {
+        __syncthreads();
+        bitonic_sort_ascending(ge, n, TS_THREADS);  // global memory is coherent within the block across the barriers
+    }
+    for (int i = threadIdx.x; i < n; i += TS_THREADS) {
+        const uint64_t e = in_smem ? s_e[i] : ge[i];
+        const uint32_t id = (uint32_t)e;
+        const size_t o = (size_t)range.x + i;
+        point_list[o] = id;
+        const float2 m = __ldg(means2D + id);
+        const float4 co = __ldg(conic_opacity + id);
+        inst_conic[o] = co;
+        inst_geom[o] = make_float4(m.x, m.y, __uint_as_float((uint32_t)(e >> 32)), __uint_as_float(id));
+        const float z = __ldg(zsil + id);
+        const float* c = rgb + 3 * (size_t)id;
+        inst_feat[2 * o] = make_float4(__ldg(c), __ldg(c + 1), __ldg(c + 2), z);
+        inst_feat[2 * o + 1] = make_float4(1.f, z * z, pack_cull_extent(co), 0.f);
+    }
 }
 
 // Block-wide sum of NV per-thread values -> out[NV] (plain stores: one row of partials per block; a
@@ -673,7 +871,8 @@ adam_kernel(int P, int iso, AdamPtrs ap, const float* __restrict__ grad, float* 
 }  // namespace
 
 // ---- host launchers --------------------------------------------------------------------------------
-void launch_frame_preprocess(const AsFrameArgs& a, const GeometryState& g, uint32_t* status, cudaStream_t st) {
+void launch_frame_preprocess(const AsFrameArgs& a, const GeometryState& g, uint32_t* status, uint32_t* tile_count,
+                             cudaStream_t st) {
     const int P = a.P, W = a.width, H = a.height;
     // ticket + one look-back word per 256-Gaussian slab (same footprint as the stand-alone scan's temp)
     cudaMemsetAsync(g.scan_temp, 0, 16 + sizeof(uint64_t) * (size_t)((P + FP_THREADS - 1) / FP_THREADS), st);
@@ -686,14 +885,27 @@ void launch_frame_preprocess(const AsFrameArgs& a, const GeometryState& g, uint3
             a.cam_trans, a.cam_trans_stride, a.sil_w2c, a.viewmatrix, a.projmatrix, W, H, gx, gy, a.tan_fovx, a.tan_fovy,
             focal_x, focal_y, a.scale_modifier, a.radii, g.radii, g.means2D, g.depths, g.conic_opacity, g.point_offsets,
             g.zsil, g.vis_list, g.scan_temp, reinterpret_cast<uint64_t*>(g.scan_temp + 4), status, a.max_2D_radius,
-            a.seen);
+            a.seen, tile_count);
     else
         frame_preprocess_kernel<false><<<blocks, FP_THREADS, 0, st>>>(
             P, a.means3D, a.unnorm_rotations, a.logit_opacities, a.log_scales, a.cam_unnorm_rot, a.cam_rot_stride,
             a.cam_trans, a.cam_trans_stride, a.sil_w2c, a.viewmatrix, a.projmatrix, W, H, gx, gy, a.tan_fovx, a.tan_fovy,
             focal_x, focal_y, a.scale_modifier, a.radii, g.radii, g.means2D, g.depths, g.conic_opacity, g.point_offsets,
             g.zsil, g.vis_list, g.scan_temp, reinterpret_cast<uint64_t*>(g.scan_temp + 4), status, a.max_2D_radius,
-            a.seen);
+            a.seen, tile_count);
+}
+
+void launch_frame_tile_binning(int P, const GeometryState& g, int W, int H, uint32_t capacity, const float* rgb,
+                               const BinningState& b, const ImageState& img, uint32_t* status, cudaStream_t st) {
+    const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y, tiles = gx * gy;
+    frame_tile_scan_kernel<<<1, 1024, 0, st>>>(img.tile_count, tiles, capacity, img.ranges, img.tile_cursor, status);
+    if (capacity == 0) return;
+    // one thread per slot of the compact visible list; the count is only known on the device
+    frame_scatter_kernel<<<(P + 255) / 256, 256, 0, st>>>(g.vis_list, g.means2D, g.depths, g.radii, gx, gy,
+                                                                 img.tile_cursor, b.keys_unsorted, status);
+    frame_tile_sort_gather_kernel<<<tiles, TS_THREADS, 0, st>>>(img.ranges, b.keys_unsorted, b.point_list, g.means2D,
+                                                                g.conic_opacity, rgb, g.zsil, b.inst_conic, b.inst_geom,
+                                                                b.inst_feat, status);
 }
 
 void launch_frame_duplicate(int P, const GeometryState& g, int W, int H, uint32_t capacity, uint64_t* keys,
@@ -736,6 +948,8 @@ void launch_frame_preprocess_backward(const AsFrameArgs& a, const GeometryState&
         pose_finalize_kernel<<<1, 256, 0, st>>>(a.cam_unnorm_rot, a.cam_rot_stride, pose_acc, blocks, a.status, grad_cam,
                                                 grad_cam_stride > 0 ? grad_cam_stride : 1);
 }
+
+int tile_sort_capacity() { return TS_CAP; }
 
 size_t pose_scratch_floats(int P) { return 16 * (size_t)((P + FP_THREADS - 1) / FP_THREADS) + 16; }
 

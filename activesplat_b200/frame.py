@@ -26,8 +26,12 @@ class FrameWorkspace:
     One workspace supports one forward/backward pair in flight.
     """
 
-    def __init__(self, P, width, height, device, capacity=None, want_means2D_grad=False):
+    def __init__(self, P, width, height, device, capacity=None, want_means2D_grad=False, binning=None):
+        """binning: None = choose on the first frame (tile buckets unless a tile holds more instances than one
+        CTA sorts in shared memory), 0 = global radix sort, 1 = tile buckets.  Results are identical."""
         L = capi.lib()
+        self.binning_mode = 1 if binning is None else int(binning)
+        self._binning_auto = binning is None
         self.P, self.W, self.H, self.device = int(P), int(width), int(height), torch.device(device)
         self.capacity = int(capacity) if capacity else max(4 * self.P, 1 << 16)
         with torch.cuda.device(self.device):
@@ -53,7 +57,7 @@ class FrameWorkspace:
         self._keep = None
         self._bg_src = None
         self.map_scratch = None
-        self.calibrated = capacity is not None  # an explicit capacity is taken as is
+        self.calibrated = capacity is not None  # an explicit capacity is taken as is (and so is the binning mode)
 
     # -- buffer management ---------------------------------------------------------------------
     def ensure_capacity(self, needed):
@@ -116,6 +120,7 @@ class FrameWorkspace:
         a.debug = int(bool(debug))
         a.max_2D_radius = max_2D_radius.data_ptr() if max_2D_radius is not None else None
         a.seen = seen.data_ptr() if seen is not None else None
+        a.binning_mode = self.binning_mode
         with torch.cuda.device(self.device):
             stream = torch.cuda.current_stream(self.device).cuda_stream
             capi.check(L.as_frame_forward(ctypes.byref(a), stream))
@@ -124,8 +129,13 @@ class FrameWorkspace:
                 # buffer with head-room (2x); after that the path never synchronises and an overflow shows up as
                 # a NaN loss / last_status()
                 self.calibrated = True
-                n, _ = self.last_status()
-                if self.ensure_capacity(2 * n):
+                s = self.status.tolist()
+                rerun = self.ensure_capacity(2 * int(s[0]))
+                if self._binning_auto and self.binning_mode == 1 and (s[1] or int(s[3]) > L.as_tile_sort_capacity()):
+                    # crowded tiles (low-resolution wide-angle views): the global sort handles any distribution
+                    self.binning_mode = a.binning_mode = 0
+                    rerun = True
+                if rerun:
                     a.binning_buffer, a.binning_capacity = self.binning.data_ptr(), self.capacity
                     capi.check(L.as_frame_forward(ctypes.byref(a), stream))
         self._args, self._keep = a, keep

@@ -144,6 +144,13 @@ int as_scratch_layout(int P, int width, int height, int num_rendered, int channe
  * status[1] is set to 1, nothing is written out of bounds, and the frame's outputs are invalid
  * (re-run with a larger buffer).  The three scratch buffers are caller-owned and reused across
  * frames; geom_buffer must be zero-filled once when it is created (as_geometry_bytes(P) bytes). */
+/* How as_frame_forward orders the (tile, depth) instances.  Both produce the reference's sorted list exactly.
+ *   AS_BINNING_GLOBAL_SORT   radix sort of all 64-bit keys (CudaRasterizer: rasterizer_impl.cu:305-310); any scene.
+ *   AS_BINNING_TILE_BUCKETS  per-tile buckets filled with atomics, each sorted by (depth, Gaussian id) by one CTA;
+ *                            fastest while no tile holds more than a few thousand instances (status[3] reports the
+ *                            largest bucket); bigger buckets are still sorted correctly, only slowly. */
+#define AS_BINNING_GLOBAL_SORT 0
+#define AS_BINNING_TILE_BUCKETS 1
 typedef struct AsFrameArgs {
     int P, width, height;
     int isotropic;                 /* log_scales is [P,1] (rotations then pass through un-transformed) */
@@ -165,7 +172,8 @@ typedef struct AsFrameArgs {
     char* image_buffer;
     char* binning_buffer;
     int binning_capacity;
-    uint32_t* status;              /* [4] device words: [0] num_rendered, [1] overflow flag, [2] visible Gaussians */
+    uint32_t* status;              /* [4] device words: [0] num_rendered, [1] overflow flag, [2] visible Gaussians,
+                                      [3] largest number of instances in one tile (binning_mode 1 only) */
     float* out_color;              /* [6,H,W]: rgb | depth, silhouette, depth^2 */
     float* out_depth;              /* [1,H,W] median depth */
     float* out_opacity;            /* [1,H,W] */
@@ -173,6 +181,7 @@ typedef struct AsFrameArgs {
     int debug;
     float* max_2D_radius;          /* [P] or NULL: updated in place, max(radius, .) where seen (splatam.py:296-298) */
     uint8_t* seen;                 /* [P] bool or NULL: radius > 0 */
+    int binning_mode;              /* AS_BINNING_GLOBAL_SORT (0) or AS_BINNING_TILE_BUCKETS (1); same results */
 } AsFrameArgs;
 
 typedef struct AsFrameBackwardArgs {
@@ -190,6 +199,7 @@ typedef struct AsFrameBackwardArgs {
 } AsFrameBackwardArgs;
 
 size_t as_pose_scratch_floats(int P);
+int as_tile_sort_capacity(void);   /* bucket size up to which AS_BINNING_TILE_BUCKETS sorts a tile in shared memory */
 int as_frame_forward(const AsFrameArgs* args, void* cuda_stream);
 int as_frame_backward(const AsFrameBackwardArgs* args, void* cuda_stream);
 
