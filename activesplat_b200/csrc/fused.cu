@@ -127,7 +127,11 @@ constexpr uint64_t FPS_AGG = 1ull << 62;
 constexpr uint64_t FPS_PREFIX = 2ull << 62;
 constexpr uint64_t FPS_VALUE_MASK = (1ull << 56) - 1ull;
 
-template <bool ISO>
+// ORDERED: point_offsets (the inclusive scan of tiles touched, rasterizer_impl.cu:279) and the visible list come out
+// in Gaussian order through a decoupled look-back -- what the global sort's duplicateWithKeys needs.  With tile
+// buckets nothing depends on that order, so blocks just reserve their span of the visible list with one atomic
+// and add their totals to status[0] / status[2] (zeroed by the launcher): no block ever waits for another.
+template <bool ISO, bool ORDERED>
 __global__ void __launch_bounds__(FP_THREADS)
 frame_preprocess_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ unnorm_rot,
                         const float* __restrict__ logit_op, const float* __restrict__ log_scales,
@@ -148,11 +152,18 @@ frame_preprocess_kernel(int P, const float* __restrict__ means3D, const float* _
     __shared__ uint32_t s_block;
     __shared__ uint32_t s_wt[FP_THREADS / 32], s_wv[FP_THREADS / 32];
     __shared__ uint32_t s_pref_t, s_pref_v;
+    __shared__ int s_rad[FP_THREADS];
+    __shared__ uint32_t s_til[FP_THREADS];
+    __shared__ uint16_t s_cand[FP_THREADS];
+    __shared__ uint32_t s_ncand;
+    __shared__ float s_bound_k;
     // blocks take their slab in the order they start, so the look-back below can never wait on a
     // block that has not been scheduled yet
-    if (threadIdx.x == 0) s_block = atomicAdd(ticket, 1u);
-    __syncthreads();
-    const uint32_t blk = s_block;
+    if (ORDERED) {
+        if (threadIdx.x == 0) s_block = atomicAdd(ticket, 1u);
+        __syncthreads();
+    }
+    const uint32_t blk = ORDERED ? s_block : blockIdx.x;
     const int row0 = blk * FP_THREADS;
     const int nrows = min(FP_THREADS, P - row0);
     load_rows(means3D, row0, nrows, 3, s_means);
@@ -160,16 +171,79 @@ frame_preprocess_kernel(int P, const float* __restrict__ means3D, const float* _
     if (threadIdx.x < 16) s_view[threadIdx.x] = __ldg(viewmatrix + threadIdx.x);
     else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = __ldg(projmatrix + threadIdx.x - 16);
     else if (threadIdx.x == 32) load_pose(ps, cam_rot, rs, cam_trans, ts, sil_w2c);
-    if (blk == 0 && threadIdx.x == 0) status[1] = 0;  // overflow flag of this frame
+    else if (threadIdx.x == 64) {
+        // constant of the radius bound of phase A: |J|_F^2 tz^2 <= fx^2 (1 + (1.3 tanfovx)^2) + fy^2 (1 + (1.3 tanfovy)^2)
+        // (cov2d clamps tx/tz, ty/tz: forward.cu:82-87), times |W|_2^2 <= largest Gershgorin row sum of W^T W
+        float w[9];
+#pragma unroll
+        for (int i = 0; i < 3; i++)
+#pragma unroll
+            for (int j = 0; j < 3; j++) w[3 * i + j] = __ldg(viewmatrix + 4 * j + i);  // rotation part (transposed layout)
+        float gmax = 0.f;
+#pragma unroll
+        for (int i = 0; i < 3; i++) {
+            float rowsum = 0.f;
+#pragma unroll
+            for (int j = 0; j < 3; j++) rowsum += fabsf(w[i] * w[j] + w[3 + i] * w[3 + j] + w[6 + i] * w[6 + j]);
+            gmax = fmaxf(gmax, rowsum);
+        }
+        const float lx = 1.3f * tanfovx, ly = 1.3f * tanfovy;
+        s_bound_k = (focal_x * focal_x * (1.f + lx * lx) + focal_y * focal_y * (1.f + ly * ly)) * gmax;
+    }
+    if (ORDERED && blk == 0 && threadIdx.x == 0) status[1] = 0;  // overflow flag of this frame
     __syncthreads();
     const int idx = row0 + threadIdx.x;
-    int my_radii = 0;
-    uint32_t my_tiles = 0;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // ---- phase A (thread = Gaussian): cheap, conservative visibility test.  Usually most of the map is behind the
+    //      camera or off the image; the expensive per-Gaussian path below then runs densely over the candidates
+    //      instead of dragging every warp through it for a few scattered lanes.
+    //      A Gaussian is dropped here only if the reference would give it radius 0 / no tiles: near cull
+    //      (auxiliary.h:154), or an empty tile rectangle even for an upper bound of its radius:
+    //      lambda_max(cov2D + 0.3 I) <= trace(J W S W^T J^T) + 0.92 <= |J|_F^2 |W|_2^2 (mod * s_max)^2 + 0.92.
+    bool cand = false;
     if (idx < P) {
+        const float px = s_means[3 * threadIdx.x], py = s_means[3 * threadIdx.x + 1], pz = s_means[3 * threadIdx.x + 2];
+        const float m0 = fmaf(ps.R[2], pz, fmaf(ps.R[1], py, ps.R[0] * px)) + ps.t[0];  // as in activate()
+        const float m1 = fmaf(ps.R[5], pz, fmaf(ps.R[4], py, ps.R[3] * px)) + ps.t[1];
+        const float m2 = fmaf(ps.R[8], pz, fmaf(ps.R[7], py, ps.R[6] * px)) + ps.t[2];
+        const float pvz = xform_row(s_view, 2, m0, m1, m2);
+        if (pvz > 0.2f) {
+            const float* ls = s_ls + (ISO ? 1 : 3) * threadIdx.x;
+            const float smax = expf(ISO ? ls[0] : fmaxf(ls[0], fmaxf(ls[1], ls[2]))) * fabsf(scale_modifier);
+            const float tr = s_bound_k * smax * smax / (pvz * pvz);
+            const float rb = ceilf(3.f * sqrtf(tr * 1.001f + 0.93f)) + 1.f;
+            const float hx = xform_row(s_proj, 0, m0, m1, m2), hy = xform_row(s_proj, 1, m0, m1, m2);
+            const float hw = xform_row(s_proj, 3, m0, m1, m2);
+            const float p_w = __frcp_rn(__fadd_rn(hw, 0.0000001f));
+            const float pix_x = ndc2pix(__fmul_rn(hx, p_w), W), pix_y = ndc2pix(__fmul_rn(hy, p_w), H);
+            cand = true;
+            if (rb < 1e8f && pix_x == pix_x && pix_y == pix_y) {  // anything not finite goes down the exact path
+                int x0, y0, x1, y1;
+                get_rect(pix_x, pix_y, __float2int_rz(rb), gx, gy, x0, y0, x1, y1);
+                cand = (x1 - x0) * (y1 - y0) != 0;
+            }
+        }
+    }
+    {
+        const uint32_t bal = __ballot_sync(0xffffffffu, cand);
+        if (lane == 0) s_wv[warp] = __popc(bal);
+        s_rad[threadIdx.x] = 0;
+        s_til[threadIdx.x] = 0;
+        __syncthreads();
+        uint32_t off = 0;
+        for (int w = 0; w < warp; w++) off += s_wv[w];
+        if (cand) s_cand[off + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)threadIdx.x;
+        if (threadIdx.x == FP_THREADS - 1) s_ncand = off + __popc(bal);
+        __syncthreads();
+    }
+    // ---- phase B (thread = candidate): the exact per-Gaussian path ----
+    if (threadIdx.x < s_ncand) {
+        const int slot = s_cand[threadIdx.x];
+        const int cidx = row0 + slot;
         Activated a;
-        activate<ISO>(ps, s_means[3 * threadIdx.x], s_means[3 * threadIdx.x + 1], s_means[3 * threadIdx.x + 2],
-                      __ldg(reinterpret_cast<const float4*>(unnorm_rot) + idx), s_ls + (ISO ? 1 : 3) * threadIdx.x,
-                      __ldg(logit_op + idx), a);
+        activate<ISO>(ps, s_means[3 * slot], s_means[3 * slot + 1], s_means[3 * slot + 2],
+                      __ldg(reinterpret_cast<const float4*>(unnorm_rot) + cidx), s_ls + (ISO ? 1 : 3) * slot,
+                      __ldg(logit_op + cidx), a);
         if (xform_row(s_view, 2, a.mc[0], a.mc[1], a.mc[2]) > 0.2f) {
             float cov3D[6];
             cov3d_from_scale_rot(a.scale[0], a.scale[1], a.scale[2], scale_modifier,
@@ -177,21 +251,26 @@ frame_preprocess_kernel(int P, const float* __restrict__ means3D, const float* _
             const PreprocessResult r = preprocess_one(a.mc[0], a.mc[1], a.mc[2], cov3D, a.opacity, s_view, s_proj, W, H,
                                                       gx, gy, tanfovx, tanfovy, focal_x, focal_y);
             if (r.radius > 0) {
-                my_radii = r.radius;
-                my_tiles = r.tiles;
-                depths[idx] = r.depth;
-                means2D_out[idx] = r.mean2D;
-                conic_opacity[idx] = r.conic_opacity;
-                zsil[idx] = ps.sil[0] * a.mc[0] + ps.sil[1] * a.mc[1] + ps.sil[2] * a.mc[2] + ps.sil[3];
+                s_rad[slot] = r.radius;
+                s_til[slot] = r.tiles;
+                depths[cidx] = r.depth;
+                means2D_out[cidx] = r.mean2D;
+                conic_opacity[cidx] = r.conic_opacity;
+                zsil[cidx] = ps.sil[0] * a.mc[0] + ps.sil[1] * a.mc[1] + ps.sil[2] * a.mc[2] + ps.sil[3];
                 if (tile_count) {  // tile-bucket binning: how many instances each tile will receive
                     int x0, y0, x1, y1;
                     get_rect(r.mean2D.x, r.mean2D.y, r.radius, gx, gy, x0, y0, x1, y1);
-                    const uint32_t sub = (uint32_t)idx & (TB_SUB - 1);
+                    const uint32_t sub = (uint32_t)cidx & (TB_SUB - 1);
                     for (int y = y0; y < y1; y++)
                         for (int x = x0; x < x1; x++) atomicAdd(tile_count + ((y * gx + x) * TB_SUB + sub), 1u);
                 }
             }
         }
+    }
+    __syncthreads();
+    const int my_radii = s_rad[threadIdx.x];
+    const uint32_t my_tiles = s_til[threadIdx.x];
+    if (idx < P) {
         if (radii) radii[idx] = my_radii;
         radii_internal[idx] = my_radii;
         // bookkeeping of get_loss (splatam.py:296-298): max_2D_radius[seen] = max(radius, .), seen = radius > 0
@@ -200,7 +279,6 @@ frame_preprocess_kernel(int P, const float* __restrict__ means3D, const float* _
     }
     // ---- fused prefix sums (replaces the separate InclusiveSum launch, rasterizer_impl.cu:279):
     //      tiles touched -> point_offsets, visible count -> compact list of visible Gaussians ----
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const bool vis = my_radii > 0;
     uint32_t incl = my_tiles;
 #pragma unroll
@@ -219,7 +297,12 @@ frame_preprocess_kernel(int P, const float* __restrict__ means3D, const float* _
         tot_t += s_wt[w];
         tot_v += s_wv[w];
     }
-    if (warp == 0) {
+    if (!ORDERED) {
+        if (threadIdx.x == 0) {
+            s_pref_v = tot_v ? atomicAdd(status + 2, tot_v) : 0u;  // my span of the visible list
+            if (tot_t) atomicAdd(status + 0, tot_t);               // num_rendered
+        }
+    } else if (warp == 0) {
         // decoupled look-back, one warp wide: lane l inspects slab blk-1-l, the window slides back by 32
         const uint64_t mine = ((uint64_t)tot_v << 32) | tot_t;
         if (lane == 0 && blk > 0) st_volatile_u64(scan_status + blk, FPS_AGG | mine);
@@ -253,7 +336,7 @@ frame_preprocess_kernel(int P, const float* __restrict__ means3D, const float* _
     }
     __syncthreads();
     if (idx < P) {
-        point_offsets[idx] = s_pref_t + woff_t + incl;
+        if (ORDERED) point_offsets[idx] = s_pref_t + woff_t + incl;
         if (vis) vis_list[s_pref_v + woff_v + __popc(bal & ((1u << lane) - 1u))] = (uint32_t)idx;
     }
 }
@@ -545,14 +628,16 @@ frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const
     __shared__ float view[16], proj[16];
     __shared__ Pose ps;
     __shared__ float s_red[16 * 8];
-    if (threadIdx.x < 16) view[threadIdx.x] = __ldg(viewmatrix + threadIdx.x);
-    else if (threadIdx.x < 32) proj[threadIdx.x - 16] = __ldg(projmatrix + threadIdx.x - 16);
-    else if (threadIdx.x == 32) load_pose(ps, cam_rot, rs, cam_trans, ts, sil_w2c);
-    __syncthreads();
-    const float gs = gscale ? __ldg(gscale) : 1.f;
-    float pacc[16];
-#pragma unroll
-    for (int k = 0; k < 16; k++) pacc[k] = 0.f;
+    const int nvis = (int)status[2];
+    // blocks past the compact visible list have no per-Gaussian work: they only zero the rows of culled Gaussians
+    // (A) and leave at once -- no matrix loads, no barriers, no pose partials (pose_finalize_kernel reads the first
+    // ceil(V/256) rows only).  With ~20 % of the map visible that is most of the grid.
+    const bool has_dense_work = blockIdx.x * FP_THREADS < nvis;
+    if (has_dense_work) {
+        if (threadIdx.x < 16) view[threadIdx.x] = __ldg(viewmatrix + threadIdx.x);
+        else if (threadIdx.x < 32) proj[threadIdx.x - 16] = __ldg(projmatrix + threadIdx.x - 16);
+        else if (threadIdx.x == 32) load_pose(ps, cam_rot, rs, cam_trans, ts, sil_w2c);
+    }
     // (A) rows of culled Gaussians are zero
     {
         const int my = blockIdx.x * FP_THREADS + threadIdx.x;
@@ -569,10 +654,15 @@ frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const
             }
         }
     }
+    if (!has_dense_work) return;
+    __syncthreads();
+    const float gs = gscale ? __ldg(gscale) : 1.f;
+    float pacc[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) pacc[k] = 0.f;
     // (B) the long per-Gaussian path runs densely over the compact list of visible Gaussians that the
     //     forward wrote (visible ones are usually a scattered minority): the first ceil(V/256) blocks are
     //     full, the rest are done after (A)
-    const int nvis = (int)status[2];
     for (int slot = blockIdx.x * FP_THREADS + threadIdx.x; slot < nvis; slot += FP_THREADS * gridDim.x) {
     const int idx = (int)vis_list[slot];
     float out[14];
@@ -874,25 +964,29 @@ adam_kernel(int P, int iso, AdamPtrs ap, const float* __restrict__ grad, float* 
 void launch_frame_preprocess(const AsFrameArgs& a, const GeometryState& g, uint32_t* status, uint32_t* tile_count,
                              cudaStream_t st) {
     const int P = a.P, W = a.width, H = a.height;
-    // ticket + one look-back word per 256-Gaussian slab (same footprint as the stand-alone scan's temp)
-    cudaMemsetAsync(g.scan_temp, 0, 16 + sizeof(uint64_t) * (size_t)((P + FP_THREADS - 1) / FP_THREADS), st);
+    const bool ordered = tile_count == nullptr;
+    if (ordered)  // ticket + one look-back word per 256-Gaussian slab (same footprint as the stand-alone scan's temp)
+        cudaMemsetAsync(g.scan_temp, 0, 16 + sizeof(uint64_t) * (size_t)((P + FP_THREADS - 1) / FP_THREADS), st);
+    else          // the blocks add their totals into status[0] / status[2]; [1] is this frame's overflow flag
+        cudaMemsetAsync(status, 0, 4 * sizeof(uint32_t), st);
     const float focal_y = H / (2.0f * a.tan_fovy), focal_x = W / (2.0f * a.tan_fovx);
     const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
     const int blocks = (P + FP_THREADS - 1) / FP_THREADS;
-    if (a.isotropic)
-        frame_preprocess_kernel<true><<<blocks, FP_THREADS, 0, st>>>(
-            P, a.means3D, a.unnorm_rotations, a.logit_opacities, a.log_scales, a.cam_unnorm_rot, a.cam_rot_stride,
-            a.cam_trans, a.cam_trans_stride, a.sil_w2c, a.viewmatrix, a.projmatrix, W, H, gx, gy, a.tan_fovx, a.tan_fovy,
-            focal_x, focal_y, a.scale_modifier, a.radii, g.radii, g.means2D, g.depths, g.conic_opacity, g.point_offsets,
-            g.zsil, g.vis_list, g.scan_temp, reinterpret_cast<uint64_t*>(g.scan_temp + 4), status, a.max_2D_radius,
-            a.seen, tile_count);
-    else
-        frame_preprocess_kernel<false><<<blocks, FP_THREADS, 0, st>>>(
-            P, a.means3D, a.unnorm_rotations, a.logit_opacities, a.log_scales, a.cam_unnorm_rot, a.cam_rot_stride,
-            a.cam_trans, a.cam_trans_stride, a.sil_w2c, a.viewmatrix, a.projmatrix, W, H, gx, gy, a.tan_fovx, a.tan_fovy,
-            focal_x, focal_y, a.scale_modifier, a.radii, g.radii, g.means2D, g.depths, g.conic_opacity, g.point_offsets,
-            g.zsil, g.vis_list, g.scan_temp, reinterpret_cast<uint64_t*>(g.scan_temp + 4), status, a.max_2D_radius,
-            a.seen, tile_count);
+#define ASB_PP(ISO_, ORD_)                                                                                          \
+    frame_preprocess_kernel<ISO_, ORD_><<<blocks, FP_THREADS, 0, st>>>(                                             \
+        P, a.means3D, a.unnorm_rotations, a.logit_opacities, a.log_scales, a.cam_unnorm_rot, a.cam_rot_stride,      \
+        a.cam_trans, a.cam_trans_stride, a.sil_w2c, a.viewmatrix, a.projmatrix, W, H, gx, gy, a.tan_fovx,           \
+        a.tan_fovy, focal_x, focal_y, a.scale_modifier, a.radii, g.radii, g.means2D, g.depths, g.conic_opacity,     \
+        g.point_offsets, g.zsil, g.vis_list, g.scan_temp, reinterpret_cast<uint64_t*>(g.scan_temp + 4), status,     \
+        a.max_2D_radius, a.seen, tile_count)
+    if (a.isotropic) {
+        if (ordered) ASB_PP(true, true);
+        else ASB_PP(true, false);
+    } else {
+        if (ordered) ASB_PP(false, true);
+        else ASB_PP(false, false);
+    }
+#undef ASB_PP
 }
 
 void launch_frame_tile_binning(int P, const GeometryState& g, int W, int H, uint32_t capacity, const float* rgb,
