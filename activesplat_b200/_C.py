@@ -12,6 +12,7 @@ Differences a caller can observe:
   * the three scratch tensors have a different (private) layout -- they are opaque bytes to Python.
 """
 import ctypes
+import threading
 
 import torch
 
@@ -38,28 +39,46 @@ def _dev_ptr(t, name, keep):
 
 
 class _Scratch:
-    """Allocator callbacks: the library asks for bytes, torch's caching allocator provides them."""
+    """Allocator callbacks: the library asks for bytes, torch's caching allocator provides them.
+
+    One instance per device, created once: building ctypes callbacks on every call is slow, and a per-call object
+    whose closures point back at it is a reference cycle -- its scratch tensors (tens of MB) would then live until the
+    cyclic collector runs, and the caching allocator would keep growing in the meantime."""
+
+    _per_device = {}
 
     def __init__(self, device):
         self.device = device
         self.tensors = {}
         self.error = None
+        self.lock = threading.Lock()  # one as_forward at a time per device through this shim
+        tensors = self.tensors
+        state = self
 
         def make(tag):
             def alloc(_ctx, nbytes):
                 try:
-                    t = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
-                    self.tensors[tag] = t
+                    t = torch.empty(int(nbytes), dtype=torch.uint8, device=device)
+                    tensors[tag] = t
                     return t.data_ptr()
                 except Exception as e:  # surfaced after the C call returns AS_ERR_ALLOC
-                    self.error = e
+                    state.error = e
                     return None
             return capi.AllocFn(alloc)
 
         self.geom, self.binning, self.img = make("geom"), make("binning"), make("img")
 
-    def get(self, tag):
-        t = self.tensors.get(tag)
+    @classmethod
+    def for_device(cls, device):
+        key = (device.type, device.index)
+        s = cls._per_device.get(key)
+        if s is None:
+            s = cls._per_device[key] = cls(device)
+        return s
+
+    def take(self, tag):
+        """Hand the tensor to the caller (nothing stays referenced here)."""
+        t = self.tensors.pop(tag, None)
         return t if t is not None else torch.empty(0, dtype=torch.uint8, device=self.device)
 
 
@@ -81,7 +100,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         out_depth = torch.empty((1, H, W), **f32)
         out_opacity = torch.empty((1, H, W), **f32)
         radii = torch.empty((P,), dtype=torch.int32, device=dev)
-        scratch = _Scratch(dev)
+        scratch = _Scratch.for_device(dev)
         a = capi.AsForwardArgs()
         a.P, a.D, a.M, a.channels = P, int(degree), int(sh.size(1)) if sh.dim() > 1 and sh.size(0) != 0 else 0, C
         a.background = _dev_ptr(background, "background", keep)
@@ -103,12 +122,16 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         a.radii = radii.data_ptr() if P > 0 else None
         a.debug = int(bool(debug))
         stream = torch.cuda.current_stream(dev).cuda_stream
-        rc = L.as_forward(ctypes.byref(a), scratch.geom, scratch.binning, scratch.img, None, stream)
-        if rc == capi.AS_ERR_ALLOC and scratch.error is not None:
-            raise scratch.error
+        with scratch.lock:
+            scratch.tensors.clear()
+            scratch.error = None
+            rc = L.as_forward(ctypes.byref(a), scratch.geom, scratch.binning, scratch.img, None, stream)
+            bufs = (scratch.take("geom"), scratch.take("binning"), scratch.take("img"))
+            err = scratch.error
+        if rc == capi.AS_ERR_ALLOC and err is not None:
+            raise err
         capi.check(rc)
-    return (rc, out_color, radii, scratch.get("geom"), scratch.get("binning"), scratch.get("img"),
-            out_depth, out_opacity)
+    return (rc, out_color, radii, bufs[0], bufs[1], bufs[2], out_depth, out_opacity)
 
 
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,

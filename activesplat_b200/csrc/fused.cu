@@ -927,35 +927,93 @@ __global__ void tracking_loss_finalize_kernel(int nblocks, const float* __restri
 // F5 Adam (torch.optim.Adam semantics: no amsgrad, no weight decay), all five tensors in one pass.
 // grad/exp_avg/exp_avg_sq are [P,14] flat (means 3 | rgb 3 | rot 4 | logit 1 | log_scales 3).
 // ------------------------------------------------------------------------------------------------
-struct AdamPtrs {
-    float* p[5];
-    float lr[5];
+struct AdamPtrs {   // plain members (no arrays): indexing a kernel-parameter array at run time would spill it to local memory
+    float *p0, *p1, *p2, *p3, *p4;
+    float s0, s1, s2, s3, s4;   // lr[t] / bias_correction1
 };
 
-// One thread per flat element e of the [P,14] gradient / state arrays: those are read and written fully
-// coalesced; the five parameter tensors are touched at neighbouring addresses by neighbouring threads.
+constexpr int AD_G = 256;  // Gaussians per block
+
+// One block updates AD_G Gaussians.  Their slices of the five parameter tensors are contiguous, so they are staged
+// through shared memory with coalesced accesses; the flat [P,14] gradient / exp_avg / exp_avg_sq rows of the block
+// are one contiguous span that the threads walk four elements at a time (128-bit accesses when aligned).
+// Arithmetic per element as torch.optim.Adam (single-tensor path): lerp_, mul_/addcmul_, sqrt / bias_correction2_sqrt
+// + eps, addcdiv_.
 __global__ void __launch_bounds__(256)
 adam_kernel(int P, int iso, AdamPtrs ap, const float* __restrict__ grad, float* __restrict__ m, float* __restrict__ v,
-            float beta1, float beta2, float eps, float bc1, float bc2_sqrt) {
-    const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= (size_t)P * 14) return;
-    const int idx = (int)(e / 14), slot = (int)(e - (size_t)idx * 14);
-    // slot -> (tensor, component): means 0-2 | rgb 3-5 | rotation 6-9 | logit opacity 10 | log scales 11-13
-    int t, k, width;
-    if (slot < 3) { t = 0; k = slot; width = 3; }
-    else if (slot < 6) { t = 1; k = slot - 3; width = 3; }
-    else if (slot < 10) { t = 2; k = slot - 6; width = 4; }
-    else if (slot < 11) { t = 3; k = 0; width = 1; }
-    else { t = 4; k = slot - 11; width = iso ? 1 : 3; if (k >= width) return; }  // isotropic: slots 12,13 unused
-    const float g = grad[e];
-    const float mm = m[e] + (g - m[e]) * (1.f - beta1);      // exp_avg.lerp_(grad, 1 - beta1)
-    const float vv = v[e] * beta2 + (1.f - beta2) * g * g;   // mul_(beta2).addcmul_(g, g, 1 - beta2)
-    m[e] = mm;
-    v[e] = vv;
-    const float denom = sqrtf(vv) / bc2_sqrt + eps;
-    const float step_size = ap.lr[t] / bc1;
-    float* p = ap.p[t] + (size_t)width * idx + k;
-    *p = *p - step_size * (mm / denom);                       // addcdiv_(exp_avg, denom, -step_size)
+            float beta1, float beta2, float eps, float bc2_sqrt) {
+    __shared__ __align__(16) float s_p[AD_G * 14];  // means [G,3] | rgb [G,3] | rot [G,4] | logit [G] | scales [G,3 or 1]
+    const int g0 = blockIdx.x * AD_G;
+    const int G = min(AD_G, P - g0);
+    const int ws = iso ? 1 : 3;
+    const int off1 = 3 * AD_G, off2 = 6 * AD_G, off3 = 10 * AD_G, off4 = 11 * AD_G;
+    // stage the parameters (scalar loads are already coalesced: consecutive threads, consecutive floats)
+    for (int i = threadIdx.x; i < 3 * G; i += 256) {
+        s_p[i] = ap.p0[3 * (size_t)g0 + i];
+        s_p[off1 + i] = ap.p1[3 * (size_t)g0 + i];
+    }
+    for (int i = threadIdx.x; i < 4 * G; i += 256) s_p[off2 + i] = ap.p2[4 * (size_t)g0 + i];
+    for (int i = threadIdx.x; i < G; i += 256) s_p[off3 + i] = ap.p3[(size_t)g0 + i];
+    for (int i = threadIdx.x; i < ws * G; i += 256) s_p[off4 + i] = ap.p4[ws * (size_t)g0 + i];
+    __syncthreads();
+    const size_t fbase = 14 * (size_t)g0;
+    const int nflat = 14 * G;
+    const bool vec = ((reinterpret_cast<uintptr_t>(grad + fbase) | reinterpret_cast<uintptr_t>(m + fbase) |
+                       reinterpret_cast<uintptr_t>(v + fbase)) & 15) == 0;
+    for (int e0 = 4 * threadIdx.x; e0 < nflat; e0 += 4 * 256) {
+        float g[4], mm[4], vv[4];
+        const int cnt = min(4, nflat - e0);
+        if (vec && cnt == 4) {
+            const float4 g4 = __ldg(reinterpret_cast<const float4*>(grad + fbase + e0));
+            const float4 m4 = *reinterpret_cast<const float4*>(m + fbase + e0);
+            const float4 v4 = *reinterpret_cast<const float4*>(v + fbase + e0);
+            g[0] = g4.x; g[1] = g4.y; g[2] = g4.z; g[3] = g4.w;
+            mm[0] = m4.x; mm[1] = m4.y; mm[2] = m4.z; mm[3] = m4.w;
+            vv[0] = v4.x; vv[1] = v4.y; vv[2] = v4.z; vv[3] = v4.w;
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+                if (i < cnt) { g[i] = grad[fbase + e0 + i]; mm[i] = m[fbase + e0 + i]; vv[i] = v[fbase + e0 + i]; }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            if (i >= cnt) break;
+            const int e = e0 + i;
+            const int il = e / 14, slot = e - il * 14;
+            // slot -> (tensor, component): means 0-2 | rgb 3-5 | rotation 6-9 | logit opacity 10 | log scales 11-13
+            int pos;
+            float step_size;
+            if (slot < 3) { pos = 3 * il + slot; step_size = ap.s0; }
+            else if (slot < 6) { pos = off1 + 3 * il + slot - 3; step_size = ap.s1; }
+            else if (slot < 10) { pos = off2 + 4 * il + slot - 6; step_size = ap.s2; }
+            else if (slot < 11) { pos = off3 + il; step_size = ap.s3; }
+            else { pos = off4 + ws * il + slot - 11; step_size = ap.s4; if (slot - 11 >= ws) continue; }  // isotropic: 12, 13 unused
+            const float nm = mm[i] + (g[i] - mm[i]) * (1.f - beta1);      // exp_avg.lerp_(grad, 1 - beta1)
+            const float nv = vv[i] * beta2 + (1.f - beta2) * g[i] * g[i];  // mul_(beta2).addcmul_(g, g, 1 - beta2)
+            mm[i] = nm;
+            vv[i] = nv;
+            // sqrt is correctly rounded; the two quotients use the 2-ulp fast division (parity bar on the updated
+            // parameters is 1e-5 relative; the IEEE division sequences tripled the kernel's instruction count)
+            const float denom = __fdividef(__fsqrt_rn(nv), bc2_sqrt) + eps;
+            s_p[pos] = s_p[pos] - step_size * __fdividef(nm, denom);      // addcdiv_(exp_avg, denom, -step_size)
+        }
+        if (vec && cnt == 4) {
+            *reinterpret_cast<float4*>(m + fbase + e0) = make_float4(mm[0], mm[1], mm[2], mm[3]);
+            *reinterpret_cast<float4*>(v + fbase + e0) = make_float4(vv[0], vv[1], vv[2], vv[3]);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+                if (i < cnt) { m[fbase + e0 + i] = mm[i]; v[fbase + e0 + i] = vv[i]; }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 3 * G; i += 256) {
+        ap.p0[3 * (size_t)g0 + i] = s_p[i];
+        ap.p1[3 * (size_t)g0 + i] = s_p[off1 + i];
+    }
+    for (int i = threadIdx.x; i < 4 * G; i += 256) ap.p2[4 * (size_t)g0 + i] = s_p[off2 + i];
+    for (int i = threadIdx.x; i < G; i += 256) ap.p3[(size_t)g0 + i] = s_p[off3 + i];
+    for (int i = threadIdx.x; i < ws * G; i += 256) ap.p4[ws * (size_t)g0 + i] = s_p[off4 + i];
 }
 
 }  // namespace
@@ -1063,15 +1121,12 @@ void launch_tracking_loss(int N, const float* c6, const float* gt_rgb, const flo
 
 void launch_adam(int P, int iso, float* const params[5], const float lr[5], const float* grad, float* m, float* v,
                  float beta1, float beta2, float eps, int step, cudaStream_t st) {
-    AdamPtrs ap;
-    for (int t = 0; t < 5; t++) {
-        ap.p[t] = params[t];
-        ap.lr[t] = lr[t];
-    }
     const float bc1 = 1.f - powf(beta1, (float)step);
     const float bc2_sqrt = sqrtf(1.f - powf(beta2, (float)step));
-    const size_t n = (size_t)P * 14;
-    adam_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(P, iso, ap, grad, m, v, beta1, beta2, eps, bc1, bc2_sqrt);
+    AdamPtrs ap;
+    ap.p0 = params[0]; ap.p1 = params[1]; ap.p2 = params[2]; ap.p3 = params[3]; ap.p4 = params[4];
+    ap.s0 = lr[0] / bc1; ap.s1 = lr[1] / bc1; ap.s2 = lr[2] / bc1; ap.s3 = lr[3] / bc1; ap.s4 = lr[4] / bc1;
+    adam_kernel<<<(P + AD_G - 1) / AD_G, 256, 0, st>>>(P, iso, ap, grad, m, v, beta1, beta2, eps, bc2_sqrt);
 }
 
 }  // namespace asb
