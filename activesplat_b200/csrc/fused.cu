@@ -613,7 +613,7 @@ __device__ __forceinline__ void block_reduce_store(float (&v)[NV], float* s_red 
 // Backward of frame_preprocess_kernel.  grad_params rows: means 3 | rgb 3 | rot 4 | logit 1 | log_scales 3.
 // pose_acc ([blocks,16] partial sums): dL/dt (3) | dL/dR (9, row-major) | dL/dq_cam through quat_mult (4).
 template <bool ISO>
-__global__ void __launch_bounds__(FP_THREADS)
+__global__ void __launch_bounds__(FP_THREADS, 4)
 frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ unnorm_rot,
                                  const float* __restrict__ logit_op, const float* __restrict__ log_scales,
                                  const float* __restrict__ cam_rot, int rs, const float* __restrict__ cam_trans, int ts,

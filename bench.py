@@ -313,14 +313,19 @@ def run_ours(args, rank, world, local_rank):
     achieved = ab.get(dom, 0) / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
     stage_ms = {s: round(v[0] / args.steps, 4) for s, v in stages.items() if v[1] > 0}
     # DRAM traffic of the dominant kernel: from the committed ncu --set full capture of the same workload
-    # (profiles/r1_ncu_kernels.json), per launch; not measured live (ncu cannot run inside a timed region)
+    # (profiles/r1_ncu_kernels_final.json, made by benchmarks/summarize_ncu.py), per launch; not measured live
+    # (ncu cannot run inside a timed region)
     traffic = None
     try:
-        ncu = json.load(open(os.path.join(ROOT, "profiles", "r1_ncu_kernels.json")))["kernels"]
-        kname = {"blend_bwd": "blend_backward_kernel<6>", "blend_fwd": "blend_forward_kernel<6>",
-                 "preprocess": "frame_preprocess_kernel<0>", "preprocess_bwd": "frame_preprocess_backward_kernel<0>"}.get(dom)
-        if kname in ncu and args.gaussians == 500_000 and (W, H) == (640, 480):
-            traffic = ncu[kname]["dram_bytes"]
+        ncu = json.load(open(os.path.join(ROOT, "profiles", "r1_ncu_kernels_final.json")))["kernels"]
+        prefix = {"blend_bwd": "blend_backward_kernel<6", "blend_fwd": "blend_forward_kernel<6",
+                  "preprocess": "frame_preprocess_kernel", "preprocess_bwd": "frame_preprocess_backward_kernel",
+                  "sort": "frame_tile_sort_gather_kernel"}.get(dom)
+        if prefix and args.gaussians == 500_000 and (W, H) == (640, 480):
+            for name, k in ncu.items():
+                if name.startswith(prefix):
+                    traffic = k["dram_bytes"]
+                    break
     except Exception:
         pass
     total_bytes = sum(ab.values())
