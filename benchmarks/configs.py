@@ -225,7 +225,7 @@ def cfg4(dev, RefRenderer, args, rank, world):
         if mk:
             fx, fy, cx, cy = scenes.compute_intrinsics(w, h, math.radians(90.0))
             views = [scenes.CameraSpec(w, h, fx, fy, cx, cy, v.w2c) for v in views]
-        n_streams = 8
+        n_streams = min(32, max(1, -(-n_views // world)))  # every view of the shard in flight: low-res views are latency-bound
         from activesplat_b200.frame import FrameWorkspace
         wss = [FrameWorkspace(P, w, h, dev) for _ in range(n_streams)]
 
