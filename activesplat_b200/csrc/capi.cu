@@ -448,6 +448,21 @@ int as_adam_step(int P, int isotropic, float* means3D, float* rgb_colors, float*
     return check(cudaGetLastError());
 }
 
+int as_dbscan_grid(int batch, int height, int width, const float* values, float value_threshold, float eps,
+                   int min_samples, int* labels, int* scratch, int max_clusters, int* n_clusters, int* stats_int,
+                   double* stats_value, void* cuda_stream) {
+    if (batch < 0 || height <= 0 || width <= 0 || max_clusters < 0 || min_samples < 1 || !(eps >= 0.f) || eps > 8.f)
+        return AS_ERR_INVALID_ARG;
+    if (batch == 0) return AS_OK;
+    if (!values || !labels || !scratch || !n_clusters || (max_clusters > 0 && (!stats_int || !stats_value)))
+        return AS_ERR_INVALID_ARG;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
+    StageScope _s(AS_STAGE_OTHER, st, 1);
+    launch_dbscan_grid(batch, height, width, values, value_threshold, eps, min_samples, labels, scratch, max_clusters,
+                       n_clusters, stats_int, stats_value, st);
+    return check(cudaGetLastError());
+}
+
 int as_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* /*projmatrix*/,
                     uint8_t* present, void* cuda_stream) {
     if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) return AS_ERR_INVALID_ARG;

@@ -344,6 +344,36 @@ def cfg5(dev, args, rank, world):
                      "keyframes_per_rank": len(mine)}}
 
 
+def scoring(dev):
+    """The step after the renders: get_invisibility_clusters on 256 down-sampled panoramas
+    (75x180), one as_dbscan_grid launch for the batch, next to the reference's CPU path (sklearn DBSCAN per image)."""
+    from activesplat_b200 import scoring as sc
+    from oracle import scoring_oracle as so
+    n = 256
+    imgs = np.stack([so.blob_image(s) for s in range(n)])
+    batch = torch.from_numpy(imgs).to(dev)
+    for _ in range(3):
+        sc.dbscan_grid(batch, 0.3, 5.0, 10)
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        labels, ncl, si, sv = sc.dbscan_grid(batch, 0.3, 5.0, 10)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / 10
+    t0 = time.time()
+    n_cpu = 16
+    for s in range(n_cpu):
+        so.get_invisibility_clusters(imgs[s], 30)
+    cpu_ms = (time.time() - t0) * 1e3 / n_cpu
+    ok = all(np.array_equal(labels[s].cpu().numpy(), so.dbscan_labels_image(imgs[s], 0.3, 5, 10)) for s in range(n_cpu))
+    return {"config": f"scoring: DBSCAN clusters of {n} panoramas 75x180 (eps 5, min_samples 10, invisibility > 0.3)",
+            "ours": {"ms_per_batch": ms, "images_per_s": n / ms * 1e3},
+            "cpu_sklearn": {"ms_per_image": cpu_ms, "images_per_s": 1e3 / cpu_ms, "images_timed": n_cpu, "cores": os.cpu_count()},
+            "labels_identical_on_checked_images": bool(ok)}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--configs", default="1,3,4")
@@ -370,6 +400,8 @@ def main():
             out["cfg4"] = cfg4(dev, RefRenderer, args, rank, world)
         elif c == 5:
             out["cfg5"] = cfg5(dev, args, rank, world)
+        elif c == 6 and rank == 0 and world == 1:
+            out["cfg6"] = scoring(dev)
         if rank == 0:
             print(json.dumps({k: v for k, v in out.items() if k == f"cfg{c}"}), flush=True)
     if rank == 0 and args.out:

@@ -233,6 +233,23 @@ int as_adam_step(int P, int isotropic, float* means3D, float* rgb_colors, float*
                  float* exp_avg_sq, const float* lrs, float beta1, float beta2, float eps, int step,
                  void* cuda_stream);
 
+/* ---- the step after the GetOpacity renders: clustering of low-visibility pixels ----------------
+ *
+ * DBSCAN over the pixels of `batch` images whose value exceeds value_threshold, replacing
+ * sklearn.cluster.DBSCAN(eps, min_samples).fit_predict(np.column_stack(np.where(img > thr))) as called by
+ * get_invisibility_clusters (src/mapper/__init__.py:92-117; eps 5, min_samples 10, threshold 0.3) and
+ * get_convexhull_volume (src/mapper/__init__.py:8-21; eps 5, min_samples 25, threshold 0.8).  The labels are
+ * sklearn's, bit for bit: clusters numbered in row-major order of their first core pixel, border pixels joined to
+ * the lowest-numbered cluster that reaches them, -1 = noise; -2 marks pixels that are not samples.
+ *   values       [batch,H,W] float (device)            labels   [batch,H,W] int32 out
+ *   scratch      [batch,H,W] int32 work space          n_clusters [batch] int32 out (may exceed max_clusters)
+ *   stats_int    [batch,max_clusters,3] int32 out: member count, sum of rows, sum of columns
+ *   stats_value  [batch,max_clusters] double out: sum of values over the members
+ * eps <= 8.  One CTA per image; asynchronous on the stream. */
+int as_dbscan_grid(int batch, int height, int width, const float* values, float value_threshold, float eps,
+                   int min_samples, int* labels, int* scratch, int max_clusters, int* n_clusters, int* stats_int,
+                   double* stats_value, void* cuda_stream);
+
 /* ---- stage-level entry points (used by the fused paths and by parity tests) ----------------- */
 
 /* Stable ascending LSD radix sort (hand-written onesweep) of n (u64 key, u32 value) pairs on key bits

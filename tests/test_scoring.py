@@ -1,0 +1,100 @@
+"""Clustering after the GetOpacity renders: get_invisibility_clusters (src/mapper/__init__.py:92-117).
+
+CPU: the oracle restatement against outputs of the reference's own function (tests/golden/ref_clusters.npz).
+GPU: as_dbscan_grid through activesplat_b200.scoring against sklearn's labels (bit-exact) and the same golden file."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import scoring_oracle as so
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_clusters.npz")
+
+
+def _golden():
+    with np.load(GOLDEN) as z:
+        return {k: z[k] for k in z.files}
+
+
+def test_oracle_matches_the_reference_function_outputs():
+    g = _golden()
+    for s in g["seeds"]:
+        centers, sums = so.get_invisibility_clusters(so.blob_image(int(s)), 30)
+        assert np.array_equal(np.array(centers, dtype=np.float64).reshape(-1, 2), g[f"centers_{s}"])
+        assert np.array_equal(np.array(sums, dtype=np.float32), g[f"sums_{s}"])
+
+
+def test_oracle_labels_image_conventions():
+    img = np.zeros((20, 30), np.float32)
+    lab = so.dbscan_labels_image(img, 0.3, 5, 10)
+    assert (lab == -2).all()                      # no samples at all (the reference returns [], [])
+    img[5:9, 5:9] = 1.0                           # 16 samples, every one within eps of >= 10 others
+    img[15, 25] = 1.0                             # an isolated sample: noise
+    lab = so.dbscan_labels_image(img, 0.3, 5, 10)
+    assert (lab[5:9, 5:9] == 0).all() and lab[15, 25] == -1 and (lab == -2).sum() == 20 * 30 - 17
+
+
+@pytest.mark.gpu
+def test_dbscan_grid_labels_are_sklearns():
+    from activesplat_b200 import scoring
+    imgs = [so.blob_image(s) for s in range(8)]
+    imgs.append(np.zeros((75, 180), np.float32))                       # empty
+    imgs.append(np.ones((75, 180), np.float32))                        # one cluster filling the image
+    chk = np.indices((75, 180)).sum(0) % 2                             # checkerboard: dense but every pixel a sample edge
+    imgs.append(chk.astype(np.float32))
+    two = np.zeros((75, 180), np.float32)                              # two clusters bridged by a thin line of border pixels
+    two[10:20, 10:20] = 1.0
+    two[10:20, 27:37] = 1.0
+    two[15, 20:27] = 1.0
+    imgs.append(two)
+    batch = torch.from_numpy(np.stack(imgs)).cuda()
+    for thr, eps, ms in ((0.3, 5.0, 10), (0.8, 5.0, 25), (0.3, 3.0, 4)):
+        labels, n, si, sv = scoring.dbscan_grid(batch, thr, eps=eps, min_samples=ms, max_clusters=128)
+        labels, n, si, sv = labels.cpu().numpy(), n.cpu().numpy(), si.cpu().numpy(), sv.cpu().numpy()
+        for b, img in enumerate(imgs):
+            want = so.dbscan_labels_image(img, thr, eps, ms)
+            assert np.array_equal(labels[b], want), (b, thr, eps, ms)          # bit-exact, noise and border pixels included
+            k = int(want.max()) + 1 if (want >= 0).any() else 0
+            assert n[b] == k
+            for c in range(k):
+                rows, cols = np.where(want == c)
+                assert si[b, c, 0] == len(rows) and si[b, c, 1] == rows.sum() and si[b, c, 2] == cols.sum()
+                assert abs(sv[b, c] - img[rows, cols].astype(np.float64).sum()) <= 1e-9 * max(1.0, len(rows))
+
+
+@pytest.mark.gpu
+def test_get_invisibility_clusters_matches_reference_outputs():
+    from activesplat_b200 import scoring
+    g = _golden()
+    for s in g["seeds"]:
+        img = torch.from_numpy(so.blob_image(int(s))).cuda()
+        centers, sums = scoring.get_invisibility_clusters(img, 30)
+        want_c, want_s = g[f"centers_{s}"], g[f"sums_{s}"]
+        assert len(sums) == len(want_s)
+        assert np.allclose(np.array(centers).reshape(-1, 2), want_c, rtol=0, atol=1e-12)   # exact integer sums / counts
+        assert np.allclose(np.array(sums, dtype=np.float64), want_s, rtol=1e-5)            # float32 pairwise sum vs double
+
+
+@pytest.mark.gpu
+def test_local_invisibility_path_from_a_panorama():
+    """src/mapper/splatam/__init__.py:793-832 after the renders, against the same steps done with numpy + the oracle."""
+    from activesplat_b200 import scoring
+    rng = np.random.default_rng(11)
+    inv = np.zeros((150, 360), np.float32)
+    inv[40:90, 250:330] = rng.uniform(0.5, 1.0, (50, 80)).astype(np.float32)   # a big unseen region off-centre
+    inv[100:110, 20:40] = 0.6
+    opacity = torch.from_numpy(1.0 - inv).cuda()
+    c2w = np.eye(4)
+    total, pose = scoring.local_invisibility_from_panorama(opacity, c2w, 30)
+    assert abs(total - float((1.0 - (1.0 - inv)).sum())) <= 1e-3 * total
+    small = 0.25 * (inv[0::2, 0::2] + inv[0::2, 1::2] + inv[1::2, 0::2] + inv[1::2, 1::2])   # INTER_AREA, factor 0.5
+    centers, sums = so.get_invisibility_clusters(small, 30)
+    c = centers[int(np.argmax(sums))]
+    h, v = np.deg2rad(c[1] / 0.5 - 60), np.deg2rad(c[0] / 0.5 - 75)
+    want = scoring.rot_axis(scoring.rot_axis(c2w, 'y', h), 'x', v)
+    assert pose is not None and np.allclose(pose, want, atol=1e-9)
+    # nothing unseen: no pose
+    total0, pose0 = scoring.local_invisibility_from_panorama(torch.ones(150, 360).cuda(), c2w, 30)
+    assert total0 == 0.0 and pose0 is None
