@@ -5,14 +5,18 @@
 //
 // One CTA per 16x16 tile, one thread per pixel (same as the reference).  What differs:
 //   * the tile's instances were gathered into contiguous per-instance records in sorted order
-//     (ranges_gather_kernel), so a batch is THREE contiguous slabs that one elected thread pulls
-//     into shared memory with cp.async.bulk (TMA engine, SASS UBLKCP) on an mbarrier, double
-//     buffered: the copy of batch k+1/k+2 overlaps the blending of batch k;
+//     (ranges_gather_kernel / frame_tile_sort_gather_kernel), so a batch is THREE contiguous slabs that one
+//     elected thread pulls into shared memory with cp.async.bulk (TMA engine, SASS UBLKCP) on an mbarrier,
+//     multi-buffered: the copy of the next batches overlaps the blending of this one;
 //   * C = 6 blends [rgb | z,1,z^2] in one sweep (the reference makes two full passes);
-//   * backward: each warp reduces a Gaussian's 6+C gradient terms with a transposing butterfly
-//     (16 shuffles instead of 80), adds them to a per-batch accumulator in shared memory, and the
-//     CTA flushes once per (tile, instance) with 128-bit vector reductions (REDG.ADD.F32x4)
-//     -- versus 9 scalar global atomics per (pixel, Gaussian) in the reference (backward.cu:523-554);
+//   * a warp owns a 16x2-pixel strip.  Per batch it keeps only the records whose ellipse of possible contribution
+//     reaches the strip, with the exact set of the strip's pixels inside that ellipse (cull_batch); a bit-matrix
+//     transpose hands every lane the records that can reach ITS pixel, and each lane walks its own list
+//     (the reference drags all 256 threads of a tile through every record of the tile);
+//   * backward: two phases per group of 16 records -- pixel lanes replay the recurrences and stage two scalars per
+//     (record, pixel); record lanes sum them over their pixels serially and commit 12 gradient terms with two
+//     vector reductions (REDG.ADD.F32x4) -- versus 9 scalar global atomics per (pixel, Gaussian) in the reference
+//     (backward.cu:523-554);
 //   * backward skips the tail of the list that no pixel of the warp/tile reached in the forward.
 // Per-pixel arithmetic, skip rules and termination are the reference's (SURVEY 8a' T10-T18) and are
 // spelled with rounding-explicit intrinsics so alpha decisions match the reference build bit for bit.

@@ -597,3 +597,90 @@ def test_noncontiguous_rotations_use_the_forward_values():
     helpers.compare_float("grad scales == reference given contiguous rotations", ours["scales"], theirs_c["scales"])
     # and the stock reference on the column-major tensor is far off (documented divergence)
     assert np.abs(theirs_cm["rot"] - g["rotations"]).max() > 0.05 * np.abs(g["rotations"]).max()
+
+
+def test_tile_buckets_and_global_sort_agree_at_full_size():
+    """cfg2-sized frame (500k Gaussians, 640x480) through both binning modes of the fused path: the sorted instance
+    list, the tile ranges, radii and every output image must be IDENTICAL (same list => same arithmetic), and each
+    tile's list must be ordered by (depth bits, Gaussian id) -- the order the reference's stable radix sort of
+    (tile, depth) keys yields (rasterizer_impl.cu:305-310).  Size-independent properties at BASELINE's full size."""
+    import ctypes
+    from activesplat_b200 import capi, scenes, splatam
+    from activesplat_b200.frame import FrameWorkspace
+    dev = torch.device("cuda:0")
+    P, W, H, K = 500_000, 640, 480, 2
+    params_cpu, cams = scenes.s_room(P, K, seed=1, W=W, H=H)
+    rots, trans = scenes.camera_track(cams)
+    params = {k: v.to(dev) for k, v in params_cpu.items()}
+    params["cam_unnorm_rots"], params["cam_trans"] = rots.to(dev), trans.to(dev)
+    cam = splatam.setup_camera(W, H, cams[0].k(), np.eye(4), device=dev)
+    cap = 1_000_000
+    L = capi.lib()
+    lay = capi.AsScratchLayout()
+    capi.check(L.as_scratch_layout(P, W, H, cap, 6, ctypes.byref(lay)))
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+
+    def run(mode, t):
+        ws = FrameWorkspace(P, W, H, dev, capacity=cap, binning=mode)
+        ws.forward(params, cam, t)
+        R, overflow = ws.last_status()
+        assert not overflow and 0 < R < cap
+        point_list = ws.binning[lay.point_list: lay.point_list + 4 * R].view(torch.int32).cpu().numpy()
+        ranges = ws.img[lay.ranges: lay.ranges + 8 * tiles].view(torch.int32).cpu().numpy().reshape(tiles, 2)
+        depths = ws.geom[lay.depths: lay.depths + 4 * P].view(torch.int32).cpu().numpy()
+        out = dict(R=R, point_list=point_list, ranges=ranges, depths=depths, radii=ws.radii.cpu().numpy(),
+                   color=ws.color6.cpu().numpy(), depth=ws.depth.cpu().numpy(), opacity=ws.opacity.cpu().numpy())
+        return ws, out
+
+    for t in range(K):
+        ws0, a = run(0, t)
+        ws1, b = run(1, t)
+        assert a["R"] == b["R"]
+        for k in ("radii", "ranges", "point_list"):
+            helpers.compare_exact(f"{k} (global sort vs tile buckets)", b[k], a[k])
+        for k in ("color", "depth", "opacity"):
+            helpers.compare_exact(f"{k} image (global sort vs tile buckets)", b[k].view(np.int32), a[k].view(np.int32))
+        # sortedness: inside every tile the key (depth bits, id) strictly increases
+        key = (a["depths"][a["point_list"]].astype(np.int64) << 32) | a["point_list"].astype(np.int64)
+        inc = np.diff(key) > 0
+        starts = a["ranges"][:, 0][a["ranges"][:, 1] > a["ranges"][:, 0]]
+        boundary = np.zeros(a["R"] - 1, bool)
+        boundary[starts[starts > 0] - 1] = True          # the pair straddling two tiles is exempt
+        assert (inc | boundary).all()
+        # the ranges tile the list without gaps or overlaps, in tile order
+        nonempty = a["ranges"][a["ranges"][:, 1] > a["ranges"][:, 0]]
+        assert nonempty[0, 0] == 0 and nonempty[-1, 1] == a["R"] and (nonempty[1:, 0] == nonempty[:-1, 1]).all()
+        assert int(ws1.status[3]) == int((a["ranges"][:, 1] - a["ranges"][:, 0]).max())   # largest bucket reported
+
+
+def test_tile_buckets_larger_than_shared_memory_still_sort_exactly():
+    """A tiny image under a big map: every tile's bucket exceeds what one CTA sorts in shared memory, so the
+    in-place (global-memory) network runs.  Same sorted list and images as the global radix sort."""
+    import ctypes
+    from activesplat_b200 import capi, scenes, splatam
+    from activesplat_b200.frame import FrameWorkspace
+    dev = torch.device("cuda:0")
+    P, W, H = 60_000, 48, 40
+    params_cpu, cams = scenes.s_room(P, 1, seed=21, W=W, H=H)
+    rots, trans = scenes.camera_track(cams)
+    params = {k: v.to(dev) for k, v in params_cpu.items()}
+    params["cam_unnorm_rots"], params["cam_trans"] = rots.to(dev), trans.to(dev)
+    cam = splatam.setup_camera(W, H, cams[0].k(), np.eye(4), device=dev)
+    cap = 400_000
+    L = capi.lib()
+    lay = capi.AsScratchLayout()
+    capi.check(L.as_scratch_layout(P, W, H, cap, 6, ctypes.byref(lay)))
+    outs = []
+    for mode in (0, 1):
+        ws = FrameWorkspace(P, W, H, dev, capacity=cap, binning=mode)
+        ws.forward(params, cam, 0)
+        R, overflow = ws.last_status()
+        assert not overflow
+        outs.append((R, ws.binning[lay.point_list: lay.point_list + 4 * R].view(torch.int32).cpu().numpy(),
+                     ws.color6.cpu().numpy().view(np.int32), ws.opacity.cpu().numpy().view(np.int32),
+                     int(ws.status[3])))
+    assert outs[1][4] > L.as_tile_sort_capacity(), "the case must exercise the big-bucket path"
+    assert outs[0][0] == outs[1][0]
+    helpers.compare_exact("point_list", outs[1][1], outs[0][1])
+    helpers.compare_exact("colour", outs[1][2], outs[0][2])
+    helpers.compare_exact("opacity", outs[1][3], outs[0][3])
