@@ -101,3 +101,75 @@ def mapping_step_keyframe_batch(frame_grad_fn, n_keyframes, flat_grad, optimizer
     allreduce_gradients(flat_grad, group)
     optimizer_step(flat_grad)
     return loss
+
+
+# ---- candidate-view sweep with low host cost per view ---------------------------------------------------------
+_VIEW_WORKSPACES = {}
+
+
+def _pack_cameras(views):
+    """setup_camera's matrices (recon_helpers.py:6-14, fp32 like the reference) for all views at once, packed
+    [n, 54] = viewmatrix^T (16) | full projection^T (16) | w2c row-major (16) | camera centre (3) | zeros (3)."""
+    import numpy as np
+    w2c = torch.as_tensor(np.stack([np.asarray(v.w2c) for v in views])).float()
+    n = w2c.shape[0]
+    cam_center = torch.inverse(w2c)[:, :3, 3]
+    view = w2c.transpose(1, 2)
+    proj = torch.zeros((n, 4, 4))
+    for i, v in enumerate(views):
+        w, h, near, far = v.width, v.height, v.near, v.far
+        proj[i] = torch.tensor([[2 * v.fx / w, 0.0, -(w - 2 * v.cx) / w, 0.0],
+                                [0.0, 2 * v.fy / h, -(h - 2 * v.cy) / h, 0.0],
+                                [0.0, 0.0, far / (far - near), -(far * near) / (far - near)],
+                                [0.0, 0.0, 1.0, 0.0]])
+    full = view.bmm(proj.transpose(1, 2))
+    return torch.cat([view.reshape(n, 16), full.reshape(n, 16), w2c.reshape(n, 16), cam_center, torch.zeros(n, 3)], 1)
+
+
+def score_candidate_views(params, views, group=None, n_streams=32, scale_modifier=1.0, return_opacity=False):
+    """The GetOpacity sweep (src/mapper/splatam/__init__.py:716-738 per view) over `views` (CameraSpec-like, all the
+    same size), sharded over the ranks of `group`; every rank receives [n_views, 2] = (sum of invisibility, mean
+    opacity).  Same renders as splatam.render_view, organised so that the host does little per view: all camera
+    matrices are built and uploaded in one go, each view is one fused forward on one of `n_streams` streams (a
+    low-resolution view is latency-bound on a few crowded tiles; in flight together they fill the GPU), and the
+    scores are reduced once for the whole shard."""
+    from . import splatam
+    from .frame import FrameWorkspace, identity_pose
+    rank, world = world_info(group)
+    mine = shard_indices(len(views), rank, world)
+    dev = params["means3D"].device
+    P = int(params["means3D"].shape[0])
+    W, H = int(views[0].width), int(views[0].height)
+    n_streams = max(1, min(n_streams, len(mine)))
+    key = (P, W, H, dev.index, n_streams)
+    if key not in _VIEW_WORKSPACES:
+        _VIEW_WORKSPACES[key] = ([FrameWorkspace(P, W, H, dev) for _ in range(n_streams)],
+                                 [torch.cuda.Stream(device=dev) for _ in range(n_streams)])
+    wss, streams = _VIEW_WORKSPACES[key]
+    rot, tr = identity_pose(dev)
+    p = {k: params[k].detach() for k in ("means3D", "rgb_colors", "unnorm_rotations", "logit_opacities", "log_scales")}
+    p["cam_unnorm_rots"], p["cam_trans"] = rot, tr
+    white = splatam._white_bg(dev)
+    ops = torch.empty((len(mine), H, W), dtype=torch.float32, device=dev)
+    if mine:
+        d = _pack_cameras([views[v] for v in mine]).pin_memory().to(dev, non_blocking=True)
+        cur = torch.cuda.current_stream(dev)
+        for st in streams:
+            st.wait_stream(cur)
+        with torch.no_grad():
+            for j, v in enumerate(mine):
+                c = views[v]
+                row = d[j]
+                cam = splatam.Camera(image_height=H, image_width=W, tanfovx=W / (2 * c.fx), tanfovy=H / (2 * c.fy),
+                                     bg=row[51:54], scale_modifier=scale_modifier, viewmatrix=row[0:16].view(1, 4, 4),
+                                     projmatrix=row[16:32].view(1, 4, 4), sh_degree=0, campos=row[48:51],
+                                     prefiltered=False, debug=False)
+                s = j % n_streams
+                with torch.cuda.stream(streams[s]):
+                    wss[s].forward(p, cam, 0, sil_w2c=row[32:48].view(4, 4), bg_rgb=white)
+                    ops[j].copy_(wss[s].opacity[0], non_blocking=True)
+        for st in streams:
+            cur.wait_stream(st)
+    local = torch.stack([(1.0 - ops).sum((1, 2)), ops.mean((1, 2))], 1) if mine else torch.zeros((0, 2), device=dev)
+    scores = gather_scores(local, len(views), rank, world, group)
+    return (scores, ops) if return_opacity else scores

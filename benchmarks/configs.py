@@ -226,16 +226,9 @@ def cfg4(dev, RefRenderer, args, rank, world):
             fx, fy, cx, cy = scenes.compute_intrinsics(w, h, math.radians(90.0))
             views = [scenes.CameraSpec(w, h, fx, fy, cx, cy, v.w2c) for v in views]
         n_streams = min(32, max(1, -(-n_views // world)))  # every view of the shard in flight: low-res views are latency-bound
-        from activesplat_b200.frame import FrameWorkspace
-        wss = [FrameWorkspace(P, w, h, dev) for _ in range(n_streams)]
-
-        def render_fn(v, slot):
-            c = views[v]
-            _, _, opacity, _ = splatam.render_view(params, c.w2c, c.k(), c.width, c.height, ws=wss[slot])
-            return opacity
 
         def run_once(_i):
-            return asd.score_views(render_fn, n_views, device=dev, n_streams=n_streams)
+            return asd.score_candidate_views(params, views, n_streams=n_streams)
 
         run_once(0)
         torch.cuda.synchronize(dev)
@@ -253,7 +246,7 @@ def cfg4(dev, RefRenderer, args, rank, world):
             dt = float(tt.item())
         res[tag] = {"ours": {"views_per_s": n_views / dt, "mpix_s": n_views * w * h / dt / 1e6,
                              "mean_invisibility": float(scores[:, 0].mean()), "streams": n_streams}}
-        del wss
+        asd._VIEW_WORKSPACES.clear()  # 32 workspaces of a 1M-Gaussian map are ~15 GB
         if RefRenderer and rank == 0 and world == 1:
             def ref_view(v):
                 c = views[v]

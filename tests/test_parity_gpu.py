@@ -684,3 +684,20 @@ def test_tile_buckets_larger_than_shared_memory_still_sort_exactly():
     helpers.compare_exact("point_list", outs[1][1], outs[0][1])
     helpers.compare_exact("colour", outs[1][2], outs[0][2])
     helpers.compare_exact("opacity", outs[1][3], outs[0][3])
+
+
+def test_score_candidate_views_equals_per_view_renders():
+    """The low-host-cost sweep (dist.score_candidate_views) renders exactly what splatam.render_view renders."""
+    from activesplat_b200 import dist as asd, scenes, splatam
+    dev = torch.device("cuda:0")
+    params_cpu, _ = scenes.s_room(4000, 1, seed=31, scale_mult=4.0)
+    params = {k: v.to(dev) for k, v in params_cpu.items()}
+    views = scenes.candidate_views(7, seed=31)
+    scores, ops = asd.score_candidate_views(params, views, n_streams=3, return_opacity=True)
+    assert scores.shape == (7, 2)
+    for j, c in enumerate(views):
+        _, _, opacity, _ = splatam.render_view(params, c.w2c, c.k(), c.width, c.height)
+        helpers.compare_exact(f"opacity of view {j}", ops[j].cpu().numpy().view(np.int32),
+                              opacity[0].cpu().numpy().view(np.int32))
+        assert abs(float(scores[j, 0]) - float((1.0 - opacity).sum())) <= 1e-4 * max(1.0, float(scores[j, 0]))
+    asd._VIEW_WORKSPACES.clear()
