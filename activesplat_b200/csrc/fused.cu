@@ -412,7 +412,7 @@ frame_ranges_gather_kernel(const uint32_t* __restrict__ n_dev, uint32_t capacity
 // Sorting by (depth, id) reproduces the stable radix sort exactly: the reference emits instances in ascending
 // Gaussian id, so equal (tile, depth) keys stay in id order.
 constexpr int TS_THREADS = 256;
-constexpr int TS_CAP = 4096;  // instances per tile sorted in shared memory; larger buckets are sorted in place (slow)
+constexpr int TS_CAP = 3584;  // instances per tile sorted in shared memory (28 KB: 8 CTAs per SM); larger buckets are sorted in place (slow)
 
 __global__ void __launch_bounds__(1024)
 frame_tile_scan_kernel(const uint32_t* __restrict__ tile_count, int tiles, uint32_t capacity, uint2* __restrict__ ranges,
@@ -566,7 +566,56 @@ frame_tile_sort_gather_kernel(const uint2* __restrict__ ranges, uint64_t* __rest
     if (n <= 0) return;
     uint64_t* ge = entries + range.x;
     const bool in_smem = n <= TS_CAP;
-    if (in_smem) {
+    const bool merged = n <= TS_CAP / 2;  // result in the upper half of s_e
+    if (merged) {
+        // Typical bucket (a few hundred entries): runs of 64 are sorted by one warp each with warp-level barriers
+        // only, then every entry finds its final position as its rank in its own run plus, by binary search, the
+        // number of smaller keys in every other run (keys are unique).  Two block barriers instead of one per stage
+        // of a block-wide network, and no padding to a power of two beyond the last run.
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        const int nruns = (n + 63) >> 6;
+        for (int i = threadIdx.x; i < nruns * 64; i += TS_THREADS) s_e[i] = i < n ? ge[i] : ~0ull;
+        __syncthreads();
+        for (int r = warp; r < nruns; r += TS_THREADS / 32) {
+            const int base = 64 * r;  // shared memory is addressed by index throughout (no generic pointers)
+            for (int k = 2, lk = 1; k <= 64; k <<= 1, lk++) {
+                {
+                    const int blk = lane >> (lk - 1), off = lane & ((k >> 1) - 1);
+                    const int i = base + (blk << lk) + off, j = base + (blk << lk) + k - 1 - off;
+                    const uint64_t x = s_e[i], y = s_e[j];
+                    if (x > y) { s_e[i] = y; s_e[j] = x; }
+                }
+                __syncwarp();
+                for (int js = k >> 2; js > 0; js >>= 1) {
+                    const int ljs = 31 - __clz(js);
+                    const int i = base + ((lane >> ljs) << (ljs + 1)) + (lane & (js - 1)), j = i + js;
+                    const uint64_t x = s_e[i], y = s_e[j];
+                    if (x > y) { s_e[i] = y; s_e[j] = x; }
+                    __syncwarp();
+                }
+            }
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < n; i += TS_THREADS) {
+            const uint64_t key = s_e[i];
+            const int own = i >> 6;
+            int pos = i & 63;
+            for (int r = 0; r < nruns; r++) {
+                if (r == own) continue;
+                int lo = 0;  // number of keys of run r below `key`, 0..64 (padding keys are the maximum: never below)
+                if (s_e[64 * r + 63] < key) {
+                    lo = 64;
+                } else {
+#pragma unroll
+                    for (int step = 32; step > 0; step >>= 1)
+                        if (s_e[64 * r + lo + step - 1] < key) lo += step;
+                }
+                pos += lo;
+            }
+            s_e[TS_CAP / 2 + pos] = key;
+        }
+        __syncthreads();
+    } else if (in_smem) {
         for (int i = threadIdx.x; i < n; i += TS_THREADS) s_e[i] = ge[i];
         __syncthreads();
         bitonic_sort_ascending(s_e, n, TS_THREADS);
@@ -575,7 +624,7 @@ frame_tile_sort_gather_kernel(const uint2* __restrict__ ranges, uint64_t* __rest
         bitonic_sort_ascending(ge, n, TS_THREADS);  // global memory is coherent within the block across the barriers
     }
     for (int i = threadIdx.x; i < n; i += TS_THREADS) {
-        const uint64_t e = in_smem ? s_e[i] : ge[i];
+        const uint64_t e = merged ? s_e[TS_CAP / 2 + i] : (in_smem ? s_e[i] : ge[i]);
         const uint32_t id = (uint32_t)e;
         const size_t o = (size_t)range.x + i;
         point_list[o] = id;
