@@ -173,13 +173,13 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
                      const float4* __restrict__ inst_geom, const float4* __restrict__ inst_feat, int W, int H,
                      int gx, const float* __restrict__ bg, float* __restrict__ out_color,
                      float* __restrict__ out_depth, float* __restrict__ out_opacity, float* __restrict__ final_T,
-                     uint32_t* __restrict__ n_contrib) {
+                     uint32_t* __restrict__ n_contrib, const uint32_t* __restrict__ tile_order) {
     constexpr int FV = BlendSmem<C>::FV;
     constexpr int NT = 32 * WARPS, PARTS = (BL_THREADS / 32) / WARPS;
     __shared__ __align__(128) BlendSmem<C> sm;
     __shared__ uint8_t s_list[WARPS][BL_BATCH];
     __shared__ uint32_t s_mask[WARPS][BL_BATCH];
-    const int tile = blockIdx.x / PARTS;
+    const int tile = tile_order ? (int)tile_order[blockIdx.x / PARTS] : (int)(blockIdx.x / PARTS);
     const int tx = tile % gx, ty = tile / gx;
     const int lane = threadIdx.x & 31;
     const int strip = (blockIdx.x % PARTS) * WARPS + (threadIdx.x >> 5);  // which 16x2 strip of the tile
@@ -383,7 +383,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
                       const float4* __restrict__ inst_geom, const float4* __restrict__ inst_feat, int W, int H,
                       int gx, const float* __restrict__ bg, const float* __restrict__ final_Ts,
                       const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
-                      float* __restrict__ gacc) {
+                      float* __restrict__ gacc, const uint32_t* __restrict__ tile_order) {
     using LY = BwdLayout<C, WARPS>;
     using SM = typename LY::SM;
     constexpr int FV = SM::FV;
@@ -397,7 +397,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
     uint8_t* list = reinterpret_cast<uint8_t*>(smem_raw + LY::off_list) + wid * BL_BATCH;
     __shared__ int s_max_contrib;
 
-    const int tile = blockIdx.x / PARTS;
+    const int tile = tile_order ? (int)tile_order[blockIdx.x / PARTS] : (int)(blockIdx.x / PARTS);
     const int tx = tile % gx, ty = tile / gx;
     const int lane = threadIdx.x & 31;
     const int strip = (blockIdx.x % PARTS) * WARPS + wid;
@@ -607,11 +607,11 @@ static int pick_warps(int tiles) {
 template <int C>
 static void launch_fwd_c(int warps, int tiles, cudaStream_t st, const uint2* ranges, const BinningState& b, int W, int H,
                          int gx, const float* bg, float* out_color, float* out_depth, float* out_opacity,
-                         float* final_T, uint32_t* n_contrib) {
+                         float* final_T, uint32_t* n_contrib, const uint32_t* tile_order) {
 #define ASB_FWD(WP)                                                                                              \
     blend_forward_kernel<C, WP><<<tiles*(8 / WP), 32 * WP, 0, st>>>(ranges, b.inst_conic, b.inst_geom, b.inst_feat, W, \
                                                                     H, gx, bg, out_color, out_depth, out_opacity,    \
-                                                                    final_T, n_contrib)
+                                                                    final_T, n_contrib, tile_order)
     if (warps == 8) ASB_FWD(8);
     else if (warps == 4) ASB_FWD(4);
     else if (warps == 2) ASB_FWD(2);
@@ -622,7 +622,7 @@ static void launch_fwd_c(int warps, int tiles, cudaStream_t st, const uint2* ran
 template <int C, int MODE>
 static void launch_bwd_c(int warps, int tiles, cudaStream_t st, const uint2* ranges, const BinningState& b, int W, int H,
                          int gx, const float* bg, const float* final_T, const uint32_t* n_contrib,
-                         const float* dL_dpix, float* gacc) {
+                         const float* dL_dpix, float* gacc, const uint32_t* tile_order) {
 #define ASB_BWD(WP)                                                                                                \
     do {                                                                                                           \
         constexpr size_t smem = BwdLayout<C, WP>::bytes;                                                           \
@@ -630,7 +630,8 @@ static void launch_bwd_c(int warps, int tiles, cudaStream_t st, const uint2* ran
             cudaFuncSetAttribute(blend_backward_kernel<C, WP, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
                                  (int)smem);                                                                       \
         blend_backward_kernel<C, WP, MODE><<<tiles*(8 / WP), 32 * WP, smem, st>>>(                                 \
-            ranges, b.inst_conic, b.inst_geom, b.inst_feat, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc);      \
+            ranges, b.inst_conic, b.inst_geom, b.inst_feat, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc,        \
+            tile_order);                                                                                           \
     } while (0)
     if (warps == 8) ASB_BWD(8);
     else if (warps == 4) ASB_BWD(4);
@@ -641,32 +642,38 @@ static void launch_bwd_c(int warps, int tiles, cudaStream_t st, const uint2* ran
 
 void launch_blend_forward(int channels, int W, int H, const uint2* ranges, const BinningState& b, const float* bg,
                           float* out_color, float* out_depth, float* out_opacity, float* final_T,
-                          uint32_t* n_contrib, cudaStream_t st) {
+                          uint32_t* n_contrib, cudaStream_t st, const uint32_t* tile_order) {
     const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
     const int tiles = gx * gy;
     if (tiles <= 0) return;
     const int warps = pick_warps(tiles);
     if (channels == 3)
-        launch_fwd_c<3>(warps, tiles, st, ranges, b, W, H, gx, bg, out_color, out_depth, out_opacity, final_T, n_contrib);
+        launch_fwd_c<3>(warps, tiles, st, ranges, b, W, H, gx, bg, out_color, out_depth, out_opacity, final_T, n_contrib,
+                        tile_order);
     else
-        launch_fwd_c<6>(warps, tiles, st, ranges, b, W, H, gx, bg, out_color, out_depth, out_opacity, final_T, n_contrib);
+        launch_fwd_c<6>(warps, tiles, st, ranges, b, W, H, gx, bg, out_color, out_depth, out_opacity, final_T, n_contrib,
+                        tile_order);
 }
 
 void launch_blend_backward(int channels, int W, int H, const uint2* ranges, const BinningState& b, const float* bg,
                            const float* final_T, const uint32_t* n_contrib, const float* dL_dpix, float* gacc,
-                           cudaStream_t st, int mode) {
+                           cudaStream_t st, int mode, const uint32_t* tile_order) {
     const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
     const int tiles = gx * gy;
     if (tiles <= 0) return;
     const int warps = pick_warps(tiles);
     if (channels == 3)
-        launch_bwd_c<3, BWD_ALL>(warps, tiles, st, ranges, b, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc);
+        launch_bwd_c<3, BWD_ALL>(warps, tiles, st, ranges, b, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc,
+                                  tile_order);
     else if (mode == BWD_MAPPING)
-        launch_bwd_c<6, BWD_MAPPING>(warps, tiles, st, ranges, b, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc);
+        launch_bwd_c<6, BWD_MAPPING>(warps, tiles, st, ranges, b, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc,
+                                  tile_order);
     else if (mode == BWD_TRACKING)
-        launch_bwd_c<6, BWD_TRACKING>(warps, tiles, st, ranges, b, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc);
+        launch_bwd_c<6, BWD_TRACKING>(warps, tiles, st, ranges, b, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc,
+                                  tile_order);
     else
-        launch_bwd_c<6, BWD_ALL>(warps, tiles, st, ranges, b, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc);
+        launch_bwd_c<6, BWD_ALL>(warps, tiles, st, ranges, b, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc,
+                                  tile_order);
 }
 
 }  // namespace asb

@@ -40,6 +40,7 @@ ImageState ImageState::fromChunk(char*& chunk, size_t N, size_t tiles) {
     img.ranges = b.take<uint2>(tiles);
     img.tile_count = b.take<uint32_t>(tiles * 8);   // TB_SUB sub-counters per tile (fused.cu)
     img.tile_cursor = b.take<uint32_t>(tiles * 8);
+    img.tile_order = b.take<uint32_t>(tiles);
     chunk = b.p;
     return img;
 }
@@ -364,7 +365,7 @@ int as_frame_forward(const AsFrameArgs* a, void* cuda_stream) {
     {
         StageScope _s(AS_STAGE_BLEND_FWD, st, 1);
         launch_blend_forward(6, W, H, img.ranges, b, a->background, a->out_color, a->out_depth, a->out_opacity,
-                             img.final_T, img.n_contrib, st);
+                             img.final_T, img.n_contrib, st, buckets ? img.tile_order : nullptr);
     }
     return stage_check(st, a->debug);
 }
@@ -388,7 +389,8 @@ int as_frame_backward(const AsFrameBackwardArgs* ba, void* cuda_stream) {
     {
         StageScope _s(AS_STAGE_BLEND_BWD, st, 1);
         launch_blend_backward(6, W, H, img.ranges, b, a->background, img.final_T, img.n_contrib, ba->dL_dpix, g.gacc, st,
-                              ba->gaussians_grad ? 1 : 2);
+                              ba->gaussians_grad ? 1 : 2,
+                              a->binning_mode == AS_BINNING_TILE_BUCKETS ? img.tile_order : nullptr);
     }
     if ((r = stage_check(st, a->debug))) return r;
     {

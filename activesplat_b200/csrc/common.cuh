@@ -51,6 +51,7 @@ struct ImageState {  // per pixel / per tile
     uint2* ranges;        // [tiles]
     uint32_t* tile_count;   // [tiles] instances per tile (frame path, tile-bucket binning)
     uint32_t* tile_cursor;  // [tiles] next free slot of each tile's bucket
+    uint32_t* tile_order;   // [tiles] tile ids, crowded tiles first: launch order of the blend kernels (tile buckets)
     static ImageState fromChunk(char*& chunk, size_t N, size_t tiles);
 };
 
@@ -108,14 +109,15 @@ void launch_ranges_and_gather(int R, int tiles, int channels, const uint64_t* ke
 
 void launch_blend_forward(int channels, int W, int H, const uint2* ranges, const BinningState& b,
                           const float* bg, float* out_color, float* out_depth, float* out_opacity,
-                          float* final_T, uint32_t* n_contrib, cudaStream_t st);
+                          float* final_T, uint32_t* n_contrib, cudaStream_t st, const uint32_t* tile_order = nullptr);
 
 // gacc: [P,12] accumulators (conic x,y,w | opacity | mean2D x,y | colour[<=6]); must be zero on entry.
 // mode (6 channels only): 0 = all 12 terms, 1 = the frame path with Gaussian gradients (the constant-1 channel of
 // [z,1,z^2] is skipped), 2 = pose-only frame path (conic, mean2D and the z / z^2 terms; the rest is left undefined).
 void launch_blend_backward(int channels, int W, int H, const uint2* ranges, const BinningState& b,
                            const float* bg, const float* final_T, const uint32_t* n_contrib,
-                           const float* dL_dpix, float* gacc, cudaStream_t st, int mode = 0);
+                           const float* dL_dpix, float* gacc, cudaStream_t st, int mode = 0,
+                           const uint32_t* tile_order = nullptr);
 
 struct PreprocessBackwardOut {
     float* dL_dmean2D;   // [P,3] or NULL

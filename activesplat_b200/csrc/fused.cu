@@ -416,9 +416,10 @@ constexpr int TS_CAP = 3584;  // instances per tile sorted in shared memory (28 
 
 __global__ void __launch_bounds__(1024)
 frame_tile_scan_kernel(const uint32_t* __restrict__ tile_count, int tiles, uint32_t capacity, uint2* __restrict__ ranges,
-                       uint32_t* __restrict__ cursor, uint32_t* status) {
+                       uint32_t* __restrict__ cursor, uint32_t* __restrict__ tile_order, uint32_t* status) {
     __shared__ uint32_t s_warp[32];
     __shared__ uint32_t s_max;
+    __shared__ uint32_t s_cls[32], s_base[32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) s_max = 0;
     __syncthreads();
@@ -478,6 +479,33 @@ frame_tile_scan_kernel(const uint32_t* __restrict__ tile_count, int tiles, uint3
     if (threadIdx.x == 0) {
         status[3] = s_max;
         if (overflow) status[1] = 1;
+    }
+    // Launch order for the blend kernels: crowded tiles first (32 size classes, counting sort), so that the last
+    // CTAs of their grids are the short ones and the tail of the kernel is short too.
+    if (threadIdx.x < 32) s_cls[threadIdx.x] = 0;
+    __syncthreads();
+    const uint32_t width = s_max / 32u + 1u;
+    for (int t = t0; t < t1; t++) {
+        const uint2 r = ranges[t];
+        atomicAdd(&s_cls[min(31u, (r.y - r.x) / width)], 1u);
+    }
+    __syncthreads();
+    if (warp == 0) {
+        const uint32_t c = s_cls[lane];
+        uint32_t incl2 = c;  // inclusive sum over classes lane..31 (descending order of size)
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t v = __shfl_down_sync(0xffffffffu, incl2, o);
+            if (lane + o < 32) incl2 += v;
+        }
+        s_base[lane] = incl2 - c;
+        s_cls[lane] = 0;
+    }
+    __syncthreads();
+    for (int t = t0; t < t1; t++) {
+        const uint2 r = ranges[t];
+        const uint32_t c = min(31u, (r.y - r.x) / width);
+        tile_order[s_base[c] + atomicAdd(&s_cls[c], 1u)] = (uint32_t)t;
     }
 }
 
@@ -1102,7 +1130,8 @@ void launch_frame_preprocess(const AsFrameArgs& a, const GeometryState& g, uint3
 void launch_frame_tile_binning(int P, const GeometryState& g, int W, int H, uint32_t capacity, const float* rgb,
                                const BinningState& b, const ImageState& img, uint32_t* status, cudaStream_t st) {
     const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y, tiles = gx * gy;
-    frame_tile_scan_kernel<<<1, 1024, 0, st>>>(img.tile_count, tiles, capacity, img.ranges, img.tile_cursor, status);
+    frame_tile_scan_kernel<<<1, 1024, 0, st>>>(img.tile_count, tiles, capacity, img.ranges, img.tile_cursor,
+                                               img.tile_order, status);
     if (capacity == 0) return;
     // one thread per slot of the compact visible list; the count is only known on the device
     frame_scatter_kernel<<<(P + 255) / 256, 256, 0, st>>>(g.vis_list, g.means2D, g.depths, g.radii, gx, gy,
