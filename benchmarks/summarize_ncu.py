@@ -24,6 +24,11 @@ METRICS = {
     "launch__registers_per_thread": ("registers", 1.0),
     "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum": ("smem_wavefronts", 1.0),
     "l1tex__throughput.avg.pct_of_peak_sustained_elapsed": ("l1tex_throughput_pct", 1.0),
+    "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed": ("dram_throughput_pct", 1.0),
+    "LTS.TriageCompute.lts__throughput.avg.pct_of_peak_sustained_elapsed": ("l2_throughput_pct", 1.0),
+    "l1tex__t_requests_pipe_lsu_mem_global_op_red.sum": ("global_red_requests", 1.0),
+    "l1tex__m_l1tex2xbar_write_sectors_mem_global_op_red.sum": ("global_red_sectors_to_l2", 1.0),
+    "l1tex__t_requests_pipe_lsu_mem_global_op_atom.sum": ("global_atom_requests", 1.0),
 }
 UNIT_SCALE = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1.0, "us": 1e3, "ms": 1e6, "usecond": 1e3,
               "nsecond": 1.0, "msecond": 1e6}
