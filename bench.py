@@ -505,14 +505,24 @@ def run_reference_arm(args):
     }
 
 
+def _emit(line, fd):
+    os.write(fd, (line + "\n").encode())
+
+
 def main():
     args = parse()
+    # Exactly ONE line may reach stdout: libraries print there too (NCCL writes "NCCL version ..." when NCCL_DEBUG is
+    # set in the environment).  Everything written to fd 1 from here on goes to stderr; the JSON line is written to
+    # the saved descriptor at the end.
+    sys.stdout.flush()
+    out_fd = os.dup(1)
+    os.dup2(2, 1)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
         if rank == 0:
-            print(json.dumps(run_reference_arm(args)), flush=True)
+            _emit(json.dumps(run_reference_arm(args)), out_fd)
         return
     if world > 1:
         import torch.distributed as dist
@@ -521,7 +531,8 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     res = run_ours(args, rank, world, local_rank)
     if rank == 0:
-        print(json.dumps(res), flush=True)
+        sys.stdout.flush()
+        _emit(json.dumps(res), out_fd)
     if world > 1:
         import torch.distributed as dist
         dist.barrier()
