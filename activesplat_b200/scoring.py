@@ -106,3 +106,34 @@ def local_invisibility_from_panorama(opacity_pano, view_c2w, cluster_invisibilit
             if np.abs(horizontal_angle) > np.deg2rad(15) or np.abs(vertical_angle) > np.deg2rad(15):
                 best_pose_c2w = rot_axis(rot_axis(view_c2w, 'y', horizontal_angle), 'x', vertical_angle)
     return sum_invisibility, best_pose_c2w
+
+
+def look_around_views(view_c2w, position=None, hfov=120, vfov=150, width=120, height=150):
+    """The camera sweep of get_local_invisibility / get_global_invisibility (src/mapper/splatam/__init__.py:707-719,
+    771-783): int(360 / hfov) views rotated about the camera's own y axis, one pixel per degree.  `position` (x, -, z)
+    moves the camera to a Voronoi node at the agent's camera height (:703-704).  Returns CameraSpec-like views."""
+    from .scenes import CameraSpec, compute_intrinsics
+    c2w = np.array(view_c2w, dtype=np.float64)
+    if position is not None:
+        c2w[0, 3] = position[0]
+        c2w[2, 3] = position[2]
+    fx, fy, cx, cy = compute_intrinsics(width, height, np.deg2rad(hfov), np.deg2rad(vfov))
+    views = []
+    for i in range(int(360 / hfov)):
+        c2w_i = rot_axis(c2w, 'y', np.deg2rad(hfov * i))
+        views.append(CameraSpec(width, height, fx, fy, cx, cy, np.linalg.inv(c2w_i)))
+    return views
+
+
+def get_local_invisibility(params, view_c2w, cluster_invisibility_threshold=30, scale_modifier=1.0):
+    """SplaTAM.get_local_invisibility (src/mapper/splatam/__init__.py:762-838) without the visualisation: renders the
+    three look-around views of the current camera, stacks their opacity side by side, and returns
+    (sum_invisibility, best_pose_c2w or None) -- what the LOCAL branch of the GetOpacity service puts into
+    targets_frustums_invisibility / targets_frustums (src/visualizer/visualizer.py:2198-2211)."""
+    from . import dist as asd
+    views = look_around_views(view_c2w)
+    _, ops = asd.score_candidate_views(params, views, n_streams=len(views), scale_modifier=scale_modifier,
+                                       return_opacity=True)
+    pano = torch.cat([ops[i] for i in range(len(views))], dim=1)  # np.hstack of the per-view opacity images (:789)
+    return local_invisibility_from_panorama(pano, view_c2w, cluster_invisibility_threshold,
+                                            width=views[0].width, height=views[0].height)

@@ -98,3 +98,42 @@ def test_local_invisibility_path_from_a_panorama():
     # nothing unseen: no pose
     total0, pose0 = scoring.local_invisibility_from_panorama(torch.ones(150, 360).cuda(), c2w, 30)
     assert total0 == 0.0 and pose0 is None
+
+
+@pytest.mark.gpu
+def test_get_local_invisibility_end_to_end_against_the_oracle_pipeline():
+    """LOCAL GetOpacity branch (src/mapper/splatam/__init__.py:762-838): three look-around renders + panorama + clusters
+    + best pose on the device, against the same pipeline built from the CPU oracles (oracle rasterizer for the
+    renders, sklearn for the clusters)."""
+    from activesplat_b200 import scenes, scoring, splatam
+    from oracle import splatam_oracle as spo
+    dev = torch.device("cuda:0")
+    # a room with one wall missing: a large unseen region on one side
+    params_cpu, _ = scenes.s_room(6000, 1, seed=41, scale_mult=6.0)
+    keep = params_cpu["means3D"][:, 0] < 3.0
+    params_cpu = {k: v[keep].contiguous() for k, v in params_cpu.items()}
+    params = {k: v.to(dev) for k, v in params_cpu.items()}
+    c2w = np.eye(4)
+    c2w[:3, 3] = [0.3, 0.0, -0.4]
+    total, pose = scoring.get_local_invisibility(params, c2w, 30)
+    # oracle pipeline on the CPU
+    ops = []
+    for v in scoring.look_around_views(c2w):
+        cam = splatam.setup_camera(v.width, v.height, v.k(), v.w2c, device="cpu")
+        rv, drv = spo.get_rendervars(params_cpu, torch.as_tensor(v.w2c).float())
+        _, _, opacity, _ = spo.render(cam, splatam.with_background(cam, [1.0, 1.0, 1.0]), rv, drv)
+        ops.append(opacity[0].numpy())
+    inv = 1.0 - np.hstack(ops)
+    want_total = float(inv.sum())
+    assert abs(total - want_total) <= 2e-4 * want_total
+    assert want_total > 100
+    small = 0.25 * (inv[0::2, 0::2] + inv[0::2, 1::2] + inv[1::2, 0::2] + inv[1::2, 1::2])
+    centers, sums = so.get_invisibility_clusters(small, 30)
+    assert len(sums) > 0
+    c = centers[int(np.argmax(sums))]
+    h, v_ = np.deg2rad(c[1] / 0.5 - 60), np.deg2rad(c[0] / 0.5 - 75)
+    if abs(h) > np.deg2rad(15) or abs(v_) > np.deg2rad(15):
+        want = scoring.rot_axis(scoring.rot_axis(c2w, 'y', h), 'x', v_)
+        assert pose is not None and np.allclose(pose, want, atol=2e-3)   # cluster centre moves by < 0.1 px
+    else:
+        assert pose is None
