@@ -21,6 +21,7 @@
 // Per-pixel arithmetic, skip rules and termination are the reference's (SURVEY 8a' T10-T18) and are
 // spelled with rounding-explicit intrinsics so alpha decisions match the reference build bit for bit.
 #include <math_constants.h>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -597,8 +598,12 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
 }  // namespace
 
 // Warps per CTA: whole tiles (8 warps) when there are plenty of tiles, finer splits for small images.
-static int pick_warps(int tiles) {
-    if (tiles >= 3 * NUM_SMS) return 8;
+static int pick_warps(int tiles, bool forward, const char* env = nullptr) {
+    if (env) {  // experiments only
+        const char* v = getenv(env);
+        if (v) return atoi(v);
+    }
+    if (tiles >= (forward ? 16 : 3) * NUM_SMS) return 8;  // forward: half-tile CTAs pack the SMs better (measured at 1200 tiles)
     if (tiles * 2 >= 3 * NUM_SMS) return 4;
     if (tiles * 4 >= 3 * NUM_SMS) return 2;
     return 1;
@@ -646,7 +651,7 @@ void launch_blend_forward(int channels, int W, int H, const uint2* ranges, const
     const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
     const int tiles = gx * gy;
     if (tiles <= 0) return;
-    const int warps = pick_warps(tiles);
+    const int warps = pick_warps(tiles, true, "ASB_FWD_WARPS");
     if (channels == 3)
         launch_fwd_c<3>(warps, tiles, st, ranges, b, W, H, gx, bg, out_color, out_depth, out_opacity, final_T, n_contrib,
                         tile_order);
@@ -661,7 +666,7 @@ void launch_blend_backward(int channels, int W, int H, const uint2* ranges, cons
     const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
     const int tiles = gx * gy;
     if (tiles <= 0) return;
-    const int warps = pick_warps(tiles);
+    const int warps = pick_warps(tiles, false, "ASB_BWD_WARPS");
     if (channels == 3)
         launch_bwd_c<3, BWD_ALL>(warps, tiles, st, ranges, b, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc,
                                   tile_order);
