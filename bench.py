@@ -358,7 +358,7 @@ def run_ours(args, rank, world, local_rank):
         "clocks": sampler.summary(),
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak if peak else None, "traffic": traffic, "peak_source": peak_src,
-                     "note": "blend kernels are instruction-issue bound (ncu: ~80 % issue-active, DRAM < 3 %), not HBM bound; "
+                     "note": "blend kernels are instruction-issue bound (ncu: ~70 % issue-active, DRAM throughput 3 %), not HBM bound; "
                              "the HBM fraction is reported because the contract asks for it (SURVEY 7, DESIGN 4)",
                      "algorithmic_bytes_per_launch": ab.get(dom, 0),
                      "whole_step": {"algorithmic_bytes": total_bytes,

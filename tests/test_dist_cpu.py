@@ -95,3 +95,20 @@ def test_shard_indices_cover_exactly():
         for world in (1, 2, 4, 8):
             got = sorted(sum((asd.shard_indices(n, r, world) for r in range(world)), []))
             assert got == list(range(n))
+
+
+def test_packed_cameras_equal_the_per_view_matrices():
+    """dist._pack_cameras (one upload for a whole candidate-view sweep) against CameraSpec.matrices(), the per-view
+    restatement of setup_camera (src/mapper/splatam/utils/recon_helpers.py:6-14): same fp32 values, bit for bit."""
+    import numpy as np
+    from activesplat_b200 import dist as asd, scenes
+    views = scenes.candidate_views(7, seed=3)
+    packed = asd._pack_cameras(views).numpy()
+    assert packed.shape == (7, 54)
+    for j, v in enumerate(views):
+        view, proj, campos = v.matrices()
+        assert np.array_equal(packed[j, 0:16].reshape(4, 4), view)
+        assert np.array_equal(packed[j, 16:32].reshape(4, 4), proj)
+        assert np.array_equal(packed[j, 32:48].reshape(4, 4), np.asarray(v.w2c, dtype=np.float32))
+        assert np.array_equal(packed[j, 48:51], campos)
+        assert (packed[j, 51:54] == 0).all()
