@@ -32,6 +32,8 @@ class FrameWorkspace:
         L = capi.lib()
         self.binning_mode = 1 if binning is None else int(binning)
         self._binning_auto = binning is None
+        self._status_host = None     # pinned copy of `status` (auto binning keeps an eye on the largest bucket)
+        self._status_event = None
         self.P, self.W, self.H, self.device = int(P), int(width), int(height), torch.device(device)
         self.capacity = int(capacity) if capacity else max(4 * self.P, 1 << 16)
         with torch.cuda.device(self.device):
@@ -120,10 +122,26 @@ class FrameWorkspace:
         a.debug = int(bool(debug))
         a.max_2D_radius = max_2D_radius.data_ptr() if max_2D_radius is not None else None
         a.seen = seen.data_ptr() if seen is not None else None
+        capturing = torch.cuda.is_current_stream_capturing()
+        if self._binning_auto and self.binning_mode == 1 and self._status_event is not None and not capturing:
+            # the status words of an EARLIER frame, copied back asynchronously: if a tile's bucket outgrew what a CTA
+            # sorts in shared memory, later frames use the global sort (no synchronisation, one or two frames late;
+            # the oversized frames themselves were still sorted correctly, only slowly)
+            if self._status_event.query():
+                if int(self._status_host[3]) > L.as_tile_sort_capacity():
+                    self.binning_mode = 0
+                self._status_event = None
         a.binning_mode = self.binning_mode
         with torch.cuda.device(self.device):
             stream = torch.cuda.current_stream(self.device).cuda_stream
             capi.check(L.as_frame_forward(ctypes.byref(a), stream))
+            if self._binning_auto and self.binning_mode == 1 and self.calibrated and self._status_event is None \
+                    and not capturing:
+                if self._status_host is None:
+                    self._status_host = torch.zeros(4, dtype=torch.int32).pin_memory()
+                self._status_host.copy_(self.status, non_blocking=True)
+                self._status_event = torch.cuda.Event()
+                self._status_event.record(torch.cuda.current_stream(self.device))
             if not self.calibrated and not torch.cuda.is_current_stream_capturing():
                 # first frame of this workspace: ONE synchronising look at the instance count sizes the binning
                 # buffer with head-room (2x); after that the path never synchronises and an overflow shows up as

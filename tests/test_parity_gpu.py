@@ -701,3 +701,31 @@ def test_score_candidate_views_equals_per_view_renders():
                               opacity[0].cpu().numpy().view(np.int32))
         assert abs(float(scores[j, 0]) - float((1.0 - opacity).sum())) <= 1e-4 * max(1.0, float(scores[j, 0]))
     asd._VIEW_WORKSPACES.clear()
+
+
+def test_auto_binning_falls_back_to_the_global_sort_without_synchronising():
+    """A workspace calibrated on a sparse frame that later sees crowded tiles notices it from the asynchronously
+    copied status words and switches to the global sort for the following frames; results never change."""
+    from activesplat_b200 import capi, scenes, splatam
+    from activesplat_b200.frame import FrameWorkspace
+    dev = torch.device("cuda:0")
+    P, W, H = 60_000, 48, 40
+    params_cpu, cams = scenes.s_room(P, 1, seed=21, W=W, H=H)
+    rots, trans = scenes.camera_track(cams)
+    params = {k: v.to(dev) for k, v in params_cpu.items()}
+    params["cam_unnorm_rots"], params["cam_trans"] = rots.to(dev), trans.to(dev)
+    cam = splatam.setup_camera(W, H, cams[0].k(), np.eye(4), device=dev)
+    sparse = {k: (v[:500].contiguous() if k not in ("cam_unnorm_rots", "cam_trans") else v) for k, v in params.items()}
+    ws = FrameWorkspace(P, W, H, dev)            # auto
+    ws.P = 500
+    ws.forward(sparse, cam, 0)                   # calibration frame: few Gaussians, small buckets
+    assert ws.binning_mode == 1
+    ws.P = P
+    ws.ensure_capacity(400_000)
+    ref = FrameWorkspace(P, W, H, dev, capacity=400_000, binning=0)
+    ref.forward(params, cam, 0)
+    for _ in range(4):                           # crowded frames: correct from the first one, global sort soon after
+        ws.forward(params, cam, 0)
+        torch.cuda.synchronize()
+        helpers.compare_exact("colour", ws.color6.cpu().numpy().view(np.int32), ref.color6.cpu().numpy().view(np.int32))
+    assert ws.binning_mode == 0
