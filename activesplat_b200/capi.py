@@ -120,6 +120,10 @@ SYMBOLS = {
     "as_mapping_loss_scratch_floats": (_Z, [_I, _I]),
     "as_mapping_loss": (_I, [_I, _I, _V, _V, _V, _F, _F, _V, _V, _V, _V, _V]),
     "as_adam_step": (_I, [_I, _I, _V, _V, _V, _V, _V, _V, _V, _V, ctypes.POINTER(ctypes.c_float), _F, _F, _F, _I, _V]),
+    "as_enable_peer_access": (_I, [_I]),
+    "as_ipc_open": (_I, [ctypes.c_char_p, ctypes.POINTER(ctypes.c_void_p)]),
+    "as_ipc_close": (_I, [_V]),
+    "as_adam_step_peer": (_I, [_I, _I, _I, _I, _I, _I, _V, _V, _V, _V, ctypes.POINTER(ctypes.c_float), _F, _F, _F, _I, _V]),
     "as_dbscan_grid": (_I, [_I, _I, _I, _V, _F, _F, _I, _V, _V, _I, _V, _V, _V, _V]),
     "as_sort_temp_bytes": (_Z, [_I]),
     "as_sort_pairs": (_I, [_V, _V, _V, _V, _I, _I, _V, _Z, _V]),

@@ -450,6 +450,48 @@ int as_adam_step(int P, int isotropic, float* means3D, float* rgb_colors, float*
     return check(cudaGetLastError());
 }
 
+int as_enable_peer_access(int peer_device) {
+    int cur = -1;
+    if (cudaGetDevice(&cur) != cudaSuccess) return AS_ERR_CUDA;
+    if (cur == peer_device) return AS_OK;
+    int can = 0;
+    if (cudaDeviceCanAccessPeer(&can, cur, peer_device) != cudaSuccess || !can) return AS_ERR_INVALID_ARG;
+    const cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+    if (e == cudaErrorPeerAccessAlreadyEnabled) {
+        cudaGetLastError();  // clear the sticky-looking (but harmless) error
+        return AS_OK;
+    }
+    return check(e);
+}
+
+int as_ipc_open(const void* handle64, void** out_ptr) {
+    if (!handle64 || !out_ptr) return AS_ERR_INVALID_ARG;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, sizeof(h));
+    return check(cudaIpcOpenMemHandle(out_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+}
+
+int as_ipc_close(void* ptr) { return ptr ? check(cudaIpcCloseMemHandle(ptr)) : AS_OK; }
+
+int as_adam_step_peer(int P, int isotropic, int world, int rank, int g_begin, int g_end, float* const* params,
+                      const float* const* grads, float* exp_avg, float* exp_avg_sq, const float* lrs, float beta1,
+                      float beta2, float eps, int step, void* cuda_stream) {
+    if (P < 0 || world < 1 || world > 8 || rank < 0 || rank >= world || step < 1 || !lrs || !params || !grads)
+        return AS_ERR_INVALID_ARG;
+    if (g_begin < 0 || g_end < g_begin || g_end > P || (g_begin & 3)) return AS_ERR_INVALID_ARG;  // 16-byte aligned slabs
+    if (g_end == g_begin) return AS_OK;
+    if (!exp_avg || !exp_avg_sq) return AS_ERR_INVALID_ARG;
+    for (int i = 0; i < 5 * world; i++)
+        if (!params[i]) return AS_ERR_INVALID_ARG;
+    for (int r = 0; r < world; r++)
+        if (!grads[r]) return AS_ERR_INVALID_ARG;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
+    StageScope _s(AS_STAGE_ADAM, st, 1);
+    launch_adam_peer(g_begin, g_end, isotropic, world, rank, params, grads, lrs, exp_avg, exp_avg_sq, beta1, beta2, eps,
+                     step, st);
+    return check(cudaGetLastError());
+}
+
 int as_dbscan_grid(int batch, int height, int width, const float* values, float value_threshold, float eps,
                    int min_samples, int* labels, int* scratch, int max_clusters, int* n_clusters, int* stats_int,
                    double* stats_value, void* cuda_stream) {

@@ -162,6 +162,9 @@ size_t mapping_loss_scratch_floats(int W, int H);
 void launch_mapping_loss(int W, int H, const float* c6, const float* gt_rgb, const float* gt_depth, float w_im,
                          float w_depth, float* dL, float* losses, float* scratch, const uint32_t* status,
                          cudaStream_t st);
+void launch_adam_peer(int g_begin, int g_end, int iso, int world, int rank, float* const* params, const float* const* grads,
+                      const float lr[5], float* m, float* v, float beta1, float beta2, float eps, int step,
+                      cudaStream_t st);
 // DBSCAN on a pixel grid, one CTA per image (scoring.cu)
 void launch_dbscan_grid(int batch, int H, int W, const float* values, float thr, float eps, int min_samples, int* labels,
                         int* scratch, int max_clusters, int* n_clusters, int* stats_i, double* stats_v, cudaStream_t st);

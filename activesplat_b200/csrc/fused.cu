@@ -1094,6 +1094,71 @@ adam_kernel(int P, int iso, AdamPtrs ap, const float* __restrict__ grad, float* 
     for (int i = threadIdx.x; i < ws * G; i += 256) ap.p4[ws * (size_t)g0 + i] = s_p[off4 + i];
 }
 
+// ---- Adam fused with the gradient exchange over peer memory (NVLink / NVSwitch) ------------------------------
+// Mapping over a keyframe batch: every rank holds the flat [P,14] gradient of ITS keyframes.  Instead of
+// all-reducing that buffer (NCCL) and running the same Adam step on every rank, rank r owns the Gaussians
+// [g_begin, g_end): its threads load those rows of every rank's gradient buffer straight over NVLink (peer pointers),
+// add them in rank order, apply Adam with the optimizer state kept only for the owned rows, and store the new
+// parameter values into the parameter tensors of every rank.  One kernel: reduce-scatter + Adam + all-gather.
+struct PeerAdamArgs {
+    float* params[8][5];    // [rank][tensor] as mapped into this process
+    const float* grads[8];  // [rank] flat [P,14]
+    float* own[5];          // this rank's parameter tensors (= params[rank])
+    float step_size[5];     // lr[t] / bias_correction1
+    int world;
+};
+
+__device__ __forceinline__ void adam_peer_one(const PeerAdamArgs& pa, int iso, size_t e, float g, float& m, float& v,
+                                              float beta1, float beta2, float eps, float bc2_sqrt) {
+    const size_t idx = e / 14;
+    const int slot = (int)(e - idx * 14);
+    int t, k, width;
+    if (slot < 3) { t = 0; k = slot; width = 3; }
+    else if (slot < 6) { t = 1; k = slot - 3; width = 3; }
+    else if (slot < 10) { t = 2; k = slot - 6; width = 4; }
+    else if (slot < 11) { t = 3; k = 0; width = 1; }
+    else { t = 4; k = slot - 11; width = iso ? 1 : 3; if (k >= width) return; }
+    const float mm = m + (g - m) * (1.f - beta1);
+    const float vv = v * beta2 + (1.f - beta2) * g * g;
+    m = mm;
+    v = vv;
+    const float denom = __fdividef(__fsqrt_rn(vv), bc2_sqrt) + eps;
+    const size_t po = (size_t)width * idx + k;
+    float* mine = t == 0 ? pa.own[0] : t == 1 ? pa.own[1] : t == 2 ? pa.own[2] : t == 3 ? pa.own[3] : pa.own[4];
+    const float ss = t == 0 ? pa.step_size[0] : t == 1 ? pa.step_size[1] : t == 2 ? pa.step_size[2]
+                   : t == 3 ? pa.step_size[3] : pa.step_size[4];
+    const float nv = mine[po] - ss * __fdividef(mm, denom);
+#pragma unroll
+    for (int r = 0; r < 8; r++) {  // unrolled: indexing a kernel parameter at run time would copy it to local memory
+        if (r < pa.world) {
+            float* dst = t == 0 ? pa.params[r][0] : t == 1 ? pa.params[r][1] : t == 2 ? pa.params[r][2]
+                       : t == 3 ? pa.params[r][3] : pa.params[r][4];
+            dst[po] = nv;
+        }
+    }
+}
+
+// One thread per flat element: neighbouring lanes touch neighbouring words of the gradient slabs AND of the parameter
+// tensors, so the remote loads and, more importantly, the remote stores leave the SM as full sectors (a 128-bit-per-thread
+// variant scattered its parameter stores across lanes and was 1.7x slower over NVLink).  Sums run in rank order and
+// every row has exactly one owner, so all ranks end up with identical parameters.
+__global__ void __launch_bounds__(256)
+adam_peer_kernel(int g_begin, int g_end, int iso, PeerAdamArgs pa, float* __restrict__ m, float* __restrict__ v,
+                 float beta1, float beta2, float eps, float bc2_sqrt) {
+    const size_t n = 14 * (size_t)(g_end - g_begin);
+    const size_t le = (size_t)blockIdx.x * blockDim.x + threadIdx.x;  // element of the owned slab
+    if (le >= n) return;
+    const size_t e = 14 * (size_t)g_begin + le;                       // element of the full [P,14] arrays
+    float g = 0.f;
+#pragma unroll
+    for (int r = 0; r < 8; r++)
+        if (r < pa.world) g += pa.grads[r][e];
+    float mm = m[le], vv = v[le];
+    adam_peer_one(pa, iso, e, g, mm, vv, beta1, beta2, eps, bc2_sqrt);
+    m[le] = mm;
+    v[le] = vv;
+}
+
 }  // namespace
 
 // ---- host launchers --------------------------------------------------------------------------------
@@ -1180,6 +1245,27 @@ void launch_frame_preprocess_backward(const AsFrameArgs& a, const GeometryState&
     if (camera_grad)
         pose_finalize_kernel<<<1, 256, 0, st>>>(a.cam_unnorm_rot, a.cam_rot_stride, pose_acc, blocks, a.status, grad_cam,
                                                 grad_cam_stride > 0 ? grad_cam_stride : 1);
+}
+
+void launch_adam_peer(int g_begin, int g_end, int iso, int world, int rank, float* const* params /*[world*5]*/,
+                      const float* const* grads /*[world]*/, const float lr[5], float* m, float* v, float beta1,
+                      float beta2, float eps, int step, cudaStream_t st) {
+    if (g_end <= g_begin) return;
+    PeerAdamArgs pa;
+    const float bc1 = 1.f - powf(beta1, (float)step);
+    const float bc2_sqrt = sqrtf(1.f - powf(beta2, (float)step));
+    for (int r = 0; r < 8; r++) {
+        for (int t = 0; t < 5; t++) pa.params[r][t] = r < world ? params[5 * r + t] : nullptr;
+        pa.grads[r] = r < world ? grads[r] : nullptr;
+    }
+    for (int t = 0; t < 5; t++) {
+        pa.own[t] = params[5 * rank + t];
+        pa.step_size[t] = lr[t] / bc1;
+    }
+    pa.world = world;
+    const size_t threads = 14 * (size_t)(g_end - g_begin);
+    adam_peer_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(g_begin, g_end, iso, pa, m, v, beta1, beta2, eps,
+                                                                      bc2_sqrt);
 }
 
 int tile_sort_capacity() { return TS_CAP; }

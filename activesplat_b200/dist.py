@@ -173,3 +173,94 @@ def score_candidate_views(params, views, group=None, n_streams=32, scale_modifie
     local = torch.stack([(1.0 - ops).sum((1, 2)), ops.mean((1, 2))], 1) if mine else torch.zeros((0, 2), device=dev)
     scores = gather_scores(local, len(views), rank, world, group)
     return (scores, ops) if return_opacity else scores
+
+
+# ---- Adam fused with the gradient exchange over peer memory ------------------------------------------------------
+class PeerShardedAdam:
+    """Drop-in for `allreduce_gradients(flat) ; FusedAdam.step(flat)` when mapping over a keyframe batch on the GPUs of
+    one box: each rank owns a contiguous slab of Gaussians, sums that slab of every rank's gradient straight out of the
+    peers' memory, updates it, and writes the new parameters into every rank's tensors (as_adam_step_peer).  Optimizer
+    state exists only for the owned slab (1/world of FusedAdam's).  Results equal the all-reduce path up to the order of
+    the float additions.
+
+    The parameter tensors and the flat gradient buffer are exported once with CUDA IPC and opened by every peer on ITS
+    device (as_ipc_open), so they must stay alive and in place; call `step()` on every rank."""
+
+    def __init__(self, params, lrs, flat_grad, group=None, betas=(0.9, 0.999), eps=1e-15):
+        import ctypes
+        from . import capi
+        from .frame import PARAM_ORDER
+        self.rank, self.world = world_info(group)
+        if self.world > 8:
+            raise ValueError("PeerShardedAdam supports up to 8 ranks (one NVSwitch box)")
+        self.group, self.params, self.flat_grad = group, params, flat_grad
+        self.betas, self.eps, self.t = betas, eps, 0
+        self.lrs = (ctypes.c_float * 5)(*[float(lrs[k]) for k in PARAM_ORDER])
+        self.P = int(params["means3D"].shape[0])
+        dev = params["means3D"].device
+        per = -(-self.P // self.world)
+        per = (per + 3) // 4 * 4  # slabs start on 16-byte boundaries of the flat [P,14] buffers
+        self.g_begin, self.g_end = min(self.P, per * self.rank), min(self.P, per * (self.rank + 1))
+        n_own = self.g_end - self.g_begin
+        self.exp_avg = torch.zeros((n_own, 14), dtype=torch.float32, device=dev)
+        self.exp_avg_sq = torch.zeros((n_own, 14), dtype=torch.float32, device=dev)
+        self._flag = torch.zeros(1, dtype=torch.float32, device=dev)
+        mine = [params[k] for k in PARAM_ORDER] + [flat_grad]
+        for t in mine:
+            assert t.is_cuda and t.is_contiguous() and t.dtype == torch.float32
+        own_ptrs = [t.data_ptr() for t in mine]
+        self._opened = {}
+        if self.world == 1:
+            ptrs = [own_ptrs]
+        else:
+            # export: CUDA IPC handle of the allocation each tensor lives in + the tensor's byte offset inside it
+            exports = []
+            for t in mine:
+                st = t.untyped_storage()
+                _dev, handle, _size, off_bytes = st._share_cuda_()[:4]
+                handle = bytes(handle)
+                if len(handle) == 66:  # torch >= 2.3: version byte + allocation-kind byte + the 64-byte cudaIpcMemHandle_t
+                    if handle[1:2] != b"c":
+                        raise RuntimeError("PeerShardedAdam needs cudaMalloc-backed tensors (expandable segments are "
+                                           "exported through a different mechanism)")
+                    handle = handle[2:]
+                if len(handle) != 64:
+                    raise RuntimeError(f"unexpected CUDA IPC handle size {len(handle)}")
+                exports.append((handle, int(off_bytes) + t.storage_offset() * t.element_size()))
+            gathered = [None] * self.world
+            dist.all_gather_object(gathered, exports, group=group)
+            ptrs = []
+            with torch.cuda.device(dev):  # open on THIS device: its kernels dereference the mapping (lazy peer access)
+                for r in range(self.world):
+                    if r == self.rank:
+                        ptrs.append(own_ptrs)
+                        continue
+                    row = []
+                    for handle, off in gathered[r]:
+                        if handle not in self._opened:
+                            base = ctypes.c_void_p()
+                            capi.check(capi.lib().as_ipc_open(handle, ctypes.byref(base)))
+                            self._opened[handle] = base.value
+                        row.append(self._opened[handle] + off)
+                    ptrs.append(row)
+            torch.cuda.synchronize(dev)
+        self._pp = (ctypes.c_void_p * (5 * self.world))(*[ptrs[r][t] for r in range(self.world) for t in range(5)])
+        self._gp = (ctypes.c_void_p * self.world)(*[ptrs[r][5] for r in range(self.world)])
+
+    def _barrier(self):
+        if self.world > 1:  # stream-ordered: completes on a rank only after every rank's earlier work on its stream
+            dist.all_reduce(self._flag, group=self.group)
+
+    @torch.no_grad()
+    def step(self):
+        from . import capi
+        self.t += 1
+        p = self.params
+        dev = p["means3D"].device
+        self._barrier()   # every rank's gradient buffer is complete
+        with torch.cuda.device(dev):
+            capi.check(capi.lib().as_adam_step_peer(
+                self.P, 1 if p["log_scales"].shape[1] == 1 else 0, self.world, self.rank, self.g_begin, self.g_end,
+                self._pp, self._gp, self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(), self.lrs, self.betas[0],
+                self.betas[1], self.eps, self.t, torch.cuda.current_stream(dev).cuda_stream))
+        self._barrier()   # every rank's slab has landed in everybody's parameters

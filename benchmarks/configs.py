@@ -270,71 +270,85 @@ def cfg4(dev, RefRenderer, args, rank, world):
 
 
 def cfg5(dev, args, rank, world):
-    """MP3D-scale mapping: 3M Gaussians, 64-keyframe batch split over ranks, one all-reduce per step."""
+    """MP3D-scale mapping: 3M Gaussians, 64-keyframe batch split over ranks.  The exchange + update step is timed two
+    ways: NCCL all-reduce of the flat gradient followed by the fused Adam on every rank, and the single kernel that
+    reduces over peer memory, updates the owned slab and writes it to every rank (dist.PeerShardedAdam)."""
     W, H, P, K = 640, 480, 3_000_000, 64
     params_cpu, cams = scenes.s_room(P, K, seed=5, W=W, H=H)
     rots, trans = scenes.camera_track(cams)
-    p = {k: v.to(dev) for k, v in params_cpu.items()}
-    p["cam_unnorm_rots"], p["cam_trans"] = rots.to(dev), trans.to(dev)
     cam = splatam.setup_camera(W, H, cams[0].k(), np.eye(4), device=dev)
     mine = asd.shard_indices(K, rank, world)
     gts = dict(zip(mine, gt_frames(params_cpu, [cams[k] for k in mine], dev, seed=15)))
-    ws = workspace_for(p, cam)
-    opt = FusedAdam(p, MAP_LRS)
     eye = torch.eye(4, device=dev)
-    t_ar = []
+    out = {}
+    for kind in ("allreduce", "peer"):
+        p = {k: v.to(dev) for k, v in params_cpu.items()}
+        p["cam_unnorm_rots"], p["cam_trans"] = rots.to(dev), trans.to(dev)
+        ws = workspace_for(p, cam)
+        opt = FusedAdam(p, MAP_LRS) if kind == "allreduce" else asd.PeerShardedAdam(p, MAP_LRS, ws.grad_params)
+        t_ex = []
 
-    def frame_grad_fn(k, accumulate):
-        with torch.no_grad():
-            ws.forward(p, cam, k, sil_w2c=eye)
-            ws.mapping_loss(gts[k][:3], gts[k][3:4], LW["im"], LW["depth"])
-            ws.backward(gaussians_grad=True, camera_grad=False, accumulate=accumulate)
-        return ws.losses[0].clone()
+        def frame_grad_fn(k, accumulate):
+            with torch.no_grad():
+                ws.forward(p, cam, k, sil_w2c=eye)
+                ws.mapping_loss(gts[k][:3], gts[k][3:4], LW["im"], LW["depth"])
+                ws.backward(gaussians_grad=True, camera_grad=False, accumulate=accumulate)
+            return ws.losses[0].clone()
 
-    def step(_i):
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        def step(_i):
+            e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            loss = None
+            for j, k in enumerate(mine):
+                l = frame_grad_fn(k, j > 0)
+                loss = l if loss is None else loss + l
+            e0.record()
+            if kind == "allreduce":
+                asd.allreduce_gradients(ws.grad_params)
+                e1.record()
+                opt.step(ws.grad_params)
+            else:
+                e1.record()
+                opt.step()
+            e2.record()
+            t_ex.append((e0, e1, e2))
+            return loss
 
-        def opt_step(flat):
-            e1.record()
-            opt.step(flat)
-
-        rank_, world_ = asd.world_info()
-        mine_ = asd.shard_indices(K, rank_, world_)
-        loss = None
-        for j, k in enumerate(mine_):
-            l = frame_grad_fn(k, j > 0)
-            loss = l if loss is None else loss + l
-        e0.record()
-        asd.allreduce_gradients(ws.grad_params)
-        opt_step(ws.grad_params)
-        t_ar.append((e0, e1))
-        return loss
-
-    for i in range(2):
-        step(i)
-    torch.cuda.synchronize(dev)
-    if world > 1:
-        torch.distributed.barrier()
-    t_ar.clear()
-    n = 3
-    t0 = time.time()
-    for i in range(n):
-        step(i)
-    torch.cuda.synchronize(dev)
-    if world > 1:
-        torch.distributed.barrier()
-    dt = (time.time() - t0) / n
-    ar_ms = float(np.mean([a.elapsed_time(b) for a, b in t_ar]))
-    if world > 1:
-        tt = torch.tensor([dt], device=dev)
-        torch.distributed.all_reduce(tt, op=torch.distributed.ReduceOp.MAX)
-        dt = float(tt.item())
-    R, over = ws.last_status()
-    assert not over
-    return {"config": f"cfg5: S-room {P} Gaussians, {K}-keyframe batch over {world} GPU(s), all-reduce of [P,14] fp32 "
-                      f"({P * 14 * 4 / 1e6:.0f} MB) + fused Adam per step",
-            "ours": {"s_per_step": dt, "mpix_s": K * W * H / dt / 1e6, "allreduce_ms": ar_ms,
-                     "keyframes_per_rank": len(mine)}}
+        for i in range(2):
+            step(i)
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            torch.distributed.barrier()
+        t_ex.clear()
+        n = 3
+        t0 = time.time()
+        for i in range(n):
+            step(i)
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            torch.distributed.barrier()
+        dt = (time.time() - t0) / n
+        ex_ms = float(np.mean([a.elapsed_time(c) for a, _, c in t_ex]))
+        ar_ms = float(np.mean([a.elapsed_time(b) for a, b, _ in t_ex]))
+        if world > 1:
+            tt = torch.tensor([dt, ex_ms], device=dev)
+            torch.distributed.all_reduce(tt, op=torch.distributed.ReduceOp.MAX)
+            dt, ex_ms = float(tt[0]), float(tt[1])
+        R, over = ws.last_status()
+        assert not over
+        out[kind] = {"s_per_step": dt, "mpix_s": K * W * H / dt / 1e6, "exchange_plus_adam_ms": ex_ms,
+                     "keyframes_per_rank": len(mine)}
+        if kind == "allreduce":
+            out[kind]["allreduce_ms"] = ar_ms
+        chk = float(p["means3D"].double().sum())
+        out[kind]["means3D_checksum"] = chk
+        del opt, p
+        from activesplat_b200 import frame as _fr
+        _fr._WORKSPACES.clear()
+    return {"config": f"cfg5: S-room {P} Gaussians, {K}-keyframe batch over {world} GPU(s); exchange of the [P,14] fp32 "
+                      f"gradient ({P * 14 * 4 / 1e6:.0f} MB) + Adam per step, by NCCL all-reduce + fused Adam and by the "
+                      "peer-memory reduce+Adam kernel",
+            "ours": out["peer"] if world > 1 else out["allreduce"], "allreduce_path": out["allreduce"],
+            "peer_path": out["peer"]}
 
 
 def scoring(dev):

@@ -233,6 +233,28 @@ int as_adam_step(int P, int isotropic, float* means3D, float* rgb_colors, float*
                  float* exp_avg_sq, const float* lrs, float beta1, float beta2, float eps, int step,
                  void* cuda_stream);
 
+/* Adam fused with the gradient exchange of keyframe-batched mapping, over peer memory (one process per GPU,
+ * NVLink / NVSwitch).  Replaces "all-reduce the flat [P,14] gradient, then as_adam_step on every rank": rank `rank` of
+ * `world` (<= 8) owns the Gaussians [g_begin, g_end) (g_begin a multiple of 4; buffers 16-byte aligned); it reads those rows of EVERY rank's gradient buffer through peer
+ * pointers, adds them in rank order, applies the Adam update with optimizer state kept only for its rows
+ * (exp_avg / exp_avg_sq are [(g_end-g_begin),14]), and writes the new values into the parameter tensors of every rank.
+ *   params  host array of 5*world device pointers: params[5*r + t] = tensor t (means3D, rgb_colors, unnorm_rotations,
+ *           logit_opacities, log_scales) of rank r as mapped into THIS process (cudaIpcOpenMemHandle or equivalent,
+ *           peer access enabled); grads: host array of `world` pointers to the ranks' flat [P,14] gradients.
+ * The caller orders the ranks around the call: every rank's gradient must be complete before any rank starts, and no
+ * rank may read its parameters or overwrite its gradient before all ranks have finished (two stream-ordered barriers,
+ * e.g. tiny NCCL all-reduces).  No reference counterpart: ActiveSplat is single-GPU. */
+/* Lets kernels launched on the current device dereference memory of `peer_device` (cudaDeviceEnablePeerAccess;
+ * already-enabled is not an error).  Needed once per (device, peer) before as_adam_step_peer. */
+int as_enable_peer_access(int peer_device);
+/* cudaIpcOpenMemHandle (64-byte handle from cudaIpcGetMemHandle in the exporting process) on the CURRENT device with
+ * lazy peer access, so that this device's kernels can use the mapping; returns the base of the exported allocation. */
+int as_ipc_open(const void* handle64, void** out_ptr);
+int as_ipc_close(void* ptr);
+int as_adam_step_peer(int P, int isotropic, int world, int rank, int g_begin, int g_end, float* const* params,
+                      const float* const* grads, float* exp_avg, float* exp_avg_sq, const float* lrs, float beta1,
+                      float beta2, float eps, int step, void* cuda_stream);
+
 /* ---- the step after the GetOpacity renders: clustering of low-visibility pixels ----------------
  *
  * DBSCAN over the pixels of `batch` images whose value exceeds value_threshold, replacing

@@ -729,3 +729,26 @@ def test_auto_binning_falls_back_to_the_global_sort_without_synchronising():
         torch.cuda.synchronize()
         helpers.compare_exact("colour", ws.color6.cpu().numpy().view(np.int32), ref.color6.cpu().numpy().view(np.int32))
     assert ws.binning_mode == 0
+
+
+def test_peer_sharded_adam_single_rank_equals_fused_adam():
+    """as_adam_step_peer with one rank (its own gradient, the whole map as its slab) against as_adam_step: same
+    arithmetic per element, so the parameters agree to the last bit after several steps."""
+    from activesplat_b200 import dist as asd
+    from activesplat_b200.frame import FusedAdam, PARAM_ORDER
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(5)
+    P = 3001
+    shapes = {"means3D": 3, "rgb_colors": 3, "unnorm_rotations": 4, "logit_opacities": 1, "log_scales": 3}
+    lrs = {"means3D": 1e-4, "rgb_colors": 2.5e-3, "unnorm_rotations": 1e-3, "logit_opacities": 5e-2, "log_scales": 1e-3}
+    a = {k: torch.randn(P, w, generator=g).to(dev) for k, w in shapes.items()}
+    b = {k: v.clone() for k, v in a.items()}
+    flat = torch.zeros((P, 14), device=dev)
+    opt_a = FusedAdam(a, lrs)
+    opt_b = asd.PeerShardedAdam(b, lrs, flat)
+    for step in range(4):
+        flat.copy_(torch.randn(P, 14, generator=g) * 10.0 ** (step - 2))
+        opt_a.step(flat)
+        opt_b.step()
+    for k in PARAM_ORDER:
+        helpers.compare_float("peer adam " + k, b[k].cpu().numpy(), a[k].cpu().numpy(), rel=1e-6)
