@@ -347,8 +347,7 @@ def cfg5(dev, args, rank, world):
     return {"config": f"cfg5: S-room {P} Gaussians, {K}-keyframe batch over {world} GPU(s); exchange of the [P,14] fp32 "
                       f"gradient ({P * 14 * 4 / 1e6:.0f} MB) + Adam per step, by NCCL all-reduce + fused Adam and by the "
                       "peer-memory reduce+Adam kernel",
-            "ours": out["peer"] if world > 1 else out["allreduce"], "allreduce_path": out["allreduce"],
-            "peer_path": out["peer"]}
+            "ours": out["allreduce"], "allreduce_path": out["allreduce"], "peer_path": out["peer"]}
 
 
 def scoring(dev):
