@@ -137,3 +137,48 @@ def test_get_local_invisibility_end_to_end_against_the_oracle_pipeline():
         assert pose is not None and np.allclose(pose, want, atol=2e-3)   # cluster centre moves by < 0.1 px
     else:
         assert pose is None
+
+
+def test_matrix_to_pose_is_the_w_positive_unit_quaternion():
+    """src/utils/gui_utils.py:138-152 (quaternion.from_rotation_matrix), checked against scipy's conversion."""
+    from scipy.spatial.transform import Rotation
+    from activesplat_b200.getopacity import matrix_to_pose
+    rng = np.random.default_rng(0)
+    for _ in range(20):
+        R = Rotation.random(random_state=int(rng.integers(1 << 30)))
+        M = np.eye(4)
+        M[:3, :3], M[:3, 3] = R.as_matrix(), rng.normal(size=3)
+        p = matrix_to_pose(M)
+        q = R.as_quat()
+        q = q if q[3] >= 0 else -q
+        assert np.allclose(p.orientation_xyzw, q, atol=1e-12) and np.array_equal(p.position, M[:3, 3])
+
+
+@pytest.mark.gpu
+def test_get_opacity_local_and_global_renders():
+    from activesplat_b200 import getopacity as go, scenes, scoring
+    dev = torch.device("cuda:0")
+    params_cpu, _ = scenes.s_room(6000, 1, seed=41, scale_mult=6.0)
+    keep = params_cpu["means3D"][:, 0] < 3.0
+    params = {k: v[keep].contiguous().to(dev) for k, v in params_cpu.items()}
+    c2w = np.eye(4)
+    c2w[:3, 3] = [0.3, 0.0, -0.4]
+    resp = go.handle_get_opacity(go.GetOpacityRequest(arrived_flag=False), params, c2w)
+    total, pose = scoring.get_local_invisibility(params, c2w, 30)
+    assert resp.targets_frustums_volume == [0.0] and len(resp.targets_frustums) == 1
+    assert abs(resp.targets_frustums_invisibility[0] - total) <= 1e-3 * total
+    if pose is None:
+        assert np.array_equal(resp.targets_frustums[0].orientation_xyzw, np.zeros(4))
+    else:
+        want = go.matrix_to_pose(pose @ go.OPENCV_TO_OPENGL)
+        assert np.allclose(resp.targets_frustums[0].orientation_xyzw, want.orientation_xyzw, atol=1e-6)
+        assert np.allclose(resp.targets_frustums[0].position, c2w[:3, 3])
+    # GLOBAL: renders for three nodes (one at the origin is skipped by the reference), sums per node
+    nodes = np.array([[1.0, 0.0, 0.5], [0.0, 0.0, 0.0], [-1.0, 0.0, -0.5]])
+    sums, ops, idx = go.global_panoramas(params, c2w, nodes)
+    assert sums.shape == (3,) and float(sums[1]) == 0.0 and ops.shape == (6, 150, 120) and idx == list(range(6))
+    for n_i, first in ((0, 0), (2, 3)):
+        want = float((1.0 - ops[first:first + 3]).sum())
+        assert abs(float(sums[n_i]) - want) <= 1e-4 * max(want, 1.0)
+    with pytest.raises(NotImplementedError):
+        go.handle_get_opacity(go.GetOpacityRequest(True, nodes, [0, 1, 2]), params, c2w)
