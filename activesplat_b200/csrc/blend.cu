@@ -506,7 +506,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
                     if ((act >> u) & 1u) {
                         const int j = jj[u];
                         const float alpha = al[u];
-                        const float inv_1ma = __frcp_rn(1.f - alpha);  // 1 - alpha is in [0.01, 1]; shared by T / (1 - alpha) and the background term
+                        const float inv_1ma = __fdividef(1.f, 1.f - alpha);  // 1 - alpha is in [0.01, 1]: the 1-ulp approximate reciprocal; shared by T / (1 - alpha) and the background term
                         T = T * inv_1ma;
                         const float4 f0 = sm.feat[s][j * FV];
                         const float4 f1 = sm.feat[s][j * FV + FV - 1];
