@@ -43,12 +43,13 @@ __device__ __forceinline__ float eval_power(const float4& co, float dx, float dy
     return __fmaf_rn(q, -0.5f, -__fmul_rn(__fmul_rn(co.y, dx), dy));
 }
 
-template <int C, int STAGES = BL_STAGES>
+template <int C, int STAGES = BL_STAGES, int BATCH_ = BL_BATCH>
 struct BlendSmem {
     static constexpr int FV = (C == 3) ? 1 : 2;
-    float4 conic[STAGES][BL_BATCH];
-    float4 geom[STAGES][BL_BATCH];
-    float4 feat[STAGES][BL_BATCH * FV];
+    static constexpr int BATCH = BATCH_;
+    float4 conic[STAGES][BATCH_];
+    float4 geom[STAGES][BATCH_];
+    float4 feat[STAGES][BATCH_ * FV];
     uint64_t bar[STAGES];
 };
 
@@ -96,7 +97,7 @@ __device__ __forceinline__ int cull_batch(const SM& sm, int s, int limit, int la
     int n = 0;
     const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll
-    for (int k = 0; k < BL_BATCH / 32; k++) {
+    for (int k = 0; k < SM::BATCH / 32; k++) {
         const int j = lane + 32 * k;
         bool ok = false;
         if (j < limit) {
@@ -336,6 +337,10 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
 //     12 gradient terms, and adds them to the CTA's per-batch accumulator.
 // The CTA flushes the accumulator once per (tile, instance) with 128-bit vector reductions (REDG.ADD.F32x4).
 constexpr int BW_GROUP = 16;   // records per group: 16 x 32 staging slots per warp
+#ifndef ASB_BW_BATCH
+#define ASB_BW_BATCH 128
+#endif
+constexpr int BW_BATCH = ASB_BW_BATCH;  // records per staged batch in the backward (64 gives 4 CTAs per SM but twice the barriers: measured slower)
 constexpr int BW_STAGES = 2;   // bulk-copy pipeline depth of the backward (a batch takes long enough to hide one copy)
 #ifndef ASB_BW_UNROLL
 #define ASB_BW_UNROLL 2
@@ -370,12 +375,12 @@ __device__ __forceinline__ constexpr bool need_colour(int ch) {
 
 template <int C, int WARPS>
 struct BwdLayout {
-    using SM = BlendSmem<C, BW_STAGES>;
+    using SM = BlendSmem<C, BW_STAGES, BW_BATCH>;
     static constexpr size_t off_qw = (sizeof(SM) + 127) / 128 * 128;
     static constexpr size_t off_dpx = off_qw + sizeof(float2) * WARPS * BW_GROUP * 32;
     static constexpr size_t off_mask = off_dpx + sizeof(float) * WARPS * C * 32;
-    static constexpr size_t off_list = off_mask + sizeof(uint32_t) * WARPS * BL_BATCH;
-    static constexpr size_t bytes = off_list + WARPS * BL_BATCH;
+    static constexpr size_t off_list = off_mask + sizeof(uint32_t) * WARPS * BW_BATCH;
+    static constexpr size_t bytes = off_list + WARPS * BW_BATCH;
 };
 
 template <int C, int WARPS, int MODE>
@@ -394,8 +399,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
     const int wid = threadIdx.x >> 5;
     float2* stg = reinterpret_cast<float2*>(smem_raw + LY::off_qw) + wid * BW_GROUP * 32;
     float* dpx = reinterpret_cast<float*>(smem_raw + LY::off_dpx) + wid * C * 32;   // [C][32]
-    uint32_t* masks = reinterpret_cast<uint32_t*>(smem_raw + LY::off_mask) + wid * BL_BATCH;
-    uint8_t* list = reinterpret_cast<uint8_t*>(smem_raw + LY::off_list) + wid * BL_BATCH;
+    uint32_t* masks = reinterpret_cast<uint32_t*>(smem_raw + LY::off_mask) + wid * BW_BATCH;
+    uint8_t* list = reinterpret_cast<uint8_t*>(smem_raw + LY::off_list) + wid * BW_BATCH;
     __shared__ int s_max_contrib;
 
     const int tile = tile_order ? (int)tile_order[blockIdx.x / PARTS] : (int)(blockIdx.x / PARTS);
@@ -427,11 +432,11 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
     __syncthreads();
     // Entries at list index >= len are skipped by every pixel of the tile (backward.cu:489-490).
     const int len = s_max_contrib;
-    const int nb = (len + BL_BATCH - 1) / BL_BATCH;
+    const int nb = (len + BW_BATCH - 1) / BW_BATCH;
     // batch k covers list indices [hi_k - cnt_k, hi_k), hi_k = len - k*BATCH, walked back to front
     if (threadIdx.x == 0) {
         for (int q = 0; q < BW_STAGES && q < nb; q++) {
-            const int hi = len - q * BL_BATCH, cnt = min(BL_BATCH, hi);
+            const int hi = len - q * BW_BATCH, cnt = min(BW_BATCH, hi);
             issue_batch(sm, q, inst_conic, inst_geom, inst_feat, range.x + (uint32_t)(hi - cnt), cnt);
         }
     }
@@ -452,8 +457,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
 
     for (int b = 0; b < nb; b++) {
         const int s = b & (BW_STAGES - 1);
-        const int hi = len - b * BL_BATCH;
-        const int cnt = min(BL_BATCH, hi);
+        const int hi = len - b * BW_BATCH;
+        const int cnt = min(BW_BATCH, hi);
         const int lo = hi - cnt;  // list index of record 0 of this batch
         mbar_wait(&sm.bar[s], (uint32_t)((b / BW_STAGES) & 1));
 
@@ -589,7 +594,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
         }
         __syncthreads();  // every warp is done with stage s
         if (threadIdx.x == 0 && b + BW_STAGES < nb) {
-            const int nhi = len - (b + BW_STAGES) * BL_BATCH, ncnt = min(BL_BATCH, nhi);
+            const int nhi = len - (b + BW_STAGES) * BW_BATCH, ncnt = min(BW_BATCH, nhi);
             issue_batch(sm, s, inst_conic, inst_geom, inst_feat, range.x + (uint32_t)(nhi - ncnt), ncnt);
         }
     }
