@@ -120,6 +120,9 @@ SYMBOLS = {
     "as_mapping_loss_scratch_floats": (_Z, [_I, _I]),
     "as_mapping_loss": (_I, [_I, _I, _V, _V, _V, _F, _F, _V, _V, _V, _V, _V]),
     "as_adam_step": (_I, [_I, _I, _V, _V, _V, _V, _V, _V, _V, _V, ctypes.POINTER(ctypes.c_float), _F, _F, _F, _I, _V]),
+    "as_pose_adam_step": (_I, [_V, _V, _I, _F, _V, _V, _I, _F, _V, _V, _F, _F, _F, _V, _V]),
+    "as_adam_step_counted": (_I, [_I, _I, _V, _V, _V, _V, _V, _V, _V, _V, ctypes.POINTER(ctypes.c_float), _F, _F, _F, _V,
+                                  _V]),
     "as_enable_peer_access": (_I, [_I]),
     "as_ipc_open": (_I, [ctypes.c_char_p, ctypes.POINTER(ctypes.c_void_p)]),
     "as_ipc_close": (_I, [_V]),

@@ -23,6 +23,8 @@
 #include <math_constants.h>
 #include <cstdlib>
 
+#include <atomic>
+
 #include "common.cuh"
 
 namespace asb {
@@ -603,11 +605,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
 }  // namespace
 
 // Warps per CTA: whole tiles (8 warps) when there are plenty of tiles, finer splits for small images.
-static int pick_warps(int tiles, bool forward, const char* env = nullptr) {
-    if (env) {  // experiments only
-        const char* v = getenv(env);
-        if (v) return atoi(v);
-    }
+static int pick_warps(int tiles, bool forward) {
     if (tiles >= (forward ? 16 : 3) * NUM_SMS) return 8;  // forward: half-tile CTAs pack the SMs better (measured at 1200 tiles)
     if (tiles * 2 >= 3 * NUM_SMS) return 4;
     if (tiles * 4 >= 3 * NUM_SMS) return 2;
@@ -636,9 +634,18 @@ static void launch_bwd_c(int warps, int tiles, cudaStream_t st, const uint2* ran
 #define ASB_BWD(WP)                                                                                                \
     do {                                                                                                           \
         constexpr size_t smem = BwdLayout<C, WP>::bytes;                                                           \
-        if (smem > 48 * 1024)                                                                                      \
-            cudaFuncSetAttribute(blend_backward_kernel<C, WP, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
-                                 (int)smem);                                                                       \
+        if (smem > 48 * 1024) {                                                                                    \
+            /* opt in to the large dynamic shared-memory carve-out once per (kernel instance, device) */           \
+            static std::atomic<unsigned> done_mask{0};                                                             \
+            int dev = 0;                                                                                           \
+            cudaGetDevice(&dev);                                                                                   \
+            const unsigned bit = 1u << (dev & 31);                                                                 \
+            if (!(done_mask.load(std::memory_order_relaxed) & bit)) {                                              \
+                cudaFuncSetAttribute(blend_backward_kernel<C, WP, MODE>,                                           \
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);                      \
+                done_mask.fetch_or(bit, std::memory_order_relaxed);                                                \
+            }                                                                                                      \
+        }                                                                                                          \
         blend_backward_kernel<C, WP, MODE><<<tiles*(8 / WP), 32 * WP, smem, st>>>(                                 \
             ranges, b.inst_conic, b.inst_geom, b.inst_feat, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc,        \
             tile_order);                                                                                           \
@@ -656,7 +663,7 @@ void launch_blend_forward(int channels, int W, int H, const uint2* ranges, const
     const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
     const int tiles = gx * gy;
     if (tiles <= 0) return;
-    const int warps = pick_warps(tiles, true, "ASB_FWD_WARPS");
+    const int warps = pick_warps(tiles, true);
     if (channels == 3)
         launch_fwd_c<3>(warps, tiles, st, ranges, b, W, H, gx, bg, out_color, out_depth, out_opacity, final_T, n_contrib,
                         tile_order);
@@ -671,7 +678,7 @@ void launch_blend_backward(int channels, int W, int H, const uint2* ranges, cons
     const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
     const int tiles = gx * gy;
     if (tiles <= 0) return;
-    const int warps = pick_warps(tiles, false, "ASB_BWD_WARPS");
+    const int warps = pick_warps(tiles, false);
     if (channels == 3)
         launch_bwd_c<3, BWD_ALL>(warps, tiles, st, ranges, b, W, H, gx, bg, final_T, n_contrib, dL_dpix, gacc,
                                   tile_order);

@@ -6,6 +6,7 @@
 //                rasterizer_impl.cu:155-194, rasterizer_impl.h:21-72
 #include <cstdio>
 #include <cstring>
+#include <atomic>
 #include <mutex>
 
 #include "common.cuh"
@@ -89,16 +90,17 @@ static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 // ---- optional per-stage timing (bench.py's roofline attribution) and launch counting ----------
 // Off by default.  When on, every stage is bracketed by two CUDA events recorded on the launching
 // stream; as_profile_read() synchronises and sums elapsed times per stage.  Process-wide (torch runs
-// backward passes on its own thread), guarded by a mutex; one device at a time.
+// backward passes on its own thread); the mutex is only taken while profiling is on -- with it off a
+// stage costs two relaxed atomic operations and the library calls stay independent of each other.
 struct Profiler {
     std::mutex mu;
-    bool on = false;
+    std::atomic<bool> on{false};
     static constexpr int MAX_EV = 8192;
     cudaEvent_t ev[MAX_EV];
     int n_created = 0;
     int n_used = 0;                   // events used since the last read (pairs: 2k, 2k+1)
     int stage_of[MAX_EV / 2];
-    long long launches = 0;           // kernels launched by this library on this thread (always counted)
+    std::atomic<long long> launches{0};  // kernels launched by this library (always counted)
 };
 static Profiler g_prof;
 
@@ -106,9 +108,10 @@ struct StageScope {
     cudaStream_t st;
     int slot = -1;
     StageScope(int stage, cudaStream_t s, int kernels) : st(s) {
+        g_prof.launches.fetch_add(kernels, std::memory_order_relaxed);
+        if (!g_prof.on.load(std::memory_order_relaxed)) return;
         std::lock_guard<std::mutex> lock(g_prof.mu);
-        g_prof.launches += kernels;
-        if (!g_prof.on || g_prof.n_used + 2 > Profiler::MAX_EV) return;
+        if (g_prof.n_used + 2 > Profiler::MAX_EV) return;
         while (g_prof.n_created < g_prof.n_used + 2) {
             if (cudaEventCreate(&g_prof.ev[g_prof.n_created]) != cudaSuccess) return;
             g_prof.n_created++;
@@ -319,6 +322,8 @@ int as_frame_forward(const AsFrameArgs* a, void* cuda_stream) {
         !a->out_opacity)
         return AS_ERR_INVALID_ARG;
     if (!aligned16(a->unnorm_rotations)) return AS_ERR_INVALID_ARG;
+    // the preprocess look-back word carries the visible count in 24 bits next to its flag bits
+    if (a->P >= (1 << 24)) return AS_ERR_INVALID_ARG;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
     const int P = a->P, W = a->width, H = a->height;
     const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y, tiles = gx * gy;
@@ -450,6 +455,35 @@ int as_adam_step(int P, int isotropic, float* means3D, float* rgb_colors, float*
     return check(cudaGetLastError());
 }
 
+int as_adam_step_counted(int P, int isotropic, float* means3D, float* rgb_colors, float* unnorm_rotations,
+                         float* logit_opacities, float* log_scales, const float* grad_params, float* exp_avg,
+                         float* exp_avg_sq, const float* lrs, float beta1, float beta2, float eps, float* step_state,
+                         void* cuda_stream) {
+    if (P < 0 || !lrs || !step_state) return AS_ERR_INVALID_ARG;
+    if (P > 0 && (!means3D || !rgb_colors || !unnorm_rotations || !logit_opacities || !log_scales || !grad_params ||
+                  !exp_avg || !exp_avg_sq))
+        return AS_ERR_INVALID_ARG;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
+    float* params[5] = {means3D, rgb_colors, unnorm_rotations, logit_opacities, log_scales};
+    StageScope _s(AS_STAGE_ADAM, st, 2);
+    launch_adam_counted(P, isotropic, params, lrs, grad_params, exp_avg, exp_avg_sq, beta1, beta2, eps, step_state, st);
+    return check(cudaGetLastError());
+}
+
+int as_pose_adam_step(float* cam_unnorm_rots, const float* grad_rots, int n_rots, float lr_rots, float* cam_trans,
+                      const float* grad_trans, int n_trans, float lr_trans, float* exp_avg, float* exp_avg_sq,
+                      float beta1, float beta2, float eps, float* step_state, void* cuda_stream) {
+    if (n_rots < 0 || n_trans < 0 || !step_state) return AS_ERR_INVALID_ARG;
+    if ((n_rots > 0 && (!cam_unnorm_rots || !grad_rots)) || (n_trans > 0 && (!cam_trans || !grad_trans)) ||
+        (n_rots + n_trans > 0 && (!exp_avg || !exp_avg_sq)))
+        return AS_ERR_INVALID_ARG;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
+    StageScope _s(AS_STAGE_ADAM, st, 2);
+    launch_pose_adam(cam_unnorm_rots, grad_rots, n_rots, lr_rots, cam_trans, grad_trans, n_trans, lr_trans, exp_avg,
+                     exp_avg_sq, beta1, beta2, eps, step_state, st);
+    return check(cudaGetLastError());
+}
+
 int as_enable_peer_access(int peer_device) {
     int cur = -1;
     if (cudaGetDevice(&cur) != cudaSuccess) return AS_ERR_CUDA;
@@ -544,7 +578,7 @@ int as_inclusive_scan_u32(const uint32_t* in, uint32_t* out, int n, uint32_t* to
 
 void as_profile_enable(int on) {
     std::lock_guard<std::mutex> lock(g_prof.mu);
-    g_prof.on = on != 0;
+    g_prof.on.store(on != 0);
 }
 
 int as_profile_read(double* ms_per_stage, int* calls_per_stage, int n_stages) {
@@ -565,10 +599,7 @@ int as_profile_read(double* ms_per_stage, int* calls_per_stage, int n_stages) {
     return r;
 }
 
-long long as_launch_count(void) {
-    std::lock_guard<std::mutex> lock(g_prof.mu);
-    return g_prof.launches;
-}
+long long as_launch_count(void) { return g_prof.launches.load(std::memory_order_relaxed); }
 
 int as_static_scan_max_n(void) { return static_scan_max_n(); }
 

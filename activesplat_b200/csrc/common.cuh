@@ -170,6 +170,11 @@ void launch_dbscan_grid(int batch, int H, int W, const float* values, float thr,
                         int* scratch, int max_clusters, int* n_clusters, int* stats_i, double* stats_v, cudaStream_t st);
 void launch_adam(int P, int iso, float* const params[5], const float lr[5], const float* grad, float* m, float* v,
                  float beta1, float beta2, float eps, int step, cudaStream_t st);
+void launch_pose_adam(float* rots, const float* g_rots, int n_rots, float lr_rots, float* trans, const float* g_trans,
+                      int n_trans, float lr_trans, float* m, float* v, float beta1, float beta2, float eps,
+                      float* step_state, cudaStream_t st);
+void launch_adam_counted(int P, int iso, float* const params[5], const float lr[5], const float* grad, float* m,
+                         float* v, float beta1, float beta2, float eps, float* step_state, cudaStream_t st);
 
 // ---------------------------------------------------------------------------------------------
 // device helpers

@@ -1017,10 +1017,18 @@ constexpr int AD_G = 256;  // Gaussians per block
 // are one contiguous span that the threads walk four elements at a time (128-bit accesses when aligned).
 // Arithmetic per element as torch.optim.Adam (single-tensor path): lerp_, mul_/addcmul_, sqrt / bias_correction2_sqrt
 // + eps, addcdiv_.
+// sched (optional, device memory): [1..5] = lr[t] / bias_correction1, [6] = sqrt(bias_correction2), written by
+// adam_advance_kernel; when given it replaces ap.s* and bc2_sqrt (the step count then lives on the device, so the
+// launch is identical every step and can sit in a CUDA graph).
 __global__ void __launch_bounds__(256)
 adam_kernel(int P, int iso, AdamPtrs ap, const float* __restrict__ grad, float* __restrict__ m, float* __restrict__ v,
-            float beta1, float beta2, float eps, float bc2_sqrt) {
+            float beta1, float beta2, float eps, float bc2_sqrt, const float* __restrict__ sched) {
     __shared__ __align__(16) float s_p[AD_G * 14];  // means [G,3] | rgb [G,3] | rot [G,4] | logit [G] | scales [G,3 or 1]
+    if (sched) {
+        ap.s0 = __ldg(sched + 1); ap.s1 = __ldg(sched + 2); ap.s2 = __ldg(sched + 3); ap.s3 = __ldg(sched + 4);
+        ap.s4 = __ldg(sched + 5);
+        bc2_sqrt = __ldg(sched + 6);
+    }
     const int g0 = blockIdx.x * AD_G;
     const int G = min(AD_G, P - g0);
     const int ws = iso ? 1 : 3;
@@ -1252,15 +1260,15 @@ void launch_adam_peer(int g_begin, int g_end, int iso, int world, int rank, floa
                       float beta2, float eps, int step, cudaStream_t st) {
     if (g_end <= g_begin) return;
     PeerAdamArgs pa;
-    const float bc1 = 1.f - powf(beta1, (float)step);
-    const float bc2_sqrt = sqrtf(1.f - powf(beta2, (float)step));
+    const double bc1 = 1.0 - pow((double)beta1, (double)step);
+    const float bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, (double)step));
     for (int r = 0; r < 8; r++) {
         for (int t = 0; t < 5; t++) pa.params[r][t] = r < world ? params[5 * r + t] : nullptr;
         pa.grads[r] = r < world ? grads[r] : nullptr;
     }
     for (int t = 0; t < 5; t++) {
         pa.own[t] = params[5 * rank + t];
-        pa.step_size[t] = lr[t] / bc1;
+        pa.step_size[t] = (float)(lr[t] / bc1);
     }
     pa.world = world;
     const size_t threads = 14 * (size_t)(g_end - g_begin);
@@ -1286,14 +1294,67 @@ void launch_tracking_loss(int N, const float* c6, const float* gt_rgb, const flo
     tracking_loss_finalize_kernel<<<1, 32, 0, st>>>(blocks, partials, w_im, w_depth, losses, status);
 }
 
+// Bias corrections in double, like torch.optim.Adam computes them on the host (1 - beta ** step in Python floats).
 void launch_adam(int P, int iso, float* const params[5], const float lr[5], const float* grad, float* m, float* v,
                  float beta1, float beta2, float eps, int step, cudaStream_t st) {
-    const float bc1 = 1.f - powf(beta1, (float)step);
-    const float bc2_sqrt = sqrtf(1.f - powf(beta2, (float)step));
+    const double bc1 = 1.0 - pow((double)beta1, (double)step);
+    const float bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, (double)step));
     AdamPtrs ap;
     ap.p0 = params[0]; ap.p1 = params[1]; ap.p2 = params[2]; ap.p3 = params[3]; ap.p4 = params[4];
-    ap.s0 = lr[0] / bc1; ap.s1 = lr[1] / bc1; ap.s2 = lr[2] / bc1; ap.s3 = lr[3] / bc1; ap.s4 = lr[4] / bc1;
-    adam_kernel<<<(P + AD_G - 1) / AD_G, 256, 0, st>>>(P, iso, ap, grad, m, v, beta1, beta2, eps, bc2_sqrt);
+    ap.s0 = (float)(lr[0] / bc1); ap.s1 = (float)(lr[1] / bc1); ap.s2 = (float)(lr[2] / bc1);
+    ap.s3 = (float)(lr[3] / bc1); ap.s4 = (float)(lr[4] / bc1);
+    adam_kernel<<<(P + AD_G - 1) / AD_G, 256, 0, st>>>(P, iso, ap, grad, m, v, beta1, beta2, eps, bc2_sqrt, nullptr);
+}
+
+// One thread: step += 1 (kept as a float-encoded integer in state[0]; exact up to 2^24 steps), then the step sizes and
+// sqrt(bias_correction2) of that step in double.
+__global__ void adam_advance_kernel(float* state, float lr0, float lr1, float lr2, float lr3, float lr4, float beta1,
+                                    float beta2) {
+    const double step = (double)state[0] + 1.0;
+    const double bc1 = 1.0 - pow((double)beta1, step);
+    state[0] = (float)step;
+    state[1] = (float)(lr0 / bc1); state[2] = (float)(lr1 / bc1); state[3] = (float)(lr2 / bc1);
+    state[4] = (float)(lr3 / bc1); state[5] = (float)(lr4 / bc1);
+    state[6] = (float)sqrt(1.0 - pow((double)beta2, step));
+}
+
+// Adam over the two camera-pose tensors (tracking: lr 1e-3 on cam_unnorm_rots, 4e-3 on cam_trans, default eps 1e-8,
+// config/splatam/online_habitat_sim.py:37-45).  A few hundred floats at most: one small grid, the step count on the device.
+__global__ void pose_adam_kernel(float* __restrict__ rots, const float* __restrict__ g_rots, int n_rots,
+                                 float* __restrict__ trans, const float* __restrict__ g_trans, int n_trans,
+                                 float* __restrict__ m, float* __restrict__ v, float beta1, float beta2, float eps,
+                                 const float* __restrict__ sched) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_rots + n_trans) return;
+    const bool is_rot = i < n_rots;
+    float* p = is_rot ? rots + i : trans + (i - n_rots);
+    const float g = is_rot ? g_rots[i] : g_trans[i - n_rots];
+    const float step_size = sched[is_rot ? 1 : 2], bc2_sqrt = sched[6];
+    const float nm = m[i] + (g - m[i]) * (1.f - beta1);
+    const float nv = v[i] * beta2 + (1.f - beta2) * g * g;
+    m[i] = nm;
+    v[i] = nv;
+    *p = *p - step_size * (nm / (sqrtf(nv) / bc2_sqrt + eps));
+}
+
+void launch_pose_adam(float* rots, const float* g_rots, int n_rots, float lr_rots, float* trans, const float* g_trans,
+                      int n_trans, float lr_trans, float* m, float* v, float beta1, float beta2, float eps,
+                      float* step_state, cudaStream_t st) {
+    adam_advance_kernel<<<1, 1, 0, st>>>(step_state, lr_rots, lr_trans, 0.f, 0.f, 0.f, beta1, beta2);
+    const int n = n_rots + n_trans;
+    if (n > 0)
+        pose_adam_kernel<<<(n + 127) / 128, 128, 0, st>>>(rots, g_rots, n_rots, trans, g_trans, n_trans, m, v, beta1,
+                                                          beta2, eps, step_state);
+}
+
+void launch_adam_counted(int P, int iso, float* const params[5], const float lr[5], const float* grad, float* m,
+                         float* v, float beta1, float beta2, float eps, float* step_state, cudaStream_t st) {
+    adam_advance_kernel<<<1, 1, 0, st>>>(step_state, lr[0], lr[1], lr[2], lr[3], lr[4], beta1, beta2);
+    if (P <= 0) return;
+    AdamPtrs ap;
+    ap.p0 = params[0]; ap.p1 = params[1]; ap.p2 = params[2]; ap.p3 = params[3]; ap.p4 = params[4];
+    ap.s0 = ap.s1 = ap.s2 = ap.s3 = ap.s4 = 0.f;
+    adam_kernel<<<(P + AD_G - 1) / AD_G, 256, 0, st>>>(P, iso, ap, grad, m, v, beta1, beta2, eps, 1.f, step_state);
 }
 
 }  // namespace asb

@@ -141,7 +141,7 @@ def score_candidate_views(params, views, group=None, n_streams=32, scale_modifie
     P = int(params["means3D"].shape[0])
     W, H = int(views[0].width), int(views[0].height)
     n_streams = max(1, min(n_streams, len(mine)))
-    key = (P, W, H, dev.index, n_streams)
+    key = (W, H, dev.index, n_streams)   # not P: the workspaces follow a growing map (FrameWorkspace.resize)
     if key not in _VIEW_WORKSPACES:
         _VIEW_WORKSPACES[key] = ([FrameWorkspace(P, W, H, dev) for _ in range(n_streams)],
                                  [torch.cuda.Stream(device=dev) for _ in range(n_streams)])
@@ -151,6 +151,7 @@ def score_candidate_views(params, views, group=None, n_streams=32, scale_modifie
     p["cam_unnorm_rots"], p["cam_trans"] = rot, tr
     white = splatam._white_bg(dev)
     ops = torch.empty((len(mine), H, W), dtype=torch.float32, device=dev)
+    stats = torch.zeros((len(mine), 4), dtype=torch.int32, device=dev)
     if mine:
         d = _pack_cameras([views[v] for v in mine]).pin_memory().to(dev, non_blocking=True)
         cur = torch.cuda.current_stream(dev)
@@ -168,8 +169,24 @@ def score_candidate_views(params, views, group=None, n_streams=32, scale_modifie
                 with torch.cuda.stream(streams[s]):
                     wss[s].forward(p, cam, 0, sil_w2c=row[32:48].view(4, 4), bg_rgb=white)
                     ops[j].copy_(wss[s].opacity[0], non_blocking=True)
+                    stats[j].copy_(wss[s].status, non_blocking=True)
         for st in streams:
             cur.wait_stream(st)
+        # a view whose instances did not fit its workspace's binning buffer rendered as background: one look at all
+        # status words after the sweep, and those views are rendered again with the buffer grown
+        host = stats.cpu()
+        for j in torch.nonzero(host[:, 1]).flatten().tolist():
+            c, row, ws = views[mine[j]], d[j], wss[j % n_streams]
+            cam = splatam.Camera(image_height=H, image_width=W, tanfovx=W / (2 * c.fx), tanfovy=H / (2 * c.fy),
+                                 bg=row[51:54], scale_modifier=scale_modifier, viewmatrix=row[0:16].view(1, 4, 4),
+                                 projmatrix=row[16:32].view(1, 4, 4), sh_degree=0, campos=row[48:51],
+                                 prefiltered=False, debug=False)
+            ws.ensure_capacity(int(host[j, 0]) + int(host[j, 0]) // 4)
+            with torch.no_grad():
+                ws.forward(p, cam, 0, sil_w2c=row[32:48].view(4, 4), bg_rgb=white)
+            if ws.last_status()[1]:
+                raise RuntimeError("activesplat_b200: candidate view still overflows its binning buffer after growing it")
+            ops[j].copy_(ws.opacity[0])
     local = torch.stack([(1.0 - ops).sum((1, 2)), ops.mean((1, 2))], 1) if mine else torch.zeros((0, 2), device=dev)
     scores = gather_scores(local, len(views), rank, world, group)
     return (scores, ops) if return_opacity else scores

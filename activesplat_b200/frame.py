@@ -7,6 +7,7 @@ that `splatam.get_loss(tracking=True)` uses; `FusedAdam` mirrors `torch.optim.Ad
 by `initialize_optimizer` (src/mapper/splatam/splatam.py:118-124) over the five Gaussian tensors.
 """
 import ctypes
+import warnings
 
 import torch
 
@@ -28,48 +29,100 @@ class FrameWorkspace:
 
     def __init__(self, P, width, height, device, capacity=None, want_means2D_grad=False, binning=None):
         """binning: None = choose on the first frame (tile buckets unless a tile holds more instances than one
-        CTA sorts in shared memory), 0 = global radix sort, 1 = tile buckets.  Results are identical."""
+        CTA sorts in shared memory), 0 = global radix sort, 1 = tile buckets.  Results are identical.
+        P is the number of Gaussians of the first frame; `resize()` follows a growing map (densification)."""
         L = capi.lib()
         self.binning_mode = 1 if binning is None else int(binning)
         self._binning_auto = binning is None
-        self._status_host = None     # pinned copy of `status` (auto binning keeps an eye on the largest bucket)
+        self._status_host = None     # pinned copy of `status` of an earlier frame, fetched without synchronising
         self._status_event = None
-        self.P, self.W, self.H, self.device = int(P), int(width), int(height), torch.device(device)
-        self.capacity = int(capacity) if capacity else max(4 * self.P, 1 << 16)
+        self.W, self.H, self.device = int(width), int(height), torch.device(device)
+        self.capacity = int(capacity) if capacity else max(4 * int(P), 1 << 16)
+        self._want_means2D_grad = bool(want_means2D_grad)
+        self.P = self.cap_P = 0
         with torch.cuda.device(self.device):
             u8 = dict(dtype=torch.uint8, device=self.device)
             f32 = dict(dtype=torch.float32, device=self.device)
-            self.geom = torch.zeros(L.as_geometry_bytes(self.P), **u8)   # accumulators must start at zero
             self.img = torch.empty(L.as_image_bytes(self.W, self.H), **u8)
             self.binning = torch.empty(L.as_binning_bytes(self.capacity, 6), **u8)
             self.status = torch.zeros(4, dtype=torch.int32, device=self.device)
             self.color6 = torch.empty((6, self.H, self.W), **f32)
             self.depth = torch.empty((1, self.H, self.W), **f32)
             self.opacity = torch.empty((1, self.H, self.W), **f32)
-            self.radii = torch.empty((self.P,), dtype=torch.int32, device=self.device)
             self.dL = torch.empty((6, self.H, self.W), **f32)
             self.losses = torch.zeros(8, **f32)
             self.loss_scratch = torch.empty(L.as_loss_scratch_floats(self.W, self.H), **f32)
-            self.grad_params = torch.zeros((self.P, 14), **f32)
-            self.grad_means2D = torch.zeros((self.P, 3), **f32) if want_means2D_grad else None
             self.grad_cam = torch.zeros(8, **f32)
-            self.pose_scratch = torch.empty(L.as_pose_scratch_floats(self.P), **f32)
             self.bg6 = torch.zeros(6, **f32)
+        self.resize(int(P))
         self._args = None
         self._keep = None
         self._bg_src = None
         self.map_scratch = None
         self.calibrated = capacity is not None  # an explicit capacity is taken as is (and so is the binning mode)
+        self._calib_P = None
+        self.generation = 0          # bumped by every forward: a backward must belong to the latest one
+        self.overflow_seen = None    # (instances, capacity) of an earlier frame that did not fit, until reported
+        self._graph_pinned = False   # a CUDA graph captured this workspace's buffers: never free them
+        self._retired = []
 
     # -- buffer management ---------------------------------------------------------------------
+    def resize(self, P):
+        """Follow the map to P Gaussians.  The per-Gaussian buffers are allocated for cap_P >= P and grow
+        geometrically (x1.5), so a map that gains a few thousand Gaussians per frame reallocates rarely and the
+        binning buffer, its calibration and the image-sized buffers are kept."""
+        P = int(P)
+        if P == self.P:
+            return
+        L = capi.lib()
+        if getattr(self, "_calib_P", None) and not (0.5 * self._calib_P <= P <= 1.25 * self._calib_P):
+            self.calibrated = False   # a different map, not a growing one: size the binning buffer again
+        with torch.cuda.device(self.device):
+            if P > self.cap_P:
+                if getattr(self, "_graph_pinned", False):
+                    self._retired.append((self._geom, self._radii, self._grad_params, self._grad_means2D, self.pose_scratch))
+                self.cap_P = max(P, int(1.5 * self.cap_P))
+                u8 = dict(dtype=torch.uint8, device=self.device)
+                f32 = dict(dtype=torch.float32, device=self.device)
+                self._geom = torch.empty(L.as_geometry_bytes(self.cap_P), **u8)
+                self._radii = torch.empty((self.cap_P,), dtype=torch.int32, device=self.device)
+                self._grad_params = torch.zeros((self.cap_P * 14,), **f32)
+                self._grad_means2D = torch.zeros((self.cap_P * 3,), **f32) if self._want_means2D_grad else None
+                self.pose_scratch = torch.empty(L.as_pose_scratch_floats(self.cap_P), **f32)
+            # the scratch layout depends on P: the backward accumulators (which the kernels expect to find zeroed, and
+            # leave zeroed) land somewhere else, so the whole geometry buffer is cleared (stream-ordered, no sync)
+            self._geom.zero_()
+            self.P = P
+            self.geom = self._geom[: L.as_geometry_bytes(P)]
+            self.radii = self._radii[:P]
+            self.grad_params = self._grad_params[: P * 14].view(P, 14)
+            self.grad_means2D = self._grad_means2D[: P * 3].view(P, 3) if self._grad_means2D is not None else None
+
     def ensure_capacity(self, needed):
         if needed <= self.capacity:
             return False
+        if self._graph_pinned:
+            self._retired.append(self.binning)
         self.capacity = int(needed) + 1024
         with torch.cuda.device(self.device):
             self.binning = torch.empty(capi.lib().as_binning_bytes(self.capacity, 6), dtype=torch.uint8,
                                        device=self.device)
         return True
+
+    def _poll_status(self):
+        """Look at the status words of an EARLIER frame if their asynchronous copy has landed (never waits):
+        switches crowded views to the global sort, grows the binning buffer ahead of need (at half full), and
+        remembers an overflow so that the caller hears about it."""
+        if self._status_event is None or not self._status_event.query():
+            return
+        self._status_event = None
+        n_inst, overflowed, _, largest = (int(x) for x in self._status_host)
+        if self._binning_auto and self.binning_mode == 1 and largest > capi.lib().as_tile_sort_capacity():
+            self.binning_mode = 0
+        if overflowed:
+            self.overflow_seen = (n_inst, self.capacity)
+        if 2 * n_inst > self.capacity:
+            self.ensure_capacity(2 * n_inst)
 
     def last_status(self):
         """(num_rendered, overflowed) of the last frame -- synchronises."""
@@ -90,6 +143,8 @@ class FrameWorkspace:
             keep.append(t)
             return t.data_ptr()
 
+        self.resize(params["means3D"].shape[0])
+        self.generation += 1
         a.P, a.width, a.height = self.P, self.W, self.H
         a.isotropic = 1 if params["log_scales"].shape[1] == 1 else 0
         a.means3D = ptr(params["means3D"].detach())
@@ -123,30 +178,36 @@ class FrameWorkspace:
         a.max_2D_radius = max_2D_radius.data_ptr() if max_2D_radius is not None else None
         a.seen = seen.data_ptr() if seen is not None else None
         capturing = torch.cuda.is_current_stream_capturing()
-        if self._binning_auto and self.binning_mode == 1 and self._status_event is not None and not capturing:
-            # the status words of an EARLIER frame, copied back asynchronously: if a tile's bucket outgrew what a CTA
-            # sorts in shared memory, later frames use the global sort (no synchronisation, one or two frames late;
-            # the oversized frames themselves were still sorted correctly, only slowly)
-            if self._status_event.query():
-                if int(self._status_host[3]) > L.as_tile_sort_capacity():
-                    self.binning_mode = 0
-                self._status_event = None
+        if not capturing:
+            # the status words of an EARLIER frame, copied back asynchronously (no synchronisation, one or two frames
+            # late): a tile bucket that outgrew what a CTA sorts in shared memory sends later frames to the global sort
+            # (the oversized frames themselves were still sorted correctly, only slowly); an instance count beyond half
+            # of the binning buffer grows it before it can overflow
+            self._poll_status()
+            a.binning_buffer, a.binning_capacity = self.binning.data_ptr(), self.capacity
+            if self.overflow_seen is not None:
+                n_inst, cap = self.overflow_seen
+                self.overflow_seen = None
+                warnings.warn(f"activesplat_b200: an earlier frame needed {n_inst} Gaussian-tile instances but the binning "
+                              f"buffer held {cap}; that frame rendered as background (NaN loss, zero gradients).  The "
+                              "buffer has been grown.", RuntimeWarning, stacklevel=3)
+        else:
+            self._graph_pinned = True
         a.binning_mode = self.binning_mode
         with torch.cuda.device(self.device):
             stream = torch.cuda.current_stream(self.device).cuda_stream
             capi.check(L.as_frame_forward(ctypes.byref(a), stream))
-            if self._binning_auto and self.binning_mode == 1 and self.calibrated and self._status_event is None \
-                    and not capturing:
+            if self.calibrated and self._status_event is None and not capturing:
                 if self._status_host is None:
                     self._status_host = torch.zeros(4, dtype=torch.int32).pin_memory()
                 self._status_host.copy_(self.status, non_blocking=True)
                 self._status_event = torch.cuda.Event()
                 self._status_event.record(torch.cuda.current_stream(self.device))
-            if not self.calibrated and not torch.cuda.is_current_stream_capturing():
+            if not self.calibrated and not capturing:
                 # first frame of this workspace: ONE synchronising look at the instance count sizes the binning
                 # buffer with head-room (2x); after that the path never synchronises and an overflow shows up as
                 # a NaN loss / last_status()
-                self.calibrated = True
+                self.calibrated, self._calib_P = True, self.P
                 s = self.status.tolist()
                 rerun = self.ensure_capacity(2 * int(s[0]))
                 if self._binning_auto and self.binning_mode == 1 and (s[1] or int(s[3]) > L.as_tile_sort_capacity()):
@@ -225,15 +286,32 @@ class FrameWorkspace:
 _WORKSPACES = {}
 
 
-def workspace_for(params, cam):
-    """One cached workspace per (P, W, H, device)."""
-    key = (int(params["means3D"].shape[0]), int(cam.image_width), int(cam.image_height),
-           params["means3D"].device.index)
+def workspace_for(params, cam, role="train"):
+    """The cached workspace of (image size, device, role).  The number of Gaussians is not part of the key: a
+    workspace follows a growing map (FrameWorkspace.resize), so densification neither leaks the previous size's
+    buffers nor re-calibrates.  role "train" serves the differentiable paths (get_loss); no-grad renders
+    (render_view, add_new_gaussians) use role "render" so that they cannot overwrite a frame whose backward is
+    still to come."""
+    dev = params["means3D"].device
+    key = (int(cam.image_width), int(cam.image_height), dev.index, role)
     ws = _WORKSPACES.get(key)
     if ws is None:
-        ws = FrameWorkspace(key[0], key[1], key[2], params["means3D"].device)
+        ws = FrameWorkspace(int(params["means3D"].shape[0]), key[0], key[1], dev)
         _WORKSPACES[key] = ws
     return ws
+
+
+def _claim_backward(ctx):
+    """A workspace holds ONE frame: the backward of a node must find the buffers of its own forward."""
+    if getattr(ctx, "spent", False):
+        raise RuntimeError("activesplat_b200: backward through a fused frame node a second time; its workspace "
+                           "buffers were consumed by the first (run the forward again)")
+    if ctx.ws.generation != ctx.generation:
+        raise RuntimeError("activesplat_b200: another frame was rendered through the same workspace between this "
+                           "node's forward and its backward, so its buffers are gone.  Call backward() before the "
+                           "next get_loss / render on this image size, or give each frame in flight its own "
+                           "FrameWorkspace (the `ws=` argument of frame.fused_render / fused_tracking_loss).")
+    ctx.spent = True
 
 
 class _FusedTrackingLoss(torch.autograd.Function):
@@ -253,7 +331,7 @@ class _FusedTrackingLoss(torch.autograd.Function):
             ws.mapping_loss(gt_rgb, gt_depth, w_im, w_depth)
         else:
             ws.tracking_loss(gt_rgb, gt_depth, w_im, w_depth, sil_thres, use_sil, mask_color)
-        ctx.ws, ctx.time_idx = ws, int(time_idx)
+        ctx.ws, ctx.time_idx, ctx.generation = ws, int(time_idx), ws.generation
         ctx.shapes = (cam_rots.shape, cam_trans.shape, log_scales.shape[1])
         ctx.gaussians_grad = any(ctx.needs_input_grad[:5])
         ctx.camera_grad = any(ctx.needs_input_grad[5:7])
@@ -263,6 +341,7 @@ class _FusedTrackingLoss(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g):
         ws = ctx.ws
+        _claim_backward(ctx)
         # d(total)/d... ; the im/depth components are returned for logging only
         scale = g[0:1].contiguous()
         T = ctx.shapes[0][-1]
@@ -291,16 +370,18 @@ class _FusedFrameRender(torch.autograd.Function):
         params = {"means3D": means3D, "rgb_colors": rgb, "unnorm_rotations": rots, "logit_opacities": logit_op,
                   "log_scales": log_scales, "cam_unnorm_rots": cam_rots, "cam_trans": cam_trans}
         ws.forward(params, cam, time_idx, sil_w2c=sil_w2c, bg_rgb=bg_rgb)
-        ctx.ws, ctx.time_idx = ws, int(time_idx)
+        ctx.ws, ctx.time_idx, ctx.generation = ws, int(time_idx), ws.generation
         ctx.shapes = (cam_rots.shape, cam_trans.shape, log_scales.shape[1])
         ctx.need = tuple(ctx.needs_input_grad[:7])
-        out = (ws.color6.clone(), ws.radii, ws.depth, ws.opacity)
+        # fresh tensors, like the reference's rasterizer returns: the workspace is overwritten by its next frame
+        out = (ws.color6.clone(), ws.radii.clone(), ws.depth.clone(), ws.opacity.clone())
         ctx.mark_non_differentiable(*out[1:])
         return out
 
     @staticmethod
     def backward(ctx, g_color6, _r, _d, _o):
         ws = ctx.ws
+        _claim_backward(ctx)
         gaussians_grad, camera_grad = any(ctx.need[:5]), any(ctx.need[5:7])
         T = ctx.shapes[0][-1]
         gcam = torch.zeros((7, T), dtype=torch.float32, device=g_color6.device) if camera_grad else None
@@ -318,8 +399,25 @@ class _FusedFrameRender(torch.autograd.Function):
 
 
 def fused_render(params, cam, time_idx, sil_w2c=None, bg_rgb=None, ws=None):
-    """(colour6 [6,H,W], radii, median depth, opacity, workspace); colour6 is differentiable w.r.t. `params`."""
-    ws = ws or workspace_for(params, cam)
+    """(colour6 [6,H,W], radii, median depth, opacity, workspace); colour6 is differentiable w.r.t. `params`.
+    Without a workspace argument, a call that needs no gradient uses the "render" workspace."""
+    if ws is None:
+        needs_grad = torch.is_grad_enabled() and any(
+            params[k].requires_grad for k in PARAM_ORDER + ("cam_unnorm_rots", "cam_trans"))
+        ws = workspace_for(params, cam, "train" if needs_grad else "render")
+        if not needs_grad:
+            # a render nobody differentiates: worth one look at the status words (synchronises, as the callers of
+            # these paths do anyway) so that a binning overflow is repaired instead of returned as a background image
+            for _ in range(3):
+                out = _FusedFrameRender.apply(
+                    params["means3D"], params["rgb_colors"], params["unnorm_rotations"], params["logit_opacities"],
+                    params["log_scales"], params["cam_unnorm_rots"], params["cam_trans"], ws, cam, time_idx, sil_w2c,
+                    bg_rgb)
+                n_inst, overflowed = ws.last_status()
+                if not overflowed:
+                    return (*out, ws)
+                ws.ensure_capacity(n_inst + n_inst // 4)
+            raise RuntimeError(f"activesplat_b200: binning buffer still too small after growing it to {ws.capacity}")
     c6, radii, depth, opacity = _FusedFrameRender.apply(
         params["means3D"], params["rgb_colors"], params["unnorm_rotations"], params["logit_opacities"],
         params["log_scales"], params["cam_unnorm_rots"], params["cam_trans"], ws, cam, time_idx, sil_w2c, bg_rgb)
@@ -366,13 +464,17 @@ class FusedAdam:
     """torch.optim.Adam(lr per tensor, betas (0.9, 0.999), eps) over the five Gaussian tensors in one kernel.
     State is flat [P,14]; `step(grad_flat)` consumes the flat gradient buffer of the frame backward."""
 
-    def __init__(self, params, lrs, betas=(0.9, 0.999), eps=1e-15):
+    def __init__(self, params, lrs, betas=(0.9, 0.999), eps=1e-15, device_step=True):
+        """device_step: keep the step count (and the bias corrections derived from it) in device memory
+        (as_adam_step_counted), which makes every step the same launch -- a mapping iteration can then be captured in
+        a CUDA graph.  False passes the host-side count to as_adam_step."""
         self.params = params
         self.lrs = (ctypes.c_float * 5)(*[float(lrs[k]) for k in PARAM_ORDER])
         self.betas, self.eps, self.t = betas, eps, 0
         P, dev = params["means3D"].shape[0], params["means3D"].device
         self.exp_avg = torch.zeros((P, 14), dtype=torch.float32, device=dev)
         self.exp_avg_sq = torch.zeros((P, 14), dtype=torch.float32, device=dev)
+        self.step_state = torch.zeros(8, dtype=torch.float32, device=dev) if device_step else None
 
     @torch.no_grad()
     def step(self, grad_flat):
@@ -382,13 +484,48 @@ class FusedAdam:
         dev = p["means3D"].device
         for k in PARAM_ORDER:
             assert p[k].is_contiguous() and p[k].dtype == torch.float32
+        args = (int(p["means3D"].shape[0]), 1 if p["log_scales"].shape[1] == 1 else 0, p["means3D"].data_ptr(),
+                p["rgb_colors"].data_ptr(), p["unnorm_rotations"].data_ptr(), p["logit_opacities"].data_ptr(),
+                p["log_scales"].data_ptr(), grad_flat.data_ptr(), self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(),
+                self.lrs, self.betas[0], self.betas[1], self.eps)
         with torch.cuda.device(dev):
-            capi.check(L.as_adam_step(int(p["means3D"].shape[0]), 1 if p["log_scales"].shape[1] == 1 else 0,
-                                      p["means3D"].data_ptr(), p["rgb_colors"].data_ptr(),
-                                      p["unnorm_rotations"].data_ptr(), p["logit_opacities"].data_ptr(),
-                                      p["log_scales"].data_ptr(), grad_flat.data_ptr(), self.exp_avg.data_ptr(),
-                                      self.exp_avg_sq.data_ptr(), self.lrs, self.betas[0], self.betas[1], self.eps,
-                                      self.t, torch.cuda.current_stream(dev).cuda_stream))
+            stream = torch.cuda.current_stream(dev).cuda_stream
+            if self.step_state is not None:
+                capi.check(L.as_adam_step_counted(*args, self.step_state.data_ptr(), stream))
+            else:
+                capi.check(L.as_adam_step(*args, self.t, stream))
+
+
+class FusedPoseAdam:
+    """torch.optim.Adam over cam_unnorm_rots / cam_trans as the tracking loop configures it
+    (initialize_optimizer(tracking=True): default betas and eps 1e-8; lrs 1e-3 / 4e-3,
+    config/splatam/online_habitat_sim.py:37-45), one small kernel with the step count on the device, so that a
+    pose-only iteration (get_loss(tracking=True) + backward + step) never touches the host and can be replayed as a
+    CUDA graph.  `step()` reads the `.grad` of the two tensors, as torch's optimizers do."""
+
+    def __init__(self, params, lrs, betas=(0.9, 0.999), eps=1e-8):
+        self.params = params
+        self.lr_rots, self.lr_trans = float(lrs["cam_unnorm_rots"]), float(lrs["cam_trans"])
+        self.betas, self.eps = betas, eps
+        r, t = params["cam_unnorm_rots"], params["cam_trans"]
+        assert r.is_contiguous() and t.is_contiguous() and r.dtype == t.dtype == torch.float32
+        n = r.numel() + t.numel()
+        self.exp_avg = torch.zeros(n, dtype=torch.float32, device=r.device)
+        self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=r.device)
+        self.step_state = torch.zeros(8, dtype=torch.float32, device=r.device)
+
+    @torch.no_grad()
+    def step(self):
+        r, t = self.params["cam_unnorm_rots"], self.params["cam_trans"]
+        gr, gt = r.grad, t.grad
+        if gr is None or gt is None:
+            raise RuntimeError("FusedPoseAdam.step(): the camera tensors have no gradient (run backward first)")
+        gr, gt = gr.contiguous(), gt.contiguous()
+        with torch.cuda.device(r.device):
+            capi.check(capi.lib().as_pose_adam_step(
+                r.data_ptr(), gr.data_ptr(), r.numel(), self.lr_rots, t.data_ptr(), gt.data_ptr(), t.numel(),
+                self.lr_trans, self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(), self.betas[0], self.betas[1],
+                self.eps, self.step_state.data_ptr(), torch.cuda.current_stream(r.device).cuda_stream))
 
 
 class GraphedStep:

@@ -256,6 +256,23 @@ def get_loss(params, curr_data, variables, iter_time_idx, loss_weights, use_sil_
     return loss, variables, weighted_losses
 
 
+class _ScreenSpaceGradientNotKept:
+    """What variables['means2D'] holds after a fused get_loss.  The reference keeps the dummy means2D tensor of the
+    COLOUR pass there so that its (disabled by default, online_habitat_sim.py:70) Gaussian-splatting densification can
+    read `.grad` (utils/slam_external.py:100-108).  The fused path renders colour and depth/silhouette in one pass and
+    does not keep a colour-only screen-space gradient, so asking for it is an error rather than a wrong number."""
+
+    @property
+    def grad(self):
+        raise NotImplementedError(
+            "activesplat_b200: the fused get_loss path does not keep the colour-pass means2D gradient "
+            "(use_gaussian_splatting_densification); render through diff_gaussian_rasterization.GaussianRasterizer "
+            "(activesplat_b200.rasterizer) if that gradient is needed")
+
+
+_NO_MEANS2D = _ScreenSpaceGradientNotKept()
+
+
 def _get_loss_tracking_fused(params, curr_data, variables, iter_time_idx, loss_weights, use_sil_for_loss, sil_thres):
     """get_loss(tracking=True) (splatam.py:178-182, 230-247) as one fused autograd node: frame transform,
     activations, the 6-channel bundle render, the masked L1 sums and the whole backward run as a dozen
@@ -273,7 +290,7 @@ def _get_loss_tracking_fused(params, curr_data, variables, iter_time_idx, loss_w
     weighted_losses = {'depth': out[2], 'im': out[1], 'loss': loss}
     # max_2D_radius / seen (splatam.py:296-298) were updated in place by the preprocess kernel
     variables['seen'] = seen
-    variables['means2D'] = None  # screen-space gradient: FrameWorkspace(want_means2D_grad=True).grad_means2D
+    variables['means2D'] = _NO_MEANS2D
     return loss, variables, weighted_losses
 
 
@@ -290,7 +307,7 @@ def _get_loss_mapping_fused(params, curr_data, variables, iter_time_idx, loss_we
     loss = out[0]
     weighted_losses = {'depth': out[2], 'im': out[1], 'loss': loss}
     variables['seen'] = seen
-    variables['means2D'] = None
+    variables['means2D'] = _NO_MEANS2D
     return loss, variables, weighted_losses
 
 

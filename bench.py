@@ -1,17 +1,26 @@
 #!/usr/bin/env python
 """bench.py -- RGB-D + silhouette render fwd+bwd throughput (Mpix/s) of the rasterizer hot path.
 
-Workload (BASELINE.json configs[1], "cfg2"): SplaTAM camera-tracking iteration on a 500k-Gaussian
-synthetic room map at 640x480.  One step = one get_loss(tracking=True) + backward
-(reference: src/mapper/splatam/splatam.py:172-301): transform to the frame, activations, ONE
-RGB-D+silhouette bundle render (colour[3] + [z,1,z^2][3] + median depth + opacity), masked L1 losses,
-and the full backward down to the camera pose.  Every step uses the next keyframe pose; N > 1 ranks
-render disjoint keyframes of the same (replicated) map -- weak scaling, no data-path collective.
+Headline workload = BASELINE.json configs[2] ("cfg3", the largest single-GPU configuration): the SplaTAM MAPPING
+iteration on a 1M-Gaussian synthetic room map at 640x480.  One step = what the reference's mapping loop does per
+iteration (src/mapper/splatam/__init__.py:447-490):
+
+    loss = get_loss(params, keyframe, ..., mapping=True)     transform to the frame, activations, ONE RGB-D+sil bundle
+                                                             (colour[3] + [z,1,z^2][3] + median depth + opacity),
+                                                             0.8 L1 + 0.2 (1 - SSIM) colour loss, masked depth L1
+    loss.backward()                                          gradients of ALL FIVE Gaussian parameter tensors
+    optimizer.step()                                         Adam over the [P,14] parameters
+
+N > 1 ranks: data-parallel mapping over a keyframe batch -- every rank renders ITS keyframe of the replicated map
+(weak scaling: one keyframe per GPU per step), the flat [P,14] gradient is summed with one NCCL all-reduce inside the
+timed region, every rank applies the same Adam step.
 
   python bench.py --gpus N --steps K --warmup W             our arm (sm_100a kernels through the C ABI)
-  python bench.py --impl reference ...                      reference arm: the CPU port of the reference
-                                                            algorithm (oracle/) on the host cores
-One JSON line on stdout (rank 0).
+  python bench.py --impl reference ...                      reference arm: the same step on the CPU port of the
+                                                            reference algorithm (oracle/) on the host cores
+`extra` holds the other BASELINE configs as named sub-results (cfg1 raw rasterizer API, cfg2 tracking with Adam on the
+pose, cfg4 candidate-view scoring sharded over the ranks, cfg5 64-keyframe batches of a 3M-Gaussian map with the
+gradient all-reduce); `--extras none` skips them.  One JSON line on stdout (rank 0).
 """
 import argparse
 import json
@@ -22,11 +31,15 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "benchmarks"))
 
 import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
-L2_BYTES = 126e6
+LOSS_WEIGHTS = dict(im=0.5, depth=1.0)  # config/splatam/online_habitat_sim.py:57-60
+MAPPING_LRS = dict(means3D=1e-4, rgb_colors=2.5e-3, unnorm_rotations=1e-3, logit_opacities=5e-2, log_scales=1e-3,
+                   cam_unnorm_rots=0.0, cam_trans=0.0)  # online_habitat_sim.py:61-69
+SIL_THRES_MAPPING = 0.98  # unused by the mapping loss; passed like the reference does
 
 
 def parse():
@@ -35,11 +48,11 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--gaussians", type=int, default=500_000)
+    ap.add_argument("--gaussians", type=int, default=1_000_000)
     ap.add_argument("--width", type=int, default=640)
     ap.add_argument("--height", type=int, default=480)
-    ap.add_argument("--keyframes", type=int, default=8, help="keyframe poses per rank")
-    ap.add_argument("--no-ref-cuda", action="store_true", help="skip the reference-CUDA comparison leg")
+    ap.add_argument("--extras", default="cfg1,cfg2,cfg4,cfg5", help="comma list of sub-results, or 'none'")
+    ap.add_argument("--no-ref-cuda", action="store_true", help="skip the reference-CUDA comparison legs")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graphs", action="store_true", help="time the eager launch path instead of CUDA-graph replays")
     return ap.parse_args()
@@ -48,18 +61,13 @@ def parse():
 # --------------------------------------------------------------------------------------------------
 # workload
 # --------------------------------------------------------------------------------------------------
-LOSS_WEIGHTS = dict(im=0.5, depth=1.0)  # config/splatam/online_habitat_sim.py:33-36
-SIL_THRES = 0.99                        # online_habitat_sim.py:25
-
-
-def make_scene(args, rank, world):
+def make_scene(args, world):
+    """The 1M-Gaussian room, `world` keyframe poses (rank r maps keyframe r), and the perturbed copy whose render is
+    the ground-truth frame."""
     from activesplat_b200 import scenes
-    K = args.keyframes
-    params, cams = scenes.s_room(args.gaussians, K * world, seed=1, W=args.width, H=args.height)
-    cams = cams[rank::world]
+    params, cams = scenes.s_room(args.gaussians, max(world, 2), seed=3, W=args.width, H=args.height)
     rots, trans = scenes.camera_track(cams)
-    gt_params = scenes.perturbed(params, seed=11)
-    return params, gt_params, cams, rots, trans
+    return params, scenes.perturbed(params, seed=13), cams, rots, trans
 
 
 class ClockSampler(threading.Thread):
@@ -106,8 +114,8 @@ class ClockSampler(threading.Thread):
 
 
 def algorithmic_bytes(P, V, R, N, tiles, sort_passes):
-    """algorithmic bytes of one RGB-D+sil bundle fwd+bwd, per stage (the reference's
-    two-pass accounting; a fused implementation moves fewer, the figure is kept for comparability)."""
+    """algorithmic bytes of one RGB-D+sil bundle fwd+bwd + loss + Adam, per stage (the reference's
+    two-pass accounting; a fused implementation moves fewer, the figure is kept so that fractions are comparable)."""
     b = {}
     b["preprocess"] = P * 52 + V * 52
     b["scan"] = P * 8
@@ -118,7 +126,27 @@ def algorithmic_bytes(P, V, R, N, tiles, sort_passes):
     b["blend_bwd"] = 2 * (R * (28 + 12) + N * (12 + 8) + 2 * V * 44)
     b["preprocess_bwd"] = 2 * V * 224
     b["loss"] = N * 64
+    b["adam"] = P * 392
     return b
+
+
+NCU_KERNEL_OF_STAGE = {"blend_bwd": "blend_backward_kernel<6", "blend_fwd": "blend_forward_kernel<6",
+                       "preprocess": "frame_preprocess_kernel", "preprocess_bwd": "frame_preprocess_backward_kernel",
+                       "sort": "frame_tile_sort_gather_kernel", "adam": "adam_kernel", "loss": "ssim_"}
+
+
+def committed_traffic(stage):
+    """DRAM bytes per launch of the stage's kernel from the committed `ncu --set full` capture of this workload
+    (profiles/r2_ncu_kernels_cfg3.json, made by benchmarks/summarize_ncu.py); None when there is no capture."""
+    try:
+        ncu = json.load(open(os.path.join(ROOT, "profiles", "r2_ncu_kernels_cfg3.json")))["kernels"]
+        prefix = NCU_KERNEL_OF_STAGE.get(stage)
+        for name, k in ncu.items():
+            if prefix and name.startswith(prefix):
+                return k["dram_bytes"]
+    except Exception:
+        pass
+    return None
 
 
 # --------------------------------------------------------------------------------------------------
@@ -127,65 +155,63 @@ def algorithmic_bytes(P, V, R, N, tiles, sort_passes):
 def run_ours(args, rank, world, local_rank):
     import torch.distributed as dist
     from activesplat_b200 import capi, splatam
+    from activesplat_b200.frame import FusedAdam, GraphedStep, PARAM_ORDER, workspace_for
+    import configs as cfgs
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(dev)
     L = capi.lib()
-    params_cpu, gt_cpu, cams, rots, trans = make_scene(args, rank, world)
-    W, H, K = args.width, args.height, len(cams)
+    params_cpu, gt_cpu, cams, rots, trans = make_scene(args, world)
+    W, H, P = args.width, args.height, args.gaussians
     N = W * H
-    params = {k: v.to(dev).requires_grad_(False) for k, v in params_cpu.items()}
+    t_idx = rank  # this rank's keyframe
+    params = {k: v.to(dev).requires_grad_(True) for k, v in params_cpu.items()}
     params["cam_unnorm_rots"] = rots.to(dev).requires_grad_(True)
     params["cam_trans"] = trans.to(dev).requires_grad_(True)
     k_mat = cams[0].k()
     cam = splatam.setup_camera(W, H, k_mat, np.eye(4), device=dev)  # identity camera
     first_w2c = torch.eye(4, device=dev)
-    variables = {"max_2D_radius": torch.zeros(args.gaussians, device=dev)}
+    variables = {"max_2D_radius": torch.zeros(P, device=dev)}
+    opt = FusedAdam(params, MAPPING_LRS)
+    ws = workspace_for(params, cam)
 
-    # ground truth: the perturbed map rendered at every keyframe pose (set-up, not timed)
-    gt_host = []
-    with torch.no_grad():
-        gtp = {k: v.to(dev) for k, v in gt_cpu.items()}
-        for t in range(K):
-            rv, drv = splatam.get_rendervars(gtp, cams[t].w2c)
-            c = splatam.setup_camera(W, H, k_mat, cams[t].w2c, device=dev)
-            im, _, depth, opacity, _ = splatam.render_bundle(c, rv, drv["colors_precomp"])
-            depth = torch.where(opacity > 0.5, depth, torch.zeros_like(depth))
-            gt_host.append(torch.cat([im, depth], 0).cpu().pin_memory())
-        del gtp
-    gt_dev = [g.to(dev) for g in gt_host]
-    # end-to-end leg: every step uploads ITS ground-truth frame from pinned host memory.  Two staging buffers and a
-    # copy stream: the upload of step i+1 runs while step i computes (what a SLAM front end does with its camera
-    # queue); step i waits for its own upload before it reads the buffer.  K is even, so keyframe t always lands in
-    # buffer t % 2 and the captured graphs can name their buffer.
-    assert K % 2 == 0
-    gt_stage = [torch.empty_like(gt_dev[0]) for _ in range(2)]
+    # ground truth: the perturbed map rendered at this rank's keyframe (set-up, not timed)
+    gt = cfgs.gt_frames(gt_cpu, [cams[t_idx]], dev, seed=None)[0]
+    gt_host = gt.cpu().pin_memory()
+    gt_dev = gt.clone()
+    # end-to-end leg: every step uploads the keyframe's RGB-D frame from pinned host memory.  Two staging buffers and
+    # a copy stream: the upload for step i+1 runs while step i computes; step i waits for its own upload.
+    gt_stage = [torch.empty_like(gt_dev) for _ in range(2)]
     copy_stream = torch.cuda.Stream(device=dev)
     copy_done = [torch.cuda.Event() for _ in range(2)]
 
     def upload(i):
-        """Start the host->device copy of step i's frame (the previous user of that buffer, step i-2, has been
-        read back by the host already)."""
-        t = i % K
         with torch.cuda.stream(copy_stream):
-            gt_stage[t % 2].copy_(gt_host[t], non_blocking=True)
-            copy_done[t % 2].record(copy_stream)
+            gt_stage[i % 2].copy_(gt_host, non_blocking=True)
+            copy_done[i % 2].record(copy_stream)
 
-    def one_step(i, e2e):
-        t = i % K
+    def fwd_bwd(src):
+        curr = {"cam": cam, "im": src[:3], "depth": src[3:4], "w2c": first_w2c}
+        for k in PARAM_ORDER:
+            params[k].grad = None
+        loss, _, _ = splatam.get_loss(params, curr, variables, t_idx, LOSS_WEIGHTS, False, SIL_THRES_MAPPING, True,
+                                      False, mapping=True)
+        loss.backward()
+        return loss
+
+    def exchange_and_update():
+        if world > 1:
+            dist.all_reduce(ws.grad_params)       # the keyframe batch's gradient: sum over ranks (NCCL, NVLink)
+        opt.step(ws.grad_params)
+
+    def eager_step(i, e2e):
         if e2e:
             upload(i + 1)
-            torch.cuda.current_stream(dev).wait_event(copy_done[t % 2])
-            g = gt_stage[t % 2]
-        else:
-            g = gt_dev[t]
-        curr = {"cam": cam, "im": g[:3], "depth": g[3:4], "w2c": first_w2c}
-        loss, _, _ = splatam.get_loss(params, curr, variables, t, LOSS_WEIGHTS, True, SIL_THRES, True, False,
-                                      tracking=True)
-        loss.backward()
-        out = float(loss.item()) if e2e else None
-        params["cam_unnorm_rots"].grad = None
-        params["cam_trans"].grad = None
-        return out
+            torch.cuda.current_stream(dev).wait_event(copy_done[i % 2])
+        loss = fwd_bwd(gt_stage[i % 2] if e2e else gt_dev)
+        exchange_and_update()
+        return float(loss.item()) if e2e else None
+
+    one_step = eager_step
 
     def barrier():
         if world > 1:
@@ -216,56 +242,45 @@ def run_ours(args, rank, world, local_rank):
         one_step(i, False)
     # eager pass with per-stage events: launch count and the roofline attribution of the dominant kernel
     ms_eager, stages, launches = timed(args.steps, False, True)
+    n_inst, overflowed = ws.last_status()
+    if overflowed:
+        raise RuntimeError(f"binning buffer overflow ({n_inst} instances): the timed frames are invalid")
+    V = int((ws.radii > 0).sum())
 
-    eager_losses = []
-    upload(0)
-    for t in range(K):
-        eager_losses.append(one_step(t, True))
-
-    # The step has no host synchronisation, so each keyframe's step is also captured as one CUDA graph
-    # (activesplat_b200.frame.GraphedStep) and replayed: same kernels, same order, no launch gaps.
+    # The step has no host synchronisation and its Adam keeps the step count on the device, so the whole iteration
+    # (forward, loss, backward, update) is also captured as ONE CUDA graph and replayed: same kernels, same order, no
+    # launch gaps.  With N > 1 the NCCL all-reduce stays an eager call between two graphs (fwd+bwd | update).
     graphed = None
     if not args.no_graphs:
         try:
-            from activesplat_b200.frame import GraphedStep
-
-            def make(t, src):
-                def fn():
-                    curr = {"cam": cam, "im": src[:3], "depth": src[3:4], "w2c": first_w2c}
-                    params["cam_unnorm_rots"].grad = None
-                    params["cam_trans"].grad = None
-                    loss, _, _ = splatam.get_loss(params, curr, variables, t, LOSS_WEIGHTS, True, SIL_THRES, True,
-                                                  False, tracking=True)
-                    loss.backward()
-                    return loss
-                return GraphedStep(fn)
-
-            g_res = [make(t, gt_dev[t]) for t in range(K)]        # GT resident on the device
-            g_e2e = [make(t, gt_stage[t % 2]) for t in range(K)]  # GT arrives through the staging buffers
-            graphed = (g_res, g_e2e)
+            if world == 1:
+                g_res = GraphedStep(lambda: (fwd_bwd(gt_dev), exchange_and_update())[0])
+                g_e2e = [GraphedStep(lambda s=s: (fwd_bwd(gt_stage[s]), exchange_and_update())[0]) for s in range(2)]
+                g_upd = None
+            else:
+                g_res = GraphedStep(lambda: fwd_bwd(gt_dev))
+                g_e2e = [GraphedStep(lambda s=s: fwd_bwd(gt_stage[s])) for s in range(2)]
+                g_upd = GraphedStep(lambda: opt.step(ws.grad_params))
+            graphed = (g_res, g_e2e, g_upd)
         except Exception as ex:  # graphs are an optimisation of the launch path, not a different code path
             sys.stderr.write(f"[bench] CUDA graph capture unavailable, timing the eager path: {ex}\n")
             graphed = None
-        params["cam_unnorm_rots"].grad = None
-        params["cam_trans"].grad = None
 
     if graphed is not None:
         def one_step(i, e2e):  # noqa: F811  (same step, replayed)
-            t = i % K
+            g_res, g_e2e, g_upd = graphed
             if e2e:
                 upload(i + 1)
-                torch.cuda.current_stream(dev).wait_event(copy_done[t % 2])
-                return float(graphed[1][t]().item())
-            graphed[0][t]()
-            return None
+                torch.cuda.current_stream(dev).wait_event(copy_done[i % 2])
+                loss = g_e2e[i % 2]()
+            else:
+                loss = g_res()
+            if g_upd is not None:
+                dist.all_reduce(ws.grad_params)
+                g_upd()
+            return float(loss.item()) if e2e else None
         for i in range(args.warmup):
             one_step(i, False)
-        # replays must reproduce the eager losses (same kernels; only atomics' summation order may differ)
-        upload(0)
-        for t in range(K):
-            lg = one_step(t, True)
-            if not abs(lg - eager_losses[t]) <= 1e-4 * abs(eager_losses[t]) + 1e-6:
-                raise RuntimeError(f"graph replay loss {lg} != eager loss {eager_losses[t]} (keyframe {t})")
     sampler = ClockSampler(local_rank)
     sampler.start()
     ms, _, _ = timed(args.steps, False, False)
@@ -274,33 +289,19 @@ def run_ours(args, rank, world, local_rank):
     upload(0)
     for i in range(min(args.warmup, 3)):
         one_step(i, True)
-    # the warm-up left step min(warmup,3)'s frame in flight; restart the sequence at step 0 for the timed region
     torch.cuda.synchronize(dev)
     upload(0)
     ms_e2e, _, _ = timed(args.steps, True, False)
-    from activesplat_b200.frame import workspace_for
-    n_inst, overflowed = workspace_for(params, cam).last_status()
+    n_inst2, overflowed = ws.last_status()
     if overflowed:
-        raise RuntimeError(f"binning buffer overflow ({n_inst} instances): the timed frames are invalid")
+        raise RuntimeError(f"binning buffer overflow ({n_inst2} instances): the timed frames are invalid")
+    final_loss = float(ws.losses[0])
+    if not np.isfinite(final_loss):
+        raise RuntimeError("non-finite loss after the timed steps")
 
-    # workload statistics for the algorithmic-byte figure (one extra forward per keyframe, untimed)
-    stats = []
-    with torch.no_grad():
-        from activesplat_b200 import _C
-        e = torch.Tensor([])
-        for t in range(K):
-            tg = splatam.transform_to_frame(params, t, False, False)
-            rv = splatam.transformed_params2rendervar(params, tg)
-            R, _, radii, *_ = _C.rasterize_gaussians(cam.bg, rv["means3D"], rv["colors_precomp"], rv["opacities"],
-                                                    rv["scales"], rv["rotations"], 1.0, e, cam.viewmatrix, cam.projmatrix,
-                                                    cam.tanfovx, cam.tanfovy, H, W, e, 0, cam.campos, False, False)
-            stats.append((R, int((radii > 0).sum())))
-    R_mean = float(np.mean([s[0] for s in stats]))
-    V_mean = float(np.mean([s[1] for s in stats]))
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
     sp = (32 + int(L.as_higher_msb(tiles)) + 7) // 8
-    ab = algorithmic_bytes(args.gaussians, V_mean, R_mean, N, tiles, sp)
-
+    ab = algorithmic_bytes(P, V, n_inst, N, tiles, sp)
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -308,155 +309,181 @@ def run_ours(args, rank, world, local_rank):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
-    dom = max((s for s in stages if stages[s][1] > 0), key=lambda s: stages[s][0])
-    dom_ms = stages[dom][0] / max(stages[dom][1], 1)
+    live = {s: v for s, v in stages.items() if v[1] > 0}
+    dom = max(live, key=lambda s: live[s][0])
+    per_stage = {}
+    for s, (tot, calls) in live.items():
+        ms_launch = tot / args.steps
+        per_stage[s] = {"ms": round(ms_launch, 4),
+                        "GB/s": round(ab[s] / (ms_launch * 1e-3) / 1e9, 1) if s in ab and ms_launch > 0 else None,
+                        "frac": round(ab[s] / (ms_launch * 1e-3) / 1e9 / peak, 4) if s in ab and ms_launch > 0 else None}
+    dom_ms = live[dom][0] / args.steps
     achieved = ab.get(dom, 0) / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
-    stage_ms = {s: round(v[0] / args.steps, 4) for s, v in stages.items() if v[1] > 0}
-    # DRAM traffic of the dominant kernel: from the committed ncu --set full capture of the same workload
-    # (profiles/r1_ncu_kernels_final.json, made by benchmarks/summarize_ncu.py), per launch; not measured live
-    # (ncu cannot run inside a timed region)
-    traffic = None
-    try:
-        ncu = json.load(open(os.path.join(ROOT, "profiles", "r1_ncu_kernels_final.json")))["kernels"]
-        prefix = {"blend_bwd": "blend_backward_kernel<6", "blend_fwd": "blend_forward_kernel<6",
-                  "preprocess": "frame_preprocess_kernel", "preprocess_bwd": "frame_preprocess_backward_kernel",
-                  "sort": "frame_tile_sort_gather_kernel"}.get(dom)
-        if prefix and args.gaussians == 500_000 and (W, H) == (640, 480):
-            for name, k in ncu.items():
-                if name.startswith(prefix):
-                    traffic = k["dram_bytes"]
-                    break
-    except Exception:
-        pass
-    total_bytes = sum(ab.values())
+    total_bytes = sum(ab[s] for s in ab if s in live or s in ("scan", "duplicate", "ranges_gather"))
+    step_ms = ms / args.steps
 
     result = {
         "metric": "RGB-D+sil render fwd+bwd Mpix/s",
         "value": N * args.steps * world / (ms * 1e-3) / 1e6,
         "unit": "Mpix/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms / args.steps,
+        "ms_per_step": step_ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "cfg2: SplaTAM tracking iteration (get_loss(tracking=True) fwd+bwd), "
-                               f"S-room {args.gaussians} Gaussians, {W}x{H}, {K} keyframe poses per rank, "
-                               "one RGB-D+sil bundle per step",
-                   "gaussians": args.gaussians, "width": W, "height": H, "instances_per_step": R_mean,
-                   "visible_per_step": V_mean,
-                   "l2": f"no flush: per-step working set (params+scratch+images) "
-                         f"{(args.gaussians * 150 + R_mean * 110 + N * 80) / 1e6:.0f} MB > L2 126 MB, pose changes every step",
-                   "parallelism": f"keyframes sharded over {world} rank(s), map replicated"},
+        "config": {"workload": "cfg3: SplaTAM mapping iteration = get_loss(mapping=True) + backward to all five Gaussian "
+                               f"parameter tensors + Adam, S-room {P} Gaussians, {W}x{H}, one keyframe per GPU per step, "
+                               "one RGB-D+sil bundle per keyframe",
+                   "gaussians": P, "width": W, "height": H, "instances_per_step": n_inst, "visible_per_step": V,
+                   "l2": f"no flush: per-step working set (parameters + Adam state + gradients {P * 14 * 4 * 4 / 1e6:.0f} MB, "
+                         f"scratch {(P * 100 + n_inst * 110 + N * 80) / 1e6:.0f} MB) exceeds the 126 MB L2, and Adam "
+                         "changes every parameter every step",
+                   "parallelism": ("single GPU" if world == 1 else
+                                   f"data-parallel mapping over a {world}-keyframe batch: map replicated, one keyframe "
+                                   f"per rank, NCCL all-reduce of the flat [P,14] fp32 gradient ({P * 56 / 1e6:.0f} MB) "
+                                   "inside the timed region, identical Adam step on every rank")},
         "e2e": {"value": N * args.steps * world / (ms_e2e * 1e-3) / 1e6, "unit": "Mpix/s",
-                "h2d_bytes_per_step": int(gt_host[0].numel() * 4), "d2h_bytes_per_step": 4,
-                "api": "activesplat_b200.splatam.get_loss + backward; every step's GT frame is copied from pinned host "
-                       "memory (double-buffered: the copy of step i+1 overlaps step i) and its loss is read back"},
+                "h2d_bytes_per_step": int(gt_host.numel() * 4), "d2h_bytes_per_step": 4,
+                "api": "activesplat_b200.splatam.get_loss(mapping=True) + loss.backward() + frame.FusedAdam.step; every "
+                       "step's RGB-D keyframe is copied from pinned host memory (double-buffered: the copy for step i+1 "
+                       "overlaps step i) and its loss is read back"},
         "gpu_launches": int(launches),
-        "launch_path": ("cuda_graph_replay (one graph per keyframe step; kernels identical to the eager path)"
+        "launch_path": ("cuda_graph_replay (one graph per step; kernels identical to the eager path)"
                         if graphed is not None else "eager"),
         "eager": {"value": N * args.steps * world / (ms_eager * 1e-3) / 1e6, "ms_per_step": ms_eager / args.steps,
-                  "note": "same steps launched eagerly with per-stage CUDA events on; stage_ms_per_step and roofline come from this pass"},
+                  "note": "same steps launched eagerly with per-stage CUDA events on; `stages` and `roofline` come from this pass"},
         "clocks": sampler.summary(),
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak if peak else None, "traffic": traffic, "peak_source": peak_src,
-                     "note": "blend kernels are instruction-issue bound (ncu: ~70 % issue-active, DRAM throughput 3 %), not HBM bound; "
-                             "the HBM fraction is reported because the contract asks for it (SURVEY 7, DESIGN 4)",
+                     "frac": achieved / peak if peak else None, "traffic": committed_traffic(dom),
+                     "peak_source": peak_src,
+                     "note": "the blend kernels are instruction-issue bound, not HBM bound (ncu, profiles/); the HBM "
+                             "fraction is reported because the contract asks for it (SURVEY 7, DESIGN 4)",
                      "algorithmic_bytes_per_launch": ab.get(dom, 0),
                      "whole_step": {"algorithmic_bytes": total_bytes,
-                                    "achieved": total_bytes / (ms / args.steps * 1e-3) / 1e9,
-                                    "frac": total_bytes / (ms / args.steps * 1e-3) / 1e9 / peak}},
-        "stage_ms_per_step": stage_ms,
+                                    "achieved": total_bytes / (step_ms * 1e-3) / 1e9,
+                                    "frac": total_bytes / (step_ms * 1e-3) / 1e9 / peak}},
+        "stages": per_stage,
+        "final_loss": final_loss,
     }
 
     if rank == 0 and not args.no_ref_cuda:
         try:
-            result["ref_cuda"] = run_ref_cuda(args, dev, params, cams, cam, first_w2c, gt_dev, K)
+            result["ref_cuda"] = run_ref_cuda(args, dev, params_cpu, rots, trans, cams, gt_dev, t_idx)
         except Exception as ex:  # the reference build may be absent on a box
-            result["ref_cuda"] = {"unavailable": f"{type(ex).__name__}: {ex}"[:200]}
+            result["ref_cuda"] = {"unavailable": f"{type(ex).__name__}: {ex}"[:300]}
     if rank == 0 and not args.no_cpu_baseline:
         result["cpu_baseline"] = cpu_baseline(args, budget_s=25.0)
+
+    # ---- the other BASELINE configs as sub-results ------------------------------------------------
+    wanted = [] if args.extras == "none" else [x.strip() for x in args.extras.split(",") if x.strip()]
+    extra = {}
+    del opt
+    for k in PARAM_ORDER:
+        params[k].grad = None
+    ref_ok = not args.no_ref_cuda
+    for name in wanted:
+        try:
+            if name == "cfg1" and world == 1:
+                extra["cfg1"] = cfgs.cfg1(dev, cfgs.load_ref_renderer() if ref_ok else None, args)
+            elif name == "cfg2" and world == 1:
+                extra["cfg2"] = cfgs.cfg2(dev, ref_ok, args)
+            elif name == "cfg4":
+                p4 = {k: params[k].detach() for k in PARAM_ORDER}
+                extra["cfg4"] = cfgs.cfg4(dev, cfgs.load_ref_renderer() if (ref_ok and world == 1) else None, args, rank,
+                                          world, params=p4)
+            elif name == "cfg5":
+                params = None
+                from activesplat_b200 import frame as _fr
+                _fr._WORKSPACES.clear()
+                torch.cuda.empty_cache()
+                extra["cfg5"] = cfgs.cfg5(dev, args, rank, world)
+        except Exception as ex:
+            extra[name] = {"failed": f"{type(ex).__name__}: {ex}"[:300]}
+    if extra:
+        result["extra"] = extra
     return result
 
 
 # --------------------------------------------------------------------------------------------------
-# comparison leg: the UNMODIFIED reference CUDA rasterizer (oracle/_ref), same step, two passes
+# comparison leg: the UNMODIFIED reference on the same GPU -- its own Python (get_loss, initialize_optimizer,
+# byte-compiled by oracle/build_ref_py.py) on its own CUDA rasterizer (oracle/_ref/ref_dgr_C.so), same step
 # --------------------------------------------------------------------------------------------------
-def run_ref_cuda(args, dev, params, cams, cam, first_w2c, gt_dev, K):
-    import importlib.util
-    from activesplat_b200 import splatam
-    from activesplat_b200.rasterizer import make_rasterize_function
-    path = os.path.join(ROOT, "oracle", "_ref", "ref_dgr_C.so")
-    spec = importlib.util.spec_from_file_location("ref_dgr_C", path)
-    ref = importlib.util.module_from_spec(spec)
-    spec.loader.exec_module(ref)
-    fn = make_rasterize_function(ref)
-    e = torch.Tensor([])
+def run_ref_cuda(args, dev, params_cpu, rots, trans, cams, gt_dev, t_idx):
+    from oracle import build_ref_py
+    ns = build_ref_py.load(build_ref_py.load_ref_extension())
     W, H = args.width, args.height
+    p = {k: torch.nn.Parameter(v.clone().to(dev)) for k, v in params_cpu.items()}
+    p["cam_unnorm_rots"] = torch.nn.Parameter(rots.clone().to(dev))
+    p["cam_trans"] = torch.nn.Parameter(trans.clone().to(dev))
+    P = p["means3D"].shape[0]
+    cam = ns.recon_helpers.setup_camera(W, H, cams[0].k(), np.eye(4))
+    curr = {"cam": cam, "im": gt_dev[:3], "depth": gt_dev[3:4], "id": t_idx, "w2c": torch.eye(4, device=dev),
+            "intrinsics": torch.tensor(cams[0].k()).float().to(dev)}
+    variables = {"max_2D_radius": torch.zeros(P, device=dev), "means2D_gradient_accum": torch.zeros(P, device=dev),
+                 "denom": torch.zeros(P, device=dev), "timestep": torch.zeros(P, device=dev)}
+    opt = ns.splatam.initialize_optimizer(p, MAPPING_LRS, tracking=False)
 
-    def raster(rv):
-        return fn.apply(rv["means3D"], rv["means2D"], e, rv["colors_precomp"], rv["opacities"], rv["scales"],
-                        rv["rotations"], e, cam)
+    def one_step():
+        nonlocal variables
+        loss, variables, _ = ns.splatam.get_loss(p, curr, variables, t_idx, LOSS_WEIGHTS, False, SIL_THRES_MAPPING, True,
+                                                 False, mapping=True)
+        loss.backward()
+        with torch.no_grad():                      # src/mapper/splatam/__init__.py:477-480
+            opt.step()
+            opt.zero_grad(set_to_none=True)
+        return loss
 
-    def one_step(i):
-        t = i % K
-        g = gt_dev[t]
-        tg = splatam.transform_to_frame(params, t, gaussians_grad=False, camera_grad=True)
-        rv = splatam.transformed_params2rendervar(params, tg)
-        drv = splatam.transformed_params2depthplussilhouette(params, first_w2c, tg)
-        im, radius, _, _ = raster(rv)           # splatam.py:208
-        depth_sil, _, _, _ = raster(drv)        # splatam.py:212
-        depth = depth_sil[0:1]
-        mask = (g[3:4] > 0) & (~torch.isnan(depth)) & (depth_sil[1] > SIL_THRES)
-        mask = mask.detach()
-        l_depth = torch.abs(g[3:4] - depth)[mask].sum()
-        l_im = torch.abs(g[:3] - im)[torch.tile(mask, (3, 1, 1))].sum()
-        (LOSS_WEIGHTS["im"] * l_im + LOSS_WEIGHTS["depth"] * l_depth).backward()
-        params["cam_unnorm_rots"].grad = None
-        params["cam_trans"].grad = None
-
-    for i in range(args.warmup):
-        one_step(i)
+    for _ in range(args.warmup):
+        one_step()
     torch.cuda.synchronize(dev)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for i in range(args.steps):
-        one_step(i)
+    for _ in range(args.steps):
+        loss = one_step()
     e1.record()
     torch.cuda.synchronize(dev)
     ms = e0.elapsed_time(e1)
     return {"value": W * H * args.steps / (ms * 1e-3) / 1e6, "unit": "Mpix/s", "ms_per_step": ms / args.steps,
-            "what": "unmodified reference diff-gaussian-rasterization compiled for sm_100a (oracle/_ref), "
-                    "same step with its two 3-channel passes, 1 GPU"}
+            "final_loss": float(loss),
+            "what": "the unmodified reference on the same GPU, same step: its own get_loss(mapping=True) (two 3-channel "
+                    "raster passes, torch-eager glue, SSIM by conv2d) + backward + torch.optim.Adam "
+                    "(initialize_optimizer), rasterizer compiled for sm_100a (oracle/_ref)"}
 
 
 # --------------------------------------------------------------------------------------------------
-# CPU legs: the oracle port of the reference algorithm on the host cores
+# CPU legs: the same mapping step on the oracle port of the reference algorithm, on the host cores
 # --------------------------------------------------------------------------------------------------
 def cpu_step_factory(args, gaussians=None, width=None, height=None):
-    from activesplat_b200 import scenes
+    from activesplat_b200 import scenes, splatam
     from oracle import raster_oracle as ro
-    ro.set_num_threads(os.cpu_count() or 1)  # torchrun exports OMP_NUM_THREADS=1; use every host core
+    from oracle import splatam_oracle as so
+    threads = os.cpu_count() or 1
+    ro.set_num_threads(threads)       # torchrun exports OMP_NUM_THREADS=1; use every host core
+    torch.set_num_threads(threads)
     P = gaussians or args.gaussians
     W, H = width or args.width, height or args.height
-    params, cams = scenes.s_room(P, args.keyframes, seed=1, W=W, H=H)
-    a = {k: v.numpy() for k, v in scenes.activated(params).items()}
-    rng = np.random.default_rng(100)
-    dL = rng.uniform(-1, 1, (6, H, W)).astype(np.float32)
-    bg = np.zeros(3, np.float32)
-    mats = [c.matrices() for c in cams]
-    feats = []
-    for c in cams:
-        z = (params["means3D"].numpy() @ c.w2c[:3, :3].T.astype(np.float32) + c.w2c[:3, 3].astype(np.float32))[:, 2:3]
-        feats.append(np.concatenate([z, np.ones_like(z), z * z], 1).astype(np.float32))
+    params, cams = scenes.s_room(P, 2, seed=3, W=W, H=H)
+    rots, trans = scenes.camera_track(cams)
+    p = {k: v.clone().requires_grad_(True) for k, v in params.items()}
+    p["cam_unnorm_rots"], p["cam_trans"] = rots.clone().requires_grad_(True), trans.clone().requires_grad_(True)
+    opt = torch.optim.Adam([{"params": [v], "name": k, "lr": MAPPING_LRS[k]} for k, v in p.items()], lr=0.0, eps=1e-15)
+    cam = splatam.setup_camera(W, H, cams[0].k(), np.eye(4), device="cpu")
+    g = torch.Generator().manual_seed(13)
+    # ground truth: the map's own render under a colour/depth perturbation (what the content is does not change the work)
+    with torch.no_grad():
+        _, _, aux = so.get_loss(p, {"cam": cam, "im": torch.zeros(3, H, W), "depth": torch.ones(1, H, W),
+                                    "w2c": torch.eye(4)}, 0, LOSS_WEIGHTS, False, SIL_THRES_MAPPING, True, False,
+                                mapping=True)
+        gt_rgb = (aux["im"] + 0.05 * torch.randn(3, H, W, generator=g)).clamp(0, 1)
+        sil = aux["depth_sil"][1:2]
+        gt_depth = torch.where(sil > 0.5, aux["depth_sil"][0:1] / sil.clamp_min(1e-6), torch.zeros(1, H, W))
+    curr = {"cam": cam, "im": gt_rgb, "depth": gt_depth, "w2c": torch.eye(4)}
 
     def step(i):
-        t = i % len(cams)
-        view, proj, _ = mats[t]
-        c = cams[t]
-        for colors, d in ((a["colors_precomp"], dL[:3]), (feats[t], dL[3:])):  # the reference's two passes
-            st = ro.forward(a["means3D"], colors, a["opacities"], a["scales"], a["rotations"], 1.0, None, view, proj,
-                            c.tanfovx, c.tanfovy, H, W, bg)
-            ro.backward(st, d)
-    return step, ro.num_threads(), W, H, P
+        loss, _, _ = so.get_loss(p, curr, 0, LOSS_WEIGHTS, False, SIL_THRES_MAPPING, True, False, mapping=True)
+        opt.zero_grad(set_to_none=True)
+        loss.backward()
+        opt.step()
+    return step, threads, W, H, P
 
 
 def cpu_baseline(args, budget_s):
@@ -470,13 +497,13 @@ def cpu_baseline(args, budget_s):
         step(i + 1)
     dt = (time.time() - t0) / n
     return {"value": W * H / dt / 1e6, "unit": "Mpix/s", "cores": threads, "kind": "port",
-            "sample": f"{n} bundle(s) (two 3-channel passes fwd+bwd) of the full workload: {P} Gaussians, {W}x{H}; "
-                      f"{dt:.2f} s per bundle"}
+            "sample": f"{n} mapping step(s) of the full workload ({P} Gaussians, {W}x{H}: two 3-channel passes fwd + full "
+                      f"backward on the C port, loss/SSIM/Adam in torch on the CPU); {dt:.2f} s per step"}
 
 
 def run_reference_arm(args):
-    """--impl reference: the reference has no CPU implementation of this path and its CUDA build is a
-    GPU program, so the timed reference arm is the C port of its algorithm (oracle/) on the host cores."""
+    """--impl reference: the reference has no CPU implementation of this path and its CUDA build is a GPU program, so
+    the timed reference arm is the port of its algorithm (oracle/) on the host cores, running the SAME step as our arm."""
     step, threads, W, H, P = cpu_step_factory(args)
     t0 = time.time()
     step(0)
@@ -485,7 +512,7 @@ def run_reference_arm(args):
     if first * (args.steps + args.warmup) > 240:  # keep the whole run within a few minutes
         step, threads, W, H, P = cpu_step_factory(args, gaussians=args.gaussians // 4, width=args.width // 2,
                                                   height=args.height // 2)
-        sample = f"reduced sample per step: {P} Gaussians, {W}x{H} (full workload would exceed the time budget)"
+        sample = f"reduced sample per step: {P} Gaussians, {W}x{H} (the full workload would exceed the time budget)"
     for i in range(args.warmup):
         step(i)
     t0 = time.time()
@@ -497,7 +524,9 @@ def run_reference_arm(args):
         "impl": "reference", "metric": "RGB-D+sil render fwd+bwd Mpix/s", "value": v, "unit": "Mpix/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "cfg2 bundle (two 3-channel passes fwd+bwd) on the CPU port of the reference algorithm; " + sample,
+        "config": {"workload": "cfg3: SplaTAM mapping iteration = get_loss(mapping=True) + backward to all five Gaussian "
+                               "parameter tensors + Adam, on the CPU port of the reference algorithm (two 3-channel "
+                               "passes); " + sample,
                    "gaussians": P, "width": W, "height": H},
         "cpu_baseline": {"value": v, "unit": "Mpix/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},

@@ -7,7 +7,8 @@
 "reference pipeline" = the reference's torch code restated (oracle/splatam_oracle.py) driving the
 UNMODIFIED reference CUDA rasterizer built for sm_100a (oracle/_ref): two raster passes per frame,
 torch-eager glue, torch.optim.Adam -- what ActiveSplat runs today.  It is a measured baseline, not a
-product path.  bench.py is the contract benchmark (cfg2); this script fills in the other rows.
+product path.  bench.py is the contract benchmark (cfg3 headline, the others as sub-results through the
+functions below); run directly, this script gives the long form of each config (cfg3 with the 60-step parameter drift).
 """
 import argparse
 import importlib.util
@@ -62,6 +63,37 @@ def load_ref_renderer(contiguous_inputs=False):
     return RefRenderer
 
 
+TRACK_LRS = dict(means3D=0.0, rgb_colors=0.0, unnorm_rotations=0.0, logit_opacities=0.0, log_scales=0.0,
+                 cam_unnorm_rots=0.001, cam_trans=0.004)  # config/splatam/online_habitat_sim.py:37-45
+
+
+def load_ref_python(contiguous_quat=False):
+    """The reference's own SplaTAM-layer Python (byte-compiled into oracle/_ref/refpy by oracle/build_ref_py.py) on
+    the reference's own CUDA rasterizer; None when either is absent.  contiguous_quat=True wraps (does not edit) its
+    quat_mult so that the rasterizer receives row-major rotations (see load_ref_renderer)."""
+    from oracle import build_ref_py
+    if not (build_ref_py.available() and os.path.exists(os.path.join(ROOT, "oracle", "_ref", "ref_dgr_C.so"))):
+        return None
+    ns = build_ref_py.load(build_ref_py.load_ref_extension())
+    if contiguous_quat:
+        orig = ns.slam_helpers.quat_mult
+        ns.slam_helpers.quat_mult = lambda a, b: orig(a, b).contiguous()
+    return ns
+
+
+def ref_frame(ns, W, H, k, gt, dev, t_idx=0):
+    """curr_data / variables as the reference's mapper builds them (src/mapper/splatam/__init__.py:354-397)."""
+    cam = ns.recon_helpers.setup_camera(W, H, k, np.eye(4))
+    curr = {"cam": cam, "im": gt[:3], "depth": gt[3:4], "id": t_idx, "w2c": torch.eye(4, device=dev),
+            "intrinsics": torch.tensor(k).float().to(dev)}
+    return curr
+
+
+def ref_variables(P, dev):
+    return {"max_2D_radius": torch.zeros(P, device=dev), "means2D_gradient_accum": torch.zeros(P, device=dev),
+            "denom": torch.zeros(P, device=dev), "timestep": torch.zeros(P, device=dev)}
+
+
 def timeit(fn, steps, warmup, dev):
     for i in range(warmup):
         fn(i)
@@ -76,7 +108,10 @@ def timeit(fn, steps, warmup, dev):
 
 
 def gt_frames(params_cpu, cams, dev, seed):
-    gtp = {k: v.to(dev) for k, v in scenes.perturbed(params_cpu, seed=seed).items()}
+    """RGB-D 'ground truth' frames: a perturbed copy of the map (seed None: `params_cpu` is already that copy)
+    rendered at the given poses."""
+    src = params_cpu if seed is None else scenes.perturbed(params_cpu, seed=seed)
+    gtp = {k: v.to(dev) for k, v in src.items()}
     out = []
     with torch.no_grad():
         for c in cams:
@@ -135,90 +170,236 @@ def cfg1(dev, RefRenderer, args):
     return res
 
 
-def cfg3(dev, RefRenderer, args):
-    """Mapping: 60 iterations fwd+bwd+Adam on 1M Gaussians over one keyframe."""
-    from oracle import splatam_oracle as so
-    W, H, P, iters = 640, 480, 1_000_000, 60
+def _pose_error(rots_a, trans_a, rots_b, trans_b, t):
+    """(rotation angle in degrees, translation distance in mm) between two poses stored SplaTAM-style."""
+    qa = torch.nn.functional.normalize(rots_a[0, :, t].detach().double(), dim=0)
+    qb = torch.nn.functional.normalize(rots_b[0, :, t].detach().double(), dim=0)
+    ang = 2 * torch.acos(torch.clamp(torch.abs((qa * qb).sum()), max=1.0))
+    return float(torch.rad2deg(ang)), float((trans_a[0, :, t].detach().double() - trans_b[0, :, t].detach().double()).norm() * 1e3)
+
+
+def cfg2(dev, with_ref, args):
+    """Camera tracking: 40 pose-only iterations (get_loss(tracking=True) + backward + Adam on cam_unnorm_rots / cam_trans,
+    lr 1e-3 / 4e-3) on a 500k-Gaussian map at 640x480, pose initialised 2 cm / 1 degree off; final pose vs the
+    reference's own loop (its get_loss + initialize_optimizer(tracking=True)) from the same start."""
+    from activesplat_b200.frame import FusedPoseAdam, GraphedStep
+    W, H, P, iters, t = 640, 480, 500_000, 40, 1
+    params_cpu, cams = scenes.s_room(P, 4, seed=1, W=W, H=H)
+    rots_gt, trans_gt = scenes.camera_track(cams)
+    gt = gt_frames(params_cpu, [cams[t]], dev, seed=11)[0]
+    # initial pose: ground truth perturbed by 2 cm and 1 degree
+    g = torch.Generator().manual_seed(2)
+    axis = torch.nn.functional.normalize(torch.randn(3, generator=g), dim=0)
+    half = math.radians(1.0) / 2
+    dq = torch.cat([torch.tensor([math.cos(half)]), math.sin(half) * axis])
+    q = rots_gt[0, :, t]
+    q0 = torch.stack([dq[0] * q[0] - dq[1] * q[1] - dq[2] * q[2] - dq[3] * q[3],
+                      dq[0] * q[1] + dq[1] * q[0] + dq[2] * q[3] - dq[3] * q[2],
+                      dq[0] * q[2] - dq[1] * q[3] + dq[2] * q[0] + dq[3] * q[1],
+                      dq[0] * q[3] + dq[1] * q[2] - dq[2] * q[1] + dq[3] * q[0]])
+    rots0, trans0 = rots_gt.clone(), trans_gt.clone()
+    rots0[0, :, t] = q0
+    trans0[0, :, t] += 0.02 * torch.nn.functional.normalize(torch.randn(3, generator=g), dim=0)
+    k = cams[0].k()
+
+    def fresh():
+        p = {k_: v.clone().to(dev).requires_grad_(True) for k_, v in params_cpu.items()}
+        p["cam_unnorm_rots"] = rots0.clone().to(dev).requires_grad_(True)
+        p["cam_trans"] = trans0.clone().to(dev).requires_grad_(True)
+        return p
+
+    res = {"config": f"cfg2: S-room {P} Gaussians, {W}x{H}, {iters} pose-only iterations (get_loss(tracking) + backward + "
+                     "Adam on the camera pose), start 2 cm / 1 deg off"}
+    start = _pose_error(rots0, trans0, rots_gt, trans_gt, t)
+    res["start_error_deg_mm"] = start
+    # ---- ours ----
+    cam = splatam.setup_camera(W, H, k, np.eye(4), device=dev)
+    cur = {"cam": cam, "im": gt[:3], "depth": gt[3:4], "w2c": torch.eye(4, device=dev)}
+
+    def run_ours(graph):
+        p = fresh()
+        opt = FusedPoseAdam(p, TRACK_LRS)
+        variables = {"max_2D_radius": torch.zeros(P, device=dev)}
+
+        def it():
+            for v in p.values():
+                v.grad = None
+            loss, _, _ = splatam.get_loss(p, cur, variables, t, LW, True, 0.99, True, False, tracking=True)
+            loss.backward()
+            opt.step()
+            return loss
+
+        it()  # sizes the workspace (one synchronising look at the instance count); then start over
+        p2 = fresh()
+        with torch.no_grad():
+            for k_ in p:
+                p[k_].copy_(p2[k_])
+        opt.exp_avg.zero_(), opt.exp_avg_sq.zero_(), opt.step_state.zero_()
+        step = it
+        if graph:
+            gs = GraphedStep(it, warmup=0)     # capture runs nothing; the first replay is iteration 1
+            step = gs
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            loss = step()
+        e1.record()
+        torch.cuda.synchronize(dev)
+        return p, e0.elapsed_time(e1) / iters, float(loss)
+
+    p_e, ms_e, loss_e = run_ours(False)
+    res["ours"] = {"ms_per_iter_eager": ms_e, "final_loss": loss_e,
+                   "final_error_vs_gt_deg_mm": _pose_error(p_e["cam_unnorm_rots"], p_e["cam_trans"], rots_gt, trans_gt, t)}
+    try:
+        p_g, ms_g, loss_g = run_ours(True)
+        res["ours"].update(ms_per_iter=ms_g, mpix_s=W * H / ms_g / 1e3, final_loss_graph=loss_g,
+                           graph_vs_eager_deg_mm=_pose_error(p_g["cam_unnorm_rots"], p_g["cam_trans"],
+                                                             p_e["cam_unnorm_rots"], p_e["cam_trans"], t))
+    except Exception as ex:
+        res["ours"]["graph_failed"] = f"{type(ex).__name__}: {ex}"[:200]
+        res["ours"].update(ms_per_iter=ms_e, mpix_s=W * H / ms_e / 1e3)
+    # ---- the reference's own loop ----
+    ns = load_ref_python() if with_ref else None
+    if ns is not None:
+        def run_ref():
+            p = fresh()
+            p = {k_: torch.nn.Parameter(v.detach()) for k_, v in p.items()}
+            opt = ns.splatam.initialize_optimizer(p, TRACK_LRS, tracking=True)
+            curr = ref_frame(ns, W, H, k, gt, dev, t)
+            variables = ref_variables(P, dev)
+            torch.cuda.synchronize(dev)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(iters):
+                loss, variables, _ = ns.splatam.get_loss(p, curr, variables, t, LW, True, 0.99, True, False, tracking=True)
+                loss.backward()
+                with torch.no_grad():
+                    opt.step()
+                    opt.zero_grad(set_to_none=True)
+            e1.record()
+            torch.cuda.synchronize(dev)
+            return p, e0.elapsed_time(e1) / iters, float(loss)
+
+        run_ref()  # warm-up (allocator, cuDNN-free but lazy module loads)
+        p_r, ms_r, loss_r = run_ref()
+        p_r2, _, _ = run_ref()
+        res["ref_cuda"] = {"ms_per_iter": ms_r, "mpix_s": W * H / ms_r / 1e3, "final_loss": loss_r,
+                           "final_error_vs_gt_deg_mm": _pose_error(p_r["cam_unnorm_rots"], p_r["cam_trans"], rots_gt, trans_gt, t)}
+        res["final_pose_ours_vs_reference_deg_mm"] = _pose_error(p_e["cam_unnorm_rots"], p_e["cam_trans"],
+                                                                 p_r["cam_unnorm_rots"], p_r["cam_trans"], t)
+        res["final_pose_reference_vs_its_second_run_deg_mm"] = _pose_error(p_r2["cam_unnorm_rots"], p_r2["cam_trans"],
+                                                                           p_r["cam_unnorm_rots"], p_r["cam_trans"], t)
+    return res
+
+
+def cfg3(dev, RefRenderer, args, iters=60):
+    """Mapping: 60 iterations fwd+bwd+Adam on 1M Gaussians over one keyframe; time per iteration and the parameter
+    drift after EXACTLY `iters` steps on both sides, against the reference's own loop (stock, and fed row-major
+    rotations) and against a second run of the reference itself."""
+    W, H, P = 640, 480, 1_000_000
     params_cpu, cams = scenes.s_room(P, 4, seed=3, W=W, H=H)
     rots, trans = scenes.camera_track(cams)
     gt = gt_frames(params_cpu, cams[:1], dev, seed=13)[0]
-    cam = splatam.setup_camera(W, H, cams[0].k(), np.eye(4), device=dev)
+    k = cams[0].k()
+    cam = splatam.setup_camera(W, H, k, np.eye(4), device=dev)
     cur = {"cam": cam, "im": gt[:3], "depth": gt[3:4], "w2c": torch.eye(4, device=dev)}
 
     def fresh():
-        p = {k: v.clone().to(dev).requires_grad_(True) for k, v in params_cpu.items()}
+        p = {k_: v.clone().to(dev).requires_grad_(True) for k_, v in params_cpu.items()}
         p["cam_unnorm_rots"] = rots.clone().to(dev).requires_grad_(True)
         p["cam_trans"] = trans.clone().to(dev).requires_grad_(True)
         return p
 
     res = {"config": f"cfg3: S-room {P} Gaussians, {W}x{H}, {iters} mapping iterations (get_loss(mapping) + backward + Adam)"}
-    # ours
-    p = fresh()
-    opt = FusedAdam(p, MAP_LRS)
-    variables = {"max_2D_radius": torch.zeros(P, device=dev)}
-    ws = workspace_for(p, cam)
 
-    def ours(i):
-        loss, _, _ = splatam.get_loss(p, cur, variables, 0, LW, False, 0.98, True, False, mapping=True)
-        loss.backward()
-        opt.step(ws.grad_params)
-        for k in PARAM_ORDER:
-            p[k].grad = None
+    def run_ours(n, profile=False):
+        p = fresh()
+        opt = FusedAdam(p, MAP_LRS)
+        variables = {"max_2D_radius": torch.zeros(P, device=dev)}
+        ws = workspace_for(p, cam)
 
-    ms = timeit(ours, iters, 5, dev)
-    n_inst, over = ws.last_status()
+        def it(i):
+            for k_ in PARAM_ORDER:
+                p[k_].grad = None
+            loss, _, _ = splatam.get_loss(p, cur, variables, 0, LW, False, 0.98, True, False, mapping=True)
+            loss.backward()
+            opt.step(ws.grad_params)
+
+        if profile:
+            capi.lib().as_profile_enable(1)
+            capi.profile_read()
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(n):
+            it(i)
+        e1.record()
+        torch.cuda.synchronize(dev)
+        st = None
+        if profile:
+            st = capi.profile_read()
+            capi.lib().as_profile_enable(0)
+        return p, e0.elapsed_time(e1) / n, st, ws.last_status()
+
+    run_ours(5)                                   # warm-up on a throw-away copy
+    p, ms, _, (n_inst, over) = run_ours(iters)    # exactly `iters` steps from the initial map
     assert not over
-    from activesplat_b200 import capi
-    capi.lib().as_profile_enable(1)
-    capi.profile_read()
-    for i in range(10):
-        ours(i)
-    st = capi.profile_read()
-    capi.lib().as_profile_enable(0)
+    _, _, st, _ = run_ours(10, profile=True)      # stage attribution, again on its own copy
     res["ours"] = {"ms_per_iter": ms, "mpix_s": W * H / ms / 1e3, "instances": n_inst,
-                   "stage_ms": {k: round(v[0] / 10, 4) for k, v in st.items() if v[1]}}
-    if RefRenderer:
-        p2 = fresh()
-        opt2 = torch.optim.Adam([{"params": [v], "name": k, "lr": MAP_LRS[k]} for k, v in p2.items()], lr=0.0, eps=1e-15)
+                   "stage_ms": {k_: round(v[0] / 10, 4) for k_, v in st.items() if v[1]}}
 
-        def ref(i):
-            loss, _, _ = so.get_loss(p2, cur, 0, LW, False, 0.98, True, False, mapping=True, Renderer=RefRenderer)
+    def run_ref(ns, n):
+        p2 = {k_: torch.nn.Parameter(v.detach()) for k_, v in fresh().items()}
+        opt2 = ns.splatam.initialize_optimizer(p2, MAP_LRS, tracking=False)
+        curr = ref_frame(ns, W, H, k, gt, dev, 0)
+        variables = ref_variables(P, dev)
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            loss, variables, _ = ns.splatam.get_loss(p2, curr, variables, 0, LW, False, 0.98, True, False, mapping=True)
             loss.backward()
-            opt2.step()
-            opt2.zero_grad(set_to_none=True)
+            with torch.no_grad():
+                opt2.step()
+                opt2.zero_grad(set_to_none=True)
+        e1.record()
+        torch.cuda.synchronize(dev)
+        return p2, e0.elapsed_time(e1) / n
 
-        ms = timeit(ref, iters, 5, dev)
-        res["ref_cuda"] = {"ms_per_iter": ms, "mpix_s": W * H / ms / 1e3}
-        # a second, identical run of the reference: its float atomics are unordered, and Adam with eps 1e-15
-        # turns every noise-level gradient into a full-size step, so the reference does not reproduce itself
-        p3 = fresh()
-        opt3 = torch.optim.Adam([{"params": [v], "name": k, "lr": MAP_LRS[k]} for k, v in p3.items()], lr=0.0, eps=1e-15)
+    def rel_l2(a, b):
+        """|a - b| / |b - initial| per tensor: the difference between two runs in units of the update itself."""
+        return {k_: float((a[k_].detach() - b[k_].detach()).norm() /
+                          ((b[k_].detach() - params_cpu[k_].to(dev)).norm() + 1e-12)) for k_ in PARAM_ORDER}
 
-        def ref_again(i):
-            loss, _, _ = so.get_loss(p3, cur, 0, LW, False, 0.98, True, False, mapping=True, Renderer=RefRenderer)
-            loss.backward()
-            opt3.step()
-            opt3.zero_grad(set_to_none=True)
-
-        timeit(ref_again, iters, 5, dev)
-        res["ref_vs_ref_rel_l2"] = {k: float((p3[k].detach() - p2[k].detach()).norm() /
-                                             ((p2[k].detach() - params_cpu[k].to(dev)).norm() + 1e-12)) for k in PARAM_ORDER}
-        # parameter drift between the two after the same number of steps (both started from the same map)
-        drift = {}
-        for k in PARAM_ORDER:
-            a_, b_ = p[k].detach(), p2[k].detach()
-            upd = b_ - params_cpu[k].to(dev)
-            drift[k] = float((a_ - b_).norm() / (upd.norm() + 1e-12))
-        res["rel_l2_param_diff_over_update"] = drift
+    ns_stock = load_ref_python() if RefRenderer is not None else None
+    if ns_stock is not None:
+        run_ref(ns_stock, 5)
+        p_stock, ms_ref = run_ref(ns_stock, iters)
+        p_stock2, _ = run_ref(ns_stock, iters)
+        ns_c = load_ref_python(contiguous_quat=True)
+        p_c, _ = run_ref(ns_c, iters)
+        p_c2, _ = run_ref(ns_c, iters)
+        res["ref_cuda"] = {"ms_per_iter": ms_ref, "mpix_s": W * H / ms_ref / 1e3}
+        res["drift_after_%d_steps" % iters] = {
+            "unit": "|a - b| / |b - initial map|, per tensor (L2)",
+            "ours_vs_reference_stock": rel_l2(p, p_stock),
+            "ours_vs_reference_fed_row_major_rotations": rel_l2(p, p_c),
+            "reference_vs_its_second_run_stock": rel_l2(p_stock2, p_stock),
+            "reference_vs_its_second_run_row_major": rel_l2(p_c2, p_c),
+            "note": "the stock reference backward misreads SplaTAM's column-major rotations (DESIGN.md 2.1), so scales and "
+                    "rotations drift from it by construction; the row-major variant is the like-for-like comparison"}
     return res
 
 
-def cfg4(dev, RefRenderer, args, rank, world):
+def cfg4(dev, RefRenderer, args, rank, world, params=None):
     """GetOpacity: 256 candidate views of a 1M-Gaussian map, forward only, views sharded over ranks."""
     from oracle import splatam_oracle as so
     P, n_views = 1_000_000, 256
-    params_cpu, _ = scenes.s_room(P, 1, seed=4)
-    params = {k: v.to(dev) for k, v in params_cpu.items()}
+    if params is None:
+        params_cpu, _ = scenes.s_room(P, 1, seed=4)
+        params = {k: v.to(dev) for k, v in params_cpu.items()}
+    P = int(params["means3D"].shape[0])
     res = {"config": f"cfg4: S-room {P} Gaussians, {n_views} candidate views, forward only, {world} GPU(s)"}
     for tag, (w, h, mk) in {"120x150": (120, 150, None), "640x480": (640, 480, "big")}.items():
         views = scenes.candidate_views(n_views, seed=4)
@@ -400,6 +581,8 @@ def main():
     for c in [int(x) for x in args.configs.split(",")]:
         if c == 1 and rank == 0 and world == 1:
             out["cfg1"] = cfg1(dev, RefRenderer, args)
+        elif c == 2 and rank == 0 and world == 1:
+            out["cfg2"] = cfg2(dev, RefRenderer is not None, args)
         elif c == 3 and rank == 0 and world == 1:
             out["cfg3"] = cfg3(dev, RefRenderer, args)
         elif c == 4:

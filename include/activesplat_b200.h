@@ -233,6 +233,24 @@ int as_adam_step(int P, int isotropic, float* means3D, float* rgb_colors, float*
                  float* exp_avg_sq, const float* lrs, float beta1, float beta2, float eps, int step,
                  void* cuda_stream);
 
+/* The same update with the step count kept on the device: step_state is 8 floats of device memory, zeroed by the
+ * caller when the optimizer is created (the reference re-creates its optimizer every mapping round,
+ * src/mapper/splatam/__init__.py:440).  Each call first advances step_state[0] by one and derives that step's
+ * bias corrections from it (in double, as torch does on the host), then updates.  The launch is identical every step,
+ * so a mapping iteration that ends in it can be captured once in a CUDA graph and replayed. */
+int as_adam_step_counted(int P, int isotropic, float* means3D, float* rgb_colors, float* unnorm_rotations,
+                         float* logit_opacities, float* log_scales, const float* grad_params, float* exp_avg,
+                         float* exp_avg_sq, const float* lrs, float beta1, float beta2, float eps, float* step_state,
+                         void* cuda_stream);
+
+/* Adam over the camera-pose tensors of a tracking loop (pose-only iterations: learning rates 1e-3 on cam_unnorm_rots
+ * [1,4,T] and 4e-3 on cam_trans [1,3,T], torch's default eps 1e-8: initialize_optimizer(tracking=True),
+ * splatam.py:118-122, config/splatam/online_habitat_sim.py:37-45).  n_rots / n_trans floats, dense; exp_avg / exp_avg_sq
+ * hold n_rots + n_trans floats; step_state as in as_adam_step_counted (zeroed when the optimizer is created). */
+int as_pose_adam_step(float* cam_unnorm_rots, const float* grad_rots, int n_rots, float lr_rots, float* cam_trans,
+                      const float* grad_trans, int n_trans, float lr_trans, float* exp_avg, float* exp_avg_sq,
+                      float beta1, float beta2, float eps, float* step_state, void* cuda_stream);
+
 /* Adam fused with the gradient exchange of keyframe-batched mapping, over peer memory (one process per GPU,
  * NVLink / NVSwitch).  Replaces "all-reduce the flat [P,14] gradient, then as_adam_step on every rank": rank `rank` of
  * `world` (<= 8) owns the Gaussians [g_begin, g_end) (g_begin a multiple of 4; buffers 16-byte aligned); it reads those rows of EVERY rank's gradient buffer through peer
