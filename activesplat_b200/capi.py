@@ -120,6 +120,7 @@ SYMBOLS = {
     "as_mapping_loss_scratch_floats": (_Z, [_I, _I]),
     "as_mapping_loss": (_I, [_I, _I, _V, _V, _V, _F, _F, _V, _V, _V, _V, _V]),
     "as_adam_step": (_I, [_I, _I, _V, _V, _V, _V, _V, _V, _V, _V, ctypes.POINTER(ctypes.c_float), _F, _F, _F, _I, _V]),
+    "as_cluster_hull_volumes": (_I, [_I, _I, _I, _V, _V, _V, ctypes.c_double, _I, _V, _V, _V]),
     "as_pose_adam_step": (_I, [_V, _V, _I, _F, _V, _V, _I, _F, _V, _V, _F, _F, _F, _V, _V]),
     "as_adam_step_counted": (_I, [_I, _I, _V, _V, _V, _V, _V, _V, _V, _V, ctypes.POINTER(ctypes.c_float), _F, _F, _F, _V,
                                   _V]),

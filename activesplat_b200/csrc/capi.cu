@@ -541,6 +541,20 @@ int as_dbscan_grid(int batch, int height, int width, const float* values, float 
     return check(cudaGetLastError());
 }
 
+int as_cluster_hull_volumes(int batch, int height, int width, const int* labels, const int* n_clusters,
+                            const float* depth, double vfov_deg, int max_clusters, double* volumes, int* n_points,
+                            void* cuda_stream) {
+    if (batch < 0 || height <= 0 || width <= 0 || width > 32000 || height > 32000 || max_clusters < 0 || !(vfov_deg > 0))
+        return AS_ERR_INVALID_ARG;
+    if (batch == 0 || max_clusters == 0) return AS_OK;
+    if (!labels || !n_clusters || !depth || !volumes || !n_points) return AS_ERR_INVALID_ARG;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
+    StageScope _s(AS_STAGE_OTHER, st, 1);
+    if (launch_cluster_hull(batch, height, width, labels, n_clusters, depth, vfov_deg, max_clusters, volumes, n_points, st))
+        return AS_ERR_INVALID_ARG;   // the image's two bit planes do not fit in shared memory
+    return check(cudaGetLastError());
+}
+
 int as_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* /*projmatrix*/,
                     uint8_t* present, void* cuda_stream) {
     if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) return AS_ERR_INVALID_ARG;

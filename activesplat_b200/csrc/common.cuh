@@ -168,6 +168,8 @@ void launch_adam_peer(int g_begin, int g_end, int iso, int world, int rank, floa
 // DBSCAN on a pixel grid, one CTA per image (scoring.cu)
 void launch_dbscan_grid(int batch, int H, int W, const float* values, float thr, float eps, int min_samples, int* labels,
                         int* scratch, int max_clusters, int* n_clusters, int* stats_i, double* stats_v, cudaStream_t st);
+int launch_cluster_hull(int batch, int H, int W, const int* labels, const int* n_clusters, const float* depth,
+                        double vfov_deg, int max_clusters, double* volumes, int* n_points, cudaStream_t st);
 void launch_adam(int P, int iso, float* const params[5], const float lr[5], const float* grad, float* m, float* v,
                  float beta1, float beta2, float eps, int step, cudaStream_t st);
 void launch_pose_adam(float* rots, const float* g_rots, int n_rots, float lr_rots, float* trans, const float* g_trans,

@@ -126,16 +126,19 @@ def _pack_cameras(views):
     return torch.cat([view.reshape(n, 16), full.reshape(n, 16), w2c.reshape(n, 16), cam_center, torch.zeros(n, 3)], 1)
 
 
-def score_candidate_views(params, views, group=None, n_streams=32, scale_modifier=1.0, return_opacity=False):
+def score_candidate_views(params, views, group=None, n_streams=32, scale_modifier=1.0, return_opacity=False,
+                          return_depth=False, shard=True):
     """The GetOpacity sweep (src/mapper/splatam/__init__.py:716-738 per view) over `views` (CameraSpec-like, all the
     same size), sharded over the ranks of `group`; every rank receives [n_views, 2] = (sum of invisibility, mean
     opacity).  Same renders as splatam.render_view, organised so that the host does little per view: all camera
     matrices are built and uploaded in one go, each view is one fused forward on one of `n_streams` streams (a
     low-resolution view is latency-bound on a few crowded tiles; in flight together they fill the GPU), and the
-    scores are reduced once for the whole shard."""
+    scores are reduced once for the whole shard.
+    return_opacity / return_depth: also return this rank's opacity / median-depth images [n_local,H,W].
+    shard=False: render every view on this rank (the caller has already split the work) and skip the gather."""
     from . import splatam
     from .frame import FrameWorkspace, identity_pose
-    rank, world = world_info(group)
+    rank, world = world_info(group) if shard else (0, 1)
     mine = shard_indices(len(views), rank, world)
     dev = params["means3D"].device
     P = int(params["means3D"].shape[0])
@@ -152,6 +155,7 @@ def score_candidate_views(params, views, group=None, n_streams=32, scale_modifie
     white = splatam._white_bg(dev)
     ops = torch.empty((len(mine), H, W), dtype=torch.float32, device=dev)
     stats = torch.zeros((len(mine), 4), dtype=torch.int32, device=dev)
+    depths = torch.empty((len(mine), H, W), dtype=torch.float32, device=dev) if return_depth else None
     if mine:
         d = _pack_cameras([views[v] for v in mine]).pin_memory().to(dev, non_blocking=True)
         cur = torch.cuda.current_stream(dev)
@@ -169,6 +173,8 @@ def score_candidate_views(params, views, group=None, n_streams=32, scale_modifie
                 with torch.cuda.stream(streams[s]):
                     wss[s].forward(p, cam, 0, sil_w2c=row[32:48].view(4, 4), bg_rgb=white)
                     ops[j].copy_(wss[s].opacity[0], non_blocking=True)
+                    if return_depth:
+                        depths[j].copy_(wss[s].depth[0], non_blocking=True)
                     stats[j].copy_(wss[s].status, non_blocking=True)
         for st in streams:
             cur.wait_stream(st)
@@ -187,9 +193,12 @@ def score_candidate_views(params, views, group=None, n_streams=32, scale_modifie
             if ws.last_status()[1]:
                 raise RuntimeError("activesplat_b200: candidate view still overflows its binning buffer after growing it")
             ops[j].copy_(ws.opacity[0])
+            if return_depth:
+                depths[j].copy_(ws.depth[0])
     local = torch.stack([(1.0 - ops).sum((1, 2)), ops.mean((1, 2))], 1) if mine else torch.zeros((0, 2), device=dev)
     scores = gather_scores(local, len(views), rank, world, group)
-    return (scores, ops) if return_opacity else scores
+    out = (scores,) + ((ops,) if return_opacity else ()) + ((depths,) if return_depth else ())
+    return out if len(out) > 1 else scores
 
 
 # ---- Adam fused with the gradient exchange over peer memory ------------------------------------------------------

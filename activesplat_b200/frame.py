@@ -120,7 +120,7 @@ class FrameWorkspace:
         if self._binning_auto and self.binning_mode == 1 and largest > capi.lib().as_tile_sort_capacity():
             self.binning_mode = 0
         if overflowed:
-            self.overflow_seen = (n_inst, self.capacity)
+            self.overflow_seen = (n_inst, self._status_cap)
         if 2 * n_inst > self.capacity:
             self.ensure_capacity(2 * n_inst)
 
@@ -201,6 +201,7 @@ class FrameWorkspace:
                 if self._status_host is None:
                     self._status_host = torch.zeros(4, dtype=torch.int32).pin_memory()
                 self._status_host.copy_(self.status, non_blocking=True)
+                self._status_cap = self.capacity
                 self._status_event = torch.cuda.Event()
                 self._status_event.record(torch.cuda.current_stream(self.device))
             if not self.calibrated and not capturing:

@@ -8,9 +8,11 @@ float32[] targets_frustums_volume}.  Handler: src/visualizer/visualizer.py:2180-
   [0], and one frustum pose: the camera turned towards the heaviest cluster of unseen pixels, converted with
   OPENCV_TO_OPENGL and matrix_to_pose like the handler does (an identity Pose when there is no such cluster), plus the
   high-loss-sample pose when the mapper has one.
-* GLOBAL query (arrived_flag true): the renders and the raw per-node invisibility sums are produced here, sharded over
-  the GPUs of the process group; the reference's per-node scores also need get_convexhull_volume (OpenCV contour
-  tracing + qhull), which is not ported -- `global_panoramas` returns what that function takes as input.
+* GLOBAL query (arrived_flag true): one invisibility and one volume per requested node
+  (SplaTAM.get_global_invisibility -> get_convexhull_volume, src/mapper/__init__.py:8-90), all nodes in one pass on
+  the device -- renders, panoramas, DBSCAN, dilation, contour, convex-hull volume -- sharded over the GPUs of the
+  process group; the reference answers the same request with a sequential loop over the nodes
+  (src/visualizer/visualizer.py:991-1001).
 """
 from dataclasses import dataclass, field
 from typing import List, Optional
@@ -79,37 +81,23 @@ def handle_local(params, view_c2w, high_loss_samples_pose_c2w=None, cluster_invi
     return resp
 
 
-def global_panoramas(params, view_c2w, nodes, group=None, scale_modifier=1.0):
-    """The render half of the GLOBAL branch (SplaTAM.get_global_invisibility, src/mapper/splatam/__init__.py:698-738)
-    for every node at once: three look-around views per node position, sharded over the ranks of `group`.
-    Returns (sum_invisibility [n_nodes] float tensor on every rank, opacity panoramas [n_local_views,150,120] of THIS
-    rank's views and their view indices) -- the inputs get_convexhull_volume works on.  A node at the origin is
-    skipped by the reference (:701-702): its sum is 0."""
-    from . import dist as asd
-    nodes = np.asarray(nodes, dtype=np.float64).reshape(-1, 3)
-    views, owner = [], []
-    for i, pos in enumerate(nodes):
-        if (pos == np.zeros(3)).all():
-            continue
-        vs = scoring.look_around_views(view_c2w, position=pos)
-        views += vs
-        owner += [i] * len(vs)
-    dev = params["means3D"].device
-    sums = torch.zeros(len(nodes), dtype=torch.float32, device=dev)
-    if not views:
-        return sums, torch.zeros((0, 150, 120), device=dev), []
-    scores, ops = asd.score_candidate_views(params, views, group=group, scale_modifier=scale_modifier,
-                                            return_opacity=True)
-    sums.index_add_(0, torch.as_tensor(owner, device=dev), scores[:, 0])
-    rank, world = asd.world_info(group)
-    return sums, ops, asd.shard_indices(len(views), rank, world)
+def handle_global(params, view_c2w, nodes, group=None, scale_modifier=1.0):
+    """The GLOBAL branch (visualizer.py:2183-2195 + the node loop :991-1001): every node's invisibility and volume in
+    one pass on the device (scoring.get_global_invisibility), nodes sharded over the ranks of `group`."""
+    invisibility, volume = scoring.get_global_invisibility(params, view_c2w, nodes, group=group,
+                                                           scale_modifier=scale_modifier)
+    resp = GetOpacityResponse()
+    resp.targets_frustums_invisibility = [float(x) for x in invisibility.cpu()]
+    resp.targets_frustums_volume = [float(x) for x in volume.cpu()]
+    return resp
 
 
 def handle_get_opacity(req: GetOpacityRequest, params, view_c2w, high_loss_samples_pose_c2w=None,
-                       cluster_invisibility_threshold=30) -> Optional[GetOpacityResponse]:
-    """visualizer.py:2180-2221.  LOCAL queries are answered completely; GLOBAL queries raise NotImplementedError after
-    the renders because the per-node volume needs get_convexhull_volume (see the module docstring)."""
+                       cluster_invisibility_threshold=30, group=None) -> Optional[GetOpacityResponse]:
+    """visualizer.py:2180-2221: `arrived_flag` selects the GLOBAL branch (one invisibility + one volume per requested
+    node, no frustum poses) or the LOCAL branch (the current camera's look-around, best pose towards the heaviest
+    cluster)."""
     if not req.arrived_flag:
         return handle_local(params, view_c2w, high_loss_samples_pose_c2w, cluster_invisibility_threshold)
-    raise NotImplementedError("GLOBAL GetOpacity needs get_convexhull_volume (OpenCV contours + qhull), which is not "
-                              "ported; global_panoramas() provides its inputs")
+    nodes = np.array([[p.x, p.y, p.z] if hasattr(p, "x") else list(p) for p in req.nodes], dtype=np.float64).reshape(-1, 3)
+    return handle_global(params, view_c2w, nodes, group=group)

@@ -5,9 +5,11 @@ Mirrors, by name and argument meaning:
   the LOCAL branch of GetOpacity src/mapper/splatam/__init__.py:762-838 (`get_local_invisibility`): panorama of three
       120x150 views (hfov 120, vfov 150: one pixel per degree), sum of invisibility, 2x area down-sampling, clusters,
       and the camera rotation towards the heaviest cluster.
-The clustering runs in libactivesplat_b200.so (`as_dbscan_grid`); there is no CPU fallback.  The GLOBAL branch's
-convex-hull volume (get_convexhull_volume: OpenCV contour tracing + qhull) is not ported; its DBSCAN step is this
-same kernel with (eps 5, min_samples 25, threshold 0.8).
+  get_convexhull_volume          src/mapper/__init__.py:8-90     (GLOBAL branch: DBSCAN eps 5 / min_samples 25 on
+      invisibility > 0.8, per cluster dilation + outer contour + back-projection + 3-D convex-hull volume)
+  the GLOBAL branch of GetOpacity src/mapper/splatam/__init__.py:698-759 (`get_global_invisibility`), all nodes at once
+The clustering and the hull volumes run in libactivesplat_b200.so (`as_dbscan_grid`, `as_cluster_hull_volumes`); there
+is no CPU fallback.
 """
 import ctypes
 
@@ -61,6 +63,37 @@ def get_invisibility_clusters(invisibility, cluster_invisibility_threshold=30, m
             centers.append(np.array([si[c, 1] / si[c, 0], si[c, 2] / si[c, 0]]))
             sums.append(np.float32(sv[c]))
     return centers, sums
+
+
+def get_convexhull_volume(depth, invisibility, vfov=150.0, max_clusters=32):
+    """src/mapper/__init__.py:8-90 for a batch of panoramas on the device.
+    depth [B,H,W] (median depth, 15 where no surface), invisibility [B,H,W] (1 - opacity), CUDA float tensors.
+    Returns (last_invisibility [B] float64, last_volume [B] float64, n_clusters [B] int32, n_points [B,max_clusters]
+    int32): per panorama the sum over its clusters of sum(invisibility of the members) * hull volume and the sum of
+    the hull volumes, plus the cluster count (a count above max_clusters means clusters were dropped: call again with
+    more) and the number of outline points each hull was built from.  No host synchronisation."""
+    if not invisibility.is_cuda:
+        raise RuntimeError("get_convexhull_volume needs CUDA tensors (there is no CPU path)")
+    inv = invisibility.detach()
+    dep = depth.detach()
+    if inv.dim() == 2:
+        inv = inv.unsqueeze(0)
+    dep = dep.reshape(inv.shape)
+    if dep.dtype != torch.float32 or not dep.is_contiguous():
+        dep = dep.contiguous().float()
+    B, H, W = inv.shape
+    labels, n_clusters, _, stats_v = dbscan_grid(inv, 0.8, eps=5.0, min_samples=25, max_clusters=max_clusters)
+    dev = inv.device
+    with torch.cuda.device(dev):
+        volumes = torch.empty((B, max_clusters), dtype=torch.float64, device=dev)
+        n_points = torch.empty((B, max_clusters), dtype=torch.int32, device=dev)
+        capi.check(capi.lib().as_cluster_hull_volumes(B, H, W, labels.data_ptr(), n_clusters.data_ptr(), dep.data_ptr(),
+                                                      float(vfov), int(max_clusters), volumes.data_ptr(),
+                                                      n_points.data_ptr(), torch.cuda.current_stream(dev).cuda_stream))
+    used = n_points != 0     # a cluster whose whole outline lies on "no surface" pixels is skipped (:60-61)
+    last_invisibility = (stats_v * volumes * used).sum(1)
+    last_volume = (volumes * used).sum(1)
+    return last_invisibility, last_volume, n_clusters, n_points
 
 
 def area_downsample_2x(img):
@@ -137,3 +170,48 @@ def get_local_invisibility(params, view_c2w, cluster_invisibility_threshold=30, 
     pano = torch.cat([ops[i] for i in range(len(views))], dim=1)  # np.hstack of the per-view opacity images (:789)
     return local_invisibility_from_panorama(pano, view_c2w, cluster_invisibility_threshold,
                                             width=views[0].width, height=views[0].height)
+
+
+def get_global_invisibility(params, view_c2w, positions, group=None, scale_modifier=1.0, max_clusters=32):
+    """SplaTAM.get_global_invisibility (src/mapper/splatam/__init__.py:698-759) for ALL Voronoi nodes of a GLOBAL
+    GetOpacity query at once (the reference loops over them, src/visualizer/visualizer.py:991-1001): per node the three
+    look-around renders at the node's position and the agent's camera height, the 150x360 panoramas of invisibility
+    and median depth, DBSCAN clusters and convex-hull volumes -- all on the device, nodes sharded over the ranks of
+    `group`.  Returns (invisibility [n_nodes], volume [n_nodes]) float64 tensors on every rank; a node at the origin
+    is skipped like the reference does (:701-702) and scores (0, 0)."""
+    from . import dist as asd
+    positions = np.asarray(positions, dtype=np.float64).reshape(-1, 3)
+    n_nodes = len(positions)
+    dev = params["means3D"].device
+    rank, world = asd.world_info(group)
+    live = [i for i in range(n_nodes) if not (positions[i] == 0).all()]
+    mine = live[rank::world]
+    local = torch.zeros((len(mine), 2), dtype=torch.float64, device=dev)
+    if mine:
+        views = []
+        for i in mine:
+            views += look_around_views(view_c2w, position=positions[i])
+        n_yaw = len(views) // len(mine)
+        _, ops, depths = asd.score_candidate_views(params, views, n_streams=min(32, len(views)), return_opacity=True,
+                                                   scale_modifier=scale_modifier, return_depth=True, shard=False)
+        H, W = ops.shape[1:]
+        # np.hstack of the per-yaw images (:731-736): view j of a node fills columns [j*W, (j+1)*W)
+        inv = (1.0 - ops).view(len(mine), n_yaw, H, W).permute(0, 2, 1, 3).reshape(len(mine), H, n_yaw * W).contiguous()
+        dep = depths.view(len(mine), n_yaw, H, W).permute(0, 2, 1, 3).reshape(len(mine), H, n_yaw * W).contiguous()
+        li, lv, n_cl, _ = get_convexhull_volume(dep, inv, vfov=150.0, max_clusters=max_clusters)
+        if int(n_cl.max()) > max_clusters:   # one read per query; the scores go to the host right after anyway
+            li, lv, _, _ = get_convexhull_volume(dep, inv, vfov=150.0, max_clusters=int(n_cl.max()))
+        local = torch.stack([li, lv], 1)
+    out = torch.zeros((n_nodes, 2), dtype=torch.float64, device=dev)
+    if world == 1:
+        out[mine] = local
+    else:
+        n_max = (len(live) + world - 1) // world
+        pad = torch.zeros((n_max, 2), dtype=torch.float64, device=dev)
+        pad[: len(mine)] = local
+        allr = torch.empty((world, n_max, 2), dtype=torch.float64, device=dev)
+        torch.distributed.all_gather_into_tensor(allr.view(world * n_max, 2), pad, group=group)
+        for r in range(world):
+            idx = live[r::world]
+            out[idx] = allr[r, : len(idx)]
+    return out[:, 0], out[:, 1]

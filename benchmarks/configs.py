@@ -172,10 +172,11 @@ def cfg1(dev, RefRenderer, args):
 
 def _pose_error(rots_a, trans_a, rots_b, trans_b, t):
     """(rotation angle in degrees, translation distance in mm) between two poses stored SplaTAM-style."""
-    qa = torch.nn.functional.normalize(rots_a[0, :, t].detach().double(), dim=0)
-    qb = torch.nn.functional.normalize(rots_b[0, :, t].detach().double(), dim=0)
+    qa = torch.nn.functional.normalize(rots_a[0, :, t].detach().double().cpu(), dim=0)
+    qb = torch.nn.functional.normalize(rots_b[0, :, t].detach().double().cpu(), dim=0)
     ang = 2 * torch.acos(torch.clamp(torch.abs((qa * qb).sum()), max=1.0))
-    return float(torch.rad2deg(ang)), float((trans_a[0, :, t].detach().double() - trans_b[0, :, t].detach().double()).norm() * 1e3)
+    dt = trans_a[0, :, t].detach().double().cpu() - trans_b[0, :, t].detach().double().cpu()
+    return float(torch.rad2deg(ang)), float(dt.norm() * 1e3)
 
 
 def cfg2(dev, with_ref, args):
@@ -246,7 +247,7 @@ def cfg2(dev, with_ref, args):
             loss = step()
         e1.record()
         torch.cuda.synchronize(dev)
-        return p, e0.elapsed_time(e1) / iters, float(loss)
+        return p, e0.elapsed_time(e1) / iters, float(loss.detach())
 
     p_e, ms_e, loss_e = run_ours(False)
     res["ours"] = {"ms_per_iter_eager": ms_e, "final_loss": loss_e,

@@ -290,6 +290,22 @@ int as_dbscan_grid(int batch, int height, int width, const float* values, float 
                    int min_samples, int* labels, int* scratch, int max_clusters, int* n_clusters, int* stats_int,
                    double* stats_value, void* cuda_stream);
 
+/* The rest of get_convexhull_volume (src/mapper/__init__.py:29-86) for every cluster as_dbscan_grid found in a batch
+ * of GLOBAL GetOpacity panoramas (eps 5, min_samples 25, threshold 0.8): the cluster's mask dilated with OpenCV's
+ * 15x15 elliptic element (cv2.dilate, :37-38), its outer contour as cv2.findContours(RETR_EXTERNAL,
+ * CHAIN_APPROX_SIMPLE) returns it (:41-42), the contour pixels back-projected as (x * rad(360 / width),
+ * y * rad(vfov / height), depth[y,x]) skipping depth == 15 (the rasterizer's "no surface" median depth, :49-66), and
+ * the volume of their 3-D convex hull (scipy.spatial.ConvexHull(...).volume, :69-78).
+ *   labels, n_clusters   as written by as_dbscan_grid          depth    [batch,H,W] float: median-depth panoramas
+ *   volumes   [batch,max_clusters] double out                   n_points [batch,max_clusters] int32 out: points that
+ *             entered the hull (0: the reference skips the cluster, :60-61; negative: more than 1024 contour vertices,
+ *             the hull was built from the first 1024)
+ * The per-node answers of the service are then  invisibility = sum_c [n_points_c != 0] stats_value_c * volume_c  and
+ * volume = sum_c volume_c (:81-90).  One CTA per (cluster, panorama); asynchronous on the stream. */
+int as_cluster_hull_volumes(int batch, int height, int width, const int* labels, const int* n_clusters,
+                            const float* depth, double vfov_deg, int max_clusters, double* volumes, int* n_points,
+                            void* cuda_stream);
+
 /* ---- stage-level entry points (used by the fused paths and by parity tests) ----------------- */
 
 /* Stable ascending LSD radix sort (hand-written onesweep) of n (u64 key, u32 value) pairs on key bits

@@ -2,7 +2,7 @@
 
 TEST INFRASTRUCTURE ONLY.  Like oracle/build_ref.py for the CUDA sources: the files are compiled from
 where they lie under /root/reference (nothing is copied into this repository); the only outputs are
-`.pyc` files under oracle/_ref/refpy/ (git-ignored, shipped to the GPU box by gpurun, where
+byte-code files (`*.bytecode`, the .pyc format) under oracle/_ref/refpy/ (git-ignored, shipped to the GPU box by gpurun, where
 /root/reference does not exist).  `load()` imports them there with the reference's own module names:
 
   mapper.splatam.splatam                 src/mapper/splatam/splatam.py      (get_loss, add_new_gaussians,
@@ -37,7 +37,7 @@ MODULES = {
 
 
 def _pyc(name):
-    return os.path.join(OUT, name + ".pyc")
+    return os.path.join(OUT, name + ".bytecode")   # not "*.pyc": gpurun's snapshot leaves those behind
 
 
 def build():

@@ -126,9 +126,13 @@ def run_loss(ns, spec):
     for k in stock:
         if k.startswith("selfnoise_"):
             out[k] = stock[k]
-    # everything that does not pass through the rotation/scale backward must not depend on the memory order
-    for k in ("loss", "im", "depth_sil", "radius"):
-        assert np.array_equal(stock[k], out[k]), k
+    # everything that does not pass through the rotation/scale backward must not depend on the memory order beyond
+    # rounding (torch normalises a column-major tensor with a differently ordered reduction: rotations differ by an ulp)
+    assert np.array_equal(stock["radius"], out["radius"])
+    for k in ("loss", "im", "depth_sil"):
+        d = float(np.abs(stock[k].astype(np.float64) - out[k]).max() / max(np.abs(out[k]).max(), 1e-30))
+        out["stock_vs_rowmajor_" + k] = np.float64(d)
+        assert d < 1e-5, (k, d)
     return out
 
 

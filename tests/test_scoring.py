@@ -173,12 +173,104 @@ def test_get_opacity_local_and_global_renders():
         want = go.matrix_to_pose(pose @ go.OPENCV_TO_OPENGL)
         assert np.allclose(resp.targets_frustums[0].orientation_xyzw, want.orientation_xyzw, atol=1e-6)
         assert np.allclose(resp.targets_frustums[0].position, c2w[:3, 3])
-    # GLOBAL: renders for three nodes (one at the origin is skipped by the reference), sums per node
-    nodes = np.array([[1.0, 0.0, 0.5], [0.0, 0.0, 0.0], [-1.0, 0.0, -0.5]])
-    sums, ops, idx = go.global_panoramas(params, c2w, nodes)
-    assert sums.shape == (3,) and float(sums[1]) == 0.0 and ops.shape == (6, 150, 120) and idx == list(range(6))
-    for n_i, first in ((0, 0), (2, 3)):
-        want = float((1.0 - ops[first:first + 3]).sum())
-        assert abs(float(sums[n_i]) - want) <= 1e-4 * max(want, 1.0)
-    with pytest.raises(NotImplementedError):
-        go.handle_get_opacity(go.GetOpacityRequest(True, nodes, [0, 1, 2]), params, c2w)
+
+
+# ---- get_convexhull_volume (GLOBAL branch, src/mapper/__init__.py:8-90) -------------------------------------------
+HULL_GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_hull.npz")
+
+
+def test_hull_oracle_matches_the_reference_function_outputs():
+    """oracle/hull_oracle.py (own dilation, border following, incremental hull) vs outputs of the reference's
+    get_convexhull_volume (OpenCV + scikit-learn + SciPy) on seeded panoramas (tests/golden/make_hull_golden.py)."""
+    from oracle import hull_oracle as ho
+    with np.load(HULL_GOLDEN) as z:
+        g = {k: z[k] for k in z.files}
+    for s in g["seeds"]:
+        depth, inv = ho.panorama(int(s))
+        li, lv = ho.get_convexhull_volume(depth, inv)
+        assert abs(lv - g[f"volume_{s}"]) <= 1e-9 * max(abs(g[f"volume_{s}"]), 1e-12), (s, lv, g[f"volume_{s}"])
+        # the reference sums invisibility * volume in float32
+        assert abs(li - g[f"invisibility_{s}"]) <= 1e-5 * max(abs(g[f"invisibility_{s}"]), 1e-12), (s, li)
+
+
+def test_hull_oracle_pieces():
+    """Element shape, single pixels, degenerate point sets."""
+    from oracle import hull_oracle as ho
+    assert ho.ellipse_rows() == [0, 4, 5, 6, 6, 7, 7, 7, 7, 7, 6, 6, 5, 4, 0]
+    m = np.zeros((40, 50), bool)
+    m[20, 25] = True
+    d = ho.dilate(m)
+    assert d.sum() == sum(2 * dx + 1 for dx in ho.ellipse_rows()) and d[13, 25] and d[20, 18] and not d[13, 24]
+    assert ho.outer_contour_simple(m) == [(25, 20)]
+    m[0, 0] = True                                                      # a component cut by the image corner
+    assert ho.dilate(m)[:8, :8].sum() > 30
+    cube = np.array([[x, y, z] for x in (0, 1) for y in (0, 1) for z in (0, 1)], float)
+    assert abs(ho.convex_hull_volume(cube) - 1.0) < 1e-12
+    assert abs(ho.convex_hull_volume(np.vstack([cube, [[0.5, 0.5, 0.5]], [[0.2, 0.9, 0.1]]])) - 1.0) < 1e-12
+    assert ho.convex_hull_volume(np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [1, 1, 0], [0.3, 0.3, 0]], float)) == 0.0
+
+
+@pytest.mark.gpu
+def test_cluster_hull_volumes_match_oracle_and_reference():
+    """as_dbscan_grid + as_cluster_hull_volumes (scoring.get_convexhull_volume) on a batch of panoramas: per panorama
+    the same (invisibility, volume) as the oracle and as the reference's own function (golden file)."""
+    from activesplat_b200 import scoring
+    from oracle import hull_oracle as ho
+    with np.load(HULL_GOLDEN) as z:
+        g = {k: z[k] for k in z.files}
+    seeds = [int(s) for s in g["seeds"]] + [100, 101, 102]
+    pans = [ho.panorama(s) for s in seeds]
+    # a panorama whose clusters all lie on "no surface" pixels, one without clusters, one that is a single cluster
+    d0, i0 = ho.panorama(200)
+    d0[:] = ho.EMPTY_DEPTH
+    pans.append((d0, i0))
+    pans.append((np.full((150, 360, 1), 2.0, np.float32), np.zeros((150, 360), np.float32)))
+    pans.append((ho.panorama(201)[0], np.ones((150, 360), np.float32)))
+    depth = torch.from_numpy(np.stack([p[0][..., 0] for p in pans])).cuda()
+    inv = torch.from_numpy(np.stack([p[1] for p in pans])).cuda()
+    li, lv, n_cl, n_pts = scoring.get_convexhull_volume(depth, inv)
+    li, lv = li.cpu().numpy(), lv.cpu().numpy()
+    assert int(n_pts.min()) >= 0                                        # no contour overflowed the vertex buffer
+    for b, (d, i) in enumerate(pans):
+        want_i, want_v = ho.get_convexhull_volume(d, i)
+        assert abs(lv[b] - want_v) <= 1e-9 * max(abs(want_v), 1e-9), (b, lv[b], want_v)
+        assert abs(li[b] - want_i) <= 1e-5 * max(abs(want_i), 1e-9), (b, li[b], want_i)
+    for k, s in enumerate(g["seeds"]):
+        assert abs(lv[k] - g[f"volume_{s}"]) <= 1e-9 * max(abs(g[f"volume_{s}"]), 1e-12)
+        assert abs(li[k] - g[f"invisibility_{s}"]) <= 1e-5 * max(abs(g[f"invisibility_{s}"]), 1e-12)
+    assert lv[len(seeds)] == 0.0 and li[len(seeds)] == 0.0 and lv[len(seeds) + 1] == 0.0
+    # one panorama alone gives the same numbers as inside the batch
+    li1, lv1, _, _ = scoring.get_convexhull_volume(depth[3], inv[3])
+    assert abs(float(lv1[0]) - lv[3]) <= 1e-12 * max(lv[3], 1e-12)
+
+
+@pytest.mark.gpu
+def test_get_opacity_global_handler_matches_oracle_pipeline():
+    """GLOBAL GetOpacity (visualizer.py:2183-2195 + :991-1001): all nodes in one pass on the device vs, per node, the
+    oracle pipeline on the same renders (panorama of the three look-around views -> hull_oracle.get_convexhull_volume)."""
+    from activesplat_b200 import dist as asd, getopacity as go, scenes, scoring
+    from oracle import hull_oracle as ho
+    dev = torch.device("cuda:0")
+    params_cpu, _ = scenes.s_room(8000, 1, seed=41, scale_mult=6.0)
+    keep = (params_cpu["means3D"][:, 0] < 2.5) | (params_cpu["means3D"][:, 2] > 3.0)   # a map with unexplored sides
+    params = {k: v[keep].contiguous().to(dev) for k, v in params_cpu.items()}
+    c2w = np.eye(4)
+    c2w[:3, 3] = [0.3, 0.0, -0.4]
+    nodes = np.array([[1.0, 0.0, 0.5], [0.0, 0.0, 0.0], [-1.0, 0.0, -0.5], [2.5, 0.0, 2.0], [-3.0, 0.0, 1.0]])
+    resp = go.handle_get_opacity(go.GetOpacityRequest(True, nodes, list(range(len(nodes)))), params, c2w)
+    assert resp.targets_frustums == [] and len(resp.targets_frustums_invisibility) == len(nodes)
+    assert resp.targets_frustums_invisibility[1] == 0.0 and resp.targets_frustums_volume[1] == 0.0   # node at the origin
+    some = 0
+    for n_i, pos in enumerate(nodes):
+        if (pos == 0).all():
+            continue
+        views = scoring.look_around_views(c2w, position=pos)
+        _, ops, deps = asd.score_candidate_views(params, views, n_streams=3, return_opacity=True, return_depth=True)
+        inv_np = 1.0 - np.hstack([o.cpu().numpy() for o in ops])
+        dep_np = np.hstack([d.cpu().numpy() for d in deps])[..., None]
+        want_i, want_v = ho.get_convexhull_volume(dep_np, inv_np)
+        got_i, got_v = resp.targets_frustums_invisibility[n_i], resp.targets_frustums_volume[n_i]
+        assert abs(got_v - want_v) <= 1e-7 * max(abs(want_v), 1e-9), (n_i, got_v, want_v)
+        assert abs(got_i - want_i) <= 1e-5 * max(abs(want_i), 1e-9), (n_i, got_i, want_i)
+        some += want_v > 0
+    assert some >= 2   # the scene leaves something to find
