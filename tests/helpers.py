@@ -15,11 +15,15 @@ from activesplat_b200 import scenes  # noqa: E402
 
 GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
 
-# Tolerance from BASELINE.json north_star: "images, depth, silhouette and gradients must agree
-# within 1e-4 relative in fp32".  Relative to the tensor's scale (max |ref|), per element, with a
-# counted allowance for pixels whose alpha sat within an ulp of a skip threshold (1/255, T<1e-4):
-# there a different exp() implementation legitimately flips the decision (SURVEY 7 "hard parts").
+# Tolerance from BASELINE.json north_star: "images, depth, silhouette and gradients must agree within 1e-4 relative
+# in fp32".  Checked PER ELEMENT: |got - ref| <= REL_TOL * max(|ref|, ABS_FLOOR * max|ref|).  The absolute floor (a tenth of
+# the tensor's largest magnitude) is there because a gradient entry far below the tensor's scale is a sum of large
+# cancelling terms, and the reference itself -- float atomics in arbitrary order -- does not reproduce such entries to
+# 1e-4 of their own value (tests/golden/ref_splatam_*: selfnoise_*).  A counted allowance covers pixels whose alpha sat
+# within an ulp of a skip threshold (1/255, T < 1e-4): there a different exp() implementation legitimately flips the
+# decision (SURVEY 7 "hard parts").  The observed worst cases go to the parity report (tests/conftest.py).
 REL_TOL = 1e-4
+ABS_FLOOR = 0.1
 FLIP_FRACTION = 2e-4   # at most this fraction of elements may exceed REL_TOL ...
 FLIP_BOUND = 2e-2      # ... and none may exceed this (a flipped 1/255 contribution is < 1e-2 of scale)
 
@@ -79,28 +83,38 @@ REPORT = {}   # test id -> {tensor name -> observed error statistics}; tests/con
 _CURRENT_TEST = ["?"]
 
 
-def compare_float(name, got, ref, rel=REL_TOL, flip_fraction=FLIP_FRACTION, flip_bound=FLIP_BOUND):
+def compare_float(name, got, ref, rel=REL_TOL, flip_fraction=FLIP_FRACTION, flip_bound=FLIP_BOUND, floor=ABS_FLOOR):
     got = np.asarray(got, dtype=np.float64)
     ref = np.asarray(ref, dtype=np.float64)
     assert got.shape == ref.shape, f"{name}: shape {got.shape} vs {ref.shape}"
     assert np.isfinite(got).all(), f"{name}: non-finite values"
     scale = max(float(np.abs(ref).max()), 1e-12)
-    err = np.abs(got - ref) / scale
+    d = np.abs(got - ref)
+    err = d / np.maximum(np.abs(ref), floor * scale)   # per element, with the absolute floor
     bad = err > rel
     frac = float(bad.mean()) if bad.size else 0.0
     worst = float(err.max()) if err.size else 0.0
     if err.size:
-        # what was observed, next to what was allowed: worst error relative to the tensor's scale, the number of
-        # elements that used the counted allowance, and the worst PER-ELEMENT relative error with absolute floors
-        # of 10 % / 1 % of the scale (|got - ref| / max(|ref|, floor))
-        d = np.abs(got - ref)
+        # what was observed, next to what was allowed
         REPORT.setdefault(_CURRENT_TEST[0], {})[name] = dict(
-            n=int(err.size), tol=rel, worst_of_scale=worst, beyond_tol=int(bad.sum()), allowed_beyond=flip_fraction,
-            worst_elem_floor10pct=float((d / np.maximum(np.abs(ref), 0.1 * scale)).max()),
+            n=int(err.size), tol=rel, floor=floor, worst=worst, beyond_tol=int(bad.sum()),
+            allowed_beyond=int(flip_fraction * bad.size), allowed_worst=flip_bound,
+            worst_of_scale=float((d / scale).max()),
             worst_elem_floor1pct=float((d / np.maximum(np.abs(ref), 0.01 * scale)).max()))
     assert frac <= flip_fraction, f"{name}: {bad.sum()} of {bad.size} elements beyond {rel:g} rel (worst {worst:.3g})"
     assert worst <= flip_bound, f"{name}: worst relative error {worst:.3g} > {flip_bound:g}"
     return worst, frac
+
+
+GRAD_FLIP_FRACTION = 1e-3
+
+
+def compare_grad(name, got, ref, **kw):
+    """compare_float for rasterizer-level gradients taken with a random dL/dpixel in [-1, 1]: every entry is a sum of
+    hundreds of terms of both signs, so more entries end up far below the tensor's scale with an error set by the
+    summation order (the reference's own two runs differ there); one entry in a thousand may use the allowance."""
+    kw.setdefault("flip_fraction", GRAD_FLIP_FRACTION)
+    return compare_float(name, got, ref, **kw)
 
 
 def compare_exact(name, got, ref, max_mismatch=0):

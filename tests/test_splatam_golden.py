@@ -25,8 +25,7 @@ PARAM_KEYS = ("means3D", "rgb_colors", "unnorm_rotations", "logit_opacities", "l
 
 def _golden(name):
     g = helpers.splatam_golden(name)
-    if g is None:
-        pytest.skip(f"tests/golden/ref_splatam_{name}.npz is missing (oracle/make_golden_splatam.py makes it)")
+    assert g is not None, f"tests/golden/ref_splatam_{name}.npz is missing (oracle/make_golden_splatam.py makes it)"
     return g
 
 
@@ -45,9 +44,9 @@ def _inputs(spec, dev, camera_fn):
 
 
 def _check_loss_outputs(tag, g, loss, wl, p, iso, rel=1e-4):
-    helpers.compare_float(f"{tag} loss", float(loss), g["loss"], rel=rel)
-    helpers.compare_float(f"{tag} loss im", float(wl["im"]), g["loss_im"], rel=rel)
-    helpers.compare_float(f"{tag} loss depth", float(wl["depth"]), g["loss_depth"], rel=rel)
+    helpers.compare_float(f"{tag} loss", float(loss.detach()), g["loss"], rel=rel)
+    helpers.compare_float(f"{tag} loss im", float(wl["im"].detach()), g["loss_im"], rel=rel)
+    helpers.compare_float(f"{tag} loss depth", float(wl["depth"].detach()), g["loss_depth"], rel=rel)
     for k in PARAM_KEYS:
         has = p[k].grad is not None
         assert has == (("grad_" + k) in g), f"{tag}: gradient presence of {k} differs from the reference"
@@ -117,10 +116,17 @@ def test_reference_noise_floor_is_recorded():
     worst = 0.0
     for name in LOSS_CASES:
         g = _golden(name)
+        iso = helpers.SPLATAM_CASES[name]["frame"].get("iso", False)
         for k, v in g.items():
-            if k.startswith("selfnoise_"):
-                worst = max(worst, float(v))
-    assert worst < 1e-4
+            if not k.startswith("selfnoise_"):
+                continue
+            if iso and k == "selfnoise_grad_unnorm_rotations":
+                # isotropic Gaussians: the rotation gradient is analytically zero and what the reference returns is
+                # cancellation noise -- two runs of the reference differ by its whole magnitude
+                assert float(v) > 0.1
+                continue
+            worst = max(worst, float(v))
+    assert 1e-7 < worst < 1e-4   # observed 2e-5 (cam_unnorm_rots, anisotropic tracking)
 
 
 # =====================================================================================================
@@ -238,7 +244,9 @@ def test_render_view_matches_reference_golden():
     p = {k: v.cuda() for k, v in params.items()}
     im, depth, opacity, sil = splatam.render_view(p, cam.w2c, cam.k(), cam.width, cam.height)
     helpers.compare_float("im", im.cpu().numpy(), g["im"])
-    helpers.compare_float("median depth", depth.cpu().numpy(), g["depth"])
+    # the median depth is the depth of the Gaussian at which T crosses 0.5: a pixel whose T lands within rounding of 0.5
+    # picks a neighbouring Gaussian on one side or the other, so a flipped pixel is off by a whole depth step
+    helpers.compare_float("median depth", depth.cpu().numpy(), g["depth"], flip_bound=1.0)
     helpers.compare_float("opacity", opacity.cpu().numpy(), g["opacity"])
     helpers.compare_float("silhouette", sil.cpu().numpy(), g["sil"])
     # and through the reference-named two-step API
@@ -246,7 +254,7 @@ def test_render_view_matches_reference_golden():
     cfg = dict(viz_w=cam.width, viz_h=cam.height, viz_near=cam.near, viz_far=cam.far)
     im2, depth2, opacity2, sil2 = splatam.render(cam.w2c, cam.k(), rv, drv, cfg)
     helpers.compare_float("render im", im2.cpu().numpy(), g["im"])
-    helpers.compare_float("render depth", depth2.cpu().numpy(), g["depth"])
+    helpers.compare_float("render depth", depth2.cpu().numpy(), g["depth"], flip_bound=1.0)
     helpers.compare_float("render opacity", opacity2.cpu().numpy(), g["opacity"])
     helpers.compare_float("render silhouette", sil2.cpu().numpy(), g["sil"])
 
