@@ -25,7 +25,8 @@ GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
 REL_TOL = 1e-4
 ABS_FLOOR = 0.1
 FLIP_FRACTION = 2e-4   # at most this fraction of elements may exceed REL_TOL ...
-FLIP_BOUND = 2e-2      # ... and none may exceed this (a flipped 1/255 contribution is < 1e-2 of scale)
+FLIP_BOUND = 5e-2      # ... and none may exceed this (a flipped alpha = 1/255 contribution is 3.9e-3 of a unit-scale
+                       # image, i.e. 3.9e-2 relative to the absolute floor)
 
 
 def depth_sil_features(means3D, w2c):
@@ -110,9 +111,10 @@ GRAD_FLIP_FRACTION = 1e-3
 
 
 def compare_grad(name, got, ref, **kw):
-    """compare_float for rasterizer-level gradients taken with a random dL/dpixel in [-1, 1]: every entry is a sum of
-    hundreds of terms of both signs, so more entries end up far below the tensor's scale with an error set by the
-    summation order (the reference's own two runs differ there); one entry in a thousand may use the allowance."""
+    """compare_float for per-Gaussian gradients: every entry is a sum of hundreds of per-pixel terms of both signs
+    (random dL/dpixel in [-1, 1] in the rasterizer-level cases), so more entries end up far below the tensor's scale
+    with an error set by the summation order (the reference's own two runs differ there), and a pixel whose alpha
+    decision flipped moves the entries of the Gaussians it touches; one entry in a thousand may use the allowance."""
     kw.setdefault("flip_fraction", GRAD_FLIP_FRACTION)
     return compare_float(name, got, ref, **kw)
 

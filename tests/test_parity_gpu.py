@@ -275,7 +275,7 @@ def test_fused_tracking_get_loss_matches_oracle(iso):
     assert pg["means3D"].grad is None and pg["unnorm_rotations"].grad is None
     assert pc["means3D"].grad is None and pc["unnorm_rotations"].grad is None
     for k in ("rgb_colors", "logit_opacities", "log_scales"):
-        helpers.compare_float("grad " + k, pg[k].grad.cpu().numpy(), pc[k].grad.numpy())
+        helpers.compare_grad("grad " + k, pg[k].grad.cpu().numpy(), pc[k].grad.numpy())
     assert int(variables["seen"].sum()) > 100
 
 
@@ -321,7 +321,7 @@ def test_fused_frame_gaussian_gradients_match_oracle(iso):
             # sides return cancellation noise, so only its magnitude is checked
             assert np.abs(pg[k].grad.cpu().numpy()).max() <= 1e-3 * np.abs(pg["log_scales"].grad.cpu().numpy()).max()
             continue
-        helpers.compare_float("grad " + k, pg[k].grad.cpu().numpy(), pc[k].grad.numpy())
+        helpers.compare_grad("grad " + k, pg[k].grad.cpu().numpy(), pc[k].grad.numpy())
     # capacity overflow is flagged, not written out of bounds
     ws_small = FrameWorkspace(pg["means3D"].shape[0], W, H, dev, capacity=max(R // 3, 16))
     ws_small.forward({k: v.detach() for k, v in pg.items()}, cam_g, t_idx)
@@ -393,7 +393,7 @@ def test_mapping_get_loss_and_adam_steps_match_oracle():
             helpers.compare_float(f"it{it} loss {k}", wl_g[k].detach().cpu().numpy(), wl_c[k].detach().numpy())
         if it == 0:
             for k in PARAM_ORDER:
-                helpers.compare_float("grad " + k, pg[k].grad.cpu().numpy(), pc[k].grad.numpy())
+                helpers.compare_grad("grad " + k, pg[k].grad.cpu().numpy(), pc[k].grad.numpy())
             assert pg["cam_trans"].grad is None and pc["cam_trans"].grad is None  # camera_grad=False in mapping
         opt_c.step()
         opt_g.step(workspace_for(pg, cam_g).grad_params)

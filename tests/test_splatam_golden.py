@@ -58,7 +58,7 @@ def _check_loss_outputs(tag, g, loss, wl, p, iso, rel=1e-4):
             # return cancellation noise, so only its magnitude is checked
             assert np.abs(got).max() <= 1e-3 * max(np.abs(g["grad_log_scales"]).max(), 1e-12)
             continue
-        helpers.compare_float(f"{tag} grad {k}", got, g["grad_" + k], rel=rel)
+        helpers.compare_grad(f"{tag} grad {k}", got, g["grad_" + k], rel=rel)
 
 
 # =====================================================================================================
@@ -203,7 +203,7 @@ def test_mapping_adam_steps_match_reference_golden():
         for v in p.values():
             v.grad = None
         loss.backward()
-        helpers.compare_float(f"loss {it}", float(loss), g[f"loss_{it}"], rel=1e-4 if it == 0 else 1e-3)
+        helpers.compare_float(f"loss {it}", float(loss.detach()), g[f"loss_{it}"], rel=1e-4 if it == 0 else 1e-3)
         opt.step(frame.workspace_for(p, curr["cam"]).grad_params)
     for k in PARAM_KEYS[:5]:
         if k == "unnorm_rotations":
