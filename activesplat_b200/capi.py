@@ -7,7 +7,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libactivesplat_b200.so")
+# ASB_LIB_PATH: developer override for A/B measurements of kernel variants (csrc/build.py build_variant)
+LIB_PATH = os.environ.get("ASB_LIB_PATH") or os.path.join(_HERE, "libactivesplat_b200.so")
 
 AS_OK = 0
 AS_ERR_INVALID_ARG = -1

@@ -343,7 +343,10 @@ constexpr int BW_GROUP = 16;   // records per group: 16 x 32 staging slots per w
 #define ASB_BW_BATCH 128
 #endif
 constexpr int BW_BATCH = ASB_BW_BATCH;  // records per staged batch in the backward (64 gives 4 CTAs per SM but twice the barriers: measured slower)
-constexpr int BW_STAGES = 2;   // bulk-copy pipeline depth of the backward (a batch takes long enough to hide one copy)
+#ifndef ASB_BW_STAGES
+#define ASB_BW_STAGES 2
+#endif
+constexpr int BW_STAGES = ASB_BW_STAGES;   // bulk-copy pipeline depth of the backward (a batch takes long enough to hide one copy)
 #ifndef ASB_BW_UNROLL
 #define ASB_BW_UNROLL 2
 #endif

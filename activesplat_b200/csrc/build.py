@@ -11,6 +11,28 @@ FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std
          "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
 
 
+def build_variant(out, extra_flags, only=None):
+    """Developer tool: a second copy of the library with extra nvcc flags (e.g. -DASB_BW_STAGES=1), objects kept in
+    a directory of their own; ASB_LIB_PATH points activesplat_b200.capi at it for an A/B measurement."""
+    objdir = out + ".obj"
+    os.makedirs(objdir, exist_ok=True)
+    procs, objs = [], []
+    for s in SOURCES:
+        o = os.path.join(objdir, s[:-3] + ".o")
+        objs.append(o)
+        flags = [f for f in FLAGS if f != "--use_fast_math=false"] + (list(extra_flags) if (only is None or s in only) else [])
+        procs.append((s, subprocess.Popen([NVCC, *flags, "-c", os.path.join(HERE, s), "-o", o], stdout=subprocess.PIPE,
+                                          stderr=subprocess.STDOUT, text=True)))
+    for s, p in procs:
+        out_txt, _ = p.communicate()
+        if p.returncode != 0:
+            raise RuntimeError("nvcc failed on %s:\n%s" % (s, out_txt))
+    r = subprocess.run([NVCC, "-shared", "-o", out, *objs, "-lcudart"], capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("link failed:\n" + r.stdout + r.stderr)
+    return out
+
+
 def build(force=False, verbose=False):
     srcs = [os.path.join(HERE, s) for s in SOURCES if os.path.exists(os.path.join(HERE, s))]
     deps = srcs + [os.path.join(HERE, "common.cuh"), os.path.join(HERE, "raster_math.cuh"),

@@ -433,7 +433,7 @@ int as_mapping_loss(int width, int height, const float* color6, const float* gt_
     if (width <= 0 || height <= 0 || !color6 || !gt_rgb || !gt_depth || !dL_dcolor6 || !losses || !scratch)
         return AS_ERR_INVALID_ARG;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
-    StageScope _s(AS_STAGE_LOSS, st, 3);
+    StageScope _s(AS_STAGE_LOSS, st, 2);
     launch_mapping_loss(width, height, color6, gt_rgb, gt_depth, w_im, w_depth, dL_dcolor6, losses, scratch,
                         frame_status, st);
     return check(cudaGetLastError());
@@ -465,7 +465,7 @@ int as_adam_step_counted(int P, int isotropic, float* means3D, float* rgb_colors
         return AS_ERR_INVALID_ARG;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
     float* params[5] = {means3D, rgb_colors, unnorm_rotations, logit_opacities, log_scales};
-    StageScope _s(AS_STAGE_ADAM, st, 2);
+    StageScope _s(AS_STAGE_ADAM, st, 1);
     launch_adam_counted(P, isotropic, params, lrs, grad_params, exp_avg, exp_avg_sq, beta1, beta2, eps, step_state, st);
     return check(cudaGetLastError());
 }

@@ -1007,99 +1007,122 @@ __global__ void tracking_loss_finalize_kernel(int nblocks, const float* __restri
 // ------------------------------------------------------------------------------------------------
 struct AdamPtrs {   // plain members (no arrays): indexing a kernel-parameter array at run time would spill it to local memory
     float *p0, *p1, *p2, *p3, *p4;
-    float s0, s1, s2, s3, s4;   // lr[t] / bias_correction1
+    float s0, s1, s2, s3, s4;   // lr[t] / bias_correction1 (plain lr[t] when the kernel is given a step_state)
 };
 
-constexpr int AD_G = 256;  // Gaussians per block
+constexpr int AD_G = 128;  // Gaussians per block = threads per block
 
-// One block updates AD_G Gaussians.  Their slices of the five parameter tensors are contiguous, so they are staged
-// through shared memory with coalesced accesses; the flat [P,14] gradient / exp_avg / exp_avg_sq rows of the block
-// are one contiguous span that the threads walk four elements at a time (128-bit accesses when aligned).
+// One block updates AD_G Gaussians, one thread per Gaussian.  The block's slices of the five parameter tensors and
+// its rows of the flat [P,14] gradient / exp_avg / exp_avg_sq are contiguous spans: they are staged through shared
+// memory with coalesced (128-bit where aligned) accesses, so that each thread can walk the 14 slots of its Gaussian with
+// compile-time slot -> (tensor, learning rate) mapping -- no per-element index arithmetic (the first version spent
+// 135 instructions per 32 elements on it and ran at half of the memory rate).
 // Arithmetic per element as torch.optim.Adam (single-tensor path): lerp_, mul_/addcmul_, sqrt / bias_correction2_sqrt
 // + eps, addcdiv_.
-// sched (optional, device memory): [1..5] = lr[t] / bias_correction1, [6] = sqrt(bias_correction2), written by
-// adam_advance_kernel; when given it replaces ap.s* and bc2_sqrt (the step count then lives on the device, so the
-// launch is identical every step and can sit in a CUDA graph).
-__global__ void __launch_bounds__(256)
-adam_kernel(int P, int iso, AdamPtrs ap, const float* __restrict__ grad, float* __restrict__ m, float* __restrict__ v,
-            float beta1, float beta2, float eps, float bc2_sqrt, const float* __restrict__ sched) {
-    __shared__ __align__(16) float s_p[AD_G * 14];  // means [G,3] | rgb [G,3] | rot [G,4] | logit [G] | scales [G,3 or 1]
-    if (sched) {
-        ap.s0 = __ldg(sched + 1); ap.s1 = __ldg(sched + 2); ap.s2 = __ldg(sched + 3); ap.s3 = __ldg(sched + 4);
-        ap.s4 = __ldg(sched + 5);
-        bc2_sqrt = __ldg(sched + 6);
+// step_state (optional, device memory): [0] = steps taken so far, [7] = block ticket.  When given, every block derives
+// the bias corrections of step [0]+1 itself (in double, as torch does on the host) and the last block to finish
+// advances [0]: the launch is identical every step, so it can sit in a CUDA graph.  ap.s* are then plain learning rates.
+__device__ __forceinline__ void adam_one(float g, float& m, float& v, float& p, float step_size, float beta1, float beta2,
+                                         float eps, float bc2_sqrt) {
+    m = m + (g - m) * (1.f - beta1);          // exp_avg.lerp_(grad, 1 - beta1)
+    v = v * beta2 + (1.f - beta2) * g * g;    // mul_(beta2).addcmul_(g, g, 1 - beta2)
+    // sqrt is correctly rounded; the two quotients use the 2-ulp fast division (parity bar on the updated
+    // parameters is 1e-5 relative; the IEEE division sequences tripled the kernel's instruction count)
+    const float denom = __fdividef(__fsqrt_rn(v), bc2_sqrt) + eps;
+    p = p - step_size * __fdividef(m, denom);  // addcdiv_(exp_avg, denom, -step_size)
+}
+
+__device__ __forceinline__ void adam_stage_in(float* dst, const float* __restrict__ src, int n, bool vec) {
+    if (vec) {
+        for (int i = 4 * threadIdx.x; i < n; i += 4 * AD_G)
+            *reinterpret_cast<float4*>(dst + i) = __ldg(reinterpret_cast<const float4*>(src + i));
+    } else {
+        for (int i = threadIdx.x; i < n; i += AD_G) dst[i] = src[i];
     }
+}
+
+__device__ __forceinline__ void adam_stage_out(float* __restrict__ dst, const float* src, int n, bool vec) {
+    if (vec) {
+        for (int i = 4 * threadIdx.x; i < n; i += 4 * AD_G)
+            *reinterpret_cast<float4*>(dst + i) = *reinterpret_cast<const float4*>(src + i);
+    } else {
+        for (int i = threadIdx.x; i < n; i += AD_G) dst[i] = src[i];
+    }
+}
+
+__global__ void __launch_bounds__(AD_G)
+adam_kernel(int P, int iso, AdamPtrs ap, const float* __restrict__ grad, float* __restrict__ m, float* __restrict__ v,
+            float beta1, float beta2, float eps, float bc2_sqrt, float* __restrict__ step_state) {
+    __shared__ __align__(16) float s_p[AD_G * 14];  // means [G,3] | rgb [G,3] | rot [G,4] | logit [G] | scales [G,3 or 1]
+    __shared__ __align__(16) float s_g[AD_G * 14], s_m[AD_G * 14], s_v[AD_G * 14];
+    __shared__ float s_sched[2];
     const int g0 = blockIdx.x * AD_G;
     const int G = min(AD_G, P - g0);
     const int ws = iso ? 1 : 3;
-    const int off1 = 3 * AD_G, off2 = 6 * AD_G, off3 = 10 * AD_G, off4 = 11 * AD_G;
-    // stage the parameters (scalar loads are already coalesced: consecutive threads, consecutive floats)
-    for (int i = threadIdx.x; i < 3 * G; i += 256) {
-        s_p[i] = ap.p0[3 * (size_t)g0 + i];
-        s_p[off1 + i] = ap.p1[3 * (size_t)g0 + i];
+    constexpr int off1 = 3 * AD_G, off2 = 6 * AD_G, off3 = 10 * AD_G, off4 = 11 * AD_G;
+    if (step_state && threadIdx.x == 0) {
+        const double step = (double)*reinterpret_cast<volatile float*>(step_state) + 1.0;
+        s_sched[0] = (float)(1.0 - pow((double)beta1, step));           // bias_correction1
+        s_sched[1] = (float)sqrt(1.0 - pow((double)beta2, step));       // sqrt(bias_correction2)
     }
-    for (int i = threadIdx.x; i < 4 * G; i += 256) s_p[off2 + i] = ap.p2[4 * (size_t)g0 + i];
-    for (int i = threadIdx.x; i < G; i += 256) s_p[off3 + i] = ap.p3[(size_t)g0 + i];
-    for (int i = threadIdx.x; i < ws * G; i += 256) s_p[off4 + i] = ap.p4[ws * (size_t)g0 + i];
-    __syncthreads();
     const size_t fbase = 14 * (size_t)g0;
     const int nflat = 14 * G;
-    const bool vec = ((reinterpret_cast<uintptr_t>(grad + fbase) | reinterpret_cast<uintptr_t>(m + fbase) |
-                       reinterpret_cast<uintptr_t>(v + fbase)) & 15) == 0;
-    for (int e0 = 4 * threadIdx.x; e0 < nflat; e0 += 4 * 256) {
-        float g[4], mm[4], vv[4];
-        const int cnt = min(4, nflat - e0);
-        if (vec && cnt == 4) {
-            const float4 g4 = __ldg(reinterpret_cast<const float4*>(grad + fbase + e0));
-            const float4 m4 = *reinterpret_cast<const float4*>(m + fbase + e0);
-            const float4 v4 = *reinterpret_cast<const float4*>(v + fbase + e0);
-            g[0] = g4.x; g[1] = g4.y; g[2] = g4.z; g[3] = g4.w;
-            mm[0] = m4.x; mm[1] = m4.y; mm[2] = m4.z; mm[3] = m4.w;
-            vv[0] = v4.x; vv[1] = v4.y; vv[2] = v4.z; vv[3] = v4.w;
+    const bool full = G == AD_G;
+    auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+    const bool vec = full && al16(grad + fbase) && al16(m + fbase) && al16(v + fbase);
+    adam_stage_in(s_g, grad + fbase, nflat, vec);
+    adam_stage_in(s_m, m + fbase, nflat, vec);
+    adam_stage_in(s_v, v + fbase, nflat, vec);
+    adam_stage_in(s_p, ap.p0 + 3 * (size_t)g0, 3 * G, full && al16(ap.p0 + 3 * (size_t)g0));
+    adam_stage_in(s_p + off1, ap.p1 + 3 * (size_t)g0, 3 * G, full && al16(ap.p1 + 3 * (size_t)g0));
+    adam_stage_in(s_p + off2, ap.p2 + 4 * (size_t)g0, 4 * G, full && al16(ap.p2 + 4 * (size_t)g0));
+    adam_stage_in(s_p + off3, ap.p3 + (size_t)g0, G, full && al16(ap.p3 + (size_t)g0));
+    adam_stage_in(s_p + off4, ap.p4 + ws * (size_t)g0, ws * G, full && al16(ap.p4 + ws * (size_t)g0));
+    __syncthreads();
+    float s0 = ap.s0, s1 = ap.s1, s2 = ap.s2, s3 = ap.s3, s4 = ap.s4;
+    if (step_state) {
+        const float bc1 = s_sched[0];
+        s0 = s0 / bc1; s1 = s1 / bc1; s2 = s2 / bc1; s3 = s3 / bc1; s4 = s4 / bc1;   // lr / bias_correction1
+        bc2_sqrt = s_sched[1];
+    }
+    const int t = threadIdx.x;
+    if (t < G) {
+        const int r = 14 * t;
+#pragma unroll
+        for (int k = 0; k < 3; k++) adam_one(s_g[r + k], s_m[r + k], s_v[r + k], s_p[3 * t + k], s0, beta1, beta2, eps, bc2_sqrt);
+#pragma unroll
+        for (int k = 0; k < 3; k++)
+            adam_one(s_g[r + 3 + k], s_m[r + 3 + k], s_v[r + 3 + k], s_p[off1 + 3 * t + k], s1, beta1, beta2, eps, bc2_sqrt);
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            adam_one(s_g[r + 6 + k], s_m[r + 6 + k], s_v[r + 6 + k], s_p[off2 + 4 * t + k], s2, beta1, beta2, eps, bc2_sqrt);
+        adam_one(s_g[r + 10], s_m[r + 10], s_v[r + 10], s_p[off3 + t], s3, beta1, beta2, eps, bc2_sqrt);
+        if (iso) {   // one log-scale per Gaussian: flat slots 12, 13 are unused and stay as they are
+            adam_one(s_g[r + 11], s_m[r + 11], s_v[r + 11], s_p[off4 + t], s4, beta1, beta2, eps, bc2_sqrt);
         } else {
 #pragma unroll
-            for (int i = 0; i < 4; i++)
-                if (i < cnt) { g[i] = grad[fbase + e0 + i]; mm[i] = m[fbase + e0 + i]; vv[i] = v[fbase + e0 + i]; }
-        }
-#pragma unroll
-        for (int i = 0; i < 4; i++) {
-            if (i >= cnt) break;
-            const int e = e0 + i;
-            const int il = e / 14, slot = e - il * 14;
-            // slot -> (tensor, component): means 0-2 | rgb 3-5 | rotation 6-9 | logit opacity 10 | log scales 11-13
-            int pos;
-            float step_size;
-            if (slot < 3) { pos = 3 * il + slot; step_size = ap.s0; }
-            else if (slot < 6) { pos = off1 + 3 * il + slot - 3; step_size = ap.s1; }
-            else if (slot < 10) { pos = off2 + 4 * il + slot - 6; step_size = ap.s2; }
-            else if (slot < 11) { pos = off3 + il; step_size = ap.s3; }
-            else { pos = off4 + ws * il + slot - 11; step_size = ap.s4; if (slot - 11 >= ws) continue; }  // isotropic: 12, 13 unused
-            const float nm = mm[i] + (g[i] - mm[i]) * (1.f - beta1);      // exp_avg.lerp_(grad, 1 - beta1)
-            const float nv = vv[i] * beta2 + (1.f - beta2) * g[i] * g[i];  // mul_(beta2).addcmul_(g, g, 1 - beta2)
-            mm[i] = nm;
-            vv[i] = nv;
-            // sqrt is correctly rounded; the two quotients use the 2-ulp fast division (parity bar on the updated
-            // parameters is 1e-5 relative; the IEEE division sequences tripled the kernel's instruction count)
-            const float denom = __fdividef(__fsqrt_rn(nv), bc2_sqrt) + eps;
-            s_p[pos] = s_p[pos] - step_size * __fdividef(nm, denom);      // addcdiv_(exp_avg, denom, -step_size)
-        }
-        if (vec && cnt == 4) {
-            *reinterpret_cast<float4*>(m + fbase + e0) = make_float4(mm[0], mm[1], mm[2], mm[3]);
-            *reinterpret_cast<float4*>(v + fbase + e0) = make_float4(vv[0], vv[1], vv[2], vv[3]);
-        } else {
-#pragma unroll
-            for (int i = 0; i < 4; i++)
-                if (i < cnt) { m[fbase + e0 + i] = mm[i]; v[fbase + e0 + i] = vv[i]; }
+            for (int k = 0; k < 3; k++)
+                adam_one(s_g[r + 11 + k], s_m[r + 11 + k], s_v[r + 11 + k], s_p[off4 + 3 * t + k], s4, beta1, beta2, eps,
+                         bc2_sqrt);
         }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < 3 * G; i += 256) {
-        ap.p0[3 * (size_t)g0 + i] = s_p[i];
-        ap.p1[3 * (size_t)g0 + i] = s_p[off1 + i];
+    adam_stage_out(m + fbase, s_m, nflat, vec);
+    adam_stage_out(v + fbase, s_v, nflat, vec);
+    adam_stage_out(ap.p0 + 3 * (size_t)g0, s_p, 3 * G, full && al16(ap.p0 + 3 * (size_t)g0));
+    adam_stage_out(ap.p1 + 3 * (size_t)g0, s_p + off1, 3 * G, full && al16(ap.p1 + 3 * (size_t)g0));
+    adam_stage_out(ap.p2 + 4 * (size_t)g0, s_p + off2, 4 * G, full && al16(ap.p2 + 4 * (size_t)g0));
+    adam_stage_out(ap.p3 + (size_t)g0, s_p + off3, G, full && al16(ap.p3 + (size_t)g0));
+    adam_stage_out(ap.p4 + ws * (size_t)g0, s_p + off4, ws * G, full && al16(ap.p4 + ws * (size_t)g0));
+    if (step_state && threadIdx.x == 0) {
+        // every block read the step count before taking its ticket; the last ticket advances it for the next launch
+        __threadfence();
+        int* ticket = reinterpret_cast<int*>(step_state + 7);
+        if (atomicAdd(ticket, 1) == (int)gridDim.x - 1) {
+            step_state[0] = *reinterpret_cast<volatile float*>(step_state) + 1.f;
+            *ticket = 0;
+        }
     }
-    for (int i = threadIdx.x; i < 4 * G; i += 256) ap.p2[4 * (size_t)g0 + i] = s_p[off2 + i];
-    for (int i = threadIdx.x; i < G; i += 256) ap.p3[(size_t)g0 + i] = s_p[off3 + i];
-    for (int i = threadIdx.x; i < ws * G; i += 256) ap.p4[ws * (size_t)g0 + i] = s_p[off4 + i];
 }
 
 // ---- Adam fused with the gradient exchange over peer memory (NVLink / NVSwitch) ------------------------------
@@ -1303,7 +1326,7 @@ void launch_adam(int P, int iso, float* const params[5], const float lr[5], cons
     ap.p0 = params[0]; ap.p1 = params[1]; ap.p2 = params[2]; ap.p3 = params[3]; ap.p4 = params[4];
     ap.s0 = (float)(lr[0] / bc1); ap.s1 = (float)(lr[1] / bc1); ap.s2 = (float)(lr[2] / bc1);
     ap.s3 = (float)(lr[3] / bc1); ap.s4 = (float)(lr[4] / bc1);
-    adam_kernel<<<(P + AD_G - 1) / AD_G, 256, 0, st>>>(P, iso, ap, grad, m, v, beta1, beta2, eps, bc2_sqrt, nullptr);
+    adam_kernel<<<(P + AD_G - 1) / AD_G, AD_G, 0, st>>>(P, iso, ap, grad, m, v, beta1, beta2, eps, bc2_sqrt, nullptr);
 }
 
 // One thread: step += 1 (kept as a float-encoded integer in state[0]; exact up to 2^24 steps), then the step sizes and
@@ -1349,12 +1372,14 @@ void launch_pose_adam(float* rots, const float* g_rots, int n_rots, float lr_rot
 
 void launch_adam_counted(int P, int iso, float* const params[5], const float lr[5], const float* grad, float* m,
                          float* v, float beta1, float beta2, float eps, float* step_state, cudaStream_t st) {
-    adam_advance_kernel<<<1, 1, 0, st>>>(step_state, lr[0], lr[1], lr[2], lr[3], lr[4], beta1, beta2);
-    if (P <= 0) return;
+    if (P <= 0) {   // nothing to update: the step still counts
+        adam_advance_kernel<<<1, 1, 0, st>>>(step_state, lr[0], lr[1], lr[2], lr[3], lr[4], beta1, beta2);
+        return;
+    }
     AdamPtrs ap;
     ap.p0 = params[0]; ap.p1 = params[1]; ap.p2 = params[2]; ap.p3 = params[3]; ap.p4 = params[4];
-    ap.s0 = ap.s1 = ap.s2 = ap.s3 = ap.s4 = 0.f;
-    adam_kernel<<<(P + AD_G - 1) / AD_G, 256, 0, st>>>(P, iso, ap, grad, m, v, beta1, beta2, eps, 1.f, step_state);
+    ap.s0 = lr[0]; ap.s1 = lr[1]; ap.s2 = lr[2]; ap.s3 = lr[3]; ap.s4 = lr[4];
+    adam_kernel<<<(P + AD_G - 1) / AD_G, AD_G, 0, st>>>(P, iso, ap, grad, m, v, beta1, beta2, eps, 1.f, step_state);
 }
 
 }  // namespace asb

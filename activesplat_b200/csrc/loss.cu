@@ -20,10 +20,13 @@ namespace asb {
 
 namespace {
 
-constexpr int ST = 16;            // output tile edge
+constexpr int TW = 32, TH = 16;   // output tile (columns x rows) of one block
 constexpr int HALO = 5;           // window_size // 2
-constexpr int SW = ST + 2 * HALO; // 26
-constexpr int SSIM_THREADS = ST * ST;
+constexpr int SWW = TW + 2 * HALO;  // 42 staged columns
+constexpr int SWP = 44;             // padded row stride of the staged halo (rows start 16-byte aligned)
+constexpr int SHH = TH + 2 * HALO;  // 26 staged rows
+constexpr int SSIM_THREADS = 128;
+constexpr int SEG = 4;              // outputs per thread along the filter direction (sliding window kept in registers)
 constexpr float SSIM_C1 = 0.0001f;  // 0.01^2
 constexpr float SSIM_C2 = 0.0009f;  // 0.03^2
 
@@ -33,83 +36,123 @@ struct Window {
 
 __device__ __forceinline__ float sgnf(float x) { return (x > 0.f) ? 1.f : ((x < 0.f) ? -1.f : 0.f); }
 
-// Loads a (ST+10)^2 window of `img` (one channel, zero outside the image) into smem.
+// Loads the (TH+10) x (TW+10) neighbourhood of a tile of `img` (one channel, zero outside the image) into smem
+// (row stride SWP; the pad columns are zeroed so that 128-bit reads past column 41 see zeros).
 __device__ __forceinline__ void load_halo(const float* __restrict__ img, int W, int H, int x0, int y0, float* sm) {
-    for (int i = threadIdx.x; i < SW * SW; i += SSIM_THREADS) {
-        const int ly = i / SW, lx = i % SW;
+    for (int i = threadIdx.x; i < SHH * SWP; i += SSIM_THREADS) {
+        const int ly = i / SWP, lx = i - ly * SWP;
         const int x = x0 + lx - HALO, y = y0 + ly - HALO;
-        sm[i] = (x >= 0 && x < W && y >= 0 && y < H) ? __ldg(img + (size_t)y * W + x) : 0.f;
+        sm[i] = (lx < SWW && x >= 0 && x < W && y >= 0 && y < H) ? __ldg(img + (size_t)y * W + x) : 0.f;
     }
 }
 
-// stats: per channel window averages -> SSIM and derivative maps.  partials[block][8]:
+// 14 consecutive values of a staged row starting at a 16-byte aligned column (4 x LDS.128; the last two are unused)
+__device__ __forceinline__ void load_run(const float* row, float (&v)[16]) {
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        const float4 t = *reinterpret_cast<const float4*>(row + 4 * q);
+        v[4 * q] = t.x; v[4 * q + 1] = t.y; v[4 * q + 2] = t.z; v[4 * q + 3] = t.w;
+    }
+}
+
+// SEG outputs of the 11-tap window over a run of SEG + 10 inputs, taps accumulated in ascending order (the order the
+// first version of these kernels used, so the results are unchanged bit for bit)
+__device__ __forceinline__ void window_run(const float (&v)[16], const Window& win, float (&out)[SEG]) {
+#pragma unroll
+    for (int o = 0; o < SEG; o++) {
+        float a = 0.f;
+#pragma unroll
+        for (int k = 0; k < 11; k++) a = fmaf(win.g[k], v[o + k], a);
+        out[o] = a;
+    }
+}
+
+// stats: per channel window averages -> SSIM and derivative maps.  partials[block][4]:
 // 0 sum|im-gt|, 1 sum SSIM, 2 sum_mask|gt_d-depth|, 3 mask count.
+// Separable window with register-resident sliding runs: a thread filters SEG = 4 neighbouring outputs from one run of
+// 14 inputs (horizontal pass: 4 x 128-bit shared loads per input map instead of 44 scalar ones; vertical pass: 14
+// conflict-free column reads per map for 4 output rows).
 __global__ void __launch_bounds__(SSIM_THREADS)
 mapping_loss_stats_kernel(int W, int H, const float* __restrict__ c6, const float* __restrict__ gt_rgb,
                           const float* __restrict__ gt_depth, Window win, float* __restrict__ dmaps,
                           float* __restrict__ partials) {
-    __shared__ float sx[SW * SW], sy[SW * SW];
-    __shared__ float sh[5][SW * ST];  // horizontally filtered: x, y, xx, yy, xy  (26 rows x 16 cols)
-    __shared__ float s_red[4 * 8];
-    const int x0 = blockIdx.x * ST, y0 = blockIdx.y * ST;
-    const int lx = threadIdx.x % ST, ly = threadIdx.x / ST;
-    const int px = x0 + lx, py = y0 + ly;
-    const bool inside = px < W && py < H;
+    __shared__ __align__(16) float sx[SHH * SWP], sy[SHH * SWP];
+    __shared__ __align__(16) float sh[5][SHH * TW];  // horizontally filtered: x, y, xx, yy, xy  (26 rows x 32 cols)
+    __shared__ float s_red[4 * (SSIM_THREADS / 32)];
+    const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TH;
     const size_t N = (size_t)W * H;
+    // vertical-pass ownership: column vc, rows vr0 .. vr0+3
+    const int vc = threadIdx.x % TW, vr0 = (threadIdx.x / TW) * SEG;
+    const int px = x0 + vc;
     float s_l1 = 0.f, s_ssim = 0.f, s_d = 0.f, s_cnt = 0.f;
     for (int ch = 0; ch < 3; ch++) {
         __syncthreads();
         load_halo(c6 + ch * N, W, H, x0, y0, sx);
         load_halo(gt_rgb + ch * N, W, H, x0, y0, sy);
         __syncthreads();
-        for (int i = threadIdx.x; i < SW * ST; i += SSIM_THREADS) {
-            const int r = i / ST, c = i % ST;
-            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
+        for (int it = threadIdx.x; it < SHH * (TW / SEG); it += SSIM_THREADS) {
+            const int r = it / (TW / SEG), c = (it - r * (TW / SEG)) * SEG;
+            float x[16], y[16], p[16], o[SEG];
+            load_run(sx + r * SWP + c, x);
+            load_run(sy + r * SWP + c, y);
+            window_run(x, win, o);
+            *reinterpret_cast<float4*>(&sh[0][r * TW + c]) = make_float4(o[0], o[1], o[2], o[3]);
+            window_run(y, win, o);
+            *reinterpret_cast<float4*>(&sh[1][r * TW + c]) = make_float4(o[0], o[1], o[2], o[3]);
 #pragma unroll
-            for (int k = 0; k < 11; k++) {
-                const float x = sx[r * SW + c + k], y = sy[r * SW + c + k], g = win.g[k];
-                a0 = fmaf(g, x, a0);
-                a1 = fmaf(g, y, a1);
-                a2 = fmaf(g, x * x, a2);
-                a3 = fmaf(g, y * y, a3);
-                a4 = fmaf(g, x * y, a4);
-            }
-            sh[0][i] = a0; sh[1][i] = a1; sh[2][i] = a2; sh[3][i] = a3; sh[4][i] = a4;
+            for (int i = 0; i < 14; i++) p[i] = x[i] * x[i];
+            window_run(p, win, o);
+            *reinterpret_cast<float4*>(&sh[2][r * TW + c]) = make_float4(o[0], o[1], o[2], o[3]);
+#pragma unroll
+            for (int i = 0; i < 14; i++) p[i] = y[i] * y[i];
+            window_run(p, win, o);
+            *reinterpret_cast<float4*>(&sh[3][r * TW + c]) = make_float4(o[0], o[1], o[2], o[3]);
+#pragma unroll
+            for (int i = 0; i < 14; i++) p[i] = x[i] * y[i];
+            window_run(p, win, o);
+            *reinterpret_cast<float4*>(&sh[4][r * TW + c]) = make_float4(o[0], o[1], o[2], o[3]);
         }
         __syncthreads();
-        float mu1 = 0.f, mu2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+        float f[5][SEG];
 #pragma unroll
-        for (int k = 0; k < 11; k++) {
-            const int i = (ly + k) * ST + lx;
-            const float g = win.g[k];
-            mu1 = fmaf(g, sh[0][i], mu1);
-            mu2 = fmaf(g, sh[1][i], mu2);
-            e11 = fmaf(g, sh[2][i], e11);
-            e22 = fmaf(g, sh[3][i], e22);
-            e12 = fmaf(g, sh[4][i], e12);
+        for (int q = 0; q < 5; q++) {
+            float v[16];
+#pragma unroll
+            for (int i = 0; i < 14; i++) v[i] = sh[q][(vr0 + i) * TW + vc];
+            window_run(v, win, f[q]);
         }
-        if (inside) {
-            const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
-            const float sig1 = e11 - mu1_sq, sig2 = e22 - mu2_sq, sig12 = e12 - mu12;
-            const float A1 = 2.f * mu12 + SSIM_C1, A2 = 2.f * sig12 + SSIM_C2;
-            const float B1 = mu1_sq + mu2_sq + SSIM_C1, B2 = sig1 + sig2 + SSIM_C2;
-            const float inv = 1.f / (B1 * B2);
-            const float S = A1 * A2 * inv;
-            s_ssim += S;
-            const size_t o = ch * N + (size_t)py * W + px;
-            dmaps[o] = (2.f * mu2 * (A2 - A1)) * inv - S * (2.f * mu1 / B1 - 2.f * mu1 / B2);  // dS/dmu1
-            dmaps[3 * N + o] = -S / B2;                                                          // dS/dE[x^2]
-            dmaps[6 * N + o] = 2.f * A1 * inv;                                                   // dS/dE[xy]
-            s_l1 += fabsf(sx[(ly + HALO) * SW + lx + HALO] - sy[(ly + HALO) * SW + lx + HALO]);
+#pragma unroll
+        for (int o = 0; o < SEG; o++) {
+            const int py = y0 + vr0 + o;
+            if (px < W && py < H) {
+                const float mu1 = f[0][o], mu2 = f[1][o], e11 = f[2][o], e22 = f[3][o], e12 = f[4][o];
+                const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
+                const float sig1 = e11 - mu1_sq, sig2 = e22 - mu2_sq, sig12 = e12 - mu12;
+                const float A1 = 2.f * mu12 + SSIM_C1, A2 = 2.f * sig12 + SSIM_C2;
+                const float B1 = mu1_sq + mu2_sq + SSIM_C1, B2 = sig1 + sig2 + SSIM_C2;
+                const float inv = 1.f / (B1 * B2);
+                const float S = A1 * A2 * inv;
+                s_ssim += S;
+                const size_t off = ch * N + (size_t)py * W + px;
+                dmaps[off] = (2.f * mu2 * (A2 - A1)) * inv - S * (2.f * mu1 / B1 - 2.f * mu1 / B2);  // dS/dmu1
+                dmaps[3 * N + off] = -S / B2;                                                          // dS/dE[x^2]
+                dmaps[6 * N + off] = 2.f * A1 * inv;                                                   // dS/dE[xy]
+                const int ci = (vr0 + o + HALO) * SWP + vc + HALO;
+                s_l1 += fabsf(sx[ci] - sy[ci]);
+            }
         }
     }
-    if (inside) {
-        const size_t p = (size_t)py * W + px;
-        const float depth = c6[3 * N + p], dsq = c6[5 * N + p], gd = gt_depth[p];
-        const float invis = dsq - depth * depth;
-        if ((gd > 0.f) && !isnan(depth) && !isnan(invis)) {
-            s_d = fabsf(gd - depth);
-            s_cnt = 1.f;
+#pragma unroll
+    for (int o = 0; o < SEG; o++) {
+        const int py = y0 + vr0 + o;
+        if (px < W && py < H) {
+            const size_t p = (size_t)py * W + px;
+            const float depth = c6[3 * N + p], dsq = c6[5 * N + p], gd = gt_depth[p];
+            const float invis = dsq - depth * depth;
+            if ((gd > 0.f) && !isnan(depth) && !isnan(invis)) {
+                s_d += fabsf(gd - depth);
+                s_cnt += 1.f;
+            }
         }
     }
     float v[4] = {s_l1, s_ssim, s_d, s_cnt};
@@ -119,38 +162,51 @@ mapping_loss_stats_kernel(int W, int H, const float* __restrict__ c6, const floa
         float x = v[k];
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
-        if (lane == 0) s_red[k * 8 + warp] = x;
+        if (lane == 0) s_red[k * (SSIM_THREADS / 32) + warp] = x;
     }
     __syncthreads();
     if (threadIdx.x < 4) {
         float x = 0.f;
 #pragma unroll
-        for (int w = 0; w < SSIM_THREADS / 32; w++) x += s_red[threadIdx.x * 8 + w];
+        for (int w = 0; w < SSIM_THREADS / 32; w++) x += s_red[threadIdx.x * (SSIM_THREADS / 32) + w];
         partials[(size_t)(blockIdx.y * gridDim.x + blockIdx.x) * 4 + threadIdx.x] = x;
     }
 }
 
+// Totals of the per-block partial sums -> the loss record.  Every block of the gradient kernel calls this (it needs the
+// mask count for its own pixels; the partials are a few KB that stay in L2), block 0 writes the record -- a separate
+// one-warp finalize launch cost 9 us of serial latency.
 // losses[0] weighted total, [1] weighted im, [2] weighted depth, [3] mask count, [4] R, [5] overflow, [6] mean SSIM
-__global__ void mapping_loss_finalize_kernel(int nblocks, const float* __restrict__ partials, float n3, float w_im,
-                                             float w_depth, float* __restrict__ losses,
-                                             const uint32_t* __restrict__ status) {
-    __shared__ float s[4][32];
+__device__ __forceinline__ float mapping_loss_totals(int nblocks, const float* __restrict__ partials, float n3, float w_im,
+                                                     float w_depth, float* __restrict__ losses,
+                                                     const uint32_t* __restrict__ status, float* s_red /*[4 * warps]*/) {
     float v[4] = {0.f, 0.f, 0.f, 0.f};
-    for (int b = threadIdx.x; b < nblocks; b += 32)
-#pragma unroll
-        for (int k = 0; k < 4; k++) v[k] += partials[(size_t)b * 4 + k];
+    for (int b = threadIdx.x; b < nblocks; b += SSIM_THREADS) {
+        const float4 q = __ldg(reinterpret_cast<const float4*>(partials) + b);
+        v[0] += q.x; v[1] += q.y; v[2] += q.z; v[3] += q.w;
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
     for (int k = 0; k < 4; k++) {
         float x = v[k];
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
-        s[k][0] = x;
+        if (lane == 0) s_red[k * (SSIM_THREADS / 32) + warp] = x;
     }
-    if (threadIdx.x == 0) {
-        const float l1 = s[0][0] / n3, ssim = s[1][0] / n3;
-        const float cnt = s[3][0];
+    __syncthreads();
+    float tot[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        float x = 0.f;
+#pragma unroll
+        for (int w = 0; w < SSIM_THREADS / 32; w++) x += s_red[k * (SSIM_THREADS / 32) + w];
+        tot[k] = x;
+    }
+    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) {
+        const float l1 = tot[0] / n3, ssim = tot[1] / n3;
+        const float cnt = tot[3];
         const float li = w_im * (0.8f * l1 + 0.2f * (1.0f - ssim));
-        const float ld = w_depth * (s[2][0] / cnt);  // mean over an empty mask is NaN in torch as well
+        const float ld = w_depth * (tot[2] / cnt);  // mean over an empty mask is NaN in torch as well
         losses[0] = li + ld;
         losses[1] = li;
         losses[2] = ld;
@@ -164,18 +220,22 @@ __global__ void mapping_loss_finalize_kernel(int nblocks, const float* __restric
         }
         losses[6] = ssim;
     }
+    return tot[3];
 }
 
 __global__ void __launch_bounds__(SSIM_THREADS)
 mapping_loss_grad_kernel(int W, int H, const float* __restrict__ c6, const float* __restrict__ gt_rgb,
                          const float* __restrict__ gt_depth, const float* __restrict__ dmaps, Window win, float w_im,
-                         float w_depth, const float* __restrict__ losses, float* __restrict__ dL) {
-    __shared__ float sm[3][SW * SW];
-    __shared__ float sh[3][SW * ST];
-    const int x0 = blockIdx.x * ST, y0 = blockIdx.y * ST;
-    const int lx = threadIdx.x % ST, ly = threadIdx.x / ST;
-    const int px = x0 + lx, py = y0 + ly;
-    const bool inside = px < W && py < H;
+                         float w_depth, int nblocks, const float* __restrict__ partials, float* __restrict__ losses,
+                         const uint32_t* __restrict__ status, float* __restrict__ dL) {
+    __shared__ __align__(16) float sm[3][SHH * SWP];
+    __shared__ __align__(16) float sh[3][SHH * TW];
+    __shared__ float s_red[4 * (SSIM_THREADS / 32)];
+    const float mask_count = mapping_loss_totals(nblocks, partials, 3.f * (float)W * (float)H, w_im, w_depth, losses,
+                                                 status, s_red);
+    const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TH;
+    const int vc = threadIdx.x % TW, vr0 = (threadIdx.x / TW) * SEG;
+    const int px = x0 + vc;
     const size_t N = (size_t)W * H;
     const float n3 = 3.f * (float)N;
     for (int ch = 0; ch < 3; ch++) {
@@ -183,44 +243,49 @@ mapping_loss_grad_kernel(int W, int H, const float* __restrict__ c6, const float
 #pragma unroll
         for (int q = 0; q < 3; q++) load_halo(dmaps + (3 * q + ch) * N, W, H, x0, y0, sm[q]);
         __syncthreads();
-        for (int i = threadIdx.x; i < SW * ST; i += SSIM_THREADS) {
-            const int r = i / ST, c = i % ST;
-            float a0 = 0.f, a1 = 0.f, a2 = 0.f;
+        for (int it = threadIdx.x; it < SHH * (TW / SEG); it += SSIM_THREADS) {
+            const int r = it / (TW / SEG), c = (it - r * (TW / SEG)) * SEG;
 #pragma unroll
-            for (int k = 0; k < 11; k++) {
-                const float g = win.g[k];
-                a0 = fmaf(g, sm[0][r * SW + c + k], a0);
-                a1 = fmaf(g, sm[1][r * SW + c + k], a1);
-                a2 = fmaf(g, sm[2][r * SW + c + k], a2);
+            for (int q = 0; q < 3; q++) {
+                float v[16], o[SEG];
+                load_run(sm[q] + r * SWP + c, v);
+                window_run(v, win, o);
+                *reinterpret_cast<float4*>(&sh[q][r * TW + c]) = make_float4(o[0], o[1], o[2], o[3]);
             }
-            sh[0][i] = a0; sh[1][i] = a1; sh[2][i] = a2;
         }
         __syncthreads();
-        float c0 = 0.f, c1 = 0.f, c2 = 0.f;
+        float f[3][SEG];
 #pragma unroll
-        for (int k = 0; k < 11; k++) {
-            const int i = (ly + k) * ST + lx;
-            const float g = win.g[k];
-            c0 = fmaf(g, sh[0][i], c0);
-            c1 = fmaf(g, sh[1][i], c1);
-            c2 = fmaf(g, sh[2][i], c2);
+        for (int q = 0; q < 3; q++) {
+            float v[16];
+#pragma unroll
+            for (int i = 0; i < 14; i++) v[i] = sh[q][(vr0 + i) * TW + vc];
+            window_run(v, win, f[q]);
         }
-        if (inside) {
-            const size_t o = ch * N + (size_t)py * W + px;
-            const float x = c6[o], y = gt_rgb[o];
-            const float dssim = c0 + 2.f * x * c1 + y * c2;  // d(sum SSIM)/d im
-            dL[o] = w_im * (0.8f * sgnf(x - y) - 0.2f * dssim) / n3;
+#pragma unroll
+        for (int o = 0; o < SEG; o++) {
+            const int py = y0 + vr0 + o;
+            if (px < W && py < H) {
+                const size_t off = ch * N + (size_t)py * W + px;
+                const float x = c6[off], y = gt_rgb[off];
+                const float dssim = f[0][o] + 2.f * x * f[1][o] + y * f[2][o];  // d(sum SSIM)/d im
+                dL[off] = w_im * (0.8f * sgnf(x - y) - 0.2f * dssim) / n3;
+            }
         }
     }
-    if (inside) {
-        const size_t p = (size_t)py * W + px;
-        const float depth = c6[3 * N + p], dsq = c6[5 * N + p], gd = gt_depth[p];
-        const float invis = dsq - depth * depth;
-        float g = 0.f;
-        if ((gd > 0.f) && !isnan(depth) && !isnan(invis)) g = -w_depth * sgnf(gd - depth) / losses[3];
-        dL[3 * N + p] = g;
-        dL[4 * N + p] = 0.f;
-        dL[5 * N + p] = 0.f;
+#pragma unroll
+    for (int o = 0; o < SEG; o++) {
+        const int py = y0 + vr0 + o;
+        if (px < W && py < H) {
+            const size_t p = (size_t)py * W + px;
+            const float depth = c6[3 * N + p], dsq = c6[5 * N + p], gd = gt_depth[p];
+            const float invis = dsq - depth * depth;
+            float g = 0.f;
+            if ((gd > 0.f) && !isnan(depth) && !isnan(invis)) g = -w_depth * sgnf(gd - depth) / mask_count;
+            dL[3 * N + p] = g;
+            dL[4 * N + p] = 0.f;
+            dL[5 * N + p] = 0.f;
+        }
     }
 }
 
@@ -239,23 +304,21 @@ Window make_window() {
 }  // namespace
 
 size_t mapping_loss_scratch_floats(int W, int H) {
-    const size_t bx = (W + ST - 1) / ST, by = (H + ST - 1) / ST;
+    const size_t bx = (W + TW - 1) / TW, by = (H + TH - 1) / TH;
     return 9 * (size_t)W * H + bx * by * 4 + 16;
 }
 
 void launch_mapping_loss(int W, int H, const float* c6, const float* gt_rgb, const float* gt_depth, float w_im,
                          float w_depth, float* dL, float* losses, float* scratch, const uint32_t* status,
                          cudaStream_t st) {
-    const dim3 grid((W + ST - 1) / ST, (H + ST - 1) / ST);
+    const dim3 grid((W + TW - 1) / TW, (H + TH - 1) / TH);
     const int nblocks = grid.x * grid.y;
     float* dmaps = scratch;
-    float* partials = scratch + 9 * (size_t)W * H;
+    float* partials = scratch + ((9 * (size_t)W * H + 3) & ~(size_t)3);   // float4 reads in the gradient kernel
     const Window win = make_window();
     mapping_loss_stats_kernel<<<grid, SSIM_THREADS, 0, st>>>(W, H, c6, gt_rgb, gt_depth, win, dmaps, partials);
-    mapping_loss_finalize_kernel<<<1, 32, 0, st>>>(nblocks, partials, 3.f * (float)W * (float)H, w_im, w_depth, losses,
-                                                   status);
     mapping_loss_grad_kernel<<<grid, SSIM_THREADS, 0, st>>>(W, H, c6, gt_rgb, gt_depth, dmaps, win, w_im, w_depth,
-                                                           losses, dL);
+                                                           nblocks, partials, losses, status, dL);
 }
 
 }  // namespace asb

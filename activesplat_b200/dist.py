@@ -23,6 +23,21 @@ def shard_indices(n, rank, world):
     return list(range(rank, n, world))
 
 
+def deal_by_weight(weights, world):
+    """Deal independent units of known, unequal cost to `world` ranks: heaviest first, each to the rank with the
+    least work so far (longest-processing-time-first).  Deterministic, so every rank computes the same deal.
+    Returns one ascending index list per rank.  Keyframes and candidate views of one map differ several-fold in
+    Gaussian-tile instances; dealt round-robin, the step waits for whichever rank drew the heavy ones."""
+    order = sorted(range(len(weights)), key=lambda i: (-float(weights[i]), i))
+    loads = [0.0] * world
+    out = [[] for _ in range(world)]
+    for i in order:
+        r = min(range(world), key=lambda q: (loads[q], q))
+        out[r].append(i)
+        loads[r] += float(weights[i])
+    return [sorted(o) for o in out]
+
+
 def gather_scores(local_scores, n_total, rank, world, group=None):
     """local_scores: [n_local, C] for units shard_indices(n_total, rank, world), in that order.
     Returns the full [n_total, C] table on every rank (rows in unit order)."""
@@ -85,13 +100,15 @@ def allreduce_gradients(flat_grad, group=None):
     return flat_grad
 
 
-def mapping_step_keyframe_batch(frame_grad_fn, n_keyframes, flat_grad, optimizer_step, group=None):
+def mapping_step_keyframe_batch(frame_grad_fn, n_keyframes, flat_grad, optimizer_step, group=None, weights=None):
     """One mapping step over a keyframe batch split across ranks.
     frame_grad_fn(k, accumulate) must add keyframe k's gradient into `flat_grad` (overwriting when
     accumulate is False) and return its loss; optimizer_step(flat_grad) applies the update.
+    weights: per-keyframe cost (e.g. the Gaussian-tile instances of the previous step) for a balanced deal
+    (deal_by_weight); without it keyframes go round-robin.
     Equivalent single-GPU computation: accumulate all n_keyframes sequentially, then one step."""
     rank, world = world_info(group)
-    mine = shard_indices(n_keyframes, rank, world)
+    mine = shard_indices(n_keyframes, rank, world) if weights is None else deal_by_weight(weights, world)[rank]
     loss = None
     for j, k in enumerate(mine):
         l = frame_grad_fn(k, j > 0)

@@ -451,85 +451,104 @@ def cfg4(dev, RefRenderer, args, rank, world, params=None):
     return res
 
 
-def cfg5(dev, args, rank, world):
-    """MP3D-scale mapping: 3M Gaussians, 64-keyframe batch split over ranks.  The exchange + update step is timed two
-    ways: NCCL all-reduce of the flat gradient followed by the fused Adam on every rank, and the single kernel that
-    reduces over peer memory, updates the owned slab and writes it to every rank (dist.PeerShardedAdam)."""
+def cfg5(dev, args, rank, world, with_peer=True):
+    """MP3D-scale mapping: 3M Gaussians, 64-keyframe batch split over ranks (dist.mapping_step_keyframe_batch).  After a
+    first round-robin step the keyframes are dealt by their measured Gaussian-tile instance counts, so that no rank
+    waits for the one that drew the heavy views.  The exchange + update is timed two ways: NCCL all-reduce of the flat
+    gradient followed by the fused Adam on every rank, and the single kernel that reduces over peer memory, updates the
+    owned slab and writes it to every rank (dist.PeerShardedAdam)."""
     W, H, P, K = 640, 480, 3_000_000, 64
     params_cpu, cams = scenes.s_room(P, K, seed=5, W=W, H=H)
     rots, trans = scenes.camera_track(cams)
     cam = splatam.setup_camera(W, H, cams[0].k(), np.eye(4), device=dev)
-    mine = asd.shard_indices(K, rank, world)
-    gts = dict(zip(mine, gt_frames(params_cpu, [cams[k] for k in mine], dev, seed=15)))
+    gts = gt_frames(params_cpu, cams, dev, seed=15)      # every rank holds every keyframe's RGB-D frame (315 MB)
     eye = torch.eye(4, device=dev)
     out = {}
-    for kind in ("allreduce", "peer"):
+    for kind in (("allreduce", "peer") if with_peer else ("allreduce",)):
         p = {k: v.to(dev) for k, v in params_cpu.items()}
         p["cam_unnorm_rots"], p["cam_trans"] = rots.to(dev), trans.to(dev)
         ws = workspace_for(p, cam)
         opt = FusedAdam(p, MAP_LRS) if kind == "allreduce" else asd.PeerShardedAdam(p, MAP_LRS, ws.grad_params)
-        t_ex = []
+        inst = torch.zeros(K, dtype=torch.int32, device=dev)
+        ev = {}
 
         def frame_grad_fn(k, accumulate):
             with torch.no_grad():
                 ws.forward(p, cam, k, sil_w2c=eye)
                 ws.mapping_loss(gts[k][:3], gts[k][3:4], LW["im"], LW["depth"])
                 ws.backward(gaussians_grad=True, camera_grad=False, accumulate=accumulate)
+            inst[k] = ws.status[0]
+            ev["frames_done"] = torch.cuda.Event(enable_timing=True)
+            ev["frames_done"].record()
             return ws.losses[0].clone()
 
-        def step(_i):
-            e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        def optimizer_step(flat):
+            ev["reduced"] = torch.cuda.Event(enable_timing=True)
+            ev["reduced"].record()
+            opt.step(flat) if kind == "allreduce" else opt.step()
+            ev["updated"] = torch.cuda.Event(enable_timing=True)
+            ev["updated"].record()
+
+        def step(weights):
+            inst.zero_()
+            if kind == "allreduce":
+                return asd.mapping_step_keyframe_batch(frame_grad_fn, K, ws.grad_params, optimizer_step, weights=weights)
+            # the peer kernel does the exchange itself: same deal, no all-reduce
+            mine = asd.shard_indices(K, rank, world) if weights is None else asd.deal_by_weight(weights, world)[rank]
             loss = None
             for j, k in enumerate(mine):
                 l = frame_grad_fn(k, j > 0)
                 loss = l if loss is None else loss + l
-            e0.record()
-            if kind == "allreduce":
-                asd.allreduce_gradients(ws.grad_params)
-                e1.record()
-                opt.step(ws.grad_params)
-            else:
-                e1.record()
-                opt.step()
-            e2.record()
-            t_ex.append((e0, e1, e2))
+            optimizer_step(ws.grad_params)
             return loss
 
-        for i in range(2):
-            step(i)
-        torch.cuda.synchronize(dev)
-        if world > 1:
-            torch.distributed.barrier()
-        t_ex.clear()
-        n = 3
-        t0 = time.time()
-        for i in range(n):
-            step(i)
-        torch.cuda.synchronize(dev)
-        if world > 1:
-            torch.distributed.barrier()
-        dt = (time.time() - t0) / n
-        ex_ms = float(np.mean([a.elapsed_time(c) for a, _, c in t_ex]))
-        ar_ms = float(np.mean([a.elapsed_time(b) for a, b, _ in t_ex]))
-        if world > 1:
-            tt = torch.tensor([dt, ex_ms], device=dev)
-            torch.distributed.all_reduce(tt, op=torch.distributed.ReduceOp.MAX)
-            dt, ex_ms = float(tt[0]), float(tt[1])
+        def measured_weights():
+            if world > 1:
+                torch.distributed.all_reduce(inst)
+            return inst.cpu().tolist()
+
+        step(None)                       # round-robin: sizes the workspace and measures every keyframe's weight
+        weights = measured_weights()
+        step(weights)
+        res = {}
+        for tag, wts in (("round_robin", None), ("by_weight", weights)):
+            torch.cuda.synchronize(dev)
+            if world > 1:
+                torch.distributed.barrier()
+            n, t_ex, t_ar = 3, [], []
+            t0 = time.time()
+            for i in range(n):
+                step(wts)
+                t_ex.append((ev["frames_done"], ev["reduced"], ev["updated"]))
+            torch.cuda.synchronize(dev)
+            if world > 1:
+                torch.distributed.barrier()
+            dt = (time.time() - t0) / n
+            ex_ms = float(np.mean([a.elapsed_time(c) for a, _, c in t_ex]))
+            ar_ms = float(np.mean([a.elapsed_time(b) for a, b, _ in t_ex]))
+            if world > 1:
+                tt = torch.tensor([dt, ex_ms, ar_ms], device=dev)
+                torch.distributed.all_reduce(tt, op=torch.distributed.ReduceOp.MAX)
+                dt, ex_ms, ar_ms = float(tt[0]), float(tt[1]), float(tt[2])
+            mine = asd.shard_indices(K, rank, world) if wts is None else asd.deal_by_weight(wts, world)[rank]
+            res[tag] = {"s_per_step": dt, "mpix_s": K * W * H / dt / 1e6, "exchange_plus_adam_ms": ex_ms,
+                        "keyframes_this_rank": len(mine)}
+            if kind == "allreduce":
+                res[tag]["allreduce_ms_incl_wait_for_slowest_rank"] = ar_ms
         R, over = ws.last_status()
         assert not over
-        out[kind] = {"s_per_step": dt, "mpix_s": K * W * H / dt / 1e6, "exchange_plus_adam_ms": ex_ms,
-                     "keyframes_per_rank": len(mine)}
-        if kind == "allreduce":
-            out[kind]["allreduce_ms"] = ar_ms
-        chk = float(p["means3D"].double().sum())
-        out[kind]["means3D_checksum"] = chk
+        best = min(res.values(), key=lambda r: r["s_per_step"])
+        out[kind] = dict(best, deals=res, means3D_checksum=float(p["means3D"].double().sum()),
+                         instances_per_keyframe_min_max=[int(min(weights)), int(max(weights))])
         del opt, p
         from activesplat_b200 import frame as _fr
         _fr._WORKSPACES.clear()
-    return {"config": f"cfg5: S-room {P} Gaussians, {K}-keyframe batch over {world} GPU(s); exchange of the [P,14] fp32 "
-                      f"gradient ({P * 14 * 4 / 1e6:.0f} MB) + Adam per step, by NCCL all-reduce + fused Adam and by the "
-                      "peer-memory reduce+Adam kernel",
-            "ours": out["allreduce"], "allreduce_path": out["allreduce"], "peer_path": out["peer"]}
+        torch.cuda.empty_cache()
+    return {"config": f"cfg5: S-room {P} Gaussians, {K}-keyframe batch over {world} GPU(s) through "
+                      f"dist.mapping_step_keyframe_batch; exchange of the [P,14] fp32 gradient ({P * 14 * 4 / 1e6:.0f} MB) "
+                      "+ Adam per step inside the timed region, by NCCL all-reduce + fused Adam"
+                      + (" and by the peer-memory reduce+Adam kernel" if with_peer else ""),
+            "ours": out["allreduce"], **({"peer_path": out["peer"]} if with_peer else {})}
 
 
 def scoring(dev):

@@ -56,7 +56,10 @@ def summarize(path):
         for col, (key, scale) in METRICS.items():
             if col not in d or d[col] == "":
                 continue
-            v = float(d[col].replace(",", ""))
+            try:
+                v = float(d[col].replace(",", ""))
+            except ValueError:      # "no data" / "n/a" for a metric the kernel did not produce
+                continue
             unit = units[head.index(col)]
             if key in ("dram_read", "dram_write"):
                 v *= UNIT_SCALE.get(unit, 1.0)

@@ -27,7 +27,7 @@ def _views_worker(rank, world, port, n_views, q):
     dist.destroy_process_group()
 
 
-def _mapping_worker(rank, world, port, n_kf, q):
+def _mapping_worker(rank, world, port, n_kf, q, weights=None):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     from activesplat_b200 import dist as asd
@@ -47,7 +47,7 @@ def _mapping_worker(rank, world, port, n_kf, q):
     def opt_step(f):
         params.sub_(0.1 * f)
 
-    asd.mapping_step_keyframe_batch(frame_grad_fn, n_kf, flat, opt_step)
+    asd.mapping_step_keyframe_batch(frame_grad_fn, n_kf, flat, opt_step, weights=weights)
     q.put((rank, params.clone()))
     dist.barrier()
     dist.destroy_process_group()
@@ -57,7 +57,9 @@ def _spawn(fn, world, *args):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = 29500 + (os.getpid() % 2000)
-    procs = [ctx.Process(target=fn, args=(r, world, port) + args + (q,)) for r in range(world)]
+    kw = args[-1] if args and isinstance(args[-1], dict) else {}
+    args = args[:-1] if kw else args
+    procs = [ctx.Process(target=fn, args=(r, world, port) + args + (q,), kwargs=kw) for r in range(world)]
     for p in procs:
         p.start()
     out = [q.get(timeout=120) for _ in procs]
@@ -87,6 +89,26 @@ def test_keyframe_batch_mapping_allreduce_matches_sequential():
         total = sum(torch.randn(50, 14, generator=torch.Generator().manual_seed(77 + k)) for k in range(n_kf))
         for r in range(2):
             torch.testing.assert_close(res[r][1], -0.1 * total, rtol=1e-6, atol=1e-6)
+
+
+def test_weighted_deal_balances_and_gives_the_same_step():
+    """deal_by_weight: every unit exactly once, loads within the heaviest unit of each other, identical on every rank;
+    a keyframe batch dealt by weight yields the same update as the sequential sum."""
+    from activesplat_b200 import dist as asd
+    g = torch.Generator().manual_seed(3)
+    for n, world in ((64, 8), (7, 2), (3, 4), (0, 2)):
+        w = (torch.rand(n, generator=g) * 5 + 0.5).tolist()
+        deal = asd.deal_by_weight(w, world)
+        assert sorted(sum(deal, [])) == list(range(n)) and len(deal) == world
+        loads = [sum(w[i] for i in d) for d in deal]
+        if n:
+            assert max(loads) - min(loads) <= max(w) + 1e-9
+    w5 = [5.0, 1.0, 1.0, 1.0, 1.0]
+    assert asd.deal_by_weight(w5, 2) == [[0], [1, 2, 3, 4]]
+    res = _spawn(_mapping_worker, 2, 5, {"weights": w5})
+    total = sum(torch.randn(50, 14, generator=torch.Generator().manual_seed(77 + k)) for k in range(5))
+    for r in range(2):
+        torch.testing.assert_close(res[r][1], -0.1 * total, rtol=1e-6, atol=1e-6)
 
 
 def test_shard_indices_cover_exactly():
