@@ -40,6 +40,21 @@ class AsForwardArgs(ctypes.Structure):
     ]
 
 
+class AsDensifyArgs(ctypes.Structure):
+    _fields_ = [
+        ("width", ctypes.c_int), ("height", ctypes.c_int),
+        ("color6", ctypes.c_void_p), ("gt_rgb", ctypes.c_void_p), ("gt_depth", ctypes.c_void_p),
+        ("sil_thres", ctypes.c_float),
+        ("fx", ctypes.c_float), ("fy", ctypes.c_float), ("cx", ctypes.c_float), ("cy", ctypes.c_float),
+        ("c2w", ctypes.c_void_p),
+        ("isotropic", ctypes.c_int), ("time_idx", ctypes.c_float),
+        ("P", ctypes.c_int), ("capacity", ctypes.c_int),
+        ("means3D", ctypes.c_void_p), ("rgb_colors", ctypes.c_void_p), ("unnorm_rotations", ctypes.c_void_p),
+        ("logit_opacities", ctypes.c_void_p), ("log_scales", ctypes.c_void_p), ("timestep", ctypes.c_void_p),
+        ("scratch", ctypes.c_void_p), ("result", ctypes.c_void_p),
+    ]
+
+
 class AsBackwardArgs(ctypes.Structure):
     _fields_ = [
         ("P", ctypes.c_int), ("D", ctypes.c_int), ("M", ctypes.c_int), ("R", ctypes.c_int),
@@ -121,6 +136,8 @@ SYMBOLS = {
     "as_mapping_loss_scratch_floats": (_Z, [_I, _I]),
     "as_mapping_loss": (_I, [_I, _I, _V, _V, _V, _F, _F, _V, _V, _V, _V, _V]),
     "as_adam_step": (_I, [_I, _I, _V, _V, _V, _V, _V, _V, _V, _V, ctypes.POINTER(ctypes.c_float), _F, _F, _F, _I, _V]),
+    "as_densify_scratch_words": (ctypes.c_size_t, [_I, _I]),
+    "as_densify": (_I, [ctypes.POINTER(AsDensifyArgs), _V]),
     "as_cluster_hull_volumes": (_I, [_I, _I, _I, _V, _V, _V, ctypes.c_double, _I, _V, _V, _V]),
     "as_pose_adam_step": (_I, [_V, _V, _I, _F, _V, _V, _I, _F, _V, _V, _F, _F, _F, _V, _V]),
     "as_adam_step_counted": (_I, [_I, _I, _V, _V, _V, _V, _V, _V, _V, _V, ctypes.POINTER(ctypes.c_float), _F, _F, _F, _V,

@@ -5,7 +5,7 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(os.path.dirname(HERE), "libactivesplat_b200.so")
-SOURCES = ["preprocess.cu", "scan_sort.cu", "blend.cu", "fused.cu", "loss.cu", "scoring.cu", "capi.cu"]
+SOURCES = ["preprocess.cu", "scan_sort.cu", "blend.cu", "fused.cu", "loss.cu", "scoring.cu", "densify.cu", "capi.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "--use_fast_math=false",
          "-Xcompiler", "-fPIC", "-Xptxas", "-v"]

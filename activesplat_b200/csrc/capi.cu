@@ -507,13 +507,14 @@ int as_ipc_open(const void* handle64, void** out_ptr) {
 
 int as_ipc_close(void* ptr) { return ptr ? check(cudaIpcCloseMemHandle(ptr)) : AS_OK; }
 
-int as_adam_step_peer(int P, int isotropic, int world, int rank, int g_begin, int g_end, float* const* params,
+int as_adam_step_peer(int P, int isotropic, int world, int rank, int e_begin, int e_end, float* const* params,
                       const float* const* grads, float* exp_avg, float* exp_avg_sq, const float* lrs, float beta1,
                       float beta2, float eps, int step, void* cuda_stream) {
     if (P < 0 || world < 1 || world > 8 || rank < 0 || rank >= world || step < 1 || !lrs || !params || !grads)
         return AS_ERR_INVALID_ARG;
-    if (g_begin < 0 || g_end < g_begin || g_end > P || (g_begin & 3)) return AS_ERR_INVALID_ARG;  // 16-byte aligned slabs
-    if (g_end == g_begin) return AS_OK;
+    const long long n_flat = (long long)(isotropic ? 12 : 14) * P;
+    if (n_flat > 0x7fffffffLL || e_begin < 0 || e_end < e_begin || e_end > n_flat) return AS_ERR_INVALID_ARG;
+    if (e_end == e_begin) return AS_OK;
     if (!exp_avg || !exp_avg_sq) return AS_ERR_INVALID_ARG;
     for (int i = 0; i < 5 * world; i++)
         if (!params[i]) return AS_ERR_INVALID_ARG;
@@ -521,8 +522,8 @@ int as_adam_step_peer(int P, int isotropic, int world, int rank, int g_begin, in
         if (!grads[r]) return AS_ERR_INVALID_ARG;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
     StageScope _s(AS_STAGE_ADAM, st, 1);
-    launch_adam_peer(g_begin, g_end, isotropic, world, rank, params, grads, lrs, exp_avg, exp_avg_sq, beta1, beta2, eps,
-                     step, st);
+    launch_adam_peer(P, e_begin, e_end, isotropic, world, rank, params, grads, lrs, exp_avg, exp_avg_sq, beta1, beta2,
+                     eps, step, st);
     return check(cudaGetLastError());
 }
 
@@ -538,6 +539,22 @@ int as_dbscan_grid(int batch, int height, int width, const float* values, float 
     StageScope _s(AS_STAGE_OTHER, st, 1);
     launch_dbscan_grid(batch, height, width, values, value_threshold, eps, min_samples, labels, scratch, max_clusters,
                        n_clusters, stats_int, stats_value, st);
+    return check(cudaGetLastError());
+}
+
+size_t as_densify_scratch_words(int width, int height) { return densify_scratch_words(width, height); }
+
+int as_densify(const AsDensifyArgs* a, void* cuda_stream) {
+    if (!a || a->width <= 0 || a->height <= 0 || a->P < 0 || a->capacity < a->P) return AS_ERR_INVALID_ARG;
+    if (!a->color6 || !a->gt_rgb || !a->gt_depth || !a->c2w || !a->means3D || !a->rgb_colors || !a->unnorm_rotations ||
+        !a->logit_opacities || !a->log_scales || !a->scratch || !a->result)
+        return AS_ERR_INVALID_ARG;
+    if (!(a->fx > 0.f) || !(a->fy > 0.f)) return AS_ERR_INVALID_ARG;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
+    StageScope _s(AS_STAGE_OTHER, st, 7);
+    launch_densify(a->width, a->height, a->color6, a->gt_rgb, a->gt_depth, a->sil_thres, a->fx, a->fy, a->cx, a->cy,
+                   a->c2w, a->isotropic, a->time_idx, a->P, a->capacity, a->means3D, a->rgb_colors, a->unnorm_rotations,
+                   a->logit_opacities, a->log_scales, a->timestep, a->scratch, a->result, st);
     return check(cudaGetLastError());
 }
 

@@ -162,12 +162,17 @@ size_t mapping_loss_scratch_floats(int W, int H);
 void launch_mapping_loss(int W, int H, const float* c6, const float* gt_rgb, const float* gt_depth, float w_im,
                          float w_depth, float* dL, float* losses, float* scratch, const uint32_t* status,
                          cudaStream_t st);
-void launch_adam_peer(int g_begin, int g_end, int iso, int world, int rank, float* const* params, const float* const* grads,
+void launch_adam_peer(int P, int e_begin, int e_end, int iso, int world, int rank, float* const* params, const float* const* grads,
                       const float lr[5], float* m, float* v, float beta1, float beta2, float eps, int step,
                       cudaStream_t st);
 // DBSCAN on a pixel grid, one CTA per image (scoring.cu)
 void launch_dbscan_grid(int batch, int H, int W, const float* values, float thr, float eps, int min_samples, int* labels,
                         int* scratch, int max_clusters, int* n_clusters, int* stats_i, double* stats_v, cudaStream_t st);
+size_t densify_scratch_words(int W, int H);
+void launch_densify(int W, int H, const float* c6, const float* gt_rgb, const float* gt_depth, float sil_thres, float fx,
+                    float fy, float cx, float cy, const float* c2w, int iso, float time_idx, int P, int capacity,
+                    float* means3D, float* rgb, float* rot, float* logit, float* log_scales, float* timestep,
+                    uint32_t* scratch, uint32_t* result, cudaStream_t st);
 int launch_cluster_hull(int batch, int H, int W, const int* labels, const int* n_clusters, const float* depth,
                         double vfov_deg, int max_clusters, double* volumes, int* n_points, cudaStream_t st);
 void launch_adam(int P, int iso, float* const params[5], const float lr[5], const float* grad, float* m, float* v,

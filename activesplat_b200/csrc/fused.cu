@@ -688,7 +688,16 @@ __device__ __forceinline__ void block_reduce_store(float (&v)[NV], float* s_red 
     }
 }
 
-// Backward of frame_preprocess_kernel.  grad_params rows: means 3 | rgb 3 | rot 4 | logit 1 | log_scales 3.
+// Flat gradient layout shared by the frame backward, the all-reduce and Adam: one buffer of 14 P floats holding the
+// five gradient tensors one after the other, each in its parameter's own [P,w] layout:
+//   means [P,3] at 0 | rgb [P,3] at 3P | rotation [P,4] at 6P | logit opacity [P,1] at 10P | log scales [P,1|3] at 11P.
+// (A first version interleaved them as [P,14] rows: Adam then spent its time mapping flat slots back to tensors, and
+// autograd had to copy every per-tensor gradient out of the rows.)  Segment k of Gaussian i, component c:
+__device__ __forceinline__ float* grad_slot(float* base, size_t P, int seg_off, int width, size_t i, int c) {
+    return base + (size_t)seg_off * P + (size_t)width * i + c;
+}
+
+// Backward of frame_preprocess_kernel.  grad_params: the flat segment layout above.
 // pose_acc ([blocks,16] partial sums): dL/dt (3) | dL/dR (9, row-major) | dL/dq_cam through quat_mult (4).
 template <bool ISO>
 __global__ void __launch_bounds__(FP_THREADS, 4)
@@ -721,9 +730,17 @@ frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const
         const int my = blockIdx.x * FP_THREADS + threadIdx.x;
         if (my < P && !(radii[my] > 0)) {
             if (gaussians_grad && grad_params && !accumulate) {
-                float* o = grad_params + 14 * (size_t)my;
+                const size_t Pz = (size_t)P, i = (size_t)my;
 #pragma unroll
-                for (int k = 0; k < 14; k += 2) *reinterpret_cast<float2*>(o + k) = make_float2(0.f, 0.f);
+                for (int c = 0; c < 3; c++) {
+                    *grad_slot(grad_params, Pz, 0, 3, i, c) = 0.f;
+                    *grad_slot(grad_params, Pz, 3, 3, i, c) = 0.f;
+                }
+#pragma unroll
+                for (int c = 0; c < 4; c++) *grad_slot(grad_params, Pz, 6, 4, i, c) = 0.f;
+                *grad_slot(grad_params, Pz, 10, 1, i, 0) = 0.f;
+#pragma unroll
+                for (int c = 0; c < (ISO ? 1 : 3); c++) *grad_slot(grad_params, Pz, 11, ISO ? 1 : 3, i, c) = 0.f;
             }
             if (grad_means2D) {
                 grad_means2D[3 * (size_t)my] = 0.f;
@@ -830,13 +847,20 @@ frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const
     }
     {
         if (gaussians_grad && grad_params) {
-            float* o = grad_params + 14 * (size_t)idx;  // 56-byte rows: 8-byte aligned
+            const size_t Pz = (size_t)P, i = (size_t)idx;
+            auto put = [&](float* dst, float val) {   // keyframe-batch accumulation adds to what is there
+                *dst = accumulate ? (*dst + val * gs) : (val * gs);
+            };
 #pragma unroll
-            for (int k = 0; k < 14; k += 2) {
-                float2 prev = make_float2(0.f, 0.f);
-                if (accumulate) prev = *reinterpret_cast<const float2*>(o + k);  // keyframe-batch accumulation
-                *reinterpret_cast<float2*>(o + k) = make_float2(prev.x + out[k] * gs, prev.y + out[k + 1] * gs);
+            for (int c = 0; c < 3; c++) {
+                put(grad_slot(grad_params, Pz, 0, 3, i, c), out[c]);
+                put(grad_slot(grad_params, Pz, 3, 3, i, c), out[3 + c]);
             }
+#pragma unroll
+            for (int c = 0; c < 4; c++) put(grad_slot(grad_params, Pz, 6, 4, i, c), out[6 + c]);
+            put(grad_slot(grad_params, Pz, 10, 1, i, 0), out[10]);
+#pragma unroll
+            for (int c = 0; c < (ISO ? 1 : 3); c++) put(grad_slot(grad_params, Pz, 11, ISO ? 1 : 3, i, c), out[11 + c]);
         }
         if (grad_means2D) {
             grad_means2D[3 * (size_t)idx] = gm2x * gs;
@@ -1010,18 +1034,11 @@ struct AdamPtrs {   // plain members (no arrays): indexing a kernel-parameter ar
     float s0, s1, s2, s3, s4;   // lr[t] / bias_correction1 (plain lr[t] when the kernel is given a step_state)
 };
 
-constexpr int AD_G = 128;  // Gaussians per block = threads per block
+constexpr int AD_THREADS = 256;
+constexpr int AD_VEC_PER_THREAD = 4;   // 128-bit groups per thread: four independent load triples in flight
 
-// One block updates AD_G Gaussians, one thread per Gaussian.  The block's slices of the five parameter tensors and
-// its rows of the flat [P,14] gradient / exp_avg / exp_avg_sq are contiguous spans: they are staged through shared
-// memory with coalesced (128-bit where aligned) accesses, so that each thread can walk the 14 slots of its Gaussian with
-// compile-time slot -> (tensor, learning rate) mapping -- no per-element index arithmetic (the first version spent
-// 135 instructions per 32 elements on it and ran at half of the memory rate).
-// Arithmetic per element as torch.optim.Adam (single-tensor path): lerp_, mul_/addcmul_, sqrt / bias_correction2_sqrt
-// + eps, addcdiv_.
-// step_state (optional, device memory): [0] = steps taken so far, [7] = block ticket.  When given, every block derives
-// the bias corrections of step [0]+1 itself (in double, as torch does on the host) and the last block to finish
-// advances [0]: the launch is identical every step, so it can sit in a CUDA graph.  ap.s* are then plain learning rates.
+// arithmetic per element as torch.optim.Adam (single-tensor path): lerp_, mul_/addcmul_, sqrt / bias_correction2_sqrt
+// + eps, addcdiv_
 __device__ __forceinline__ void adam_one(float g, float& m, float& v, float& p, float step_size, float beta1, float beta2,
                                          float eps, float bc2_sqrt) {
     m = m + (g - m) * (1.f - beta1);          // exp_avg.lerp_(grad, 1 - beta1)
@@ -1032,88 +1049,89 @@ __device__ __forceinline__ void adam_one(float g, float& m, float& v, float& p, 
     p = p - step_size * __fdividef(m, denom);  // addcdiv_(exp_avg, denom, -step_size)
 }
 
-__device__ __forceinline__ void adam_stage_in(float* dst, const float* __restrict__ src, int n, bool vec) {
-    if (vec) {
-        for (int i = 4 * threadIdx.x; i < n; i += 4 * AD_G)
-            *reinterpret_cast<float4*>(dst + i) = __ldg(reinterpret_cast<const float4*>(src + i));
-    } else {
-        for (int i = threadIdx.x; i < n; i += AD_G) dst[i] = src[i];
-    }
+// which tensor a flat element belongs to, its learning-rate-derived step size and where its parameter lives
+struct AdamSeg {
+    float* p;
+    float step;
+};
+__device__ __forceinline__ AdamSeg adam_segment(const AdamPtrs& ap, size_t P, size_t e, const float (&st)[5]) {
+    AdamSeg r;
+    if (e < 3 * P) { r.p = ap.p0 + e; r.step = st[0]; }
+    else if (e < 6 * P) { r.p = ap.p1 + (e - 3 * P); r.step = st[1]; }
+    else if (e < 10 * P) { r.p = ap.p2 + (e - 6 * P); r.step = st[2]; }
+    else if (e < 11 * P) { r.p = ap.p3 + (e - 10 * P); r.step = st[3]; }
+    else { r.p = ap.p4 + (e - 11 * P); r.step = st[4]; }
+    return r;
 }
 
-__device__ __forceinline__ void adam_stage_out(float* __restrict__ dst, const float* src, int n, bool vec) {
-    if (vec) {
-        for (int i = 4 * threadIdx.x; i < n; i += 4 * AD_G)
-            *reinterpret_cast<float4*>(dst + i) = *reinterpret_cast<const float4*>(src + i);
-    } else {
-        for (int i = threadIdx.x; i < n; i += AD_G) dst[i] = src[i];
-    }
-}
-
-__global__ void __launch_bounds__(AD_G)
-adam_kernel(int P, int iso, AdamPtrs ap, const float* __restrict__ grad, float* __restrict__ m, float* __restrict__ v,
+// Gradient, exp_avg and exp_avg_sq share the flat segment layout (see grad_slot) and every segment has its
+// parameter's own layout, so the update is one elementwise stream over `n` = (11 + ws) P floats: 128-bit loads of
+// g, m, v and the parameter, 128-bit stores of m, v and the parameter, four groups per thread in flight.  A group that
+// straddles two tensors or is not 16-byte aligned in its parameter tensor (P not a multiple of 4) takes the scalar path.
+// step_state (optional, device memory): [0] = steps taken so far, [7] = block ticket.  When given, every block derives
+// the bias corrections of step [0]+1 itself (in double, as torch does on the host) and the last block to finish
+// advances [0]: the launch is identical every step, so it can sit in a CUDA graph.  ap.s* are then plain learning rates.
+__global__ void __launch_bounds__(AD_THREADS)
+adam_kernel(int P_, int iso, AdamPtrs ap, const float* __restrict__ grad, float* __restrict__ m, float* __restrict__ v,
             float beta1, float beta2, float eps, float bc2_sqrt, float* __restrict__ step_state) {
-    __shared__ __align__(16) float s_p[AD_G * 14];  // means [G,3] | rgb [G,3] | rot [G,4] | logit [G] | scales [G,3 or 1]
-    __shared__ __align__(16) float s_g[AD_G * 14], s_m[AD_G * 14], s_v[AD_G * 14];
     __shared__ float s_sched[2];
-    const int g0 = blockIdx.x * AD_G;
-    const int G = min(AD_G, P - g0);
-    const int ws = iso ? 1 : 3;
-    constexpr int off1 = 3 * AD_G, off2 = 6 * AD_G, off3 = 10 * AD_G, off4 = 11 * AD_G;
-    if (step_state && threadIdx.x == 0) {
-        const double step = (double)*reinterpret_cast<volatile float*>(step_state) + 1.0;
-        s_sched[0] = (float)(1.0 - pow((double)beta1, step));           // bias_correction1
-        s_sched[1] = (float)sqrt(1.0 - pow((double)beta2, step));       // sqrt(bias_correction2)
-    }
-    const size_t fbase = 14 * (size_t)g0;
-    const int nflat = 14 * G;
-    const bool full = G == AD_G;
-    auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
-    const bool vec = full && al16(grad + fbase) && al16(m + fbase) && al16(v + fbase);
-    adam_stage_in(s_g, grad + fbase, nflat, vec);
-    adam_stage_in(s_m, m + fbase, nflat, vec);
-    adam_stage_in(s_v, v + fbase, nflat, vec);
-    adam_stage_in(s_p, ap.p0 + 3 * (size_t)g0, 3 * G, full && al16(ap.p0 + 3 * (size_t)g0));
-    adam_stage_in(s_p + off1, ap.p1 + 3 * (size_t)g0, 3 * G, full && al16(ap.p1 + 3 * (size_t)g0));
-    adam_stage_in(s_p + off2, ap.p2 + 4 * (size_t)g0, 4 * G, full && al16(ap.p2 + 4 * (size_t)g0));
-    adam_stage_in(s_p + off3, ap.p3 + (size_t)g0, G, full && al16(ap.p3 + (size_t)g0));
-    adam_stage_in(s_p + off4, ap.p4 + ws * (size_t)g0, ws * G, full && al16(ap.p4 + ws * (size_t)g0));
-    __syncthreads();
-    float s0 = ap.s0, s1 = ap.s1, s2 = ap.s2, s3 = ap.s3, s4 = ap.s4;
+    const size_t P = (size_t)P_;
+    const size_t n = (size_t)(iso ? 12 : 14) * P;
+    float st[5] = {ap.s0, ap.s1, ap.s2, ap.s3, ap.s4};
     if (step_state) {
+        if (threadIdx.x == 0) {
+            const double step = (double)*reinterpret_cast<volatile float*>(step_state) + 1.0;
+            s_sched[0] = (float)(1.0 - pow((double)beta1, step));           // bias_correction1
+            s_sched[1] = (float)sqrt(1.0 - pow((double)beta2, step));       // sqrt(bias_correction2)
+        }
+        __syncthreads();
         const float bc1 = s_sched[0];
-        s0 = s0 / bc1; s1 = s1 / bc1; s2 = s2 / bc1; s3 = s3 / bc1; s4 = s4 / bc1;   // lr / bias_correction1
+#pragma unroll
+        for (int k = 0; k < 5; k++) st[k] = st[k] / bc1;                    // lr / bias_correction1
         bc2_sqrt = s_sched[1];
     }
-    const int t = threadIdx.x;
-    if (t < G) {
-        const int r = 14 * t;
+    const size_t ngroups = (n + 3) / 4;
+    const size_t g0 = ((size_t)blockIdx.x * AD_THREADS) * AD_VEC_PER_THREAD + threadIdx.x;
+    float4 gg[AD_VEC_PER_THREAD], mm[AD_VEC_PER_THREAD], vv[AD_VEC_PER_THREAD], pp[AD_VEC_PER_THREAD];
+    AdamSeg seg[AD_VEC_PER_THREAD];
+    bool fast[AD_VEC_PER_THREAD];
 #pragma unroll
-        for (int k = 0; k < 3; k++) adam_one(s_g[r + k], s_m[r + k], s_v[r + k], s_p[3 * t + k], s0, beta1, beta2, eps, bc2_sqrt);
-#pragma unroll
-        for (int k = 0; k < 3; k++)
-            adam_one(s_g[r + 3 + k], s_m[r + 3 + k], s_v[r + 3 + k], s_p[off1 + 3 * t + k], s1, beta1, beta2, eps, bc2_sqrt);
-#pragma unroll
-        for (int k = 0; k < 4; k++)
-            adam_one(s_g[r + 6 + k], s_m[r + 6 + k], s_v[r + 6 + k], s_p[off2 + 4 * t + k], s2, beta1, beta2, eps, bc2_sqrt);
-        adam_one(s_g[r + 10], s_m[r + 10], s_v[r + 10], s_p[off3 + t], s3, beta1, beta2, eps, bc2_sqrt);
-        if (iso) {   // one log-scale per Gaussian: flat slots 12, 13 are unused and stay as they are
-            adam_one(s_g[r + 11], s_m[r + 11], s_v[r + 11], s_p[off4 + t], s4, beta1, beta2, eps, bc2_sqrt);
-        } else {
-#pragma unroll
-            for (int k = 0; k < 3; k++)
-                adam_one(s_g[r + 11 + k], s_m[r + 11 + k], s_v[r + 11 + k], s_p[off4 + 3 * t + k], s4, beta1, beta2, eps,
-                         bc2_sqrt);
+    for (int u = 0; u < AD_VEC_PER_THREAD; u++) {
+        const size_t q = g0 + (size_t)u * AD_THREADS, e = 4 * q;
+        fast[u] = false;
+        if (q < ngroups && e + 3 < n) {
+            seg[u] = adam_segment(ap, P, e, st);
+            const AdamSeg last = adam_segment(ap, P, e + 3, st);
+            fast[u] = (last.p == seg[u].p + 3) && ((reinterpret_cast<uintptr_t>(seg[u].p) & 15) == 0);
+        }
+        if (fast[u]) {
+            gg[u] = __ldg(reinterpret_cast<const float4*>(grad + e));
+            mm[u] = *reinterpret_cast<const float4*>(m + e);
+            vv[u] = *reinterpret_cast<const float4*>(v + e);
+            pp[u] = *reinterpret_cast<const float4*>(seg[u].p);
         }
     }
-    __syncthreads();
-    adam_stage_out(m + fbase, s_m, nflat, vec);
-    adam_stage_out(v + fbase, s_v, nflat, vec);
-    adam_stage_out(ap.p0 + 3 * (size_t)g0, s_p, 3 * G, full && al16(ap.p0 + 3 * (size_t)g0));
-    adam_stage_out(ap.p1 + 3 * (size_t)g0, s_p + off1, 3 * G, full && al16(ap.p1 + 3 * (size_t)g0));
-    adam_stage_out(ap.p2 + 4 * (size_t)g0, s_p + off2, 4 * G, full && al16(ap.p2 + 4 * (size_t)g0));
-    adam_stage_out(ap.p3 + (size_t)g0, s_p + off3, G, full && al16(ap.p3 + (size_t)g0));
-    adam_stage_out(ap.p4 + ws * (size_t)g0, s_p + off4, ws * G, full && al16(ap.p4 + ws * (size_t)g0));
+#pragma unroll
+    for (int u = 0; u < AD_VEC_PER_THREAD; u++) {
+        const size_t q = g0 + (size_t)u * AD_THREADS, e = 4 * q;
+        if (fast[u]) {
+            const float s1 = seg[u].step;
+            adam_one(gg[u].x, mm[u].x, vv[u].x, pp[u].x, s1, beta1, beta2, eps, bc2_sqrt);
+            adam_one(gg[u].y, mm[u].y, vv[u].y, pp[u].y, s1, beta1, beta2, eps, bc2_sqrt);
+            adam_one(gg[u].z, mm[u].z, vv[u].z, pp[u].z, s1, beta1, beta2, eps, bc2_sqrt);
+            adam_one(gg[u].w, mm[u].w, vv[u].w, pp[u].w, s1, beta1, beta2, eps, bc2_sqrt);
+            *reinterpret_cast<float4*>(m + e) = mm[u];
+            *reinterpret_cast<float4*>(v + e) = vv[u];
+            *reinterpret_cast<float4*>(seg[u].p) = pp[u];
+        } else if (q < ngroups) {
+            for (size_t k = e; k < min(e + 4, n); k++) {
+                const AdamSeg sg = adam_segment(ap, P, k, st);
+                float a = m[k], b = v[k], c = *sg.p;
+                adam_one(grad[k], a, b, c, sg.step, beta1, beta2, eps, bc2_sqrt);
+                m[k] = a; v[k] = b; *sg.p = c;
+            }
+        }
+    }
     if (step_state && threadIdx.x == 0) {
         // every block read the step count before taking its ticket; the last ticket advances it for the next launch
         __threadfence();
@@ -1125,6 +1143,11 @@ adam_kernel(int P, int iso, AdamPtrs ap, const float* __restrict__ grad, float* 
     }
 }
 
+static int adam_blocks(int P, int iso) {
+    const size_t groups = ((size_t)(iso ? 12 : 14) * P + 3) / 4;
+    return (int)((groups + (size_t)AD_THREADS * AD_VEC_PER_THREAD - 1) / ((size_t)AD_THREADS * AD_VEC_PER_THREAD));
+}
+
 // ---- Adam fused with the gradient exchange over peer memory (NVLink / NVSwitch) ------------------------------
 // Mapping over a keyframe batch: every rank holds the flat [P,14] gradient of ITS keyframes.  Instead of
 // all-reducing that buffer (NCCL) and running the same Adam step on every rank, rank r owns the Gaussians
@@ -1133,61 +1156,49 @@ adam_kernel(int P, int iso, AdamPtrs ap, const float* __restrict__ grad, float* 
 // parameter values into the parameter tensors of every rank.  One kernel: reduce-scatter + Adam + all-gather.
 struct PeerAdamArgs {
     float* params[8][5];    // [rank][tensor] as mapped into this process
-    const float* grads[8];  // [rank] flat [P,14]
+    const float* grads[8];  // [rank] flat gradient buffers (segment layout)
     float* own[5];          // this rank's parameter tensors (= params[rank])
     float step_size[5];     // lr[t] / bias_correction1
     int world;
 };
 
-__device__ __forceinline__ void adam_peer_one(const PeerAdamArgs& pa, int iso, size_t e, float g, float& m, float& v,
-                                              float beta1, float beta2, float eps, float bc2_sqrt) {
-    const size_t idx = e / 14;
-    const int slot = (int)(e - idx * 14);
-    int t, k, width;
-    if (slot < 3) { t = 0; k = slot; width = 3; }
-    else if (slot < 6) { t = 1; k = slot - 3; width = 3; }
-    else if (slot < 10) { t = 2; k = slot - 6; width = 4; }
-    else if (slot < 11) { t = 3; k = 0; width = 1; }
-    else { t = 4; k = slot - 11; width = iso ? 1 : 3; if (k >= width) return; }
-    const float mm = m + (g - m) * (1.f - beta1);
-    const float vv = v * beta2 + (1.f - beta2) * g * g;
-    m = mm;
-    v = vv;
-    const float denom = __fdividef(__fsqrt_rn(vv), bc2_sqrt) + eps;
-    const size_t po = (size_t)width * idx + k;
+// One thread per flat element (segment layout, see grad_slot): neighbouring lanes touch neighbouring words of the
+// gradient slabs AND of the parameter tensors, so the remote loads and, more importantly, the remote stores leave the SM
+// as full sectors (a 128-bit-per-thread variant scattered its parameter stores across lanes and was 1.7x slower over
+// NVLink).  Sums run in rank order and every element has exactly one owner, so all ranks end up with identical
+// parameters.  The rank owns the flat elements [e_begin, e_end); m, v hold only those.
+__global__ void __launch_bounds__(256)
+adam_peer_kernel(size_t P, size_t e_begin, size_t e_end, PeerAdamArgs pa, float* __restrict__ m, float* __restrict__ v,
+                 float beta1, float beta2, float eps, float bc2_sqrt) {
+    const size_t le = (size_t)blockIdx.x * blockDim.x + threadIdx.x;  // element of the owned slab
+    if (e_begin + le >= e_end) return;
+    const size_t e = e_begin + le;
+    float g = 0.f;
+#pragma unroll
+    for (int r = 0; r < 8; r++)
+        if (r < pa.world) g += pa.grads[r][e];
+    int t;
+    size_t po;
+    if (e < 3 * P) { t = 0; po = e; }
+    else if (e < 6 * P) { t = 1; po = e - 3 * P; }
+    else if (e < 10 * P) { t = 2; po = e - 6 * P; }
+    else if (e < 11 * P) { t = 3; po = e - 10 * P; }
+    else { t = 4; po = e - 11 * P; }
     float* mine = t == 0 ? pa.own[0] : t == 1 ? pa.own[1] : t == 2 ? pa.own[2] : t == 3 ? pa.own[3] : pa.own[4];
     const float ss = t == 0 ? pa.step_size[0] : t == 1 ? pa.step_size[1] : t == 2 ? pa.step_size[2]
                    : t == 3 ? pa.step_size[3] : pa.step_size[4];
-    const float nv = mine[po] - ss * __fdividef(mm, denom);
+    float mm = m[le], vv = v[le], pv = mine[po];
+    adam_one(g, mm, vv, pv, ss, beta1, beta2, eps, bc2_sqrt);
+    m[le] = mm;
+    v[le] = vv;
 #pragma unroll
     for (int r = 0; r < 8; r++) {  // unrolled: indexing a kernel parameter at run time would copy it to local memory
         if (r < pa.world) {
             float* dst = t == 0 ? pa.params[r][0] : t == 1 ? pa.params[r][1] : t == 2 ? pa.params[r][2]
                        : t == 3 ? pa.params[r][3] : pa.params[r][4];
-            dst[po] = nv;
+            dst[po] = pv;
         }
     }
-}
-
-// One thread per flat element: neighbouring lanes touch neighbouring words of the gradient slabs AND of the parameter
-// tensors, so the remote loads and, more importantly, the remote stores leave the SM as full sectors (a 128-bit-per-thread
-// variant scattered its parameter stores across lanes and was 1.7x slower over NVLink).  Sums run in rank order and
-// every row has exactly one owner, so all ranks end up with identical parameters.
-__global__ void __launch_bounds__(256)
-adam_peer_kernel(int g_begin, int g_end, int iso, PeerAdamArgs pa, float* __restrict__ m, float* __restrict__ v,
-                 float beta1, float beta2, float eps, float bc2_sqrt) {
-    const size_t n = 14 * (size_t)(g_end - g_begin);
-    const size_t le = (size_t)blockIdx.x * blockDim.x + threadIdx.x;  // element of the owned slab
-    if (le >= n) return;
-    const size_t e = 14 * (size_t)g_begin + le;                       // element of the full [P,14] arrays
-    float g = 0.f;
-#pragma unroll
-    for (int r = 0; r < 8; r++)
-        if (r < pa.world) g += pa.grads[r][e];
-    float mm = m[le], vv = v[le];
-    adam_peer_one(pa, iso, e, g, mm, vv, beta1, beta2, eps, bc2_sqrt);
-    m[le] = mm;
-    v[le] = vv;
 }
 
 }  // namespace
@@ -1278,10 +1289,11 @@ void launch_frame_preprocess_backward(const AsFrameArgs& a, const GeometryState&
                                                 grad_cam_stride > 0 ? grad_cam_stride : 1);
 }
 
-void launch_adam_peer(int g_begin, int g_end, int iso, int world, int rank, float* const* params /*[world*5]*/,
+void launch_adam_peer(int P, int e_begin, int e_end, int iso, int world, int rank, float* const* params /*[world*5]*/,
                       const float* const* grads /*[world]*/, const float lr[5], float* m, float* v, float beta1,
                       float beta2, float eps, int step, cudaStream_t st) {
-    if (g_end <= g_begin) return;
+    (void)iso;
+    if (e_end <= e_begin) return;
     PeerAdamArgs pa;
     const double bc1 = 1.0 - pow((double)beta1, (double)step);
     const float bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, (double)step));
@@ -1294,9 +1306,9 @@ void launch_adam_peer(int g_begin, int g_end, int iso, int world, int rank, floa
         pa.step_size[t] = (float)(lr[t] / bc1);
     }
     pa.world = world;
-    const size_t threads = 14 * (size_t)(g_end - g_begin);
-    adam_peer_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(g_begin, g_end, iso, pa, m, v, beta1, beta2, eps,
-                                                                      bc2_sqrt);
+    const size_t threads = (size_t)(e_end - e_begin);
+    adam_peer_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>((size_t)P, (size_t)e_begin, (size_t)e_end, pa, m, v,
+                                                                      beta1, beta2, eps, bc2_sqrt);
 }
 
 int tile_sort_capacity() { return TS_CAP; }
@@ -1326,7 +1338,7 @@ void launch_adam(int P, int iso, float* const params[5], const float lr[5], cons
     ap.p0 = params[0]; ap.p1 = params[1]; ap.p2 = params[2]; ap.p3 = params[3]; ap.p4 = params[4];
     ap.s0 = (float)(lr[0] / bc1); ap.s1 = (float)(lr[1] / bc1); ap.s2 = (float)(lr[2] / bc1);
     ap.s3 = (float)(lr[3] / bc1); ap.s4 = (float)(lr[4] / bc1);
-    adam_kernel<<<(P + AD_G - 1) / AD_G, AD_G, 0, st>>>(P, iso, ap, grad, m, v, beta1, beta2, eps, bc2_sqrt, nullptr);
+    adam_kernel<<<adam_blocks(P, iso), AD_THREADS, 0, st>>>(P, iso, ap, grad, m, v, beta1, beta2, eps, bc2_sqrt, nullptr);
 }
 
 // One thread: step += 1 (kept as a float-encoded integer in state[0]; exact up to 2^24 steps), then the step sizes and
@@ -1379,7 +1391,7 @@ void launch_adam_counted(int P, int iso, float* const params[5], const float lr[
     AdamPtrs ap;
     ap.p0 = params[0]; ap.p1 = params[1]; ap.p2 = params[2]; ap.p3 = params[3]; ap.p4 = params[4];
     ap.s0 = lr[0]; ap.s1 = lr[1]; ap.s2 = lr[2]; ap.s3 = lr[3]; ap.s4 = lr[4];
-    adam_kernel<<<(P + AD_G - 1) / AD_G, AD_G, 0, st>>>(P, iso, ap, grad, m, v, beta1, beta2, eps, 1.f, step_state);
+    adam_kernel<<<adam_blocks(P, iso), AD_THREADS, 0, st>>>(P, iso, ap, grad, m, v, beta1, beta2, eps, 1.f, step_state);
 }
 
 }  // namespace asb

@@ -85,8 +85,8 @@ mapping_loss_stats_kernel(int W, int H, const float* __restrict__ c6, const floa
     const int vc = threadIdx.x % TW, vr0 = (threadIdx.x / TW) * SEG;
     const int px = x0 + vc;
     float s_l1 = 0.f, s_ssim = 0.f, s_d = 0.f, s_cnt = 0.f;
-    for (int ch = 0; ch < 3; ch++) {
-        __syncthreads();
+    {
+        const int ch = blockIdx.z;   // one colour channel per block: three times the blocks, a third of the serial chain
         load_halo(c6 + ch * N, W, H, x0, y0, sx);
         load_halo(gt_rgb + ch * N, W, H, x0, y0, sy);
         __syncthreads();
@@ -142,16 +142,18 @@ mapping_loss_stats_kernel(int W, int H, const float* __restrict__ c6, const floa
             }
         }
     }
+    if (blockIdx.z == 0) {   // the depth term rides with channel 0
 #pragma unroll
-    for (int o = 0; o < SEG; o++) {
-        const int py = y0 + vr0 + o;
-        if (px < W && py < H) {
-            const size_t p = (size_t)py * W + px;
-            const float depth = c6[3 * N + p], dsq = c6[5 * N + p], gd = gt_depth[p];
-            const float invis = dsq - depth * depth;
-            if ((gd > 0.f) && !isnan(depth) && !isnan(invis)) {
-                s_d += fabsf(gd - depth);
-                s_cnt += 1.f;
+        for (int o = 0; o < SEG; o++) {
+            const int py = y0 + vr0 + o;
+            if (px < W && py < H) {
+                const size_t p = (size_t)py * W + px;
+                const float depth = c6[3 * N + p], dsq = c6[5 * N + p], gd = gt_depth[p];
+                const float invis = dsq - depth * depth;
+                if ((gd > 0.f) && !isnan(depth) && !isnan(invis)) {
+                    s_d += fabsf(gd - depth);
+                    s_cnt += 1.f;
+                }
             }
         }
     }
@@ -169,7 +171,7 @@ mapping_loss_stats_kernel(int W, int H, const float* __restrict__ c6, const floa
         float x = 0.f;
 #pragma unroll
         for (int w = 0; w < SSIM_THREADS / 32; w++) x += s_red[threadIdx.x * (SSIM_THREADS / 32) + w];
-        partials[(size_t)(blockIdx.y * gridDim.x + blockIdx.x) * 4 + threadIdx.x] = x;
+        partials[(size_t)((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 4 + threadIdx.x] = x;
     }
 }
 
@@ -231,15 +233,17 @@ mapping_loss_grad_kernel(int W, int H, const float* __restrict__ c6, const float
     __shared__ __align__(16) float sm[3][SHH * SWP];
     __shared__ __align__(16) float sh[3][SHH * TW];
     __shared__ float s_red[4 * (SSIM_THREADS / 32)];
-    const float mask_count = mapping_loss_totals(nblocks, partials, 3.f * (float)W * (float)H, w_im, w_depth, losses,
-                                                 status, s_red);
+    // only the blocks that also write the depth gradient (z == 0) need the mask count; block (0,0,0) writes the record
+    float mask_count = 1.f;
+    if (blockIdx.z == 0)
+        mask_count = mapping_loss_totals(nblocks, partials, 3.f * (float)W * (float)H, w_im, w_depth, losses, status, s_red);
     const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TH;
     const int vc = threadIdx.x % TW, vr0 = (threadIdx.x / TW) * SEG;
     const int px = x0 + vc;
     const size_t N = (size_t)W * H;
     const float n3 = 3.f * (float)N;
-    for (int ch = 0; ch < 3; ch++) {
-        __syncthreads();
+    {
+        const int ch = blockIdx.z;
 #pragma unroll
         for (int q = 0; q < 3; q++) load_halo(dmaps + (3 * q + ch) * N, W, H, x0, y0, sm[q]);
         __syncthreads();
@@ -273,6 +277,7 @@ mapping_loss_grad_kernel(int W, int H, const float* __restrict__ c6, const float
             }
         }
     }
+    if (blockIdx.z != 0) return;
 #pragma unroll
     for (int o = 0; o < SEG; o++) {
         const int py = y0 + vr0 + o;
@@ -305,14 +310,14 @@ Window make_window() {
 
 size_t mapping_loss_scratch_floats(int W, int H) {
     const size_t bx = (W + TW - 1) / TW, by = (H + TH - 1) / TH;
-    return 9 * (size_t)W * H + bx * by * 4 + 16;
+    return 9 * (size_t)W * H + 3 * bx * by * 4 + 16;
 }
 
 void launch_mapping_loss(int W, int H, const float* c6, const float* gt_rgb, const float* gt_depth, float w_im,
                          float w_depth, float* dL, float* losses, float* scratch, const uint32_t* status,
                          cudaStream_t st) {
-    const dim3 grid((W + TW - 1) / TW, (H + TH - 1) / TH);
-    const int nblocks = grid.x * grid.y;
+    const dim3 grid((W + TW - 1) / TW, (H + TH - 1) / TH, 3);
+    const int nblocks = grid.x * grid.y * grid.z;
     float* dmaps = scratch;
     float* partials = scratch + ((9 * (size_t)W * H + 3) & ~(size_t)3);   // float4 reads in the gradient kernel
     const Window win = make_window();

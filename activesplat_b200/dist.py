@@ -4,7 +4,7 @@ Two axes shard naturally; the reference itself is single-GPU (no 
   * candidate-view / keyframe RENDERS are independent given the (replicated) map: views are dealt
     round-robin to ranks, no collective on the data path, one tiny all_gather of the per-view scores
     (the GetOpacity sweep of src/visualizer/visualizer.py:991-1001 + src/mapper/splatam/__init__.py:698-759);
-  * MAPPING over a keyframe batch: every rank accumulates the flat [P,14] parameter gradient of its
+  * MAPPING over a keyframe batch: every rank accumulates the flat (14 P floats) parameter gradient of its
     keyframes, one all_reduce(SUM) over NVLink, then the identical fused Adam step on every rank.
 The host-side logic here is backend-agnostic (tested with gloo on CPU); the renders are injected.
 """
@@ -93,7 +93,7 @@ def score_views(render_fn, n_views, device="cpu", group=None, n_streams=1):
 
 
 def allreduce_gradients(flat_grad, group=None):
-    """Sum the flat [P,14] per-Gaussian gradient buffer across ranks (one collective per mapping step)."""
+    """Sum the flat per-Gaussian gradient buffer (14 P floats) across ranks (one collective per mapping step)."""
     _, world = world_info(group)
     if world > 1:
         dist.all_reduce(flat_grad, op=dist.ReduceOp.SUM, group=group)
@@ -221,7 +221,7 @@ def score_candidate_views(params, views, group=None, n_streams=32, scale_modifie
 # ---- Adam fused with the gradient exchange over peer memory ------------------------------------------------------
 class PeerShardedAdam:
     """Drop-in for `allreduce_gradients(flat) ; FusedAdam.step(flat)` when mapping over a keyframe batch on the GPUs of
-    one box: each rank owns a contiguous slab of Gaussians, sums that slab of every rank's gradient straight out of the
+    one box: each rank owns a contiguous slab of the flat buffer, sums that slab of every rank's gradient straight out of the
     peers' memory, updates it, and writes the new parameters into every rank's tensors (as_adam_step_peer).  Optimizer
     state exists only for the owned slab (1/world of FusedAdam's).  Results equal the all-reduce path up to the order of
     the float additions.
@@ -241,12 +241,13 @@ class PeerShardedAdam:
         self.lrs = (ctypes.c_float * 5)(*[float(lrs[k]) for k in PARAM_ORDER])
         self.P = int(params["means3D"].shape[0])
         dev = params["means3D"].device
-        per = -(-self.P // self.world)
-        per = (per + 3) // 4 * 4  # slabs start on 16-byte boundaries of the flat [P,14] buffers
-        self.g_begin, self.g_end = min(self.P, per * self.rank), min(self.P, per * (self.rank + 1))
+        n_flat = (12 if params["log_scales"].shape[1] == 1 else 14) * self.P   # elements in use (segment layout)
+        per = -(-n_flat // self.world)
+        per = (per + 3) // 4 * 4  # slabs start on 16-byte boundaries of the flat buffers
+        self.g_begin, self.g_end = min(n_flat, per * self.rank), min(n_flat, per * (self.rank + 1))
         n_own = self.g_end - self.g_begin
-        self.exp_avg = torch.zeros((n_own, 14), dtype=torch.float32, device=dev)
-        self.exp_avg_sq = torch.zeros((n_own, 14), dtype=torch.float32, device=dev)
+        self.exp_avg = torch.zeros(n_own, dtype=torch.float32, device=dev)
+        self.exp_avg_sq = torch.zeros(n_own, dtype=torch.float32, device=dev)
         self._flag = torch.zeros(1, dtype=torch.float32, device=dev)
         mine = [params[k] for k in PARAM_ORDER] + [flat_grad]
         for t in mine:

@@ -14,8 +14,30 @@ import torch
 from . import capi
 
 PARAM_ORDER = ("means3D", "rgb_colors", "unnorm_rotations", "logit_opacities", "log_scales")
-SLOTS = {"means3D": (0, 3), "rgb_colors": (3, 6), "unnorm_rotations": (6, 10), "logit_opacities": (10, 11),
-         "log_scales": (11, 14)}
+# The flat gradient / Adam-state layout (include/activesplat_b200.h, AsFrameBackwardArgs.grad_params): 14 P floats, the
+# five tensors one after the other, each in its parameter's own [P,w] layout.  SEGMENTS: name -> (offset / P, width).
+SEGMENTS = {"means3D": (0, 3), "rgb_colors": (3, 3), "unnorm_rotations": (6, 4), "logit_opacities": (10, 1),
+            "log_scales": (11, 3)}
+
+
+def flat_views(flat, P, scale_width=3):
+    """The five per-tensor views [P,w] of a flat buffer in the segment layout (contiguous, no copies)."""
+    flat = flat.reshape(-1)
+    out = {}
+    for k in PARAM_ORDER:
+        off, w = SEGMENTS[k]
+        w = scale_width if k == "log_scales" else w
+        out[k] = flat[off * P: off * P + w * P].view(P, w)
+    return out
+
+
+def pack_flat(tensors, P, device=None):
+    """A flat buffer in the segment layout from per-tensor [P,w] arrays (tests, tools)."""
+    dev = device if device is not None else tensors["means3D"].device
+    flat = torch.zeros(14 * P, dtype=torch.float32, device=dev)
+    for k, v in flat_views(flat, P, tensors["log_scales"].shape[1]).items():
+        v.copy_(tensors[k])
+    return flat
 
 
 class FrameWorkspace:
@@ -95,7 +117,7 @@ class FrameWorkspace:
             self.P = P
             self.geom = self._geom[: L.as_geometry_bytes(P)]
             self.radii = self._radii[:P]
-            self.grad_params = self._grad_params[: P * 14].view(P, 14)
+            self.grad_params = self._grad_params[: P * 14]   # flat segment layout (see SEGMENTS)
             self.grad_means2D = self._grad_means2D[: P * 3].view(P, 3) if self._grad_means2D is not None else None
 
     def ensure_capacity(self, needed):
@@ -262,7 +284,7 @@ class FrameWorkspace:
 
     def backward(self, dL_dpix=None, grad_scale=None, gaussians_grad=True, camera_grad=False, accumulate=False,
                  grad_cam_out=None, grad_cam_stride=1):
-        """as_frame_backward for the last forward.  Returns (grad_params [P,14], grad_cam).
+        """as_frame_backward for the last forward.  Returns (grad_params: 14 P floats in the flat segment layout, grad_cam).
         grad_cam_out/grad_cam_stride: write the 7 pose gradients at grad_cam_out[k * stride] instead."""
         L = capi.lib()
         b = capi.AsFrameBackwardArgs()
@@ -300,6 +322,24 @@ def workspace_for(params, cam, role="train"):
         ws = FrameWorkspace(int(params["means3D"].shape[0]), key[0], key[1], dev)
         _WORKSPACES[key] = ws
     return ws
+
+
+_PARAM_GRADS = [True]
+
+
+class gradients_stay_in_workspace:
+    """Context manager for training loops that step with FusedAdam: inside it, backward() of the fused nodes leaves the
+    five Gaussian tensors' `.grad` at None and delivers their gradients ONLY in the workspace's flat buffer
+    (`workspace.grad_params`, which FusedAdam.step consumes) -- autograd otherwise copies 56 bytes per Gaussian out of
+    that buffer into five `.grad` tensors every iteration.  Camera-pose gradients are delivered as usual."""
+
+    def __enter__(self):
+        self.prev = _PARAM_GRADS[0]
+        _PARAM_GRADS[0] = False
+        return self
+
+    def __exit__(self, *a):
+        _PARAM_GRADS[0] = self.prev
 
 
 def _claim_backward(ctx):
@@ -351,11 +391,12 @@ class _FusedTrackingLoss(torch.autograd.Function):
                              grad_cam_out=gcam[:, ctx.time_idx:] if gcam is not None else None, grad_cam_stride=T)
         outs = [None] * 20
         if ctx.gaussians_grad:
-            ls_w = ctx.shapes[2]
-            views = (gp[:, 0:3], gp[:, 3:6], gp[:, 6:10], gp[:, 10:11], gp[:, 11:11 + ls_w])
-            for i in range(5):
+            # copies: the workspace buffer is rewritten by the next frame, and autograd would otherwise adopt these
+            # contiguous views as .grad (use FusedAdam.step(ws.grad_params) to consume the buffer without copies)
+            views = flat_views(gp, ws.P, ctx.shapes[2])
+            for i, k in enumerate(PARAM_ORDER):
                 if ctx.need[i]:
-                    outs[i] = views[i]
+                    outs[i] = views[k].clone() if _PARAM_GRADS[0] else None
         if ctx.camera_grad:
             outs[5], outs[6] = gcam[0:4].unsqueeze(0), gcam[4:7].unsqueeze(0)
         return tuple(outs)
@@ -390,10 +431,10 @@ class _FusedFrameRender(torch.autograd.Function):
                              grad_cam_out=gcam[:, ctx.time_idx:] if gcam is not None else None, grad_cam_stride=T)
         outs = [None] * 12
         if gaussians_grad:
-            views = (gp[:, 0:3], gp[:, 3:6], gp[:, 6:10], gp[:, 10:11], gp[:, 11:11 + ctx.shapes[2]])
-            for i in range(5):
+            views = flat_views(gp, ws.P, ctx.shapes[2])
+            for i, k in enumerate(PARAM_ORDER):
                 if ctx.need[i]:
-                    outs[i] = views[i]
+                    outs[i] = views[k].clone() if _PARAM_GRADS[0] else None
         if camera_grad:
             outs[5], outs[6] = gcam[0:4].unsqueeze(0), gcam[4:7].unsqueeze(0)
         return tuple(outs)
@@ -463,7 +504,8 @@ def fused_mapping_loss(params, cam, time_idx, sil_w2c, gt_rgb, gt_depth, w_im, w
 
 class FusedAdam:
     """torch.optim.Adam(lr per tensor, betas (0.9, 0.999), eps) over the five Gaussian tensors in one kernel.
-    State is flat [P,14]; `step(grad_flat)` consumes the flat gradient buffer of the frame backward."""
+    State is flat (14 P floats, segment layout); `step(grad_flat)` consumes the flat gradient buffer of the frame
+    backward (`workspace.grad_params`); `step()` without it packs the tensors' `.grad` first."""
 
     def __init__(self, params, lrs, betas=(0.9, 0.999), eps=1e-15, device_step=True):
         """device_step: keep the step count (and the bias corrections derived from it) in device memory
@@ -473,16 +515,21 @@ class FusedAdam:
         self.lrs = (ctypes.c_float * 5)(*[float(lrs[k]) for k in PARAM_ORDER])
         self.betas, self.eps, self.t = betas, eps, 0
         P, dev = params["means3D"].shape[0], params["means3D"].device
-        self.exp_avg = torch.zeros((P, 14), dtype=torch.float32, device=dev)
-        self.exp_avg_sq = torch.zeros((P, 14), dtype=torch.float32, device=dev)
+        self.exp_avg = torch.zeros(14 * P, dtype=torch.float32, device=dev)
+        self.exp_avg_sq = torch.zeros(14 * P, dtype=torch.float32, device=dev)
         self.step_state = torch.zeros(8, dtype=torch.float32, device=dev) if device_step else None
 
     @torch.no_grad()
-    def step(self, grad_flat):
+    def step(self, grad_flat=None):
         L = capi.lib()
         self.t += 1
         p = self.params
         dev = p["means3D"].device
+        if grad_flat is None:
+            grad_flat = pack_flat({k: (p[k].grad if p[k].grad is not None else torch.zeros_like(p[k]))
+                                   for k in PARAM_ORDER}, int(p["means3D"].shape[0]))
+        if grad_flat.numel() < 14 * int(p["means3D"].shape[0]):
+            raise ValueError("FusedAdam.step: the flat gradient buffer holds fewer than 14 * P floats")
         for k in PARAM_ORDER:
             assert p[k].is_contiguous() and p[k].dtype == torch.float32
         args = (int(p["means3D"].shape[0]), 1 if p["log_scales"].shape[1] == 1 else 0, p["means3D"].data_ptr(),

@@ -313,90 +313,153 @@ def _get_loss_mapping_fused(params, curr_data, variables, iter_time_idx, loss_we
 
 def get_pointcloud(color, depth, intrinsics, w2c, transform_pts=True, mask=None, compute_mean_sq_dist=False,
                    mean_sq_dist_method="projective"):
-    """Back-projection of an RGB-D frame (src/mapper/splatam/splatam.py:25-75)."""
-    dev = color.device
-    width, height = color.shape[2], color.shape[1]
-    CX, CY, FX, FY = intrinsics[0][2], intrinsics[1][2], intrinsics[0][0], intrinsics[1][1]
-    x_grid, y_grid = torch.meshgrid(torch.arange(width, device=dev).float(), torch.arange(height, device=dev).float(),
-                                    indexing='xy')
-    xx = ((x_grid - CX) / FX).reshape(-1)
-    yy = ((y_grid - CY) / FY).reshape(-1)
-    depth_z = depth[0].reshape(-1)
-    pts_cam = torch.stack((xx * depth_z, yy * depth_z, depth_z), dim=-1)
+    """Back-projection of an RGB-D frame into a coloured point cloud [n,6] (+ the squared 1-pixel footprint of each
+    point, the initial Gaussian scale): the reference's get_pointcloud (src/mapper/splatam/splatam.py:25-75), used for
+    map initialisation.  Densification does the same arithmetic inside as_densify."""
+    if mean_sq_dist_method != "projective":
+        raise ValueError(f"Unknown mean_sq_dist_method {mean_sq_dist_method}")
+    _, H, W = color.shape
+    fx, fy, cx, cy = intrinsics[0][0], intrinsics[1][1], intrinsics[0][2], intrinsics[1][2]
+    v, u = torch.meshgrid(torch.arange(H, device=color.device, dtype=torch.float32),
+                          torch.arange(W, device=color.device, dtype=torch.float32), indexing='ij')
+    z = depth[0].reshape(-1)
+    pts = torch.stack((((u - cx) / fx).reshape(-1) * z, ((v - cy) / fy).reshape(-1) * z, z), dim=-1)
     if transform_pts:
-        pts4 = torch.cat((pts_cam, torch.ones(height * width, 1, device=dev)), dim=1)
-        pts = (torch.inverse(w2c) @ pts4.T).T[:, :3]
-    else:
-        pts = pts_cam
-    if compute_mean_sq_dist:
-        if mean_sq_dist_method != "projective":
-            raise ValueError(f"Unknown mean_sq_dist_method {mean_sq_dist_method}")
-        mean3_sq_dist = (depth_z / ((FX + FY) / 2)) ** 2
-    cols = torch.permute(color, (1, 2, 0)).reshape(-1, 3)
-    point_cld = torch.cat((pts, cols), -1)
+        c2w = torch.inverse(w2c)
+        pts = pts @ c2w[:3, :3].T + c2w[:3, 3]
+    cloud = torch.cat((pts, color.permute(1, 2, 0).reshape(-1, 3)), dim=-1)
+    msd = (z / ((fx + fy) / 2)) ** 2
     if mask is not None:
-        point_cld = point_cld[mask]
-        if compute_mean_sq_dist:
-            mean3_sq_dist = mean3_sq_dist[mask]
-    return (point_cld, mean3_sq_dist) if compute_mean_sq_dist else point_cld
+        cloud, msd = cloud[mask], msd[mask]
+    return (cloud, msd) if compute_mean_sq_dist else cloud
 
 
 def initialize_new_params(new_pt_cld, mean3_sq_dist, gaussian_distribution):
-    """splatam.py:304-329."""
-    num_pts, dev = new_pt_cld.shape[0], new_pt_cld.device
-    unnorm_rots = torch.zeros((num_pts, 4), device=dev)
-    unnorm_rots[:, 0] = 1.0
-    if gaussian_distribution == "isotropic":
-        log_scales = torch.tile(torch.log(torch.sqrt(mean3_sq_dist))[..., None], (1, 1))
-    elif gaussian_distribution == "anisotropic":
-        log_scales = torch.tile(torch.log(torch.sqrt(mean3_sq_dist))[..., None], (1, 3))
-    else:
+    """Parameters of Gaussians created from a point cloud (splatam.py:304-329): identity rotation, logit opacity 0,
+    log scale = log of the 1-pixel footprint, one scale per Gaussian ("isotropic") or three equal ones."""
+    reps = {"isotropic": 1, "anisotropic": 3}.get(gaussian_distribution)
+    if reps is None:
         raise ValueError(f"Unknown gaussian_distribution {gaussian_distribution}")
-    params = {'means3D': new_pt_cld[:, :3], 'rgb_colors': new_pt_cld[:, 3:6], 'unnorm_rotations': unnorm_rots,
-              'logit_opacities': torch.zeros((num_pts, 1), dtype=torch.float, device=dev), 'log_scales': log_scales}
-    return {k: torch.nn.Parameter(v.float().contiguous().requires_grad_(True)) for k, v in params.items()}
+    n, dev = new_pt_cld.shape[0], new_pt_cld.device
+    identity = torch.tensor([1.0, 0.0, 0.0, 0.0], device=dev).expand(n, 4)
+    fresh = {'means3D': new_pt_cld[:, :3], 'rgb_colors': new_pt_cld[:, 3:6], 'unnorm_rotations': identity,
+             'logit_opacities': torch.zeros((n, 1), device=dev),
+             'log_scales': torch.log(torch.sqrt(mean3_sq_dist)).reshape(n, 1).expand(n, reps)}
+    return {k: torch.nn.Parameter(v.float().contiguous().requires_grad_(True)) for k, v in fresh.items()}
+
+
+class _MapStore:
+    """Capacity behind a params dict: the five Gaussian tensors (and variables['timestep']) as views of buffers that
+    hold more rows than the map has, so that densification appends in place.  Found again through the identity of the
+    dict; if the caller swapped a tensor for one of its own, the store is rebuilt from what the dict holds now."""
+    KEYS = ("means3D", "rgb_colors", "unnorm_rotations", "logit_opacities", "log_scales")
+
+    def __init__(self, params, variables, room):
+        self.P = int(params['means3D'].shape[0])
+        self.capacity = 0
+        self.buf, self.timestep = {}, None
+        self._adopt(params, variables, self.P + int(room))
+
+    def _adopt(self, params, variables, capacity):
+        dev = params['means3D'].device
+        capacity = max(int(capacity), self.P)
+        new = {k: torch.empty((capacity,) + tuple(params[k].shape[1:]), dtype=torch.float32, device=dev) for k in self.KEYS}
+        for k in self.KEYS:
+            new[k][:self.P].copy_(params[k].detach()[:self.P])
+        ts = torch.zeros(capacity, dtype=torch.float32, device=dev)
+        t_old = variables.get('timestep')
+        if t_old is not None:
+            ts[:min(self.P, t_old.shape[0])].copy_(t_old[:self.P])
+        self.buf, self.timestep, self.capacity = new, ts, capacity
+
+    def matches(self, params, variables):
+        if int(params['means3D'].shape[0]) != self.P:
+            return False
+        if any(params[k].data_ptr() != self.buf[k].data_ptr() for k in self.KEYS):
+            return False
+        t = variables.get('timestep')
+        return t is not None and t.data_ptr() == self.timestep.data_ptr()
+
+    def publish(self, params, variables, P):
+        """Point the dict at rows [0, P) of the buffers (new leaf Parameters, like the reference's re-wrapping)."""
+        self.P = int(P)
+        for k in self.KEYS:
+            params[k] = torch.nn.Parameter(self.buf[k][:self.P], requires_grad=True)
+        variables['timestep'] = self.timestep[:self.P]
+
+
+_MAP_STORES = {}
+
+
+def _map_store(params, variables, room):
+    st = _MAP_STORES.get(id(params))
+    if st is None or not st.matches(params, variables):
+        st = _MapStore(params, variables, room)
+        st.publish(params, variables, st.P)
+        _MAP_STORES[id(params)] = st
+        if len(_MAP_STORES) > 8:   # dicts that went away
+            _MAP_STORES.pop(next(iter(_MAP_STORES)))
+    return st
 
 
 def add_new_gaussians(params, variables, curr_data, sil_thres, time_idx, mean_sq_dist_method, gaussian_distribution):
-    """Silhouette-driven densification (splatam.py:332-379): render the depth/silhouette of the current map
-    at the frame's pose, find pixels the map does not explain, back-project them as new Gaussians.
-    The render is one fused forward from the raw parameters (no gradients)."""
+    """Silhouette-driven densification (src/mapper/splatam/splatam.py:332-379): render depth and silhouette of the
+    current map at the frame's pose, take the pixels the map does not explain, back-project them as new Gaussians.
+    One fused forward from the raw parameters, then as_densify: median, mask, ordered compaction and the new rows are
+    produced on the device and written behind the existing rows of tensors that were allocated with head-room (no
+    torch.cat of the whole map; the map grows by at most one frame of pixels per call).  One host read: the count."""
+    import ctypes
+    from . import capi
     from .frame import fused_render
+    if mean_sq_dist_method != "projective":
+        raise ValueError(f"Unknown mean_sq_dist_method {mean_sq_dist_method}")
+    if gaussian_distribution not in ("isotropic", "anisotropic"):
+        raise ValueError(f"Unknown gaussian_distribution {gaussian_distribution}")
     dev = params['means3D'].device
+    H, W = curr_data['im'].shape[1], curr_data['im'].shape[2]
+    store = _map_store(params, variables, room=W * H)
     with torch.no_grad():
         p = {k: v.detach() for k, v in params.items()}
         c6, _, _, _, _ = fused_render(p, curr_data['cam'], int(time_idx), curr_data['w2c'])
-    depth_sil = c6[3:]
-    silhouette = depth_sil[1, :, :]
-    non_presence_sil_mask = (silhouette < sil_thres)
-    gt_depth = curr_data['depth'][0, :, :]
-    render_depth = depth_sil[0, :, :]
-    depth_error = torch.abs(gt_depth - render_depth) * (gt_depth > 0)
-    non_presence_depth_mask = (render_depth > gt_depth) * (depth_error > 2 * depth_error.median())
-    presence_sil_mask = (silhouette > sil_thres)
-    good_depth_mask = presence_sil_mask * (gt_depth < 5)
-    non_presence_depth_mask = non_presence_depth_mask & good_depth_mask
-    non_presence_mask = (non_presence_sil_mask | non_presence_depth_mask).reshape(-1)
-    if torch.sum(non_presence_mask) > 0:
-        curr_cam_rot = F.normalize(params['cam_unnorm_rots'][..., time_idx].detach())
-        curr_cam_tran = params['cam_trans'][..., time_idx].detach()
-        curr_w2c = torch.eye(4, device=dev)
-        curr_w2c[:3, :3] = build_rotation(curr_cam_rot)
-        curr_w2c[:3, 3] = curr_cam_tran
-        valid_depth_mask = (curr_data['depth'][0, :, :] > 0)
-        non_presence_mask = non_presence_mask & valid_depth_mask.reshape(-1)
-        new_pt_cld, mean3_sq_dist = get_pointcloud(curr_data['im'], curr_data['depth'], curr_data['intrinsics'], curr_w2c,
-                                                   mask=non_presence_mask, compute_mean_sq_dist=True,
-                                                   mean_sq_dist_method=mean_sq_dist_method)
-        new_params = initialize_new_params(new_pt_cld, mean3_sq_dist, gaussian_distribution)
-        for k, v in new_params.items():
-            params[k] = torch.nn.Parameter(torch.cat((params[k], v), dim=0).requires_grad_(True))
-        num_pts = params['means3D'].shape[0]
-        variables['means2D_gradient_accum'] = torch.zeros(num_pts, device=dev).float()
-        variables['denom'] = torch.zeros(num_pts, device=dev).float()
-        variables['max_2D_radius'] = torch.zeros(num_pts, device=dev).float()
-        new_timestep = time_idx * torch.ones(new_pt_cld.shape[0], device=dev).float()
-        variables['timestep'] = torch.cat((variables['timestep'], new_timestep), dim=0)
+        # the frame's pose (splatam.py:357-362) and its inverse, on the device
+        w2c = torch.eye(4, device=dev)
+        w2c[:3, :3] = build_rotation(F.normalize(params['cam_unnorm_rots'][..., time_idx].detach()))[0]
+        w2c[:3, 3] = params['cam_trans'][..., time_idx].detach().reshape(3)
+        c2w = torch.inverse(w2c).contiguous()
+        k = curr_data['intrinsics']
+        k = k.detach().cpu().numpy() if torch.is_tensor(k) else np.asarray(k)
+        L = capi.lib()
+        scratch = torch.empty(L.as_densify_scratch_words(W, H), dtype=torch.int32, device=dev)
+        result = torch.zeros(8, dtype=torch.int32, device=dev)
+        gt_rgb, gt_depth = curr_data['im'].contiguous().float(), curr_data['depth'].contiguous().float()
+        for _ in range(2):
+            a = capi.AsDensifyArgs()
+            a.width, a.height = W, H
+            a.color6, a.gt_rgb, a.gt_depth = c6.data_ptr(), gt_rgb.data_ptr(), gt_depth.data_ptr()
+            a.sil_thres = float(sil_thres)
+            a.fx, a.fy, a.cx, a.cy = float(k[0][0]), float(k[1][1]), float(k[0][2]), float(k[1][2])
+            a.c2w = c2w.data_ptr()
+            a.isotropic = 1 if gaussian_distribution == "isotropic" else 0
+            a.time_idx = float(time_idx)
+            a.P, a.capacity = store.P, store.capacity
+            a.means3D, a.rgb_colors = store.buf['means3D'].data_ptr(), store.buf['rgb_colors'].data_ptr()
+            a.unnorm_rotations = store.buf['unnorm_rotations'].data_ptr()
+            a.logit_opacities, a.log_scales = store.buf['logit_opacities'].data_ptr(), store.buf['log_scales'].data_ptr()
+            a.timestep = store.timestep.data_ptr()
+            a.scratch, a.result = scratch.data_ptr(), result.data_ptr()
+            with torch.cuda.device(dev):
+                capi.check(L.as_densify(ctypes.byref(a), torch.cuda.current_stream(dev).cuda_stream))
+            n_new, overflow, _, n_mask = result[:4].tolist()   # the one synchronisation: what follows needs the new P
+            if not overflow:
+                break
+            store._adopt(params, variables, int(1.5 * (store.P + n_new)) + W * H)   # grow, then write again
+            store.publish(params, variables, store.P)
+    if n_mask > 0:                                   # splatam.py:355: otherwise nothing is touched
+        num_pts = store.P + n_new
+        store.publish(params, variables, num_pts)
+        variables['means2D_gradient_accum'] = torch.zeros(num_pts, device=dev)
+        variables['denom'] = torch.zeros(num_pts, device=dev)
+        variables['max_2D_radius'] = torch.zeros(num_pts, device=dev)
     return params, variables
 
 

@@ -9,10 +9,10 @@ iteration (src/mapper/splatam/__init__.py:447-490):
                                                              (colour[3] + [z,1,z^2][3] + median depth + opacity),
                                                              0.8 L1 + 0.2 (1 - SSIM) colour loss, masked depth L1
     loss.backward()                                          gradients of ALL FIVE Gaussian parameter tensors
-    optimizer.step()                                         Adam over the [P,14] parameters
+    optimizer.step()                                         Adam over the 14 P parameters
 
 N > 1 ranks: data-parallel mapping over a keyframe batch -- every rank renders ITS keyframe of the replicated map
-(weak scaling: one keyframe per GPU per step), the flat [P,14] gradient is summed with one NCCL all-reduce inside the
+(weak scaling: one keyframe per GPU per step), the flat per-Gaussian gradient (14 floats each) is summed with one NCCL all-reduce inside the
 timed region, every rank applies the same Adam step.
 
   python bench.py --gpus N --steps K --warmup W             our arm (sm_100a kernels through the C ABI)
@@ -155,7 +155,7 @@ def committed_traffic(stage):
 def run_ours(args, rank, world, local_rank):
     import torch.distributed as dist
     from activesplat_b200 import capi, splatam
-    from activesplat_b200.frame import FusedAdam, GraphedStep, PARAM_ORDER, workspace_for
+    from activesplat_b200.frame import FusedAdam, GraphedStep, PARAM_ORDER, gradients_stay_in_workspace, workspace_for
     import configs as cfgs
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(dev)
@@ -195,7 +195,8 @@ def run_ours(args, rank, world, local_rank):
             params[k].grad = None
         loss, _, _ = splatam.get_loss(params, curr, variables, t_idx, LOSS_WEIGHTS, False, SIL_THRES_MAPPING, True,
                                       False, mapping=True)
-        loss.backward()
+        with gradients_stay_in_workspace():   # FusedAdam reads the flat buffer: no per-tensor .grad copies
+            loss.backward()
         return loss
 
     def exchange_and_update():
@@ -339,11 +340,12 @@ def run_ours(args, rank, world, local_rank):
                          "changes every parameter every step",
                    "parallelism": ("single GPU" if world == 1 else
                                    f"data-parallel mapping over a {world}-keyframe batch: map replicated, one keyframe "
-                                   f"per rank, NCCL all-reduce of the flat [P,14] fp32 gradient ({P * 56 / 1e6:.0f} MB) "
+                                   f"per rank, NCCL all-reduce of the flat fp32 gradient, 14 floats per Gaussian ({P * 56 / 1e6:.0f} MB) "
                                    "inside the timed region, identical Adam step on every rank")},
         "e2e": {"value": N * args.steps * world / (ms_e2e * 1e-3) / 1e6, "unit": "Mpix/s",
                 "h2d_bytes_per_step": int(gt_host.numel() * 4), "d2h_bytes_per_step": 4,
-                "api": "activesplat_b200.splatam.get_loss(mapping=True) + loss.backward() + frame.FusedAdam.step; every "
+                "api": "activesplat_b200.splatam.get_loss(mapping=True) + loss.backward() (inside "
+                       "frame.gradients_stay_in_workspace()) + frame.FusedAdam.step(workspace.grad_params); every "
                        "step's RGB-D keyframe is copied from pinned host memory (double-buffered: the copy for step i+1 "
                        "overlaps step i) and its loss is read back"},
         "gpu_launches": int(launches),

@@ -26,7 +26,7 @@ import torch  # noqa: E402
 
 from activesplat_b200 import capi, dist as asd  # noqa: E402
 from activesplat_b200 import scenes, splatam  # noqa: E402
-from activesplat_b200.frame import PARAM_ORDER, FusedAdam, workspace_for  # noqa: E402
+from activesplat_b200.frame import PARAM_ORDER, FusedAdam, gradients_stay_in_workspace, workspace_for  # noqa: E402
 
 LW = dict(im=0.5, depth=1.0)
 MAP_LRS = dict(means3D=1e-4, rgb_colors=2.5e-3, unnorm_rotations=1e-3, logit_opacities=5e-2, log_scales=1e-3,
@@ -324,7 +324,8 @@ def cfg3(dev, RefRenderer, args, iters=60):
             for k_ in PARAM_ORDER:
                 p[k_].grad = None
             loss, _, _ = splatam.get_loss(p, cur, variables, 0, LW, False, 0.98, True, False, mapping=True)
-            loss.backward()
+            with gradients_stay_in_workspace():
+                loss.backward()
             opt.step(ws.grad_params)
 
         if profile:
@@ -545,7 +546,7 @@ def cfg5(dev, args, rank, world, with_peer=True):
         _fr._WORKSPACES.clear()
         torch.cuda.empty_cache()
     return {"config": f"cfg5: S-room {P} Gaussians, {K}-keyframe batch over {world} GPU(s) through "
-                      f"dist.mapping_step_keyframe_batch; exchange of the [P,14] fp32 gradient ({P * 14 * 4 / 1e6:.0f} MB) "
+                      f"dist.mapping_step_keyframe_batch; exchange of the flat fp32 gradient, 14 floats per Gaussian ({P * 14 * 4 / 1e6:.0f} MB) "
                       "+ Adam per step inside the timed region, by NCCL all-reduce + fused Adam"
                       + (" and by the peer-memory reduce+Adam kernel" if with_peer else ""),
             "ours": out["allreduce"], **({"peer_path": out["peer"]} if with_peer else {})}

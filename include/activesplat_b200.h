@@ -190,7 +190,9 @@ typedef struct AsFrameBackwardArgs {
     const float* grad_scale;       /* device scalar multiplied into every output gradient; NULL = 1 */
     int gaussians_grad;            /* transform_to_frame(gaussians_grad=...) */
     int camera_grad;               /* transform_to_frame(camera_grad=...) */
-    float* grad_params;            /* [P,14] flat: means 3 | rgb 3 | rotation 4 | logit opacity 1 | log scales 3 */
+    float* grad_params;            /* 14 P floats, the five gradient tensors one after the other, each in its parameter's
+                                    * layout: means [P,3] at 0 | rgb [P,3] at 3P | rotation [P,4] at 6P | logit opacity
+                                    * [P,1] at 10P | log scales [P,1 or 3] at 11P (the "flat segment layout") */
     float* grad_means2D;           /* [P,3] or NULL (NDC-unit screen gradient used by densification) */
     float* grad_cam;               /* 7 values, element k at grad_cam[k*grad_cam_stride]: d/d cam_unnorm_rot (4) | d/d cam_trans (3) */
     float* pose_scratch;           /* as_pose_scratch_floats(P) device floats (per-block partial sums; no init needed) */
@@ -226,7 +228,8 @@ int as_mapping_loss(int width, int height, const float* color6, const float* gt_
                     const uint32_t* frame_status, void* cuda_stream);
 
 /* torch.optim.Adam step (splatam.py:118-124: betas (0.9,0.999), eps 1e-15, no weight decay) over the five
- * parameter tensors at once; grad/exp_avg/exp_avg_sq are the flat [P,14] layout of AsFrameBackwardArgs.
+ * parameter tensors at once; grad/exp_avg/exp_avg_sq are in the flat segment layout of AsFrameBackwardArgs.grad_params
+ * (14 P floats each): the update is one elementwise stream over them.
  * lrs[5]: means3D, rgb_colors, unnorm_rotations, logit_opacities, log_scales.  step counts from 1. */
 int as_adam_step(int P, int isotropic, float* means3D, float* rgb_colors, float* unnorm_rotations,
                  float* logit_opacities, float* log_scales, const float* grad_params, float* exp_avg,
@@ -252,13 +255,14 @@ int as_pose_adam_step(float* cam_unnorm_rots, const float* grad_rots, int n_rots
                       float beta1, float beta2, float eps, float* step_state, void* cuda_stream);
 
 /* Adam fused with the gradient exchange of keyframe-batched mapping, over peer memory (one process per GPU,
- * NVLink / NVSwitch).  Replaces "all-reduce the flat [P,14] gradient, then as_adam_step on every rank": rank `rank` of
- * `world` (<= 8) owns the Gaussians [g_begin, g_end) (g_begin a multiple of 4; buffers 16-byte aligned); it reads those rows of EVERY rank's gradient buffer through peer
- * pointers, adds them in rank order, applies the Adam update with optimizer state kept only for its rows
- * (exp_avg / exp_avg_sq are [(g_end-g_begin),14]), and writes the new values into the parameter tensors of every rank.
+ * NVLink / NVSwitch).  Replaces "all-reduce the flat gradient, then as_adam_step on every rank": rank `rank` of
+ * `world` (<= 8) owns the flat elements [e_begin, e_end) of the segment layout ((11 + 1|3) P elements in use); it reads
+ * those elements of EVERY rank's gradient buffer through peer pointers, adds them in rank order, applies the Adam update
+ * with optimizer state kept only for them (exp_avg / exp_avg_sq hold e_end - e_begin floats), and writes the new values
+ * into the parameter tensors of every rank.
  *   params  host array of 5*world device pointers: params[5*r + t] = tensor t (means3D, rgb_colors, unnorm_rotations,
  *           logit_opacities, log_scales) of rank r as mapped into THIS process (cudaIpcOpenMemHandle or equivalent,
- *           peer access enabled); grads: host array of `world` pointers to the ranks' flat [P,14] gradients.
+ *           peer access enabled); grads: host array of `world` pointers to the ranks' flat gradient buffers.
  * The caller orders the ranks around the call: every rank's gradient must be complete before any rank starts, and no
  * rank may read its parameters or overwrite its gradient before all ranks have finished (two stream-ordered barriers,
  * e.g. tiny NCCL all-reduces).  No reference counterpart: ActiveSplat is single-GPU. */
@@ -269,7 +273,7 @@ int as_enable_peer_access(int peer_device);
  * lazy peer access, so that this device's kernels can use the mapping; returns the base of the exported allocation. */
 int as_ipc_open(const void* handle64, void** out_ptr);
 int as_ipc_close(void* ptr);
-int as_adam_step_peer(int P, int isotropic, int world, int rank, int g_begin, int g_end, float* const* params,
+int as_adam_step_peer(int P, int isotropic, int world, int rank, int e_begin, int e_end, float* const* params,
                       const float* const* grads, float* exp_avg, float* exp_avg_sq, const float* lrs, float beta1,
                       float beta2, float eps, int step, void* cuda_stream);
 
@@ -289,6 +293,42 @@ int as_adam_step_peer(int P, int isotropic, int world, int rank, int g_begin, in
 int as_dbscan_grid(int batch, int height, int width, const float* values, float value_threshold, float eps,
                    int min_samples, int* labels, int* scratch, int max_clusters, int* n_clusters, int* stats_int,
                    double* stats_value, void* cuda_stream);
+
+/* Silhouette-driven densification: add_new_gaussians + get_pointcloud + initialize_new_params
+ * (src/mapper/splatam/splatam.py:332-379, 25-75, 304-329) on the device, writing the new Gaussians behind row P of
+ * parameter tensors that were allocated with room for `capacity` rows (the reference re-allocates all five tensors with
+ * torch.cat on every call).  color6 is the rendered bundle of the current map at the frame's pose (as_frame_forward's
+ * out_color: channel 3 = depth, 4 = silhouette).  Pixels are taken where the silhouette is below sil_thres, or where
+ * the map lies behind the measured depth by more than twice the MEDIAN depth error (exact lower median, as
+ * torch.median) on pixels with silhouette above the threshold and measured depth below 5 m; always only where the
+ * measured depth is positive.  New rows, in row-major pixel order: mean = c2w * back-projection, colour = gt_rgb,
+ * rotation (1,0,0,0), logit opacity 0, log scale log(sqrt((z / ((fx + fy) / 2))^2)), timestep = time_idx.
+ *   result (8 x uint32, device): [0] number of new Gaussians, [1] 1 if they did not fit (nothing was written: grow
+ *   the tensors and call again), [2] bits of the median depth error, [3] size of the mask before the positive-depth
+ *   test (the reference does nothing at all when this is 0, :355).
+ * Asynchronous on the stream; the caller reads result[0] to learn the new P. */
+typedef struct AsDensifyArgs {
+    int width, height;
+    const float* color6;      /* [6,H,W] */
+    const float* gt_rgb;      /* [3,H,W] */
+    const float* gt_depth;    /* [1,H,W] */
+    float sil_thres;
+    float fx, fy, cx, cy;     /* curr_data['intrinsics'] */
+    const float* c2w;         /* [4,4] row-major, device: inverse of the frame's w2c (:357-362) */
+    int isotropic;            /* log_scales is [P,1] */
+    float time_idx;
+    int P, capacity;          /* rows in use / rows allocated in the tensors below */
+    float* means3D;           /* [capacity,3] */
+    float* rgb_colors;        /* [capacity,3] */
+    float* unnorm_rotations;  /* [capacity,4] */
+    float* logit_opacities;   /* [capacity,1] */
+    float* log_scales;        /* [capacity,1 or 3] */
+    float* timestep;          /* [capacity] or NULL (variables['timestep'], :376-377) */
+    uint32_t* scratch;        /* as_densify_scratch_words(width, height) x uint32 */
+    uint32_t* result;         /* 8 x uint32 */
+} AsDensifyArgs;
+size_t as_densify_scratch_words(int width, int height);
+int as_densify(const AsDensifyArgs* args, void* cuda_stream);
 
 /* The rest of get_convexhull_volume (src/mapper/__init__.py:29-86) for every cluster as_dbscan_grid found in a batch
  * of GLOBAL GetOpacity panoramas (eps 5, min_samples 25, threshold 0.8): the cluster's mask dilated with OpenCV's

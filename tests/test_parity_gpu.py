@@ -335,7 +335,7 @@ def test_fused_frame_gaussian_gradients_match_oracle(iso):
 
 def test_fused_adam_matches_torch_adam():
     """as_adam_step vs torch.optim.Adam(eps=1e-15) as configured by initialize_optimizer (splatam.py:118-124)."""
-    from activesplat_b200.frame import FusedAdam, PARAM_ORDER, SLOTS
+    from activesplat_b200.frame import FusedAdam, PARAM_ORDER, pack_flat
     from activesplat_b200 import scenes
     lrs = dict(means3D=1e-4, rgb_colors=2.5e-3, unnorm_rotations=1e-3, logit_opacities=5e-2, log_scales=1e-3)
     for iso in (False, True):
@@ -349,12 +349,11 @@ def test_fused_adam_matches_torch_adam():
         fa = FusedAdam(mine, lrs)
         g = torch.Generator().manual_seed(5)
         for step in range(4):
-            flat = torch.randn(5000, 14, generator=g) * (10.0 ** (step - 2))
+            grads = {k: torch.randn(ref[k].shape, generator=g) * (10.0 ** (step - 2)) for k in PARAM_ORDER}
             for k in PARAM_ORDER:
-                a, b = SLOTS[k]
-                ref[k].grad = flat[:, a:a + ref[k].shape[1]].clone()
+                ref[k].grad = grads[k].clone()
             opt.step()
-            fa.step(flat.to(dev))
+            fa.step(pack_flat(grads, 5000).to(dev))   # the flat segment layout of the frame backward
         for k in PARAM_ORDER:
             helpers.compare_float("adam " + k, mine[k].cpu().numpy(), ref[k].detach().numpy(), rel=1e-5)
 
