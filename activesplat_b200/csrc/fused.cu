@@ -729,19 +729,8 @@ frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const
     {
         const int my = blockIdx.x * FP_THREADS + threadIdx.x;
         if (my < P && !(radii[my] > 0)) {
-            if (gaussians_grad && grad_params && !accumulate) {
-                const size_t Pz = (size_t)P, i = (size_t)my;
-#pragma unroll
-                for (int c = 0; c < 3; c++) {
-                    *grad_slot(grad_params, Pz, 0, 3, i, c) = 0.f;
-                    *grad_slot(grad_params, Pz, 3, 3, i, c) = 0.f;
-                }
-#pragma unroll
-                for (int c = 0; c < 4; c++) *grad_slot(grad_params, Pz, 6, 4, i, c) = 0.f;
-                *grad_slot(grad_params, Pz, 10, 1, i, 0) = 0.f;
-#pragma unroll
-                for (int c = 0; c < (ISO ? 1 : 3); c++) *grad_slot(grad_params, Pz, 11, ISO ? 1 : 3, i, c) = 0.f;
-            }
+            // (the flat parameter gradient was cleared as a whole by the launcher: one streaming memset instead of
+            // fourteen strided scalar stores per culled Gaussian)
             if (grad_means2D) {
                 grad_means2D[3 * (size_t)my] = 0.f;
                 grad_means2D[3 * (size_t)my + 1] = 0.f;
@@ -1272,6 +1261,8 @@ void launch_frame_preprocess_backward(const AsFrameArgs& a, const GeometryState&
     const int P = a.P, W = a.width, H = a.height;
     const float h_y = H / (2.0f * a.tan_fovy), h_x = W / (2.0f * a.tan_fovx);
     const int blocks = (P + FP_THREADS - 1) / FP_THREADS;
+    if (gaussians_grad && grad_params && !accumulate)   // rows of culled Gaussians are zero; the kernel writes the visible ones
+        cudaMemsetAsync(grad_params, 0, sizeof(float) * 14 * (size_t)P, st);
     if (a.isotropic)
         frame_preprocess_backward_kernel<true><<<blocks, FP_THREADS, 0, st>>>(
             P, a.means3D, a.unnorm_rotations, a.logit_opacities, a.log_scales, a.cam_unnorm_rot, a.cam_rot_stride,

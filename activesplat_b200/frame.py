@@ -87,6 +87,8 @@ class FrameWorkspace:
         self.overflow_seen = None    # (instances, capacity) of an earlier frame that did not fit, until reported
         self._graph_pinned = False   # a CUDA graph captured this workspace's buffers: never free them
         self._retired = []
+        self._side = None            # side stream for clearing the gradient buffer next to the forward
+        self._grad_cleared = False
 
     # -- buffer management ---------------------------------------------------------------------
     def resize(self, P):
@@ -152,10 +154,24 @@ class FrameWorkspace:
         return int(s[0]), bool(s[1])
 
     # -- forward / backward --------------------------------------------------------------------
-    def forward(self, params, cam, time_idx, sil_w2c=None, bg_rgb=None, debug=False, max_2D_radius=None, seen=None):
+    def forward(self, params, cam, time_idx, sil_w2c=None, bg_rgb=None, debug=False, max_2D_radius=None, seen=None,
+                clear_gradient=False):
         """as_frame_forward.  params: dict with the five Gaussian tensors + cam_unnorm_rots [1,4,T] +
-        cam_trans [1,3,T]; cam: GaussianRasterizationSettings.  Results land in color6/depth/opacity/radii."""
+        cam_trans [1,3,T]; cam: GaussianRasterizationSettings.  Results land in color6/depth/opacity/radii.
+        clear_gradient: the caller will run a non-accumulating backward with Gaussian gradients on this frame; the flat
+        gradient buffer is then cleared now, on a side stream next to the (latency-bound) forward kernels, instead of
+        in front of the backward's last kernel."""
         L = capi.lib()
+        self._grad_cleared = False
+        self.resize(params["means3D"].shape[0])
+        if clear_gradient:
+            cur = torch.cuda.current_stream(self.device)
+            if self._side is None:
+                self._side = torch.cuda.Stream(device=self.device)
+            self._side.wait_stream(cur)          # everything that read the buffer so far (Adam, all-reduce) is ahead
+            with torch.cuda.stream(self._side):
+                self.grad_params.zero_()
+            self._grad_cleared = True
         a = capi.AsFrameArgs()
         keep = []
 
@@ -299,6 +315,11 @@ class FrameWorkspace:
         b.grad_cam = gc.data_ptr()
         b.grad_cam_stride = int(grad_cam_stride)
         b.pose_scratch = self.pose_scratch.data_ptr()
+        if self._grad_cleared and gaussians_grad and not accumulate:
+            # the buffer was zeroed during the forward: adding to it equals writing it
+            torch.cuda.current_stream(self.device).wait_stream(self._side)
+            accumulate = True
+        self._grad_cleared = False
         b.accumulate = int(bool(accumulate))
         self._keep.append(dL)
         with torch.cuda.device(self.device):
@@ -367,7 +388,8 @@ class _FusedTrackingLoss(torch.autograd.Function):
                 gt_rgb, gt_depth, w_im, w_depth, sil_thres, use_sil, mask_color, max_2D_radius=None, seen=None):
         params = {"means3D": means3D, "rgb_colors": rgb, "unnorm_rotations": rots, "logit_opacities": logit_op,
                   "log_scales": log_scales, "cam_unnorm_rots": cam_rots, "cam_trans": cam_trans}
-        ws.forward(params, cam, time_idx, sil_w2c=sil_w2c, max_2D_radius=max_2D_radius, seen=seen)
+        ws.forward(params, cam, time_idx, sil_w2c=sil_w2c, max_2D_radius=max_2D_radius, seen=seen,
+                   clear_gradient=any(ctx.needs_input_grad[:5]))
         if isinstance(use_sil, str):
             ws.mapping_loss(gt_rgb, gt_depth, w_im, w_depth)
         else:
@@ -411,7 +433,7 @@ class _FusedFrameRender(torch.autograd.Function):
     def forward(ctx, means3D, rgb, rots, logit_op, log_scales, cam_rots, cam_trans, ws, cam, time_idx, sil_w2c, bg_rgb):
         params = {"means3D": means3D, "rgb_colors": rgb, "unnorm_rotations": rots, "logit_opacities": logit_op,
                   "log_scales": log_scales, "cam_unnorm_rots": cam_rots, "cam_trans": cam_trans}
-        ws.forward(params, cam, time_idx, sil_w2c=sil_w2c, bg_rgb=bg_rgb)
+        ws.forward(params, cam, time_idx, sil_w2c=sil_w2c, bg_rgb=bg_rgb, clear_gradient=any(ctx.needs_input_grad[:5]))
         ctx.ws, ctx.time_idx, ctx.generation = ws, int(time_idx), ws.generation
         ctx.shapes = (cam_rots.shape, cam_trans.shape, log_scales.shape[1])
         ctx.need = tuple(ctx.needs_input_grad[:7])

@@ -184,10 +184,26 @@ def run_ours(args, rank, world, local_rank):
     copy_stream = torch.cuda.Stream(device=dev)
     copy_done = [torch.cuda.Event() for _ in range(2)]
 
+    step_done = [torch.cuda.Event() for _ in range(2)]
+    loss_host = [torch.zeros(1).pin_memory() for _ in range(2)]
+    loss_seen = []
+
     def upload(i):
+        """Host -> device copy of step i's frame into staging buffer i % 2, ordered after the step that last read it."""
         with torch.cuda.stream(copy_stream):
+            if i >= 2:
+                copy_stream.wait_event(step_done[i % 2])
             gt_stage[i % 2].copy_(gt_host, non_blocking=True)
             copy_done[i % 2].record(copy_stream)
+
+    def read_back(i, loss):
+        """Device -> host copy of step i's loss (pinned, asynchronous); the host consumes step i-1's value while step i
+        runs, so the GPU never waits for the host between steps."""
+        loss_host[i % 2].copy_(loss.detach().reshape(1), non_blocking=True)
+        step_done[i % 2].record()
+        if i >= 1:
+            step_done[(i - 1) % 2].synchronize()
+            loss_seen.append(float(loss_host[(i - 1) % 2]))
 
     def fwd_bwd(src):
         curr = {"cam": cam, "im": src[:3], "depth": src[3:4], "w2c": first_w2c}
@@ -210,7 +226,8 @@ def run_ours(args, rank, world, local_rank):
             torch.cuda.current_stream(dev).wait_event(copy_done[i % 2])
         loss = fwd_bwd(gt_stage[i % 2] if e2e else gt_dev)
         exchange_and_update()
-        return float(loss.item()) if e2e else None
+        if e2e:
+            read_back(i, loss)
 
     one_step = eager_step
 
@@ -279,7 +296,8 @@ def run_ours(args, rank, world, local_rank):
             if g_upd is not None:
                 dist.all_reduce(ws.grad_params)
                 g_upd()
-            return float(loss.item()) if e2e else None
+            if e2e:
+                read_back(i, loss)
         for i in range(args.warmup):
             one_step(i, False)
     sampler = ClockSampler(local_rank)
@@ -347,7 +365,8 @@ def run_ours(args, rank, world, local_rank):
                 "api": "activesplat_b200.splatam.get_loss(mapping=True) + loss.backward() (inside "
                        "frame.gradients_stay_in_workspace()) + frame.FusedAdam.step(workspace.grad_params); every "
                        "step's RGB-D keyframe is copied from pinned host memory (double-buffered: the copy for step i+1 "
-                       "overlaps step i) and its loss is read back"},
+                       "overlaps step i) and every step's loss is copied to pinned host memory and read by the host one "
+                       "step later (the last one after the final synchronisation)"},
         "gpu_launches": int(launches),
         "launch_path": ("cuda_graph_replay (one graph per step; kernels identical to the eager path)"
                         if graphed is not None else "eager"),
