@@ -338,7 +338,12 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
 //     pixels of one row serially in registers -- no butterfly, every lane busy on its own record -- forms the
 //     12 gradient terms, and adds them to the CTA's per-batch accumulator.
 // The CTA flushes the accumulator once per (tile, instance) with 128-bit vector reductions (REDG.ADD.F32x4).
-constexpr int BW_GROUP = 16;   // records per group: 16 x 32 staging slots per warp
+#ifndef ASB_BW_GROUP
+#define ASB_BW_GROUP 16
+#endif
+constexpr int BW_GROUP = ASB_BW_GROUP;   // records per group (16 or 8): BW_GROUP x 32 staging slots per warp
+constexpr int BW_SPLIT = 16 / BW_GROUP;  // phase-2 lanes per (record, pixel row): each sums 16 / BW_SPLIT pixels of the row
+static_assert(BW_GROUP == 16 || BW_GROUP == 8, "phase 2 maps 32 lanes to BW_GROUP records x 2 rows x BW_SPLIT segments");
 #ifndef ASB_BW_BATCH
 #define ASB_BW_BATCH 128
 #endif
@@ -457,7 +462,9 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
     }
     float last_alpha = 0.f;
     const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;  // backward.cu:460-461
-    const int rl = lane & (BW_GROUP - 1), row = lane >> 4;   // phase-2 identity of this lane: (record, pixel row)
+    // phase-2 identity of this lane: (record rl, pixel row, segment of the row)
+    const int rl = lane & (BW_GROUP - 1), row = lane >> 4, seg = (lane & 15) / BW_GROUP;
+    const uint32_t seg_bits = (BW_SPLIT == 1) ? 0xffffu : (0xffu << (8 * seg));
     const float row_y = strip_y0 + (float)row;
 
     for (int b = 0; b < nb; b++) {
@@ -476,7 +483,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
             const bool have = rl < gs;
             const int jr = have ? (int)list[gbase + rl] : 0;           // both half-warps hold the group's records
             const uint32_t mrow = have ? ((masks[gbase + rl] >> (16 * row)) & 0xffffu) : 0u;  // my record, my row
-            uint32_t hits = half_warp_bit_transpose(mrow, lane);       // records of the group that reach MY pixel
+            // records of the group that reach MY pixel (with 8-record groups only the first 8 lanes of a half-warp pass a row)
+            uint32_t hits = half_warp_bit_transpose((BW_SPLIT == 1 || seg == 0) ? mrow : 0u, lane);
 
             // ---- phase 1: lane = pixel, back to front ----
 #pragma unroll 1
@@ -550,7 +558,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
                 const float4 ge = sm.geom[s][jr];
                 const float2* my_stg = stg + rl * 32 + 16 * row;
                 const float* my_dpx = dpx + 16 * row;
-                uint32_t bits = mrow;
+                uint32_t bits = mrow & seg_bits;
                 while (bits) {
                     const int k = __ffs((int)bits) - 1;
                     bits &= bits - 1u;
@@ -582,9 +590,10 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
 #pragma unroll
                 for (int i = 0; i < 12; i++) {
                     const bool used = i < 6 ? (i != 3 || MODE != BWD_TRACKING) : (i - 6 < C && need_colour<C, MODE>(i - 6));
+                    if (used && BW_SPLIT == 2) v[i] += __shfl_xor_sync(0xffffffffu, v[i], 8);   // the two halves of the row
                     if (used) v[i] += __shfl_xor_sync(0xffffffffu, v[i], 16);
                 }
-                if (have) {
+                if (have && seg == 0) {
                     float* dst = gacc + (size_t)__float_as_uint(ge.w) * GACC_STRIDE;
                     if (row == 0) {
                         red_add_v4(dst, v[0], v[1], v[2], v[3]);

@@ -1261,8 +1261,11 @@ void launch_frame_preprocess_backward(const AsFrameArgs& a, const GeometryState&
     const int P = a.P, W = a.width, H = a.height;
     const float h_y = H / (2.0f * a.tan_fovy), h_x = W / (2.0f * a.tan_fovx);
     const int blocks = (P + FP_THREADS - 1) / FP_THREADS;
-    if (gaussians_grad && grad_params && !accumulate)   // rows of culled Gaussians are zero; the kernel writes the visible ones
+    // accumulate: 0 = overwrite (the buffer is cleared here: rows of culled Gaussians are zero, the kernel writes the
+    // visible ones), 1 = add to what is there, 2 = overwrite a buffer the caller has already cleared
+    if (gaussians_grad && grad_params && accumulate == 0)
         cudaMemsetAsync(grad_params, 0, sizeof(float) * 14 * (size_t)P, st);
+    accumulate = accumulate == 1 ? 1 : 0;
     if (a.isotropic)
         frame_preprocess_backward_kernel<true><<<blocks, FP_THREADS, 0, st>>>(
             P, a.means3D, a.unnorm_rotations, a.logit_opacities, a.log_scales, a.cam_unnorm_rot, a.cam_rot_stride,

@@ -315,12 +315,13 @@ class FrameWorkspace:
         b.grad_cam = gc.data_ptr()
         b.grad_cam_stride = int(grad_cam_stride)
         b.pose_scratch = self.pose_scratch.data_ptr()
+        mode = int(bool(accumulate))
         if self._grad_cleared and gaussians_grad and not accumulate:
-            # the buffer was zeroed during the forward: adding to it equals writing it
+            # the buffer was zeroed during the forward (side stream): the backward only writes the visible rows
             torch.cuda.current_stream(self.device).wait_stream(self._side)
-            accumulate = True
+            mode = 2
         self._grad_cleared = False
-        b.accumulate = int(bool(accumulate))
+        b.accumulate = mode
         self._keep.append(dL)
         with torch.cuda.device(self.device):
             capi.check(L.as_frame_backward(ctypes.byref(b), torch.cuda.current_stream(self.device).cuda_stream))

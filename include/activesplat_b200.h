@@ -196,7 +196,9 @@ typedef struct AsFrameBackwardArgs {
     float* grad_means2D;           /* [P,3] or NULL (NDC-unit screen gradient used by densification) */
     float* grad_cam;               /* 7 values, element k at grad_cam[k*grad_cam_stride]: d/d cam_unnorm_rot (4) | d/d cam_trans (3) */
     float* pose_scratch;           /* as_pose_scratch_floats(P) device floats (per-block partial sums; no init needed) */
-    int accumulate;                /* non-zero: grad_params += (keyframe-batch accumulation) instead of = */
+    int accumulate;                /* 0: grad_params = (cleared first, then the visible Gaussians' rows are written);
+                                    * 1: grad_params += (keyframe-batch accumulation); 2: =, into a buffer the caller has
+                                    * already cleared (e.g. on another stream while the forward ran) */
     int grad_cam_stride;           /* 0 or 1 = packed */
 } AsFrameBackwardArgs;
 
