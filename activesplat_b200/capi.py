@@ -139,6 +139,8 @@ SYMBOLS = {
     "as_densify_scratch_words": (ctypes.c_size_t, [_I, _I]),
     "as_densify": (_I, [ctypes.POINTER(AsDensifyArgs), _V]),
     "as_cluster_hull_volumes": (_I, [_I, _I, _I, _V, _V, _V, ctypes.c_double, _I, _V, _V, _V]),
+    "as_adam_step_range": (_I, [_I, _I, _V, _V, _V, _V, _V, _V, _V, _V, ctypes.POINTER(ctypes.c_float), _F, _F, _F, _V,
+                                ctypes.c_longlong, ctypes.c_longlong, _I, _V]),
     "as_pose_adam_step": (_I, [_V, _V, _I, _F, _V, _V, _I, _F, _V, _V, _F, _F, _F, _V, _V]),
     "as_adam_step_counted": (_I, [_I, _I, _V, _V, _V, _V, _V, _V, _V, _V, ctypes.POINTER(ctypes.c_float), _F, _F, _F, _V,
                                   _V]),

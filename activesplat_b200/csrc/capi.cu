@@ -39,8 +39,8 @@ ImageState ImageState::fromChunk(char*& chunk, size_t N, size_t tiles) {
     img.final_T = b.take<float>(N);
     img.n_contrib = b.take<uint32_t>(N);
     img.ranges = b.take<uint2>(tiles);
-    img.tile_count = b.take<uint32_t>(tiles * 8);   // TB_SUB sub-counters per tile (fused.cu)
-    img.tile_cursor = b.take<uint32_t>(tiles * 8);
+    img.tile_count = b.take<uint32_t>(tiles * TB_SUB);   // sub-counters per tile (fused.cu)
+    img.tile_cursor = b.take<uint32_t>(tiles * TB_SUB);
     img.tile_order = b.take<uint32_t>(tiles);
     chunk = b.p;
     return img;
@@ -336,7 +336,7 @@ int as_frame_forward(const AsFrameArgs* a, void* cuda_stream) {
     BinningState b = BinningState::fromChunk(bchunk, (size_t)cap, 6);
     int r;
     const bool buckets = a->binning_mode == AS_BINNING_TILE_BUCKETS;
-    if (buckets) cudaMemsetAsync(img.tile_count, 0, sizeof(uint32_t) * (size_t)tiles * 8, st);
+    if (buckets) cudaMemsetAsync(img.tile_count, 0, sizeof(uint32_t) * (size_t)tiles * TB_SUB, st);
     {
         StageScope _s(AS_STAGE_PREPROCESS, st, 1);
         launch_frame_preprocess(*a, g, a->status, buckets ? img.tile_count : nullptr, st);
@@ -466,7 +466,24 @@ int as_adam_step_counted(int P, int isotropic, float* means3D, float* rgb_colors
     cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
     float* params[5] = {means3D, rgb_colors, unnorm_rotations, logit_opacities, log_scales};
     StageScope _s(AS_STAGE_ADAM, st, 1);
-    launch_adam_counted(P, isotropic, params, lrs, grad_params, exp_avg, exp_avg_sq, beta1, beta2, eps, step_state, st);
+    launch_adam_counted(P, isotropic, params, lrs, grad_params, exp_avg, exp_avg_sq, beta1, beta2, eps, step_state, 0,
+                        ~(size_t)0, 1, st);
+    return check(cudaGetLastError());
+}
+
+int as_adam_step_range(int P, int isotropic, float* means3D, float* rgb_colors, float* unnorm_rotations,
+                       float* logit_opacities, float* log_scales, const float* grad_params, float* exp_avg,
+                       float* exp_avg_sq, const float* lrs, float beta1, float beta2, float eps, float* step_state,
+                       long long e_begin, long long e_end, int advance_step, void* cuda_stream) {
+    if (P < 0 || !lrs || !step_state || e_begin < 0 || e_end < e_begin || (e_begin & 3)) return AS_ERR_INVALID_ARG;
+    if (P > 0 && (!means3D || !rgb_colors || !unnorm_rotations || !logit_opacities || !log_scales || !grad_params ||
+                  !exp_avg || !exp_avg_sq))
+        return AS_ERR_INVALID_ARG;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
+    float* params[5] = {means3D, rgb_colors, unnorm_rotations, logit_opacities, log_scales};
+    StageScope _s(AS_STAGE_ADAM, st, 1);
+    launch_adam_counted(P, isotropic, params, lrs, grad_params, exp_avg, exp_avg_sq, beta1, beta2, eps, step_state,
+                        (size_t)e_begin, (size_t)e_end, advance_step, st);
     return check(cudaGetLastError());
 }
 

@@ -8,6 +8,14 @@
 
 namespace asb {
 
+// tile-bucket binning: every tile's counter is split TB_SUB ways (by Gaussian id) so that the atomics of a crowded
+// tile do not all serialise on one address; a tile's bucket is its TB_SUB sub-buckets back to back
+#ifndef ASB_TB_SUB
+#define ASB_TB_SUB 8
+#endif
+constexpr int TB_SUB = ASB_TB_SUB;
+
+
 constexpr int TILE_X = 16;  // dgr/cuda_rasterizer/config.h:16-17 (BLOCK_X, BLOCK_Y)
 constexpr int TILE_Y = 16;
 constexpr int TILE_PIX = TILE_X * TILE_Y;
@@ -50,7 +58,7 @@ struct ImageState {  // per pixel / per tile
     uint32_t* n_contrib;  // [N]
     uint2* ranges;        // [tiles]
     uint32_t* tile_count;   // [tiles] instances per tile (frame path, tile-bucket binning)
-    uint32_t* tile_cursor;  // [tiles] next free slot of each tile's bucket
+    uint32_t* tile_cursor;  // [tiles * TB_SUB] next free slot of each tile's sub-buckets
     uint32_t* tile_order;   // [tiles] tile ids, crowded tiles first: launch order of the blend kernels (tile buckets)
     static ImageState fromChunk(char*& chunk, size_t N, size_t tiles);
 };
@@ -181,7 +189,8 @@ void launch_pose_adam(float* rots, const float* g_rots, int n_rots, float lr_rot
                       int n_trans, float lr_trans, float* m, float* v, float beta1, float beta2, float eps,
                       float* step_state, cudaStream_t st);
 void launch_adam_counted(int P, int iso, float* const params[5], const float lr[5], const float* grad, float* m,
-                         float* v, float beta1, float beta2, float eps, float* step_state, cudaStream_t st);
+                         float* v, float beta1, float beta2, float eps, float* step_state, size_t e_begin, size_t e_end,
+                         int advance, cudaStream_t st);
 
 // ---------------------------------------------------------------------------------------------
 // device helpers

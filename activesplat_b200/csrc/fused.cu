@@ -119,9 +119,6 @@ __device__ __forceinline__ void load_rows(const float* __restrict__ src, int row
 
 // Look-back state of the scan fused into frame_preprocess_kernel: one u64 per block,
 // flag (2 bits, 62..63) | visible count (24 bits, 32..55) | tiles touched (32 bits, 0..31).
-// tile-bucket binning: every tile's counter is split TB_SUB ways (by Gaussian id) so that the atomics of a
-// crowded tile do not all serialise on one address; a tile's bucket is its TB_SUB sub-buckets back to back
-constexpr int TB_SUB = 8;
 
 constexpr uint64_t FPS_AGG = 1ull << 62;
 constexpr uint64_t FPS_PREFIX = 2ull << 62;
@@ -1062,10 +1059,11 @@ __device__ __forceinline__ AdamSeg adam_segment(const AdamPtrs& ap, size_t P, si
 // advances [0]: the launch is identical every step, so it can sit in a CUDA graph.  ap.s* are then plain learning rates.
 __global__ void __launch_bounds__(AD_THREADS)
 adam_kernel(int P_, int iso, AdamPtrs ap, const float* __restrict__ grad, float* __restrict__ m, float* __restrict__ v,
-            float beta1, float beta2, float eps, float bc2_sqrt, float* __restrict__ step_state) {
+            float beta1, float beta2, float eps, float bc2_sqrt, float* __restrict__ step_state, size_t e_begin,
+            size_t e_end, int advance) {
     __shared__ float s_sched[2];
     const size_t P = (size_t)P_;
-    const size_t n = (size_t)(iso ? 12 : 14) * P;
+    const size_t n = min((size_t)(iso ? 12 : 14) * P, e_end);   // this launch updates the flat elements [e_begin, n)
     float st[5] = {ap.s0, ap.s1, ap.s2, ap.s3, ap.s4};
     if (step_state) {
         if (threadIdx.x == 0) {
@@ -1080,7 +1078,7 @@ adam_kernel(int P_, int iso, AdamPtrs ap, const float* __restrict__ grad, float*
         bc2_sqrt = s_sched[1];
     }
     const size_t ngroups = (n + 3) / 4;
-    const size_t g0 = ((size_t)blockIdx.x * AD_THREADS) * AD_VEC_PER_THREAD + threadIdx.x;
+    const size_t g0 = e_begin / 4 + ((size_t)blockIdx.x * AD_THREADS) * AD_VEC_PER_THREAD + threadIdx.x;
     float4 gg[AD_VEC_PER_THREAD], mm[AD_VEC_PER_THREAD], vv[AD_VEC_PER_THREAD], pp[AD_VEC_PER_THREAD];
     AdamSeg seg[AD_VEC_PER_THREAD];
     bool fast[AD_VEC_PER_THREAD];
@@ -1121,7 +1119,7 @@ adam_kernel(int P_, int iso, AdamPtrs ap, const float* __restrict__ grad, float*
             }
         }
     }
-    if (step_state && threadIdx.x == 0) {
+    if (step_state && advance && threadIdx.x == 0) {
         // every block read the step count before taking its ticket; the last ticket advances it for the next launch
         __threadfence();
         int* ticket = reinterpret_cast<int*>(step_state + 7);
@@ -1132,8 +1130,9 @@ adam_kernel(int P_, int iso, AdamPtrs ap, const float* __restrict__ grad, float*
     }
 }
 
-static int adam_blocks(int P, int iso) {
-    const size_t groups = ((size_t)(iso ? 12 : 14) * P + 3) / 4;
+static int adam_blocks(int P, int iso, size_t e_begin = 0, size_t e_end = ~(size_t)0) {
+    const size_t n = std::min((size_t)(iso ? 12 : 14) * P, e_end);
+    const size_t groups = n > e_begin ? (n + 3) / 4 - e_begin / 4 : 0;
     return (int)((groups + (size_t)AD_THREADS * AD_VEC_PER_THREAD - 1) / ((size_t)AD_THREADS * AD_VEC_PER_THREAD));
 }
 
@@ -1332,7 +1331,8 @@ void launch_adam(int P, int iso, float* const params[5], const float lr[5], cons
     ap.p0 = params[0]; ap.p1 = params[1]; ap.p2 = params[2]; ap.p3 = params[3]; ap.p4 = params[4];
     ap.s0 = (float)(lr[0] / bc1); ap.s1 = (float)(lr[1] / bc1); ap.s2 = (float)(lr[2] / bc1);
     ap.s3 = (float)(lr[3] / bc1); ap.s4 = (float)(lr[4] / bc1);
-    adam_kernel<<<adam_blocks(P, iso), AD_THREADS, 0, st>>>(P, iso, ap, grad, m, v, beta1, beta2, eps, bc2_sqrt, nullptr);
+    adam_kernel<<<adam_blocks(P, iso), AD_THREADS, 0, st>>>(P, iso, ap, grad, m, v, beta1, beta2, eps, bc2_sqrt, nullptr, 0,
+                                                            ~(size_t)0, 0);
 }
 
 // One thread: step += 1 (kept as a float-encoded integer in state[0]; exact up to 2^24 steps), then the step sizes and
@@ -1377,15 +1377,18 @@ void launch_pose_adam(float* rots, const float* g_rots, int n_rots, float lr_rot
 }
 
 void launch_adam_counted(int P, int iso, float* const params[5], const float lr[5], const float* grad, float* m,
-                         float* v, float beta1, float beta2, float eps, float* step_state, cudaStream_t st) {
-    if (P <= 0) {   // nothing to update: the step still counts
+                         float* v, float beta1, float beta2, float eps, float* step_state, size_t e_begin, size_t e_end,
+                         int advance, cudaStream_t st) {
+    if (P <= 0 || adam_blocks(P, iso, e_begin, e_end) == 0) {   // nothing to update: the step still counts
+        if (!advance) return;
         adam_advance_kernel<<<1, 1, 0, st>>>(step_state, lr[0], lr[1], lr[2], lr[3], lr[4], beta1, beta2);
         return;
     }
     AdamPtrs ap;
     ap.p0 = params[0]; ap.p1 = params[1]; ap.p2 = params[2]; ap.p3 = params[3]; ap.p4 = params[4];
     ap.s0 = lr[0]; ap.s1 = lr[1]; ap.s2 = lr[2]; ap.s3 = lr[3]; ap.s4 = lr[4];
-    adam_kernel<<<adam_blocks(P, iso), AD_THREADS, 0, st>>>(P, iso, ap, grad, m, v, beta1, beta2, eps, 1.f, step_state);
+    adam_kernel<<<adam_blocks(P, iso, e_begin, e_end), AD_THREADS, 0, st>>>(P, iso, ap, grad, m, v, beta1, beta2, eps, 1.f,
+                                                                            step_state, e_begin, e_end, advance);
 }
 
 }  // namespace asb

@@ -567,6 +567,33 @@ class FusedAdam:
                 capi.check(L.as_adam_step(*args, self.t, stream))
 
 
+    @torch.no_grad()
+    def step_range(self, grad_flat, e_begin, e_end, advance):
+        """The update of the flat elements [e_begin, e_end) only (e_begin a multiple of 4): used when the gradient
+        arrives in chunks (dist.allreduce_and_step).  All chunks of one step see the same step count; `advance` goes
+        with the last one."""
+        if self.step_state is None:
+            raise RuntimeError("FusedAdam.step_range needs device_step=True")
+        L = capi.lib()
+        p = self.params
+        dev = p["means3D"].device
+        if advance:
+            self.t += 1
+        with torch.cuda.device(dev):
+            capi.check(L.as_adam_step_range(
+                int(p["means3D"].shape[0]), 1 if p["log_scales"].shape[1] == 1 else 0, p["means3D"].data_ptr(),
+                p["rgb_colors"].data_ptr(), p["unnorm_rotations"].data_ptr(), p["logit_opacities"].data_ptr(),
+                p["log_scales"].data_ptr(), grad_flat.data_ptr(), self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(),
+                self.lrs, self.betas[0], self.betas[1], self.eps, self.step_state.data_ptr(), int(e_begin), int(e_end),
+                int(bool(advance)), torch.cuda.current_stream(dev).cuda_stream))
+
+    @property
+    def n_flat(self):
+        """Flat elements in use: (11 + 1 or 3) per Gaussian."""
+        p = self.params
+        return (12 if p["log_scales"].shape[1] == 1 else 14) * int(p["means3D"].shape[0])
+
+
 class FusedPoseAdam:
     """torch.optim.Adam over cam_unnorm_rots / cam_trans as the tracking loop configures it
     (initialize_optimizer(tracking=True): default betas and eps 1e-8; lrs 1e-3 / 4e-3,

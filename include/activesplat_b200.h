@@ -248,6 +248,15 @@ int as_adam_step_counted(int P, int isotropic, float* means3D, float* rgb_colors
                          float* exp_avg_sq, const float* lrs, float beta1, float beta2, float eps, float* step_state,
                          void* cuda_stream);
 
+/* as_adam_step_counted restricted to the flat elements [e_begin, e_end) of the segment layout (e_begin a multiple of
+ * 4): a mapping step over several GPUs all-reduces the gradient in chunks and updates each chunk as soon as it has
+ * arrived, while the next one is still on the wire.  Every chunk of a step sees the same step count; pass
+ * advance_step != 0 with the LAST chunk only. */
+int as_adam_step_range(int P, int isotropic, float* means3D, float* rgb_colors, float* unnorm_rotations,
+                       float* logit_opacities, float* log_scales, const float* grad_params, float* exp_avg,
+                       float* exp_avg_sq, const float* lrs, float beta1, float beta2, float eps, float* step_state,
+                       long long e_begin, long long e_end, int advance_step, void* cuda_stream);
+
 /* Adam over the camera-pose tensors of a tracking loop (pose-only iterations: learning rates 1e-3 on cam_unnorm_rots
  * [1,4,T] and 4e-3 on cam_trans [1,3,T], torch's default eps 1e-8: initialize_optimizer(tracking=True),
  * splatam.py:118-122, config/splatam/online_habitat_sim.py:37-45).  n_rots / n_trans floats, dense; exp_avg / exp_avg_sq

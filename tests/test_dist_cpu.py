@@ -53,6 +53,46 @@ def _mapping_worker(rank, world, port, n_kf, q, weights=None):
     dist.destroy_process_group()
 
 
+class _SgdStandIn:
+    """step / step_range / n_flat of FusedAdam, as plain SGD on a CPU tensor (the chunking logic is what is tested)."""
+
+    def __init__(self, params, n_flat):
+        self.params, self.n_flat, self.calls, self.advanced = params, n_flat, [], 0
+
+    def step(self, flat):
+        self.step_range(flat, 0, self.n_flat, True)
+
+    def step_range(self, flat, e0, e1, advance):
+        self.calls.append((e0, e1))
+        self.advanced += int(bool(advance))
+        self.params[e0:e1].sub_(0.1 * flat[e0:e1])
+
+
+def _chunked_worker(rank, world, port, n, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from activesplat_b200 import dist as asd
+    flat = torch.randn(n + 7, generator=torch.Generator().manual_seed(500 + rank))   # tail beyond n_flat: untouched
+    params = torch.zeros(n + 7)
+    opt = _SgdStandIn(params, n)
+    asd.allreduce_and_step(flat, opt, n_chunks=4)
+    q.put((rank, params.clone(), opt.calls, opt.advanced))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_chunked_allreduce_and_step_equals_allreduce_then_step():
+    for n in (4000, 4001, 10):
+        res = _spawn(_chunked_worker, 2, n)
+        total = sum(torch.randn(n + 7, generator=torch.Generator().manual_seed(500 + r)) for r in range(2))
+        for r in range(2):
+            _, params, calls, advanced = res[r]
+            torch.testing.assert_close(params[:n], -0.1 * total[:n])
+            assert float(params[n:].abs().max()) == 0.0 and advanced == 1
+            assert calls[0][0] == 0 and calls[-1][1] == n and all(a[1] == b[0] for a, b in zip(calls, calls[1:]))
+            assert all(c[0] % 4 == 0 for c in calls)
+
+
 def _spawn(fn, world, *args):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()

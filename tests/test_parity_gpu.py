@@ -358,6 +358,31 @@ def test_fused_adam_matches_torch_adam():
             helpers.compare_float("adam " + k, mine[k].cpu().numpy(), ref[k].detach().numpy(), rel=1e-5)
 
 
+def test_adam_in_chunks_equals_adam_in_one_launch():
+    """as_adam_step_range over [0,a) [a,b) [b,n) with the step advanced by the last chunk == as_adam_step_counted,
+    bit for bit, over several steps (dist.allreduce_and_step relies on it)."""
+    from activesplat_b200.frame import FusedAdam, PARAM_ORDER
+    lrs = dict(means3D=1e-4, rgb_colors=2.5e-3, unnorm_rotations=1e-3, logit_opacities=5e-2, log_scales=1e-3)
+    dev = "cuda:0"
+    g = torch.Generator().manual_seed(9)
+    for P, iso in ((5003, False), (4096, True)):
+        shapes = {"means3D": 3, "rgb_colors": 3, "unnorm_rotations": 4, "logit_opacities": 1, "log_scales": 1 if iso else 3}
+        a = {k: torch.randn(P, w, generator=g).to(dev) for k, w in shapes.items()}
+        b = {k: v.clone() for k, v in a.items()}
+        oa, ob = FusedAdam(a, lrs), FusedAdam(b, lrs)
+        n = ob.n_flat
+        cuts = [0, (n // 3) // 4 * 4, (2 * n // 3) // 4 * 4, n]
+        for step in range(3):
+            flat = (torch.randn(14 * P, generator=g) * 10.0 ** (step - 1)).to(dev)
+            oa.step(flat)
+            for i in range(3):
+                ob.step_range(flat, cuts[i], cuts[i + 1], advance=(i == 2))
+        assert float(oa.step_state[0]) == 3.0 and float(ob.step_state[0]) == 3.0
+        for k in PARAM_ORDER:
+            assert torch.equal(a[k], b[k]), k
+        assert torch.equal(oa.exp_avg[:n], ob.exp_avg[:n]) and torch.equal(oa.exp_avg_sq[:n], ob.exp_avg_sq[:n])
+
+
 def test_mapping_get_loss_and_adam_steps_match_oracle():
     """get_loss(mapping=True) (0.8 L1 + 0.2 (1-SSIM) colour loss, masked mean depth loss, splatam.py:239-249)
     + Adam, three iterations: losses, gradients of all five tensors, and the parameters after the steps,
