@@ -108,7 +108,9 @@ def allreduce_and_step(flat_grad, optimizer, n_chunks=4, group=None):
     allreduce_gradients + optimizer.step: the update is elementwise."""
     _, world = world_info(group)
     flat = flat_grad.reshape(-1)
-    if world == 1:
+    if world == 1 or n_chunks <= 1:
+        if world > 1:
+            dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
         optimizer.step(flat)
         return
     n = optimizer.n_flat

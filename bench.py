@@ -54,6 +54,8 @@ def parse():
     ap.add_argument("--extras", default="cfg1,cfg2,cfg4,cfg5", help="comma list of sub-results, or 'none'")
     ap.add_argument("--no-ref-cuda", action="store_true", help="skip the reference-CUDA comparison legs")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--allreduce-chunks", type=int, default=1,
+                    help="N > 1: pieces the gradient all-reduce is issued in (each piece updated on arrival)")
     ap.add_argument("--no-graphs", action="store_true", help="time the eager launch path instead of CUDA-graph replays")
     return ap.parse_args()
 
@@ -219,7 +221,7 @@ def run_ours(args, rank, world, local_rank):
 
     def exchange_and_update():
         # the keyframe batch's gradient: sum over ranks (NCCL over NVLink, in chunks), each chunk updated on arrival
-        asd.allreduce_and_step(ws.grad_params, opt)
+        asd.allreduce_and_step(ws.grad_params, opt, n_chunks=args.allreduce_chunks)
 
     def eager_step(i, e2e):
         if e2e:
@@ -280,7 +282,14 @@ def run_ours(args, rank, world, local_rank):
             else:
                 g_res = GraphedStep(lambda: fwd_bwd(gt_dev))
                 g_e2e = [GraphedStep(lambda s=s: fwd_bwd(gt_stage[s])) for s in range(2)]
-                g_upd = exchange_and_update
+                g_adam = GraphedStep(lambda: opt.step(ws.grad_params))
+
+                def g_upd():
+                    if args.allreduce_chunks > 1:
+                        exchange_and_update()
+                    else:
+                        dist.all_reduce(ws.grad_params)
+                        g_adam()
             graphed = (g_res, g_e2e, g_upd)
         except Exception as ex:  # graphs are an optimisation of the launch path, not a different code path
             sys.stderr.write(f"[bench] CUDA graph capture unavailable, timing the eager path: {ex}\n")
@@ -360,8 +369,8 @@ def run_ours(args, rank, world, local_rank):
                    "parallelism": ("single GPU" if world == 1 else
                                    f"data-parallel mapping over a {world}-keyframe batch: map replicated, one keyframe "
                                    f"per rank, NCCL all-reduce of the flat fp32 gradient, 14 floats per Gaussian ({P * 56 / 1e6:.0f} MB), "
-                                   "in 4 chunks inside the timed region, each chunk's Adam update overlapping the next "
-                                   "chunk's all-reduce; identical parameters on every rank")},
+                                   f"inside the timed region ({args.allreduce_chunks} piece(s), each updated on arrival); "
+                                   "identical parameters on every rank")},
         "e2e": {"value": N * args.steps * world / (ms_e2e * 1e-3) / 1e6, "unit": "Mpix/s",
                 "h2d_bytes_per_step": int(gt_host.numel() * 4), "d2h_bytes_per_step": 4,
                 "api": "activesplat_b200.splatam.get_loss(mapping=True) + loss.backward() (inside "
