@@ -197,61 +197,46 @@ def get_loss(params, curr_data, variables, iter_time_idx, loss_weights, use_sil_
                                         sil_thres)
     if (not tracking and use_l1 and not ignore_outlier_depth_loss and params['means3D'].is_cuda):
         return _get_loss_mapping_fused(params, curr_data, variables, iter_time_idx, loss_weights, mapping and do_ba)
-    losses = {}
-    gaussians_grad = not tracking
-    camera_grad = tracking or (mapping and do_ba)
-    if params['means3D'].is_cuda:
-        # fused frame node: transform + activations + features + 6-channel render, backward to raw params
-        from .frame import fused_render
-        p = dict(params)
-        if not gaussians_grad:
-            p['means3D'], p['unnorm_rotations'] = p['means3D'].detach(), p['unnorm_rotations'].detach()
-        if not camera_grad:
-            p['cam_unnorm_rots'], p['cam_trans'] = p['cam_unnorm_rots'].detach(), p['cam_trans'].detach()
-        c6, radius, _, _, _ = fused_render(p, curr_data['cam'], int(iter_time_idx), curr_data['w2c'])
-        im, depth_sil = c6[:3], c6[3:]
-        variables['means2D'] = None
-    else:
-        tg = transform_to_frame(params, iter_time_idx, gaussians_grad=gaussians_grad, camera_grad=camera_grad)
-        rendervar = transformed_params2rendervar(params, tg)
-        depth_sil_colors = get_depth_and_silhouette(tg['means3D'], curr_data['w2c'])
-        rendervar['means2D'].retain_grad()
-        im, radius, _, _, depth_sil = render_bundle(curr_data['cam'], rendervar, depth_sil_colors)
-        variables['means2D'] = rendervar['means2D']
-    depth = depth_sil[0, :, :].unsqueeze(0)
-    silhouette = depth_sil[1, :, :]
-    presence_sil_mask = (silhouette > sil_thres)
-    depth_sq = depth_sil[2, :, :].unsqueeze(0)
-    invisibility = (depth_sq - depth ** 2).detach()
-    nan_mask = (~torch.isnan(depth)) & (~torch.isnan(invisibility))
-    if ignore_outlier_depth_loss:
-        depth_error = torch.abs(curr_data['depth'] - depth) * (curr_data['depth'] > 0)
-        mask = (depth_error < 10 * depth_error.median()) & (curr_data['depth'] > 0)
-    else:
-        mask = (curr_data['depth'] > 0)
-    mask = mask & nan_mask
+    # The remaining combinations (outlier-rejecting depth mask, or no L1 depth term) are not on ActiveSplat's path
+    # (config/splatam/online_habitat_sim.py:26-29,52-54): the bundle still comes from the fused frame node, differentiable
+    # down to the raw parameters and the pose; only the masking and the reductions are torch ops.
+    if not params['means3D'].is_cuda:
+        raise RuntimeError("activesplat_b200.splatam.get_loss needs CUDA tensors (there is no CPU path)")
+    from .frame import fused_render
+    frozen = set()
+    if tracking:
+        frozen |= {'means3D', 'unnorm_rotations'}          # transform_to_frame(gaussians_grad=False)
+    if not (tracking or (mapping and do_ba)):
+        frozen |= {'cam_unnorm_rots', 'cam_trans'}         # transform_to_frame(camera_grad=False)
+    p = {k: (v.detach() if k in frozen else v) for k, v in params.items()}
+    bundle, radius, _, _, _ = fused_render(p, curr_data['cam'], int(iter_time_idx), curr_data['w2c'])
+    variables['means2D'] = _NO_MEANS2D
+    rgb, z, sil, z_sq = bundle[0:3], bundle[3:4], bundle[4], bundle[5:6]
+    gt_rgb, gt_z = curr_data['im'], curr_data['depth']
+    z_err = (gt_z - z).abs()
+    valid = (gt_z > 0) & ~torch.isnan(z) & ~torch.isnan((z_sq - z * z).detach())
+    if ignore_outlier_depth_loss:                          # splatam.py:223-226: ten times the median error
+        masked_err = z_err * (gt_z > 0)
+        valid = valid & (masked_err < 10 * masked_err.median())
     if tracking and use_sil_for_loss:
-        mask = mask & presence_sil_mask
+        valid = valid & (sil > sil_thres)
+    valid = valid.detach()
+    terms = {}
     if use_l1:
-        mask = mask.detach()
-        if tracking:
-            losses['depth'] = torch.abs(curr_data['depth'] - depth)[mask].sum()
-        else:
-            losses['depth'] = torch.abs(curr_data['depth'] - depth)[mask].mean()
-    if tracking and (use_sil_for_loss or ignore_outlier_depth_loss):
-        color_mask = torch.tile(mask, (3, 1, 1)).detach()
-        losses['im'] = torch.abs(curr_data['im'] - im)[color_mask].sum()
-    elif tracking:
-        losses['im'] = torch.abs(curr_data['im'] - im).sum()
+        picked = z_err[valid]
+        terms['depth'] = picked.sum() if tracking else picked.mean()
+    if tracking:
+        rgb_err = (gt_rgb - rgb).abs()
+        if use_sil_for_loss or ignore_outlier_depth_loss:
+            rgb_err = rgb_err[valid.expand_as(rgb_err)]
+        terms['im'] = rgb_err.sum()
     else:
-        losses['im'] = 0.8 * l1_loss_v1(im, curr_data['im']) + 0.2 * (1.0 - calc_ssim(im, curr_data['im']))
-    weighted_losses = {k: v * loss_weights[k] for k, v in losses.items()}
+        terms['im'] = 0.8 * l1_loss_v1(rgb, gt_rgb) + 0.2 * (1.0 - calc_ssim(rgb, gt_rgb))
+    weighted_losses = {k: v * loss_weights[k] for k, v in terms.items()}
     loss = sum(weighted_losses.values())
-    seen = radius > 0
-    # == max_2D_radius[seen] = max(radius[seen], max_2D_radius[seen]) (splatam.py:296-298) without the
-    # boolean-index host sync: radius is 0 exactly where the Gaussian was not seen
+    # max_2D_radius[seen] = max(radius[seen], ...) without a boolean-index host sync: radius is 0 where unseen
     variables['max_2D_radius'] = torch.maximum(variables['max_2D_radius'], radius.to(variables['max_2D_radius'].dtype))
-    variables['seen'] = seen
+    variables['seen'] = radius > 0
     weighted_losses['loss'] = loss
     return loss, variables, weighted_losses
 
