@@ -466,27 +466,23 @@ class _FusedFrameRender(torch.autograd.Function):
 def fused_render(params, cam, time_idx, sil_w2c=None, bg_rgb=None, ws=None):
     """(colour6 [6,H,W], radii, median depth, opacity, workspace); colour6 is differentiable w.r.t. `params`.
     Without a workspace argument, a call that needs no gradient uses the "render" workspace."""
+    needs_grad = torch.is_grad_enabled() and any(
+        params[k].requires_grad for k in PARAM_ORDER + ("cam_unnorm_rots", "cam_trans"))
     if ws is None:
-        needs_grad = torch.is_grad_enabled() and any(
-            params[k].requires_grad for k in PARAM_ORDER + ("cam_unnorm_rots", "cam_trans"))
         ws = workspace_for(params, cam, "train" if needs_grad else "render")
-        if not needs_grad:
-            # a render nobody differentiates: worth one look at the status words (synchronises, as the callers of
-            # these paths do anyway) so that a binning overflow is repaired instead of returned as a background image
-            for _ in range(3):
-                out = _FusedFrameRender.apply(
-                    params["means3D"], params["rgb_colors"], params["unnorm_rotations"], params["logit_opacities"],
-                    params["log_scales"], params["cam_unnorm_rots"], params["cam_trans"], ws, cam, time_idx, sil_w2c,
-                    bg_rgb)
-                n_inst, overflowed = ws.last_status()
-                if not overflowed:
-                    return (*out, ws)
-                ws.ensure_capacity(n_inst + n_inst // 4)
-            raise RuntimeError(f"activesplat_b200: binning buffer still too small after growing it to {ws.capacity}")
-    c6, radii, depth, opacity = _FusedFrameRender.apply(
-        params["means3D"], params["rgb_colors"], params["unnorm_rotations"], params["logit_opacities"],
-        params["log_scales"], params["cam_unnorm_rots"], params["cam_trans"], ws, cam, time_idx, sil_w2c, bg_rgb)
-    return c6, radii, depth, opacity, ws
+    args = (params["means3D"], params["rgb_colors"], params["unnorm_rotations"], params["logit_opacities"],
+            params["log_scales"], params["cam_unnorm_rots"], params["cam_trans"], ws, cam, time_idx, sil_w2c, bg_rgb)
+    if needs_grad or torch.cuda.is_current_stream_capturing():
+        return (*_FusedFrameRender.apply(*args), ws)
+    # a render nobody differentiates: worth one look at the status words (synchronises, as the callers of these paths do
+    # anyway) so that a binning overflow is repaired instead of returned as a background image
+    for _ in range(3):
+        out = _FusedFrameRender.apply(*args)
+        n_inst, overflowed = ws.last_status()
+        if not overflowed:
+            return (*out, ws)
+        ws.ensure_capacity(n_inst + n_inst // 4)
+    raise RuntimeError(f"activesplat_b200: binning buffer still too small after growing it to {ws.capacity}")
 
 
 _IDENTITY_POSE = {}

@@ -333,6 +333,41 @@ def test_fused_frame_gaussian_gradients_match_oracle(iso):
     helpers.compare_exact("re-run after growing", ws_small.color6.cpu().numpy(), ws.color6.cpu().numpy())
 
 
+def test_workspace_guards():
+    """One frame per workspace: the backward of a node whose buffers were overwritten raises (instead of differentiating
+    another frame); a second backward raises; a no-grad render through a workspace whose binning buffer is too small
+    is repaired; the screen-space gradient the fused path does not keep says so."""
+    from activesplat_b200 import frame, splatam
+    params, cams, gt_rgb, gt_depth = helpers.frame_case(P=1500, W=96, H=64, seed=5)
+    dev = "cuda:0"
+    p = {k: v.clone().to(dev).requires_grad_(True) for k, v in params.items()}
+    cam = splatam.setup_camera(96, 64, cams[0].k(), np.eye(4), device=dev)
+    cur = {"cam": cam, "im": gt_rgb.to(dev), "depth": gt_depth.to(dev), "w2c": torch.eye(4, device=dev)}
+    var = {"max_2D_radius": torch.zeros(1500, device=dev)}
+    lw = dict(im=0.5, depth=1.0)
+    loss0, var, _ = splatam.get_loss(p, cur, var, 0, lw, False, 0.98, True, False, mapping=True)
+    loss1, var, _ = splatam.get_loss(p, cur, var, 1, lw, False, 0.98, True, False, mapping=True)
+    with pytest.raises(RuntimeError, match="another frame was rendered"):
+        loss0.backward()
+    loss1.backward(retain_graph=True)
+    with pytest.raises(RuntimeError, match="a second time"):
+        loss1.backward()
+    with pytest.raises(NotImplementedError, match="means2D"):
+        var["means2D"].grad
+    # a no-grad render does not disturb a frame whose backward is still to come (separate workspace) ...
+    loss2, var, _ = splatam.get_loss(p, cur, var, 2, lw, False, 0.98, True, False, mapping=True)
+    with torch.no_grad():
+        splatam.render_view({k: v.detach() for k, v in p.items()}, cams[0].w2c, cams[0].k(), 96, 64)
+    loss2.backward()
+    # ... and repairs an overflow of its binning buffer instead of returning a background image
+    small = frame.FrameWorkspace(1500, 96, 64, dev, capacity=64)
+    with torch.no_grad():
+        im_s, _, op_s, _ = splatam.render_view({k: v.detach() for k, v in p.items()}, cams[0].w2c, cams[0].k(), 96, 64, ws=small)
+        im_r, _, op_r, _ = splatam.render_view({k: v.detach() for k, v in p.items()}, cams[0].w2c, cams[0].k(), 96, 64)
+    assert small.capacity > 64 and float(op_r.max()) > 0.5
+    assert torch.equal(im_s, im_r) and torch.equal(op_s, op_r)
+
+
 def test_fused_adam_matches_torch_adam():
     """as_adam_step vs torch.optim.Adam(eps=1e-15) as configured by initialize_optimizer (splatam.py:118-124)."""
     from activesplat_b200.frame import FusedAdam, PARAM_ORDER, pack_flat
