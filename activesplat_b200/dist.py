@@ -100,12 +100,13 @@ def allreduce_gradients(flat_grad, group=None):
     return flat_grad
 
 
-def allreduce_and_step(flat_grad, optimizer, n_chunks=4, group=None):
-    """Sum the flat gradient across ranks and apply the optimizer, pipelined: the buffer is all-reduced in `n_chunks`
-    pieces issued back to back on NCCL's stream, and each piece is updated (FusedAdam.step_range) as soon as it has
-    arrived, while the next ones are still on the wire -- the update of a 1M-Gaussian map takes about as long as
-    moving its gradient over NVLink, so most of it disappears behind the exchange.  Same result as
-    allreduce_gradients + optimizer.step: the update is elementwise."""
+def allreduce_and_step(flat_grad, optimizer, n_chunks=1, group=None):
+    """Sum the flat gradient across ranks and apply the optimizer: the exchange + update of a mapping step.
+    n_chunks > 1 pipelines the two: the buffer is all-reduced in pieces issued back to back on NCCL's stream and each
+    piece is updated (FusedAdam.step_range) as soon as it has arrived, while the next ones are still on the wire.  Same
+    result (the update is elementwise).  Measured on 2 B200s with a 56 MB gradient (1M Gaussians): one piece 0.874 ms
+    per step, two 0.901, four 0.958 -- every extra NCCL launch costs more than the overlap returns, also inside a CUDA
+    graph -- so one piece is the default; the option is kept for larger maps and slower links."""
     _, world = world_info(group)
     flat = flat_grad.reshape(-1)
     if world == 1 or n_chunks <= 1:

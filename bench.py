@@ -56,6 +56,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--allreduce-chunks", type=int, default=1,
                     help="N > 1: pieces the gradient all-reduce is issued in (each piece updated on arrival)")
+    ap.add_argument("--graph-collective", action="store_true",
+                    help="N > 1: capture the all-reduce and the update in the step's CUDA graph as well")
     ap.add_argument("--no-graphs", action="store_true", help="time the eager launch path instead of CUDA-graph replays")
     return ap.parse_args()
 
@@ -275,7 +277,7 @@ def run_ours(args, rank, world, local_rank):
     graphed = None
     if not args.no_graphs:
         try:
-            if world == 1:
+            if world == 1 or args.graph_collective:
                 g_res = GraphedStep(lambda: (fwd_bwd(gt_dev), exchange_and_update())[0])
                 g_e2e = [GraphedStep(lambda s=s: (fwd_bwd(gt_stage[s]), exchange_and_update())[0]) for s in range(2)]
                 g_upd = None
