@@ -95,6 +95,7 @@ class AsFrameArgs(ctypes.Structure):
         ("debug", ctypes.c_int),
         ("max_2D_radius", ctypes.c_void_p), ("seen", ctypes.c_void_p),
         ("binning_mode", ctypes.c_int),
+        ("chunk_scratch", ctypes.c_void_p),
     ]
 
 
@@ -136,6 +137,7 @@ SYMBOLS = {
     "as_mapping_loss_scratch_floats": (_Z, [_I, _I]),
     "as_mapping_loss": (_I, [_I, _I, _V, _V, _V, _F, _F, _V, _V, _V, _V, _V]),
     "as_adam_step": (_I, [_I, _I, _V, _V, _V, _V, _V, _V, _V, _V, ctypes.POINTER(ctypes.c_float), _F, _F, _F, _I, _V]),
+    "as_chunk_scratch_bytes": (_Z, [_I, _I, _I]),
     "as_densify_scratch_words": (ctypes.c_size_t, [_I, _I]),
     "as_densify": (_I, [ctypes.POINTER(AsDensifyArgs), _V]),
     "as_cluster_hull_volumes": (_I, [_I, _I, _I, _V, _V, _V, ctypes.c_double, _I, _V, _V, _V]),

@@ -325,6 +325,236 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
     }
 }
 
+// ---- forward, split along the list ("chunked") ------------------------------------------------------
+// A low-resolution wide-angle candidate view puts 10^4-10^5 records on each of a few dozen tiles; one warp per strip
+// then walks them serially (1.4 of a 1.9 ms view, with 640 warps on the whole GPU).  Here a tile's list is cut into
+// chunks of BL_CHUNK records and every chunk gets its own CTA, in two passes:
+//   pass A  transmittance only: T_k = product of (1 - alpha) over the chunk's accepted records, from T = 1
+//           (a pixel stops once its chunk-local T drops below 1e-4: everything behind it is dead anyway);
+//   pass B  the reference's loop, unchanged, from the TRUE transmittance at the chunk's start, prefix_k = T_0 ... T_{k-1}:
+//           the 1e-4 stop rule and the T = 0.5 median-depth rule fire inside whichever chunk they belong to; a chunk
+//           whose prefix is already below 1e-4 does nothing;
+//   combine sums the chunks' colour contributions in list order, takes the median depth from the chunk that set it and
+//           the final T from the last live chunk.
+// Differences from the single walk: T at a chunk start is a product of chunk products (rounding ~1e-7), and
+// n_contrib is not produced -- this path is for renders that nobody differentiates (GetOpacity sweeps).
+constexpr int BL_CHUNK = 1024;       // records per chunk (8 staged batches)
+constexpr int CHUNK_FIELDS = 9;      // per (chunk, pixel): T_k | colour sums [6] | median depth or -1 | T after the chunk
+
+// per tile: number of chunks and the index of its first chunk; per chunk: its tile.  One block.
+__global__ void __launch_bounds__(1024)
+blend_chunk_table_kernel(const uint2* __restrict__ ranges, int tiles, int max_chunks, int* __restrict__ chunk_base,
+                         int* __restrict__ chunk_tile) {
+    __shared__ int s_scan[1024];
+    __shared__ int s_carry;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    for (int base = 0; base < tiles; base += 1024) {
+        const int t = base + threadIdx.x;
+        int n = 0;
+        if (t < tiles) {
+            const uint2 r = ranges[t];
+            n = (int)((r.y - r.x + BL_CHUNK - 1) / BL_CHUNK);
+        }
+        s_scan[threadIdx.x] = n;
+        __syncthreads();
+        for (int off = 1; off < 1024; off <<= 1) {
+            const int v = (threadIdx.x >= off) ? s_scan[threadIdx.x - off] : 0;
+            __syncthreads();
+            s_scan[threadIdx.x] += v;
+            __syncthreads();
+        }
+        const int first = s_carry + s_scan[threadIdx.x] - n;
+        if (t < tiles) {
+            chunk_base[t] = first;
+            for (int k = 0; k < n && first + k < max_chunks; k++) chunk_tile[first + k] = t;
+        }
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry += s_scan[1023];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) chunk_base[tiles] = min(s_carry, max_chunks);
+}
+
+template <int C, int PASS>
+__global__ void __launch_bounds__(BL_THREADS)
+blend_forward_chunk_kernel(const uint2* __restrict__ ranges, const float4* __restrict__ inst_conic,
+                           const float4* __restrict__ inst_geom, const float4* __restrict__ inst_feat, int W, int H,
+                           int gx, int tiles, const int* __restrict__ chunk_base, const int* __restrict__ chunk_tile,
+                           float* __restrict__ scratch) {
+    constexpr int FV = BlendSmem<C>::FV;
+    const int chunk = blockIdx.x;
+    if (chunk >= chunk_base[tiles]) return;
+    __shared__ __align__(128) BlendSmem<C> sm;
+    __shared__ uint8_t s_list[BL_THREADS / 32][BL_BATCH];
+    __shared__ uint32_t s_mask[BL_THREADS / 32][BL_BATCH];
+    const int tile = chunk_tile[chunk];
+    const int k = chunk - chunk_base[tile];
+    const int tx = tile % gx, ty = tile / gx;
+    const int lane = threadIdx.x & 31, strip = threadIdx.x >> 5;
+    const int px = tx * TILE_X + (lane & (TILE_X - 1));
+    const int py = ty * TILE_Y + 2 * strip + (lane >> 4);
+    const bool inside = px < W && py < H;
+    const float pxf = (float)px, pyf = (float)py;
+    const float strip_x0 = (float)(tx * TILE_X), strip_y0 = (float)(ty * TILE_Y + 2 * strip);
+    const uint2 tr = ranges[tile];
+    const uint32_t begin = tr.x + (uint32_t)k * BL_CHUNK;
+    const int len = (int)min((uint32_t)BL_CHUNK, tr.y - begin);
+    const int nb = (len + BL_BATCH - 1) / BL_BATCH;
+    const int pix = strip * 32 + lane;                                   // pixel slot of the tile
+    float* mine = scratch + (size_t)chunk * CHUNK_FIELDS * TILE_PIX + pix;   // field f at mine[f * TILE_PIX]
+
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int q = 0; q < BL_STAGES; q++) mbar_init(&sm.bar[q], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0)
+        for (int q = 0; q < BL_STAGES && q < nb; q++)
+            issue_batch(sm, q, inst_conic, inst_geom, inst_feat, begin + q * BL_BATCH, min(BL_BATCH, len - q * BL_BATCH));
+
+    float T = 1.0f;
+    if (PASS == 2) {   // the true transmittance at the start of this chunk
+        const float* tk = scratch + (size_t)chunk_base[tile] * CHUNK_FIELDS * TILE_PIX + pix;
+        for (int j = 0; j < k; j++) T *= tk[(size_t)j * CHUNK_FIELDS * TILE_PIX];
+    }
+    bool done = !inside || (PASS == 2 && T < 0.0001f);
+    float D = -1.0f;
+    float acc[C];
+#pragma unroll
+    for (int ch = 0; ch < C; ch++) acc[ch] = 0.f;
+
+    int consumed = 0;
+    for (int b = 0; b < nb; b++) {
+        const int s = b & (BL_STAGES - 1);
+        mbar_wait(&sm.bar[s], (uint32_t)((b / BL_STAGES) & 1));
+        const int cnt = min(BL_BATCH, len - b * BL_BATCH);
+        bool warp_done = __all_sync(0xffffffffu, done);
+        if (!warp_done) {
+            uint8_t* list = s_list[strip];
+            uint32_t* masks = s_mask[strip];
+            const int n = cull_batch(sm, s, cnt, lane, strip_x0, strip_y0, list, masks);
+#pragma unroll 1
+            for (int g0 = 0; g0 < n && !warp_done; g0 += 32) {
+                const bool have = g0 + lane < n;
+                const int jmine = have ? (int)list[g0 + lane] : 0;
+                uint32_t hits = warp_bit_transpose(have ? masks[g0 + lane] : 0u, lane);
+                if (done) hits = 0u;
+#pragma unroll 1
+                while (__any_sync(0xffffffffu, hits != 0u)) {
+                    int jj[FW_UNROLL];
+                    uint32_t valid = 0u;
+#pragma unroll
+                    for (int u = 0; u < FW_UNROLL; u++) {
+                        const bool has = hits != 0u;
+                        const int r = has ? (__ffs((int)hits) - 1) : 0;
+                        hits &= hits - 1u;
+                        jj[u] = __shfl_sync(0xffffffffu, jmine, r);
+                        if (has) valid |= 1u << u;
+                    }
+                    float al[FW_UNROLL];
+                    uint32_t hit = 0u;
+#pragma unroll
+                    for (int u = 0; u < FW_UNROLL; u++) {
+                        const float4 co = sm.conic[s][jj[u]];
+                        const float4 ge = sm.geom[s][jj[u]];
+                        const float dx = __fsub_rn(ge.x, pxf), dy = __fsub_rn(ge.y, pyf);
+                        const float power = eval_power(co, dx, dy);
+                        const float alpha = fminf(0.99f, __fmul_rn(co.w, expf(power)));
+                        al[u] = alpha;
+                        if (((valid >> u) & 1u) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f)) hit |= 1u << u;
+                    }
+#pragma unroll
+                    for (int u = 0; u < FW_UNROLL; u++) {
+                        const int j = jj[u];
+                        const float alpha = al[u];
+                        const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
+                        const bool h = ((hit >> u) & 1u) && !done;
+                        const bool stop = h && (test_T < 0.0001f);
+                        if (PASS == 1) {
+                            T = h ? test_T : T;       // pass A keeps the product (below 1e-4 = "dead from here on")
+                            done = done || stop;
+                        } else {
+                            const bool blend = h && !stop;   // forward.cu:355-359: stop BEFORE blending it
+                            done = done || stop;
+                            const float4 f0 = sm.feat[s][j * FV];
+                            acc[0] = blend ? __fmaf_rn(__fmul_rn(f0.x, alpha), T, acc[0]) : acc[0];
+                            acc[1] = blend ? __fmaf_rn(__fmul_rn(f0.y, alpha), T, acc[1]) : acc[1];
+                            acc[2] = blend ? __fmaf_rn(__fmul_rn(f0.z, alpha), T, acc[2]) : acc[2];
+                            if (C == 6) {
+                                const float4 f1 = sm.feat[s][j * FV + FV - 1];
+                                acc[3 % C] = blend ? __fmaf_rn(__fmul_rn(f0.w, alpha), T, acc[3 % C]) : acc[3 % C];
+                                acc[4 % C] = blend ? __fmaf_rn(__fmul_rn(f1.x, alpha), T, acc[4 % C]) : acc[4 % C];
+                                acc[5 % C] = blend ? __fmaf_rn(__fmul_rn(f1.y, alpha), T, acc[5 % C]) : acc[5 % C];
+                            }
+                            if (blend && T > 0.5f && test_T < 0.5f) D = sm.geom[s][j].z;   // forward.cu:370-374
+                            T = blend ? test_T : T;
+                        }
+                    }
+                    if (done) hits = 0u;
+                }
+                warp_done = __all_sync(0xffffffffu, done);
+            }
+            __syncwarp();
+        }
+        consumed = b + 1;
+        if (__syncthreads_count(done) == BL_THREADS) break;
+        if (threadIdx.x == 0 && b + BL_STAGES < nb) {
+            const int nstart = (b + BL_STAGES) * BL_BATCH;
+            issue_batch(sm, s, inst_conic, inst_geom, inst_feat, begin + nstart, min(BL_BATCH, len - nstart));
+        }
+    }
+    if (consumed >= 1)
+        for (int q = consumed; q < nb && q < consumed - 1 + BL_STAGES; q++)
+            mbar_wait(&sm.bar[q & (BL_STAGES - 1)], (uint32_t)((q / BL_STAGES) & 1));
+
+    if (PASS == 1) {
+        mine[0] = T;
+    } else {
+#pragma unroll
+        for (int ch = 0; ch < C; ch++) mine[(1 + ch) * TILE_PIX] = acc[ch];
+        mine[7 * TILE_PIX] = D;
+        mine[8 * TILE_PIX] = T;
+    }
+}
+
+// one CTA per tile: the chunks' results in list order -> the images
+template <int C>
+__global__ void __launch_bounds__(BL_THREADS)
+blend_chunk_combine_kernel(int W, int H, int gx, const int* __restrict__ chunk_base, const float* __restrict__ scratch,
+                           const float* __restrict__ bg, float* __restrict__ out_color, float* __restrict__ out_depth,
+                           float* __restrict__ out_opacity, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib) {
+    const int tile = blockIdx.x;
+    const int tx = tile % gx, ty = tile / gx;
+    const int lane = threadIdx.x & 31, strip = threadIdx.x >> 5;
+    const int px = tx * TILE_X + (lane & (TILE_X - 1));
+    const int py = ty * TILE_Y + 2 * strip + (lane >> 4);
+    if (px >= W || py >= H) return;
+    const int c0 = chunk_base[tile], c1 = chunk_base[tile + 1];
+    float acc[C];
+#pragma unroll
+    for (int ch = 0; ch < C; ch++) acc[ch] = 0.f;
+    float T = 1.0f, prefix = 1.0f, D = 15.0f;   // median depth default (forward.cu:309)
+    bool d_set = false;
+    for (int c = c0; c < c1 && !(prefix < 0.0001f); c++) {
+        const float* f = scratch + (size_t)c * CHUNK_FIELDS * TILE_PIX + threadIdx.x;
+#pragma unroll
+        for (int ch = 0; ch < C; ch++) acc[ch] += f[(1 + ch) * TILE_PIX];
+        const float d = f[7 * TILE_PIX];
+        if (!d_set && d >= 0.f) { D = d; d_set = true; }
+        T = f[8 * TILE_PIX];
+        prefix *= f[0];
+    }
+    const size_t pix_id = (size_t)W * py + px;
+    final_T[pix_id] = T;
+    n_contrib[pix_id] = 0u;   // not produced on this path (no backward follows it)
+#pragma unroll
+    for (int ch = 0; ch < C; ch++) out_color[(size_t)ch * H * W + pix_id] = __fmaf_rn(T, __ldg(bg + ch), acc[ch]);
+    out_depth[pix_id] = D;
+    out_opacity[pix_id] = __fsub_rn(1.f, T);
+}
+
 // ---- backward -----------------------------------------------------------------------------------
 // The reference walks every pixel back to front and issues 9 global atomics per (pixel, Gaussian)
 // (backward.cu:486-554).  Here a warp handles its 16x2 strip in groups of BW_GROUP surviving records:
@@ -682,6 +912,34 @@ void launch_blend_forward(int channels, int W, int H, const uint2* ranges, const
     else
         launch_fwd_c<6>(warps, tiles, st, ranges, b, W, H, gx, bg, out_color, out_depth, out_opacity, final_T, n_contrib,
                         tile_order);
+}
+
+// scratch of the chunked forward: chunk_base [tiles + 1] | chunk_tile [max_chunks] | per-chunk fields
+int blend_chunk_count_bound(int capacity, int tiles) { return capacity / BL_CHUNK + tiles + 1; }
+size_t blend_chunk_scratch_bytes(int capacity, int tiles) {
+    const size_t mc = (size_t)blend_chunk_count_bound(capacity, tiles);
+    const size_t ints = ((size_t)tiles + 1 + mc + 3) / 4 * 4;
+    return ints * sizeof(int) + mc * CHUNK_FIELDS * TILE_PIX * sizeof(float);
+}
+
+void launch_blend_forward_chunked(int W, int H, const uint2* ranges, const BinningState& b, int capacity, const float* bg,
+                                  float* out_color, float* out_depth, float* out_opacity, float* final_T,
+                                  uint32_t* n_contrib, void* scratch, cudaStream_t st) {
+    const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
+    const int tiles = gx * gy;
+    if (tiles <= 0) return;
+    const int mc = blend_chunk_count_bound(capacity, tiles);
+    int* chunk_base = reinterpret_cast<int*>(scratch);
+    int* chunk_tile = chunk_base + tiles + 1;
+    const size_t ints = ((size_t)tiles + 1 + mc + 3) / 4 * 4;
+    float* fields = reinterpret_cast<float*>(chunk_base + ints);
+    blend_chunk_table_kernel<<<1, 1024, 0, st>>>(ranges, tiles, mc, chunk_base, chunk_tile);
+    blend_forward_chunk_kernel<6, 1><<<mc, BL_THREADS, 0, st>>>(ranges, b.inst_conic, b.inst_geom, b.inst_feat, W, H, gx,
+                                                                tiles, chunk_base, chunk_tile, fields);
+    blend_forward_chunk_kernel<6, 2><<<mc, BL_THREADS, 0, st>>>(ranges, b.inst_conic, b.inst_geom, b.inst_feat, W, H, gx,
+                                                                tiles, chunk_base, chunk_tile, fields);
+    blend_chunk_combine_kernel<6><<<tiles, BL_THREADS, 0, st>>>(W, H, gx, chunk_base, fields, bg, out_color, out_depth,
+                                                               out_opacity, final_T, n_contrib);
 }
 
 void launch_blend_backward(int channels, int W, int H, const uint2* ranges, const BinningState& b, const float* bg,

@@ -367,12 +367,21 @@ int as_frame_forward(const AsFrameArgs* a, void* cuda_stream) {
         }
     }
     if ((r = stage_check(st, a->debug))) return r;
-    {
+    if (a->chunk_scratch) {   // crowded tiles: the lists are blended in chunks, one CTA per chunk (forward-only renders)
+        StageScope _s(AS_STAGE_BLEND_FWD, st, 4);
+        launch_blend_forward_chunked(W, H, img.ranges, b, cap, a->background, a->out_color, a->out_depth, a->out_opacity,
+                                     img.final_T, img.n_contrib, a->chunk_scratch, st);
+    } else {
         StageScope _s(AS_STAGE_BLEND_FWD, st, 1);
         launch_blend_forward(6, W, H, img.ranges, b, a->background, a->out_color, a->out_depth, a->out_opacity,
                              img.final_T, img.n_contrib, st, buckets ? img.tile_order : nullptr);
     }
     return stage_check(st, a->debug);
+}
+
+size_t as_chunk_scratch_bytes(int binning_capacity, int width, int height) {
+    const int tiles = ((width + TILE_X - 1) / TILE_X) * ((height + TILE_Y - 1) / TILE_Y);
+    return blend_chunk_scratch_bytes(binning_capacity > 0 ? binning_capacity : 0, tiles);
 }
 
 int as_frame_backward(const AsFrameBackwardArgs* ba, void* cuda_stream) {

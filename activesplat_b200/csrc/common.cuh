@@ -115,6 +115,11 @@ void launch_ranges_and_gather(int R, int tiles, int channels, const uint64_t* ke
                               const uint32_t* point_list, const GeometryState& g, const float* features,
                               const BinningState& b, uint2* ranges, cudaStream_t st);
 
+int blend_chunk_count_bound(int capacity, int tiles);
+size_t blend_chunk_scratch_bytes(int capacity, int tiles);
+void launch_blend_forward_chunked(int W, int H, const uint2* ranges, const BinningState& b, int capacity, const float* bg,
+                                  float* out_color, float* out_depth, float* out_opacity, float* final_T,
+                                  uint32_t* n_contrib, void* scratch, cudaStream_t st);
 void launch_blend_forward(int channels, int W, int H, const uint2* ranges, const BinningState& b,
                           const float* bg, float* out_color, float* out_depth, float* out_opacity,
                           float* final_T, uint32_t* n_contrib, cudaStream_t st, const uint32_t* tile_order = nullptr);

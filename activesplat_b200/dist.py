@@ -211,7 +211,7 @@ def score_candidate_views(params, views, group=None, n_streams=32, scale_modifie
                                      prefiltered=False, debug=False)
                 s = j % n_streams
                 with torch.cuda.stream(streams[s]):
-                    wss[s].forward(p, cam, 0, sil_w2c=row[32:48].view(4, 4), bg_rgb=white)
+                    wss[s].forward(p, cam, 0, sil_w2c=row[32:48].view(4, 4), bg_rgb=white, forward_only=True)
                     ops[j].copy_(wss[s].opacity[0], non_blocking=True)
                     if return_depth:
                         depths[j].copy_(wss[s].depth[0], non_blocking=True)
@@ -229,7 +229,7 @@ def score_candidate_views(params, views, group=None, n_streams=32, scale_modifie
                                  prefiltered=False, debug=False)
             ws.ensure_capacity(int(host[j, 0]) + int(host[j, 0]) // 4)
             with torch.no_grad():
-                ws.forward(p, cam, 0, sil_w2c=row[32:48].view(4, 4), bg_rgb=white)
+                ws.forward(p, cam, 0, sil_w2c=row[32:48].view(4, 4), bg_rgb=white, forward_only=True)
             if ws.last_status()[1]:
                 raise RuntimeError("activesplat_b200: candidate view still overflows its binning buffer after growing it")
             ops[j].copy_(ws.opacity[0])

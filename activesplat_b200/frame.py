@@ -89,6 +89,8 @@ class FrameWorkspace:
         self._retired = []
         self._side = None            # side stream for clearing the gradient buffer next to the forward
         self._grad_cleared = False
+        self._chunked = False        # the last forward blended in chunks (no n_contrib: no backward may follow)
+        self._chunk_scratch = None
 
     # -- buffer management ---------------------------------------------------------------------
     def resize(self, P):
@@ -155,14 +157,18 @@ class FrameWorkspace:
 
     # -- forward / backward --------------------------------------------------------------------
     def forward(self, params, cam, time_idx, sil_w2c=None, bg_rgb=None, debug=False, max_2D_radius=None, seen=None,
-                clear_gradient=False):
+                clear_gradient=False, forward_only=False):
         """as_frame_forward.  params: dict with the five Gaussian tensors + cam_unnorm_rots [1,4,T] +
         cam_trans [1,3,T]; cam: GaussianRasterizationSettings.  Results land in color6/depth/opacity/radii.
         clear_gradient: the caller will run a non-accumulating backward with Gaussian gradients on this frame; the flat
         gradient buffer is then cleared now, on a side stream next to the (latency-bound) forward kernels, instead of
-        in front of the backward's last kernel."""
+        in front of the backward's last kernel.
+        forward_only: no backward will follow.  If this workspace has seen crowded tiles (auto binning fell back to the
+        global sort: low-resolution wide-angle candidate views), the tiles' lists are then blended in chunks, one CTA per
+        chunk (AsFrameArgs.chunk_scratch), instead of one serial walk per pixel strip."""
         L = capi.lib()
         self._grad_cleared = False
+        self._chunked = bool(forward_only and self._binning_auto and self.binning_mode == 0)
         self.resize(params["means3D"].shape[0])
         if clear_gradient:
             cur = torch.cuda.current_stream(self.device)
@@ -232,6 +238,15 @@ class FrameWorkspace:
         else:
             self._graph_pinned = True
         a.binning_mode = self.binning_mode
+        a.chunk_scratch = None
+        if self._chunked:
+            need = L.as_chunk_scratch_bytes(self.capacity, self.W, self.H)
+            if self._chunk_scratch is None or self._chunk_scratch.numel() < need:
+                if self._graph_pinned and self._chunk_scratch is not None:
+                    self._retired.append(self._chunk_scratch)
+                with torch.cuda.device(self.device):
+                    self._chunk_scratch = torch.empty(need, dtype=torch.uint8, device=self.device)
+            a.chunk_scratch = self._chunk_scratch.data_ptr()
         with torch.cuda.device(self.device):
             stream = torch.cuda.current_stream(self.device).cuda_stream
             capi.check(L.as_frame_forward(ctypes.byref(a), stream))
@@ -254,6 +269,8 @@ class FrameWorkspace:
                     self.binning_mode = a.binning_mode = 0
                     rerun = True
                 if rerun:
+                    a.chunk_scratch = None   # sized for the old capacity; this one frame takes the single walk
+                    self._chunked = False
                     a.binning_buffer, a.binning_capacity = self.binning.data_ptr(), self.capacity
                     capi.check(L.as_frame_forward(ctypes.byref(a), stream))
         self._args, self._keep = a, keep
@@ -303,6 +320,9 @@ class FrameWorkspace:
         """as_frame_backward for the last forward.  Returns (grad_params: 14 P floats in the flat segment layout, grad_cam).
         grad_cam_out/grad_cam_stride: write the 7 pose gradients at grad_cam_out[k * stride] instead."""
         L = capi.lib()
+        if self._chunked:
+            raise RuntimeError("activesplat_b200: the last forward of this workspace was forward_only (chunked blend); "
+                               "it has no backward")
         b = capi.AsFrameBackwardArgs()
         b.frame = ctypes.pointer(self._args)
         dL = self.dL if dL_dpix is None else dL_dpix.contiguous()
@@ -434,7 +454,8 @@ class _FusedFrameRender(torch.autograd.Function):
     def forward(ctx, means3D, rgb, rots, logit_op, log_scales, cam_rots, cam_trans, ws, cam, time_idx, sil_w2c, bg_rgb):
         params = {"means3D": means3D, "rgb_colors": rgb, "unnorm_rotations": rots, "logit_opacities": logit_op,
                   "log_scales": log_scales, "cam_unnorm_rots": cam_rots, "cam_trans": cam_trans}
-        ws.forward(params, cam, time_idx, sil_w2c=sil_w2c, bg_rgb=bg_rgb, clear_gradient=any(ctx.needs_input_grad[:5]))
+        ws.forward(params, cam, time_idx, sil_w2c=sil_w2c, bg_rgb=bg_rgb, clear_gradient=any(ctx.needs_input_grad[:5]),
+                   forward_only=not any(ctx.needs_input_grad[:7]))
         ctx.ws, ctx.time_idx, ctx.generation = ws, int(time_idx), ws.generation
         ctx.shapes = (cam_rots.shape, cam_trans.shape, log_scales.shape[1])
         ctx.need = tuple(ctx.needs_input_grad[:7])

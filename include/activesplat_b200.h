@@ -182,7 +182,14 @@ typedef struct AsFrameArgs {
     float* max_2D_radius;          /* [P] or NULL: updated in place, max(radius, .) where seen (splatam.py:296-298) */
     uint8_t* seen;                 /* [P] bool or NULL: radius > 0 */
     int binning_mode;              /* AS_BINNING_GLOBAL_SORT (0) or AS_BINNING_TILE_BUCKETS (1); same results */
+    void* chunk_scratch;           /* NULL, or as_chunk_scratch_bytes(binning_capacity, width, height) bytes (16-byte
+                                    * aligned): blend every tile's list in chunks of 1024 records, one CTA per chunk, and
+                                    * combine -- for low-resolution wide-angle views with 10^4-10^5 records per tile,
+                                    * where one serial walk per pixel strip leaves the GPU idle.  Images agree with the
+                                    * single walk to rounding (T at a chunk start is a product of chunk products);
+                                    * n_contrib is not produced, so no as_frame_backward may follow. */
 } AsFrameArgs;
+size_t as_chunk_scratch_bytes(int binning_capacity, int width, int height);
 
 typedef struct AsFrameBackwardArgs {
     const AsFrameArgs* frame;      /* the arguments of the matching as_frame_forward */

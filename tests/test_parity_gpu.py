@@ -333,6 +333,42 @@ def test_fused_frame_gaussian_gradients_match_oracle(iso):
     helpers.compare_exact("re-run after growing", ws_small.color6.cpu().numpy(), ws.color6.cpu().numpy())
 
 
+def test_chunked_forward_equals_the_single_walk():
+    """Crowded low-resolution view (GetOpacity camera, ~10^4 records per tile): blending every tile's list in chunks of
+    1024 records (pass A transmittance, pass B the reference loop from the true T, combine) gives the images of the
+    single serial walk to rounding; the median depth and the 1e-4 stop rule fire in the right chunk."""
+    from activesplat_b200 import scenes, splatam
+    from activesplat_b200.frame import FrameWorkspace, identity_pose
+    dev = torch.device("cuda:0")
+    params_cpu, _ = scenes.s_room(300_000, 1, seed=4)
+    params = {k: v.to(dev) for k, v in params_cpu.items()}
+    rot, tr = identity_pose(dev)
+    p = dict(params, cam_unnorm_rots=rot, cam_trans=tr)
+    worst_len = 0
+    for view in scenes.candidate_views(6, seed=4)[::2]:
+        cam, sil_w2c = splatam._camera_one_upload(view.width, view.height, view.k(), view.w2c, 0.01, 100, 1.0, dev)
+        ws = FrameWorkspace(300_000, view.width, view.height, dev)
+        with torch.no_grad():
+            ws.forward(p, cam, 0, sil_w2c=sil_w2c, bg_rgb=torch.ones(3, device=dev))      # calibrates
+            ws.binning_mode = 0                                                            # what auto binning does for crowded views
+            ws.forward(p, cam, 0, sil_w2c=sil_w2c, bg_rgb=torch.ones(3, device=dev))
+            assert not ws._chunked
+            ref = [t.clone() for t in (ws.color6, ws.depth, ws.opacity)]
+            R, over = ws.last_status()
+            assert not over
+            ws.forward(p, cam, 0, sil_w2c=sil_w2c, bg_rgb=torch.ones(3, device=dev), forward_only=True)
+            assert ws._chunked
+            got = [t.clone() for t in (ws.color6, ws.depth, ws.opacity)]
+        worst_len = max(worst_len, R // 80)
+        helpers.compare_float("chunked colour6", got[0].cpu().numpy(), ref[0].cpu().numpy(), rel=1e-5)
+        helpers.compare_float("chunked opacity", got[2].cpu().numpy(), ref[2].cpu().numpy(), rel=1e-5)
+        # a pixel whose T lands within rounding of 0.5 may take the neighbouring Gaussian's depth
+        helpers.compare_float("chunked median depth", got[1].cpu().numpy(), ref[1].cpu().numpy(), rel=1e-6, flip_bound=1.0)
+        with pytest.raises(RuntimeError, match="forward_only"):
+            ws.backward(dL_dpix=torch.zeros_like(ws.color6))
+    assert worst_len > 2048   # several chunks per tile on average: the split was exercised
+
+
 def test_workspace_guards():
     """One frame per workspace: the backward of a node whose buffers were overwritten raises (instead of differentiating
     another frame); a second backward raises; a no-grad render through a workspace whose binning buffer is too small
