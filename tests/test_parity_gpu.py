@@ -349,8 +349,7 @@ def test_chunked_forward_equals_the_single_walk():
         cam, sil_w2c = splatam._camera_one_upload(view.width, view.height, view.k(), view.w2c, 0.01, 100, 1.0, dev)
         ws = FrameWorkspace(300_000, view.width, view.height, dev)
         with torch.no_grad():
-            ws.forward(p, cam, 0, sil_w2c=sil_w2c, bg_rgb=torch.ones(3, device=dev))      # calibrates
-            ws.binning_mode = 0                                                            # what auto binning does for crowded views
+            ws.forward(p, cam, 0, sil_w2c=sil_w2c, bg_rgb=torch.ones(3, device=dev))      # calibrates, sees the deep lists
             ws.forward(p, cam, 0, sil_w2c=sil_w2c, bg_rgb=torch.ones(3, device=dev))
             assert not ws._chunked
             ref = [t.clone() for t in (ws.color6, ws.depth, ws.opacity)]
