@@ -340,14 +340,14 @@ def test_chunked_forward_equals_the_single_walk():
     from activesplat_b200 import scenes, splatam
     from activesplat_b200.frame import FrameWorkspace, identity_pose
     dev = torch.device("cuda:0")
-    params_cpu, _ = scenes.s_room(300_000, 1, seed=4)
+    params_cpu, _ = scenes.s_room(700_000, 1, seed=4)
     params = {k: v.to(dev) for k, v in params_cpu.items()}
     rot, tr = identity_pose(dev)
     p = dict(params, cam_unnorm_rots=rot, cam_trans=tr)
     worst_len = 0
     for view in scenes.candidate_views(6, seed=4)[::2]:
         cam, sil_w2c = splatam._camera_one_upload(view.width, view.height, view.k(), view.w2c, 0.01, 100, 1.0, dev)
-        ws = FrameWorkspace(300_000, view.width, view.height, dev)
+        ws = FrameWorkspace(700_000, view.width, view.height, dev)
         with torch.no_grad():
             ws.forward(p, cam, 0, sil_w2c=sil_w2c, bg_rgb=torch.ones(3, device=dev))      # calibrates, sees the deep lists
             ws.forward(p, cam, 0, sil_w2c=sil_w2c, bg_rgb=torch.ones(3, device=dev))
