@@ -449,6 +449,31 @@ def cfg4(dev, RefRenderer, args, rank, world, params=None):
             dt = time.time() - t0
             res[tag]["ref_cuda"] = {"views_per_s": n_ref / dt, "mpix_s": n_ref * w * h / dt / 1e6, "views_timed": n_ref,
                                     "max_score_diff": float((torch.stack(rs)[:, 0] - scores[:n_ref, 0]).abs().max())}
+    # A whole GLOBAL GetOpacity query (visualizer.py:2183-2195 + :991-1001): 86 Voronoi nodes x 3 look-around views,
+    # panoramas, DBSCAN clusters and convex-hull volumes per node -- renders AND scoring, nodes sharded over the ranks.
+    from activesplat_b200 import scoring
+    nodes = scenes.candidate_views(86 * 3, seed=4)[::3]
+    positions = np.stack([np.linalg.inv(np.asarray(v.w2c))[:3, 3] for v in nodes])
+    c2w = np.eye(4)
+    scoring.get_global_invisibility(params, c2w, positions)
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        torch.distributed.barrier()
+    t0 = time.time()
+    for _ in range(3):
+        inv, vol = scoring.get_global_invisibility(params, c2w, positions)
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        torch.distributed.barrier()
+    dt = (time.time() - t0) / 3
+    if world > 1:
+        tt = torch.tensor([dt], device=dev)
+        torch.distributed.all_reduce(tt, op=torch.distributed.ReduceOp.MAX)
+        dt = float(tt.item())
+    res["global_query_86_nodes"] = {"ms_per_query": dt * 1e3, "nodes_with_volume": int((vol > 0).sum()),
+                                    "sum_volume": float(vol.sum()),
+                                    "what": "scoring.get_global_invisibility: 258 renders + per-node DBSCAN + hull volume"}
+    asd._VIEW_WORKSPACES.clear()
     return res
 
 
