@@ -1020,8 +1020,14 @@ struct AdamPtrs {   // plain members (no arrays): indexing a kernel-parameter ar
     float s0, s1, s2, s3, s4;   // lr[t] / bias_correction1 (plain lr[t] when the kernel is given a step_state)
 };
 
-constexpr int AD_THREADS = 256;
-constexpr int AD_VEC_PER_THREAD = 4;   // 128-bit groups per thread: four independent load triples in flight
+#ifndef ASB_AD_THREADS
+#define ASB_AD_THREADS 128
+#endif
+constexpr int AD_THREADS = ASB_AD_THREADS;
+#ifndef ASB_AD_VEC
+#define ASB_AD_VEC 2
+#endif
+constexpr int AD_VEC_PER_THREAD = ASB_AD_VEC;   // 128-bit groups per thread: that many independent load quadruples in flight
 
 // arithmetic per element as torch.optim.Adam (single-tensor path): lerp_, mul_/addcmul_, sqrt / bias_correction2_sqrt
 // + eps, addcdiv_
@@ -1098,9 +1104,25 @@ adam_kernel(int P_, int iso, AdamPtrs ap, const float* __restrict__ grad, float*
             pp[u] = *reinterpret_cast<const float4*>(seg[u].p);
         }
     }
+    // A group whose gradient and both moments are all zero does not move: m and v stay 0 and the parameter changes by
+    // step_size * 0 / (0 + eps) = 0 exactly -- the Gaussians no keyframe of this optimizer has seen yet (four out of
+    // five in a mapping round over a large map).  Nothing is written back for them: the result is the dense update
+    // bit for bit, at two thirds of its memory traffic.  (Not loading their parameters either was measured slower: the
+    // parameter load then waits for the other three, and the kernel is short of loads in flight as it is.)
+    bool idle[AD_VEC_PER_THREAD];
+#pragma unroll
+    for (int u = 0; u < AD_VEC_PER_THREAD; u++) {
+        idle[u] = false;
+        if (fast[u]) {
+            const float4 a = gg[u], b = mm[u], c = vv[u];
+            idle[u] = a.x == 0.f && a.y == 0.f && a.z == 0.f && a.w == 0.f && b.x == 0.f && b.y == 0.f && b.z == 0.f &&
+                      b.w == 0.f && c.x == 0.f && c.y == 0.f && c.z == 0.f && c.w == 0.f;
+        }
+    }
 #pragma unroll
     for (int u = 0; u < AD_VEC_PER_THREAD; u++) {
         const size_t q = g0 + (size_t)u * AD_THREADS, e = 4 * q;
+        if (fast[u] && idle[u]) continue;
         if (fast[u]) {
             const float s1 = seg[u].step;
             adam_one(gg[u].x, mm[u].x, vv[u].x, pp[u].x, s1, beta1, beta2, eps, bc2_sqrt);
