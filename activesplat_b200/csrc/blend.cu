@@ -81,6 +81,20 @@ __device__ __forceinline__ float inst_level(const SM& sm, int s, int j) {
     return FV == 1 ? f.w : f.z;
 }
 
+// single-instruction reciprocal / square root (MUFU.RCP, MUFU.SQRT; ~1 ulp).  Used where the argument's range is known
+// (1 - alpha in [0.01, 1] in the backward) or where the result only feeds the conservative culling intervals, whose
+// 0.02-pixel margin is orders of magnitude above the approximation error.
+__device__ __forceinline__ float rcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float sqrt_approx(float x) {   // NaN for x < 0, like sqrtf
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
 // columns (bit k = column k of the tile) with |column - c| <= hw
 __device__ __forceinline__ uint32_t column_bits(float c, float hw) {
     const int lo = max(0, __float2int_ru(c - hw));             // -inf saturates to INT_MIN
@@ -129,13 +143,13 @@ __device__ __forceinline__ int cull_batch(const SM& sm, int s, int limit, int la
             const float4 ge = sm.geom[s][j];
             const float L = inst_level(sm, s, j);
             const float det = co.x * co.z - co.y * co.y;
-            const float inv_a = 1.0f / co.x;
+            const float inv_a = rcp_approx(co.x);
             const float rel = ge.x - strip_x0;
             const float dy0 = ge.y - strip_y0, dy1 = dy0 - 1.0f;
             // row r: A dx^2 + 2 B dy dx + (C dy^2 - L) <= 0  =>  pixel column in  rel + (B dy -+ sqrt(D)) / A
             const float D0 = co.x * L - det * dy0 * dy0, D1 = co.x * L - det * dy1 * dy1;
             const float c0 = rel + co.y * dy0 * inv_a, c1 = rel + co.y * dy1 * inv_a;
-            const float h0 = sqrtf(D0) * inv_a + 0.02f, h1 = sqrtf(D1) * inv_a + 0.02f;  // NaN when D < 0
+            const float h0 = sqrt_approx(D0) * inv_a + 0.02f, h1 = sqrt_approx(D1) * inv_a + 0.02f;  // NaN when D < 0
             uint32_t b0 = (D0 >= 0.f) ? column_bits(c0, h0) : 0u;
             uint32_t b1 = (D1 >= 0.f) ? column_bits(c1, h1) : 0u;
             if (!(L < CUDART_INF_F) || !(c0 == c0) || !(D0 == D0) || !(h0 == h0 || D0 < 0.f)) b0 = 0xffffu;
@@ -270,7 +284,8 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
                         // skip rules of forward.cu:343-353 (written so that NaN behaves as in the reference)
                         if (((valid >> u) & 1u) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f)) hit |= 1u << u;
                     }
-                    // order-dependent part, branch-free: the only serial chain is T -> test_T -> T
+                    // order-dependent part: the only serial chain is T -> test_T -> T (a branch per record measured
+                    // faster than selects: the selects became a multiply-add into a temporary plus a move, per channel)
 #pragma unroll
                     for (int u = 0; u < FW_UNROLL; u++) {
                         const int j = jj[u];
@@ -280,19 +295,21 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
                         const bool stop = h && (test_T < 0.0001f);  // forward.cu:355-359: stop BEFORE blending it
                         const bool blend = h && !stop;
                         done = done || stop;
-                        const float4 f0 = sm.feat[s][j * FV];
-                        acc[0] = blend ? __fmaf_rn(__fmul_rn(f0.x, alpha), T, acc[0]) : acc[0];
-                        acc[1] = blend ? __fmaf_rn(__fmul_rn(f0.y, alpha), T, acc[1]) : acc[1];
-                        acc[2] = blend ? __fmaf_rn(__fmul_rn(f0.z, alpha), T, acc[2]) : acc[2];
-                        if (C == 6) {
-                            const float4 f1 = sm.feat[s][j * FV + FV - 1];
-                            acc[3 % C] = blend ? __fmaf_rn(__fmul_rn(f0.w, alpha), T, acc[3 % C]) : acc[3 % C];
-                            acc[4 % C] = blend ? __fmaf_rn(__fmul_rn(f1.x, alpha), T, acc[4 % C]) : acc[4 % C];
-                            acc[5 % C] = blend ? __fmaf_rn(__fmul_rn(f1.y, alpha), T, acc[5 % C]) : acc[5 % C];
+                        if (blend) {
+                            const float4 f0 = sm.feat[s][j * FV];
+                            acc[0] = __fmaf_rn(__fmul_rn(f0.x, alpha), T, acc[0]);
+                            acc[1] = __fmaf_rn(__fmul_rn(f0.y, alpha), T, acc[1]);
+                            acc[2] = __fmaf_rn(__fmul_rn(f0.z, alpha), T, acc[2]);
+                            if (C == 6) {
+                                const float4 f1 = sm.feat[s][j * FV + FV - 1];
+                                acc[3 % C] = __fmaf_rn(__fmul_rn(f0.w, alpha), T, acc[3 % C]);
+                                acc[4 % C] = __fmaf_rn(__fmul_rn(f1.x, alpha), T, acc[4 % C]);
+                                acc[5 % C] = __fmaf_rn(__fmul_rn(f1.y, alpha), T, acc[5 % C]);
+                            }
+                            if (T > 0.5f && test_T < 0.5f) D = sm.geom[s][j].z;                  // forward.cu:370-374
+                            last_contributor = (uint32_t)(b * BL_BATCH + j + 1);                 // :335,380
+                            T = test_T;
                         }
-                        if (blend && T > 0.5f && test_T < 0.5f) D = sm.geom[s][j].z;                  // forward.cu:370-374
-                        last_contributor = blend ? (uint32_t)(b * BL_BATCH + j + 1) : last_contributor;  // :335,380
-                        T = blend ? test_T : T;
                     }
                     if (done) hits = 0u;
                 }
@@ -603,6 +620,22 @@ __device__ __forceinline__ uint32_t half_warp_bit_transpose(uint32_t x, int lane
 // same column of different records (phase 2) and lanes writing the same record (phase 1) hit distinct banks
 __device__ __forceinline__ int stage_slot(int r, int p) { return r * 32 + (p ^ r); }  // r < 16: the row bit survives
 
+// 32-bit shared-window address of the staging tile + raw vector accesses: the generic-pointer form made the compiler
+// rebuild the window base (S2UR/ULEA chain) at every store of the inner loop
+__device__ __forceinline__ void sts_float2(uint32_t addr, float x, float y) {
+    asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(addr), "f"(x), "f"(y) : "memory");
+}
+__device__ __forceinline__ float2 lds_float2(uint32_t addr) {
+    float2 v;
+    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr) : "memory");
+    return v;
+}
+// index of the highest set bit, -1 (all ones) for 0: one FLO instead of the clz / subtract / xor sequence
+__device__ __forceinline__ int find_msb(uint32_t x) {
+    int r;
+    asm("bfind.u32 %0, %1;" : "=r"(r) : "r"(x));
+    return r;
+}
 // Which of the 12 per-Gaussian terms the caller consumes (conic x,y,w | opacity | mean2D x,y | colour 0..5):
 //   BWD_ALL       everything (rasterizer API)
 //   BWD_MAPPING   fused frame path with Gaussian gradients: colour 4 is the constant 1 of [z,1,z^2], never read
@@ -638,6 +671,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
     SM& sm = *reinterpret_cast<SM*>(smem_raw);
     const int wid = threadIdx.x >> 5;
     float2* stg = reinterpret_cast<float2*>(smem_raw + LY::off_qw) + wid * BW_GROUP * 32;
+    const uint32_t stg_s = (uint32_t)__cvta_generic_to_shared(stg);
     float* dpx = reinterpret_cast<float*>(smem_raw + LY::off_dpx) + wid * C * 32;   // [C][32]
     uint32_t* masks = reinterpret_cast<uint32_t*>(smem_raw + LY::off_mask) + wid * BW_BATCH;
     uint8_t* list = reinterpret_cast<uint8_t*>(smem_raw + LY::off_list) + wid * BW_BATCH;
@@ -724,8 +758,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
 #pragma unroll
                 for (int u = 0; u < BW_UNROLL; u++) {
                     const bool has = hits != 0u;
-                    const int r = has ? (31 - __clz((int)hits)) : 0;
-                    hits &= ~(1u << r);      // no-op when hits == 0 (bit 0 is clear then)
+                    const int r = find_msb(hits) & 31;   // 31 when hits == 0: clearing bit 31 of 0 is a no-op
+                    hits &= ~(1u << r);
                     rr[u] = r;
                     jj[u] = __shfl_sync(0xffffffffu, jr, r);
                     if (has) valid |= 1u << u;
@@ -754,7 +788,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
                     if ((act >> u) & 1u) {
                         const int j = jj[u];
                         const float alpha = al[u];
-                        const float inv_1ma = __fdividef(1.f, 1.f - alpha);  // 1 - alpha is in [0.01, 1]: the 1-ulp approximate reciprocal; shared by T / (1 - alpha) and the background term
+                        const float inv_1ma = rcp_approx(1.f - alpha);    // 1 - alpha is in [0.01, 1]: the 1-ulp approximate reciprocal; shared by T / (1 - alpha) and the background term
                         T = T * inv_1ma;
                         const float4 f0 = sm.feat[s][j * FV];
                         const float4 f1 = sm.feat[s][j * FV + FV - 1];
@@ -775,7 +809,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
                         q = Gs[u] * dL_dalpha;
                         w = alpha * T;                                      // dchannel_dcolor (:513)
                     }
-                    if ((valid >> u) & 1u) stg[stage_slot(rr[u], lane)] = make_float2(q, w);
+                    if ((valid >> u) & 1u) sts_float2(stg_s + 8u * (uint32_t)stage_slot(rr[u], lane), q, w);
                 }
             }
             __syncwarp();
@@ -788,12 +822,14 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
                 const float4 ge = sm.geom[s][jr];
                 const float2* my_stg = stg + rl * 32 + 16 * row;
                 const float* my_dpx = dpx + 16 * row;
-                uint32_t bits = mrow & seg_bits;
-                while (bits) {
-                    const int k = __ffs((int)bits) - 1;
-                    bits &= bits - 1u;
+                // a row's reachable columns are one interval (column_bits): walk it with a counter
+                const uint32_t bits = mrow & seg_bits;
+                const int k_end = find_msb(bits);                            // -1 for an empty row
+                const int k_begin = __ffs((int)(bits | 0x10000u)) - 1;          // 16 for an empty row
+                float xk = strip_x0 + (float)k_begin;
+                for (int k = k_begin; k <= k_end; k++, xk += 1.0f) {
                     const float2 qw = my_stg[k ^ rl];
-                    const float dx = __fsub_rn(ge.x, strip_x0 + (float)k);   // same dx the pixel lane used
+                    const float dx = __fsub_rn(ge.x, xk);                    // same dx the pixel lane used
                     const float qdx = qw.x * dx;
                     Sq += qw.x;
                     Sx += qdx;
