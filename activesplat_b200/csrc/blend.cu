@@ -616,9 +616,11 @@ __device__ __forceinline__ uint32_t half_warp_bit_transpose(uint32_t x, int lane
     return x;
 }
 
-// staging slot of (record r of the group, pixel lane p): the column is XOR-swizzled by r so that lanes reading the
-// same column of different records (phase 2) and lanes writing the same record (phase 1) hit distinct banks
-__device__ __forceinline__ int stage_slot(int r, int p) { return r * 32 + (p ^ r); }  // r < 16: the row bit survives
+// staging slot of (record r of the group, pixel lane p): rows are padded to 33 slots, so lanes reading the same
+// column of different records (phase 2) hit distinct banks, lanes writing one record (phase 1) do too, and a lane
+// walks its row with immediate offsets (an XOR swizzle cost three address instructions per pixel)
+constexpr int STG_STRIDE = 33;
+__device__ __forceinline__ int stage_slot(int r, int p) { return r * STG_STRIDE + p; }
 
 // 32-bit shared-window address of the staging tile + raw vector accesses: the generic-pointer form made the compiler
 // rebuild the window base (S2UR/ULEA chain) at every store of the inner loop
@@ -650,7 +652,7 @@ template <int C, int WARPS>
 struct BwdLayout {
     using SM = BlendSmem<C, BW_STAGES, BW_BATCH>;
     static constexpr size_t off_qw = (sizeof(SM) + 127) / 128 * 128;
-    static constexpr size_t off_dpx = off_qw + sizeof(float2) * WARPS * BW_GROUP * 32;
+    static constexpr size_t off_dpx = off_qw + sizeof(float2) * WARPS * BW_GROUP * STG_STRIDE;
     static constexpr size_t off_mask = off_dpx + sizeof(float) * WARPS * C * 32;
     static constexpr size_t off_list = off_mask + sizeof(uint32_t) * WARPS * BW_BATCH;
     static constexpr size_t bytes = off_list + WARPS * BW_BATCH;
@@ -670,7 +672,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
     extern __shared__ __align__(128) unsigned char smem_raw[];
     SM& sm = *reinterpret_cast<SM*>(smem_raw);
     const int wid = threadIdx.x >> 5;
-    float2* stg = reinterpret_cast<float2*>(smem_raw + LY::off_qw) + wid * BW_GROUP * 32;
+    float2* stg = reinterpret_cast<float2*>(smem_raw + LY::off_qw) + wid * BW_GROUP * STG_STRIDE;
     const uint32_t stg_s = (uint32_t)__cvta_generic_to_shared(stg);
     float* dpx = reinterpret_cast<float*>(smem_raw + LY::off_dpx) + wid * C * 32;   // [C][32]
     uint32_t* masks = reinterpret_cast<uint32_t*>(smem_raw + LY::off_mask) + wid * BW_BATCH;
@@ -820,7 +822,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
 #pragma unroll
                 for (int ch = 0; ch < C; ch++) cc[ch] = 0.f;
                 const float4 ge = sm.geom[s][jr];
-                const float2* my_stg = stg + rl * 32 + 16 * row;
+                const float2* my_stg = stg + stage_slot(rl, 16 * row);
                 const float* my_dpx = dpx + 16 * row;
                 // a row's reachable columns are one interval (column_bits): walk it with a counter
                 const uint32_t bits = mrow & seg_bits;
@@ -828,7 +830,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
                 const int k_begin = __ffs((int)(bits | 0x10000u)) - 1;          // 16 for an empty row
                 float xk = strip_x0 + (float)k_begin;
                 for (int k = k_begin; k <= k_end; k++, xk += 1.0f) {
-                    const float2 qw = my_stg[k ^ rl];
+                    const float2 qw = my_stg[k];
                     const float dx = __fsub_rn(ge.x, xk);                    // same dx the pixel lane used
                     const float qdx = qw.x * dx;
                     Sq += qw.x;
