@@ -185,7 +185,7 @@ __device__ __forceinline__ uint32_t warp_bit_transpose(uint32_t x, int lane) {
 // WARPS warps per CTA: a CTA blends 2*WARPS pixel rows of one tile, so 8/WARPS CTAs share a tile (each
 // stages the tile's records for itself).  Small images have few tiles; splitting them keeps all SMs busy
 // and spreads a heavy tile over several SMs.  Per-pixel results do not depend on WARPS.
-template <int C, int WARPS>
+template <int C, int WARPS, bool FRAME>
 __global__ void __launch_bounds__(32 * WARPS)
 blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict__ inst_conic,
                      const float4* __restrict__ inst_geom, const float4* __restrict__ inst_feat, int W, int H,
@@ -301,10 +301,17 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
                             acc[1] = __fmaf_rn(__fmul_rn(f0.y, alpha), T, acc[1]);
                             acc[2] = __fmaf_rn(__fmul_rn(f0.z, alpha), T, acc[2]);
                             if (C == 6) {
-                                const float4 f1 = sm.feat[s][j * FV + FV - 1];
                                 acc[3 % C] = __fmaf_rn(__fmul_rn(f0.w, alpha), T, acc[3 % C]);
-                                acc[4 % C] = __fmaf_rn(__fmul_rn(f1.x, alpha), T, acc[4 % C]);
-                                acc[5 % C] = __fmaf_rn(__fmul_rn(f1.y, alpha), T, acc[5 % C]);
+                                if (FRAME) {
+                                    // fused frame path: the second triple is (z, 1, z^2) by construction (fused.cu
+                                    // gathers): 1 * alpha = alpha, z^2 is the same product the gather stored
+                                    acc[4 % C] = __fmaf_rn(alpha, T, acc[4 % C]);
+                                    acc[5 % C] = __fmaf_rn(__fmul_rn(__fmul_rn(f0.w, f0.w), alpha), T, acc[5 % C]);
+                                } else {
+                                    const float4 f1 = sm.feat[s][j * FV + FV - 1];
+                                    acc[4 % C] = __fmaf_rn(__fmul_rn(f1.x, alpha), T, acc[4 % C]);
+                                    acc[5 % C] = __fmaf_rn(__fmul_rn(f1.y, alpha), T, acc[5 % C]);
+                                }
                             }
                             if (T > 0.5f && test_T < 0.5f) D = sm.geom[s][j].z;                  // forward.cu:370-374
                             last_contributor = (uint32_t)(b * BL_BATCH + j + 1);                 // :335,380
@@ -738,6 +745,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
         const int hi = len - b * BW_BATCH;
         const int cnt = min(BW_BATCH, hi);
         const int lo = hi - cnt;  // list index of record 0 of this batch
+        const int last_in_batch = last_contributor - lo;   // the pixel's last contributor relative to this batch
         mbar_wait(&sm.bar[s], (uint32_t)((b / BW_STAGES) & 1));
 
         // records at list index >= warp_max are skipped by the whole warp; so are records whose box cannot
@@ -780,7 +788,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
                     al[u] = alpha;
                     Gs[u] = G;
                     // the reference's `contributor` after its decrement is lo + j (backward.cu:486-490)
-                    if (((valid >> u) & 1u) && (lo + j) < last_contributor && !(power > 0.0f) &&
+                    if (((valid >> u) & 1u) && j < last_in_batch && !(power > 0.0f) &&
                         !(alpha < 1.0f / 255.0f))
                         act |= 1u << u;
                 }
@@ -793,10 +801,20 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
                         const float inv_1ma = rcp_approx(1.f - alpha);    // 1 - alpha is in [0.01, 1]: the 1-ulp approximate reciprocal; shared by T / (1 - alpha) and the background term
                         T = T * inv_1ma;
                         const float4 f0 = sm.feat[s][j * FV];
-                        const float4 f1 = sm.feat[s][j * FV + FV - 1];
                         float col[C];
                         col[0] = f0.x; col[1] = f0.y; col[2] = f0.z;
-                        if (C == 6) { col[3 % C] = f0.w; col[4 % C] = f1.x; col[5 % C] = f1.y; }
+                        if (C == 6) {
+                            col[3 % C] = f0.w;
+                            if (MODE != BWD_ALL) {
+                                // fused frame path: the second triple is (z, 1, z^2) by construction (fused.cu gathers),
+                                // so the second feature vector need not be read
+                                col[4 % C] = 1.f;
+                                col[5 % C] = __fmul_rn(f0.w, f0.w);
+                            } else {
+                                const float4 f1 = sm.feat[s][j * FV + FV - 1];
+                                col[4 % C] = f1.x; col[5 % C] = f1.y;
+                            }
+                        }
                         // backward.cu:516-528 keeps accum_rec[ch] and sums (col[ch] - accum_rec[ch]) * dL_dpixel[ch];
                         // only that sum is ever used, so the recurrence is carried on the two dot products
                         //   cdot = sum col[ch] dL_dpixel[ch]   and   adot = sum accum_rec[ch] dL_dpixel[ch]
@@ -892,12 +910,12 @@ static int pick_warps(int tiles, bool forward) {
     return 1;
 }
 
-template <int C>
+template <int C, bool FRAME>
 static void launch_fwd_c(int warps, int tiles, cudaStream_t st, const uint2* ranges, const BinningState& b, int W, int H,
                          int gx, const float* bg, float* out_color, float* out_depth, float* out_opacity,
                          float* final_T, uint32_t* n_contrib, const uint32_t* tile_order) {
 #define ASB_FWD(WP)                                                                                              \
-    blend_forward_kernel<C, WP><<<tiles*(8 / WP), 32 * WP, 0, st>>>(ranges, b.inst_conic, b.inst_geom, b.inst_feat, W, \
+    blend_forward_kernel<C, WP, FRAME><<<tiles*(8 / WP), 32 * WP, 0, st>>>(ranges, b.inst_conic, b.inst_geom, b.inst_feat, W, \
                                                                     H, gx, bg, out_color, out_depth, out_opacity,    \
                                                                     final_T, n_contrib, tile_order)
     if (warps == 8) ASB_FWD(8);
@@ -939,17 +957,20 @@ static void launch_bwd_c(int warps, int tiles, cudaStream_t st, const uint2* ran
 
 void launch_blend_forward(int channels, int W, int H, const uint2* ranges, const BinningState& b, const float* bg,
                           float* out_color, float* out_depth, float* out_opacity, float* final_T,
-                          uint32_t* n_contrib, cudaStream_t st, const uint32_t* tile_order) {
+                          uint32_t* n_contrib, cudaStream_t st, const uint32_t* tile_order, bool frame_features) {
     const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
     const int tiles = gx * gy;
     if (tiles <= 0) return;
     const int warps = pick_warps(tiles, true);
     if (channels == 3)
-        launch_fwd_c<3>(warps, tiles, st, ranges, b, W, H, gx, bg, out_color, out_depth, out_opacity, final_T, n_contrib,
-                        tile_order);
+        launch_fwd_c<3, false>(warps, tiles, st, ranges, b, W, H, gx, bg, out_color, out_depth, out_opacity, final_T,
+                               n_contrib, tile_order);
+    else if (frame_features)
+        launch_fwd_c<6, true>(warps, tiles, st, ranges, b, W, H, gx, bg, out_color, out_depth, out_opacity, final_T,
+                              n_contrib, tile_order);
     else
-        launch_fwd_c<6>(warps, tiles, st, ranges, b, W, H, gx, bg, out_color, out_depth, out_opacity, final_T, n_contrib,
-                        tile_order);
+        launch_fwd_c<6, false>(warps, tiles, st, ranges, b, W, H, gx, bg, out_color, out_depth, out_opacity, final_T,
+                               n_contrib, tile_order);
 }
 
 // scratch of the chunked forward: chunk_base [tiles + 1] | chunk_tile [max_chunks] | per-chunk fields

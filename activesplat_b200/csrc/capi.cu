@@ -374,7 +374,7 @@ int as_frame_forward(const AsFrameArgs* a, void* cuda_stream) {
     } else {
         StageScope _s(AS_STAGE_BLEND_FWD, st, 1);
         launch_blend_forward(6, W, H, img.ranges, b, a->background, a->out_color, a->out_depth, a->out_opacity,
-                             img.final_T, img.n_contrib, st, buckets ? img.tile_order : nullptr);
+                             img.final_T, img.n_contrib, st, buckets ? img.tile_order : nullptr, true);
     }
     return stage_check(st, a->debug);
 }

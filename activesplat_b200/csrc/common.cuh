@@ -122,7 +122,8 @@ void launch_blend_forward_chunked(int W, int H, const uint2* ranges, const Binni
                                   uint32_t* n_contrib, void* scratch, cudaStream_t st);
 void launch_blend_forward(int channels, int W, int H, const uint2* ranges, const BinningState& b,
                           const float* bg, float* out_color, float* out_depth, float* out_opacity,
-                          float* final_T, uint32_t* n_contrib, cudaStream_t st, const uint32_t* tile_order = nullptr);
+                          float* final_T, uint32_t* n_contrib, cudaStream_t st, const uint32_t* tile_order = nullptr,
+                          bool frame_features = false);  // frame_features: channels 3..5 are (z, 1, z^2) (fused frame path)
 
 // gacc: [P,12] accumulators (conic x,y,w | opacity | mean2D x,y | colour[<=6]); must be zero on entry.
 // mode (6 channels only): 0 = all 12 terms, 1 = the frame path with Gaussian gradients (the constant-1 channel of
