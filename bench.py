@@ -184,40 +184,61 @@ def run_ours(args, rank, world, local_rank):
     gt_dev = gt.clone()
     # end-to-end leg: every step uploads the keyframe's RGB-D frame from pinned host memory.  Two staging buffers and
     # a copy stream: the upload for step i+1 runs while step i computes; step i waits for its own upload.
-    gt_stage = [torch.empty_like(gt_dev) for _ in range(2)]
+    DEPTH = int(os.environ.get("ASB_E2E_DEPTH", "3"))   # staging buffers = steps the host may run ahead of the GPU
+    gt_stage = [torch.empty_like(gt_dev) for _ in range(DEPTH)]
     copy_stream = torch.cuda.Stream(device=dev)
-    copy_done = [torch.cuda.Event() for _ in range(2)]
+    copy_done = [torch.cuda.Event() for _ in range(DEPTH)]
 
-    step_done = [torch.cuda.Event() for _ in range(2)]
-    loss_host = [torch.zeros(1).pin_memory() for _ in range(2)]
+    step_done = [torch.cuda.Event() for _ in range(DEPTH)]
+    loss_host = [torch.zeros(1).pin_memory() for _ in range(DEPTH)]
     loss_seen = []
 
     def upload(i):
-        """Host -> device copy of step i's frame into staging buffer i % 2, ordered after the step that last read it."""
+        """Host -> device copy of step i's frame into staging buffer i % DEPTH, ordered after the step that last read it."""
         with torch.cuda.stream(copy_stream):
-            if i >= 2:
-                copy_stream.wait_event(step_done[i % 2])
-            gt_stage[i % 2].copy_(gt_host, non_blocking=True)
-            copy_done[i % 2].record(copy_stream)
+            if i >= DEPTH:
+                copy_stream.wait_event(step_done[i % DEPTH])
+            gt_stage[i % DEPTH].copy_(gt_host, non_blocking=True)
+            copy_done[i % DEPTH].record(copy_stream)
+
+    rb_stream = torch.cuda.Stream(device=dev)
+    rb_fork = [torch.cuda.Event() for _ in range(DEPTH)]
+    rb_join = [torch.cuda.Event() for _ in range(DEPTH)]
+
+    def loss_to_host(slot, loss):
+        """Device -> host copy of the step's loss into pinned memory, on a side stream forked right after the loss kernel
+        and joined at the end of the step: the copy runs beside the backward instead of between two steps (in the
+        captured step it is a parallel branch of the graph)."""
+        cur = torch.cuda.current_stream(dev)
+        rb_fork[slot].record(cur)
+        with torch.cuda.stream(rb_stream):
+            rb_stream.wait_event(rb_fork[slot])
+            loss_host[slot].copy_(loss.detach().reshape(1), non_blocking=True)
+            rb_join[slot].record(rb_stream)
 
     def read_back(i, loss):
-        """Device -> host copy of step i's loss (pinned, asynchronous); the host consumes step i-1's value while step i
-        runs, so the GPU never waits for the host between steps."""
-        loss_host[i % 2].copy_(loss.detach().reshape(1), non_blocking=True)
-        step_done[i % 2].record()
-        if i >= 1:
-            step_done[(i - 1) % 2].synchronize()
-            loss_seen.append(float(loss_host[(i - 1) % 2]))
+        """The host consumes step i-1's loss (copied by loss_to_host inside that step) while step i runs, so the GPU never
+        waits for the host between steps."""
+        step_done[i % DEPTH].record()
+        if i >= DEPTH - 1:
+            j = i - (DEPTH - 1)
+            step_done[j % DEPTH].synchronize()
+            loss_seen.append(float(loss_host[j % DEPTH]))
 
-    def fwd_bwd(src):
+    def fwd_bwd(src, host_slot=None):
         curr = {"cam": cam, "im": src[:3], "depth": src[3:4], "w2c": first_w2c}
         for k in PARAM_ORDER:
             params[k].grad = None
         loss, _, _ = splatam.get_loss(params, curr, variables, t_idx, LOSS_WEIGHTS, False, SIL_THRES_MAPPING, True,
                                       False, mapping=True)
+        if host_slot is not None:
+            loss_to_host(host_slot, loss)
         with gradients_stay_in_workspace():   # FusedAdam reads the flat buffer: no per-tensor .grad copies
             loss.backward()
         return loss
+
+    def join_read_back(slot):
+        torch.cuda.current_stream(dev).wait_event(rb_join[slot])
 
     from activesplat_b200 import dist as asd
 
@@ -228,10 +249,11 @@ def run_ours(args, rank, world, local_rank):
     def eager_step(i, e2e):
         if e2e:
             upload(i + 1)
-            torch.cuda.current_stream(dev).wait_event(copy_done[i % 2])
-        loss = fwd_bwd(gt_stage[i % 2] if e2e else gt_dev)
+            torch.cuda.current_stream(dev).wait_event(copy_done[i % DEPTH])
+        loss = fwd_bwd(gt_stage[i % DEPTH], i % DEPTH) if e2e else fwd_bwd(gt_dev)
         exchange_and_update()
         if e2e:
+            join_read_back(i % DEPTH)
             read_back(i, loss)
 
     one_step = eager_step
@@ -279,11 +301,12 @@ def run_ours(args, rank, world, local_rank):
         try:
             if world == 1 or args.graph_collective:
                 g_res = GraphedStep(lambda: (fwd_bwd(gt_dev), exchange_and_update())[0])
-                g_e2e = [GraphedStep(lambda s=s: (fwd_bwd(gt_stage[s]), exchange_and_update())[0]) for s in range(2)]
+                g_e2e = [GraphedStep(lambda s=s: (fwd_bwd(gt_stage[s], s), exchange_and_update(), join_read_back(s))[0])
+                         for s in range(DEPTH)]
                 g_upd = None
             else:
                 g_res = GraphedStep(lambda: fwd_bwd(gt_dev))
-                g_e2e = [GraphedStep(lambda s=s: fwd_bwd(gt_stage[s])) for s in range(2)]
+                g_e2e = [GraphedStep(lambda s=s: (fwd_bwd(gt_stage[s], s), join_read_back(s))[0]) for s in range(DEPTH)]
                 g_adam = GraphedStep(lambda: opt.step(ws.grad_params))
 
                 def g_upd():
@@ -302,8 +325,8 @@ def run_ours(args, rank, world, local_rank):
             g_res, g_e2e, g_upd = graphed
             if e2e:
                 upload(i + 1)
-                torch.cuda.current_stream(dev).wait_event(copy_done[i % 2])
-                loss = g_e2e[i % 2]()
+                torch.cuda.current_stream(dev).wait_event(copy_done[i % DEPTH])
+                loss = g_e2e[i % DEPTH]()
             else:
                 loss = g_res()
             if g_upd is not None:
@@ -377,9 +400,10 @@ def run_ours(args, rank, world, local_rank):
                 "h2d_bytes_per_step": int(gt_host.numel() * 4), "d2h_bytes_per_step": 4,
                 "api": "activesplat_b200.splatam.get_loss(mapping=True) + loss.backward() (inside "
                        "frame.gradients_stay_in_workspace()) + frame.FusedAdam.step(workspace.grad_params); every "
-                       "step's RGB-D keyframe is copied from pinned host memory (double-buffered: the copy for step i+1 "
-                       "overlaps step i) and every step's loss is copied to pinned host memory and read by the host one "
-                       "step later (the last one after the final synchronisation)"},
+                       f"step's RGB-D keyframe is copied from pinned host memory ({DEPTH} staging buffers: the copy for step "
+                       "i+1 overlaps step i) and every step's loss is copied to pinned host memory on a side stream beside "
+                       f"the backward and read by the host {DEPTH - 1} step(s) later (the last ones after the final "
+                       "synchronisation)"},
         "gpu_launches": int(launches),
         "launch_path": ("cuda_graph_replay (one graph per step; kernels identical to the eager path)"
                         if graphed is not None else "eager"),
