@@ -685,6 +685,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
     uint32_t* masks = reinterpret_cast<uint32_t*>(smem_raw + LY::off_mask) + wid * BW_BATCH;
     uint8_t* list = reinterpret_cast<uint8_t*>(smem_raw + LY::off_list) + wid * BW_BATCH;
     __shared__ int s_max_contrib;
+    __shared__ int s_released[BW_STAGES];   // warps that are through with the stage's current batch
 
     const int tile = tile_order ? (int)tile_order[blockIdx.x / PARTS] : (int)(blockIdx.x / PARTS);
     const int tx = tile % gx, ty = tile / gx;
@@ -706,7 +707,10 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
     if (threadIdx.x == 0) {
         s_max_contrib = 0;
 #pragma unroll
-        for (int q = 0; q < BW_STAGES; q++) mbar_init(&sm.bar[q], 1);
+        for (int q = 0; q < BW_STAGES; q++) {
+            mbar_init(&sm.bar[q], 1);
+            s_released[q] = 0;
+        }
         mbar_fence_init();
     }
     __syncthreads();
@@ -741,7 +745,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
     const float row_y = strip_y0 + (float)row;
 
     for (int b = 0; b < nb; b++) {
-        const int s = b & (BW_STAGES - 1);
+        const int s = b % BW_STAGES;
         const int hi = len - b * BW_BATCH;
         const int cnt = min(BW_BATCH, hi);
         const int lo = hi - cnt;  // list index of record 0 of this batch
@@ -892,10 +896,20 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const float4* __restrict
             }
             __syncwarp();  // the staging tile is rewritten by the next group
         }
-        __syncthreads();  // every warp is done with stage s
-        if (threadIdx.x == 0 && b + BW_STAGES < nb) {
-            const int nhi = len - (b + BW_STAGES) * BW_BATCH, ncnt = min(BW_BATCH, nhi);
-            issue_batch(sm, s, inst_conic, inst_geom, inst_feat, range.x + (uint32_t)(nhi - ncnt), ncnt);
+        // No CTA-wide barrier per batch: a warp that is through with stage s moves on to the next batch (already
+        // staged) while slower strips finish; the LAST warp to leave the stage refills it.  The copy into stage s
+        // is issued only after every warp's reads of it (ordered by the fence + the counter), and a warp reaches the
+        // refilled stage only through the copy's mbarrier.
+        __syncwarp();
+        if (lane == 0) {
+            __threadfence_block();
+            if (atomicAdd(&s_released[s], 1) == WARPS - 1) {
+                s_released[s] = 0;
+                if (b + BW_STAGES < nb) {
+                    const int nhi = len - (b + BW_STAGES) * BW_BATCH, ncnt = min(BW_BATCH, nhi);
+                    issue_batch(sm, s, inst_conic, inst_geom, inst_feat, range.x + (uint32_t)(nhi - ncnt), ncnt);
+                }
+            }
         }
     }
 }
