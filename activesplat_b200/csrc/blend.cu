@@ -212,9 +212,22 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
     const int len = (int)(range.y - range.x);
     const int nb = (len + BL_BATCH - 1) / BL_BATCH;
 
+    // Warps are not held together by a CTA-wide barrier per batch: a warp that is through with a stage moves on to the
+    // next (already staged) batch, and the LAST warp to leave a stage refills it -- or, once every warp has reported
+    // all of its pixels finished (forward.cu:315-317), sets s_stop and completes the stage's barrier without data so
+    // that nobody waits for a batch that will never come.
+    __shared__ int s_released[BL_STAGES];   // warps that are through with the stage's current batch
+    __shared__ int s_done_warps;            // warps whose 32 pixels are all finished
+    __shared__ volatile int s_stop, s_last_issued;
     if (threadIdx.x == 0) {
 #pragma unroll
-        for (int q = 0; q < BL_STAGES; q++) mbar_init(&sm.bar[q], 1);
+        for (int q = 0; q < BL_STAGES; q++) {
+            mbar_init(&sm.bar[q], 1);
+            s_released[q] = 0;
+        }
+        s_done_warps = 0;
+        s_stop = 0;
+        s_last_issued = min(BL_STAGES, nb) - 1;
         mbar_fence_init();
     }
     __syncthreads();
@@ -225,6 +238,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
     }
 
     bool done = !inside;
+    bool reported = false;   // this warp is counted in s_done_warps
     float T = 1.0f;
     float D = 15.0f;  // median depth default (forward.cu:309)
     uint32_t last_contributor = 0;
@@ -232,10 +246,12 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
 #pragma unroll
     for (int ch = 0; ch < C; ch++) acc[ch] = 0.f;
 
-    int consumed = 0;
+    int waited = 0;   // batches whose barrier this warp has waited on
     for (int b = 0; b < nb; b++) {
         const int s = b & (BL_STAGES - 1);
         mbar_wait(&sm.bar[s], (uint32_t)((b / BL_STAGES) & 1));
+        waited = b + 1;
+        if (__shfl_sync(0xffffffffu, (int)s_stop, 0)) break;   // every pixel of the tile is finished (one read per warp: the decision is uniform)
         const int cnt = min(BL_BATCH, len - b * BL_BATCH);
         // The per-pixel loop of forward.cu:332-381, restructured so that every lane works on a record that can
         // actually reach ITS pixel:
@@ -324,19 +340,31 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const float4* __restrict_
             }
             __syncwarp();  // the list is rewritten by the next batch
         }
-        consumed = b + 1;
-        // all 256 pixels finished => stop (forward.cu:315-317); the barrier also frees stage s for reuse
-        if (__syncthreads_count(done) == NT) break;
-        if (threadIdx.x == 0 && b + BL_STAGES < nb) {
-            const int nstart = (b + BL_STAGES) * BL_BATCH;
-            issue_batch(sm, s, inst_conic, inst_geom, inst_feat, range.x + nstart, min(BL_BATCH, len - nstart));
+        __syncwarp();
+        if (lane == 0) {
+            if (warp_done && !reported) atomicAdd(&s_done_warps, 1);   // before the release: the last one out sees it
+            __threadfence_block();
+            if (atomicAdd(&s_released[s], 1) == WARPS - 1) {
+                s_released[s] = 0;
+                if (b + BL_STAGES < nb) {
+                    if (*(volatile int*)&s_done_warps == WARPS) {
+                        s_stop = 1;
+                        __threadfence_block();
+                        mbar_arrive(&sm.bar[s]);
+                    } else {
+                        const int nstart = (b + BL_STAGES) * BL_BATCH;
+                        issue_batch(sm, s, inst_conic, inst_geom, inst_feat, range.x + nstart, min(BL_BATCH, len - nstart));
+                        s_last_issued = b + BL_STAGES;
+                    }
+                }
+            }
         }
+        reported = reported || warp_done;
     }
-    // copies that were issued but never consumed must land before this CTA's shared memory is released:
-    // after an early exit at batch consumed-1, batches consumed .. consumed+BL_STAGES-2 are still in flight
-    if (consumed >= 1)
-        for (int q = consumed; q < nb && q < consumed - 1 + BL_STAGES; q++)
-            mbar_wait(&sm.bar[q & (BL_STAGES - 1)], (uint32_t)((q / BL_STAGES) & 1));
+    // copies that were issued but never consumed must land before this CTA's shared memory is released (after an
+    // early stop the batches up to s_last_issued are still in flight; s_last_issued is final once s_stop is visible)
+    for (int q = waited; q <= s_last_issued; q++)
+        mbar_wait(&sm.bar[q & (BL_STAGES - 1)], (uint32_t)((q / BL_STAGES) & 1));
 
     if (inside) {
         const size_t pix_id = (size_t)W * py + px;

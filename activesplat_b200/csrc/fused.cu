@@ -583,10 +583,11 @@ frame_tile_sort_gather_kernel(const uint2* __restrict__ ranges, uint64_t* __rest
                               const float4* __restrict__ conic_opacity, const float* __restrict__ rgb,
                               const float* __restrict__ zsil, float4* __restrict__ inst_conic,
                               float4* __restrict__ inst_geom, float4* __restrict__ inst_feat,
-                              const uint32_t* __restrict__ status) {
+                              const uint32_t* __restrict__ status, const uint32_t* __restrict__ tile_order) {
     __shared__ uint64_t s_e[TS_CAP];
     if (status[1]) return;
-    const uint2 range = ranges[blockIdx.x];
+    // crowded buckets first (their sort costs the most): the grid's last CTAs are the short ones
+    const uint2 range = ranges[tile_order[blockIdx.x]];
     const int n = (int)(range.y - range.x);
     if (n <= 0) return;
     uint64_t* ge = entries + range.x;
@@ -1255,7 +1256,7 @@ void launch_frame_tile_binning(int P, const GeometryState& g, int W, int H, uint
                                                                  img.tile_cursor, b.keys_unsorted, status);
     frame_tile_sort_gather_kernel<<<tiles, TS_THREADS, 0, st>>>(img.ranges, b.keys_unsorted, b.point_list, g.means2D,
                                                                 g.conic_opacity, rgb, g.zsil, b.inst_conic, b.inst_geom,
-                                                                b.inst_feat, status);
+                                                                b.inst_feat, status, img.tile_order);
 }
 
 void launch_frame_duplicate(int P, const GeometryState& g, int W, int H, uint32_t capacity, uint64_t* keys,
