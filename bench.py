@@ -141,9 +141,9 @@ NCU_KERNEL_OF_STAGE = {"blend_bwd": "blend_backward_kernel<6", "blend_fwd": "ble
 
 def committed_traffic(stage):
     """DRAM bytes per launch of the stage's kernel from the committed `ncu --set full` capture of this workload
-    (profiles/r2_ncu_kernels_cfg3.json, made by benchmarks/summarize_ncu.py); None when there is no capture."""
+    (profiles/r2_ncu_kernels_final.json, made by benchmarks/summarize_ncu.py); None when there is no capture."""
     try:
-        ncu = json.load(open(os.path.join(ROOT, "profiles", "r2_ncu_kernels_cfg3.json")))["kernels"]
+        ncu = json.load(open(os.path.join(ROOT, "profiles", "r2_ncu_kernels_final.json")))["kernels"]
         prefix = NCU_KERNEL_OF_STAGE.get(stage)
         for name, k in ncu.items():
             if prefix and name.startswith(prefix):

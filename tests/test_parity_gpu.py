@@ -747,6 +747,42 @@ def test_tile_buckets_and_global_sort_agree_at_full_size():
         assert int(ws1.status[3]) == int((a["ranges"][:, 1] - a["ranges"][:, 0]).max())   # largest bucket reported
 
 
+@pytest.mark.parametrize("shape", [(640, 480, 300_000), (160, 128, 60_000), (64, 48, 20_000), (32, 32, 8_000)])
+def test_blend_pipelines_repeat_exactly(shape):
+    """The blend kernels' warps are not held together by a block barrier per batch (the last warp out of a stage
+    refills it; the forward stops through a data-less barrier completion).  A race there would show up as a run that
+    differs from the others: the forward of one frame, repeated, must give bit-identical images, final T and
+    n_contrib, and the backward the same gradients up to the order of its float reductions.  The shapes cover every
+    CTA shape (8, 4, 2 and 1 warps per CTA) and lists of many batches per tile."""
+    from activesplat_b200 import scenes, splatam
+    from activesplat_b200.frame import FrameWorkspace
+    W, H, P = shape
+    dev = torch.device("cuda:0")
+    params_cpu, cams = scenes.s_room(P, 2, seed=7, W=W, H=H)
+    rots, trans = scenes.camera_track(cams)
+    params = {k: v.to(dev) for k, v in params_cpu.items()}
+    params["cam_unnorm_rots"], params["cam_trans"] = rots.to(dev), trans.to(dev)
+    cam = splatam.setup_camera(W, H, cams[0].k(), np.eye(4), device=dev)
+    ws = FrameWorkspace(P, W, H, dev, capacity=8 * P, binning=1)
+    dL = torch.from_numpy(np.random.default_rng(5).uniform(-1, 1, (6, H, W)).astype(np.float32)).to(dev)
+    first = None
+    for rep in range(12):
+        ws.forward(params, cam, 1)
+        R, overflow = ws.last_status()
+        assert not overflow and R > 0
+        imgs = (ws.color6.clone(), ws.depth.clone(), ws.opacity.clone())
+        gp, _ = ws.backward(dL_dpix=dL, gaussians_grad=True, camera_grad=False)
+        gp = gp[:14 * P].clone()
+        assert torch.isfinite(gp).all()
+        if first is None:
+            first = (imgs, gp)
+            continue
+        for a, b in zip(imgs, first[0]):
+            assert torch.equal(a, b), f"forward run {rep} differs from run 0 at {shape}"
+        scale = float(first[1].abs().max())
+        assert float((gp - first[1]).abs().max()) <= 2e-5 * scale, f"backward run {rep} differs from run 0 at {shape}"
+
+
 def test_tile_buckets_larger_than_shared_memory_still_sort_exactly():
     """A tiny image under a big map: every tile's bucket exceeds what one CTA sorts in shared memory, so the
     in-place (global-memory) network runs.  Same sorted list and images as the global radix sort."""
