@@ -530,18 +530,19 @@ blend_forward_chunk_kernel(const uint2* __restrict__ ranges, const float4* __res
                         } else {
                             const bool blend = h && !stop;   // forward.cu:355-359: stop BEFORE blending it
                             done = done || stop;
-                            const float4 f0 = sm.feat[s][j * FV];
-                            acc[0] = blend ? __fmaf_rn(__fmul_rn(f0.x, alpha), T, acc[0]) : acc[0];
-                            acc[1] = blend ? __fmaf_rn(__fmul_rn(f0.y, alpha), T, acc[1]) : acc[1];
-                            acc[2] = blend ? __fmaf_rn(__fmul_rn(f0.z, alpha), T, acc[2]) : acc[2];
-                            if (C == 6) {
-                                const float4 f1 = sm.feat[s][j * FV + FV - 1];
-                                acc[3 % C] = blend ? __fmaf_rn(__fmul_rn(f0.w, alpha), T, acc[3 % C]) : acc[3 % C];
-                                acc[4 % C] = blend ? __fmaf_rn(__fmul_rn(f1.x, alpha), T, acc[4 % C]) : acc[4 % C];
-                                acc[5 % C] = blend ? __fmaf_rn(__fmul_rn(f1.y, alpha), T, acc[5 % C]) : acc[5 % C];
+                            if (blend) {   // as in blend_forward_kernel<C, WARPS, true>: this path only serves the frame entry
+                                const float4 f0 = sm.feat[s][j * FV];
+                                acc[0] = __fmaf_rn(__fmul_rn(f0.x, alpha), T, acc[0]);
+                                acc[1] = __fmaf_rn(__fmul_rn(f0.y, alpha), T, acc[1]);
+                                acc[2] = __fmaf_rn(__fmul_rn(f0.z, alpha), T, acc[2]);
+                                if (C == 6) {   // the second triple is (z, 1, z^2) by construction
+                                    acc[3 % C] = __fmaf_rn(__fmul_rn(f0.w, alpha), T, acc[3 % C]);
+                                    acc[4 % C] = __fmaf_rn(alpha, T, acc[4 % C]);
+                                    acc[5 % C] = __fmaf_rn(__fmul_rn(__fmul_rn(f0.w, f0.w), alpha), T, acc[5 % C]);
+                                }
+                                if (T > 0.5f && test_T < 0.5f) D = sm.geom[s][j].z;   // forward.cu:370-374
+                                T = test_T;
                             }
-                            if (blend && T > 0.5f && test_T < 0.5f) D = sm.geom[s][j].z;   // forward.cu:370-374
-                            T = blend ? test_T : T;
                         }
                     }
                     if (done) hits = 0u;

@@ -747,7 +747,7 @@ def test_tile_buckets_and_global_sort_agree_at_full_size():
         assert int(ws1.status[3]) == int((a["ranges"][:, 1] - a["ranges"][:, 0]).max())   # largest bucket reported
 
 
-@pytest.mark.parametrize("shape", [(640, 480, 300_000), (160, 128, 60_000), (64, 48, 20_000), (32, 32, 8_000)])
+@pytest.mark.parametrize("shape", [(640, 480, 300_000), (320, 240, 150_000), (192, 160, 80_000), (64, 48, 20_000)])
 def test_blend_pipelines_repeat_exactly(shape):
     """The blend kernels' warps are not held together by a block barrier per batch (the last warp out of a stage
     refills it; the forward stops through a data-less barrier completion).  A race there would show up as a run that
