@@ -19,6 +19,10 @@ namespace asb {
 namespace {
 
 constexpr int FP_THREADS = 256;
+#ifndef ASB_FP_GPB
+#define ASB_FP_GPB 4
+#endif
+constexpr int FP_GPB = ASB_FP_GPB;   // Gaussians per thread of the frame preprocess (its cheap visibility screen)
 
 struct Pose {        // shared-memory copy of the frame pose
     float q[4];      // normalised camera quaternion (r,x,y,z)
@@ -129,7 +133,9 @@ constexpr uint64_t FPS_VALUE_MASK = (1ull << 56) - 1ull;
 // buckets nothing depends on that order, so blocks just reserve their span of the visible list with one atomic
 // and add their totals to status[0] / status[2] (zeroed by the launcher): no block ever waits for another.
 // NT threads = Gaussians per block.
-template <bool ISO, bool ORDERED, int NT>
+// GPB Gaussians per thread: a block screens a slab of NT * GPB Gaussians, so that the exact path behind the screen (a
+// fifth to a quarter of them survive) finds a candidate for nearly every thread instead of for two warps out of eight.
+template <bool ISO, bool ORDERED, int NT, int GPB>
 __global__ void __launch_bounds__(NT)
 frame_preprocess_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ unnorm_rot,
                         const float* __restrict__ logit_op, const float* __restrict__ log_scales,
@@ -143,16 +149,17 @@ frame_preprocess_kernel(int P, const float* __restrict__ means3D, const float* _
                         uint32_t* __restrict__ vis_list, uint32_t* ticket, uint64_t* scan_status, uint32_t* status,
                         float* __restrict__ max_2D_radius, uint8_t* __restrict__ seen,
                         uint32_t* __restrict__ tile_count) {
-    __shared__ __align__(16) float s_means[NT * 3];
-    __shared__ __align__(16) float s_ls[NT * 3];
+    constexpr int SLAB = NT * GPB;
+    __shared__ __align__(16) float s_means[SLAB * 3];
+    __shared__ __align__(16) float s_ls[SLAB * (ISO ? 1 : 3)];
     __shared__ float s_view[16], s_proj[16];
     __shared__ Pose ps;
     __shared__ uint32_t s_block;
     __shared__ uint32_t s_wt[NT / 32], s_wv[NT / 32];
     __shared__ uint32_t s_pref_t, s_pref_v;
-    __shared__ int s_rad[NT];
-    __shared__ uint32_t s_til[NT];
-    __shared__ uint16_t s_cand[NT];
+    __shared__ int s_rad[SLAB];
+    __shared__ uint32_t s_til[SLAB];
+    __shared__ uint16_t s_cand[SLAB];
     __shared__ uint32_t s_ncand;
     __shared__ float s_bound_k;
     // blocks take their slab in the order they start, so the look-back below can never wait on a
@@ -162,13 +169,14 @@ frame_preprocess_kernel(int P, const float* __restrict__ means3D, const float* _
         __syncthreads();
     }
     const uint32_t blk = ORDERED ? s_block : blockIdx.x;
-    const int row0 = blk * NT;
-    const int nrows = min(NT, P - row0);
+    const int row0 = blk * SLAB;
+    const int nrows = min(SLAB, P - row0);
     load_rows(means3D, row0, nrows, 3, s_means);
     load_rows(log_scales, row0, nrows, ISO ? 1 : 3, s_ls);
     if (threadIdx.x < 16) s_view[threadIdx.x] = __ldg(viewmatrix + threadIdx.x);
     else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = __ldg(projmatrix + threadIdx.x - 16);
     else if (threadIdx.x == 32) load_pose(ps, cam_rot, rs, cam_trans, ts, sil_w2c);
+    else if (threadIdx.x == 33) s_ncand = 0;
     else if (threadIdx.x == 64) {
         // constant of the radius bound of phase A: |J|_F^2 tz^2 <= fx^2 (1 + (1.3 tanfovx)^2) + fy^2 (1 + (1.3 tanfovy)^2)
         // (cov2d clamps tx/tz, ty/tz: forward.cu:82-87), times |W|_2^2 <= largest Gershgorin row sum of W^T W
@@ -190,53 +198,55 @@ frame_preprocess_kernel(int P, const float* __restrict__ means3D, const float* _
     }
     if (ORDERED && blk == 0 && threadIdx.x == 0) status[1] = 0;  // overflow flag of this frame
     __syncthreads();
-    const int idx = row0 + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    // ---- phase A (thread = Gaussian): cheap, conservative visibility test.  Usually most of the map is behind the
-    //      camera or off the image; the expensive per-Gaussian path below then runs densely over the candidates
-    //      instead of dragging every warp through it for a few scattered lanes.
+    // ---- phase A (thread = GPB Gaussians, one after the other): cheap, conservative visibility test.  Usually most
+    //      of the map is behind the camera or off the image; the expensive per-Gaussian path below then runs densely
+    //      over the candidates instead of dragging every warp through it for a few scattered lanes.
     //      A Gaussian is dropped here only if the reference would give it radius 0 / no tiles: near cull
     //      (auxiliary.h:154), or an empty tile rectangle even for an upper bound of its radius:
     //      lambda_max(cov2D + 0.3 I) <= trace(J W S W^T J^T) + 0.92 <= |J|_F^2 |W|_2^2 (mod * s_max)^2 + 0.92.
-    bool cand = false;
-    if (idx < P) {
-        const float px = s_means[3 * threadIdx.x], py = s_means[3 * threadIdx.x + 1], pz = s_means[3 * threadIdx.x + 2];
-        const float m0 = fmaf(ps.R[2], pz, fmaf(ps.R[1], py, ps.R[0] * px)) + ps.t[0];  // as in activate()
-        const float m1 = fmaf(ps.R[5], pz, fmaf(ps.R[4], py, ps.R[3] * px)) + ps.t[1];
-        const float m2 = fmaf(ps.R[8], pz, fmaf(ps.R[7], py, ps.R[6] * px)) + ps.t[2];
-        const float pvz = xform_row(s_view, 2, m0, m1, m2);
-        if (pvz > 0.2f) {
-            const float* ls = s_ls + (ISO ? 1 : 3) * threadIdx.x;
-            const float smax = expf(ISO ? ls[0] : fmaxf(ls[0], fmaxf(ls[1], ls[2]))) * fabsf(scale_modifier);
-            const float tr = s_bound_k * smax * smax / (pvz * pvz);
-            const float rb = ceilf(3.f * sqrtf(tr * 1.001f + 0.93f)) + 1.f;
-            const float hx = xform_row(s_proj, 0, m0, m1, m2), hy = xform_row(s_proj, 1, m0, m1, m2);
-            const float hw = xform_row(s_proj, 3, m0, m1, m2);
-            const float p_w = __frcp_rn(__fadd_rn(hw, 0.0000001f));
-            const float pix_x = ndc2pix(__fmul_rn(hx, p_w), W), pix_y = ndc2pix(__fmul_rn(hy, p_w), H);
-            cand = true;
-            if (rb < 1e8f && pix_x == pix_x && pix_y == pix_y) {  // anything not finite goes down the exact path
-                int x0, y0, x1, y1;
-                get_rect(pix_x, pix_y, __float2int_rz(rb), gx, gy, x0, y0, x1, y1);
-                cand = (x1 - x0) * (y1 - y0) != 0;
+#pragma unroll
+    for (int g = 0; g < GPB; g++) {
+        const int li = threadIdx.x + g * NT;   // slot of the slab
+        bool cand = false;
+        if (row0 + li < P) {
+            const float px = s_means[3 * li], py = s_means[3 * li + 1], pz = s_means[3 * li + 2];
+            const float m0 = fmaf(ps.R[2], pz, fmaf(ps.R[1], py, ps.R[0] * px)) + ps.t[0];  // as in activate()
+            const float m1 = fmaf(ps.R[5], pz, fmaf(ps.R[4], py, ps.R[3] * px)) + ps.t[1];
+            const float m2 = fmaf(ps.R[8], pz, fmaf(ps.R[7], py, ps.R[6] * px)) + ps.t[2];
+            const float pvz = xform_row(s_view, 2, m0, m1, m2);
+            if (pvz > 0.2f) {
+                const float* ls = s_ls + (ISO ? 1 : 3) * li;
+                const float smax = expf(ISO ? ls[0] : fmaxf(ls[0], fmaxf(ls[1], ls[2]))) * fabsf(scale_modifier);
+                const float tr = s_bound_k * smax * smax / (pvz * pvz);
+                const float rb = ceilf(3.f * sqrtf(tr * 1.001f + 0.93f)) + 1.f;
+                const float hx = xform_row(s_proj, 0, m0, m1, m2), hy = xform_row(s_proj, 1, m0, m1, m2);
+                const float hw = xform_row(s_proj, 3, m0, m1, m2);
+                const float p_w = __frcp_rn(__fadd_rn(hw, 0.0000001f));
+                const float pix_x = ndc2pix(__fmul_rn(hx, p_w), W), pix_y = ndc2pix(__fmul_rn(hy, p_w), H);
+                cand = true;
+                if (rb < 1e8f && pix_x == pix_x && pix_y == pix_y) {  // anything not finite goes down the exact path
+                    int x0, y0, x1, y1;
+                    get_rect(pix_x, pix_y, __float2int_rz(rb), gx, gy, x0, y0, x1, y1);
+                    cand = (x1 - x0) * (y1 - y0) != 0;
+                }
             }
         }
-    }
-    {
+        s_rad[li] = 0;
+        s_til[li] = 0;
+        // candidates go to the list in arrival order (one shared-memory atomic per warp and round): nothing below
+        // depends on their order
         const uint32_t bal = __ballot_sync(0xffffffffu, cand);
-        if (lane == 0) s_wv[warp] = __popc(bal);
-        s_rad[threadIdx.x] = 0;
-        s_til[threadIdx.x] = 0;
-        __syncthreads();
-        uint32_t off = 0;
-        for (int w = 0; w < warp; w++) off += s_wv[w];
-        if (cand) s_cand[off + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)threadIdx.x;
-        if (threadIdx.x == NT - 1) s_ncand = off + __popc(bal);
-        __syncthreads();
+        uint32_t base = 0;
+        if (lane == 0 && bal) base = atomicAdd(&s_ncand, (uint32_t)__popc(bal));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (cand) s_cand[base + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)li;
     }
+    __syncthreads();
     // ---- phase B (thread = candidate): the exact per-Gaussian path ----
-    if (threadIdx.x < s_ncand) {
-        const int slot = s_cand[threadIdx.x];
+    const int ncand = (int)s_ncand;
+    for (int c = threadIdx.x; c < ncand; c += NT) {
+        const int slot = s_cand[c];
         const int cidx = row0 + slot;
         Activated a;
         activate<ISO>(ps, s_means[3 * slot], s_means[3 * slot + 1], s_means[3 * slot + 2],
@@ -266,27 +276,38 @@ frame_preprocess_kernel(int P, const float* __restrict__ means3D, const float* _
         }
     }
     __syncthreads();
-    const int my_radii = s_rad[threadIdx.x];
-    const uint32_t my_tiles = s_til[threadIdx.x];
-    if (idx < P) {
-        if (radii) radii[idx] = my_radii;
-        radii_internal[idx] = my_radii;
-        // bookkeeping of get_loss (splatam.py:296-298): max_2D_radius[seen] = max(radius, .), seen = radius > 0
-        if (max_2D_radius && my_radii > 0) max_2D_radius[idx] = fmaxf(max_2D_radius[idx], (float)my_radii);
-        if (seen) seen[idx] = my_radii > 0 ? 1 : 0;
+    // per-Gaussian outputs, coalesced: slot threadIdx.x + g * NT
+#pragma unroll
+    for (int g = 0; g < GPB; g++) {
+        const int li = threadIdx.x + g * NT, idx = row0 + li;
+        if (idx < P) {
+            const int rad = s_rad[li];
+            if (radii) radii[idx] = rad;
+            radii_internal[idx] = rad;
+            // bookkeeping of get_loss (splatam.py:296-298): max_2D_radius[seen] = max(radius, .), seen = radius > 0
+            if (max_2D_radius && rad > 0) max_2D_radius[idx] = fmaxf(max_2D_radius[idx], (float)rad);
+            if (seen) seen[idx] = rad > 0 ? 1 : 0;
+        }
     }
     // ---- fused prefix sums (replaces the separate InclusiveSum launch, rasterizer_impl.cu:279):
-    //      tiles touched -> point_offsets, visible count -> compact list of visible Gaussians ----
-    const bool vis = my_radii > 0;
-    uint32_t incl = my_tiles;
+    //      tiles touched -> point_offsets, visible count -> compact list of visible Gaussians.
+    //      Thread t owns the GPB consecutive slots t * GPB ..: a serial prefix inside the thread, then a warp scan of the
+    //      threads' totals ----
+    uint32_t my_t[GPB], my_v = 0, sum_t = 0, cnt_v = 0;   // inclusive tile sums, visibility bits
+#pragma unroll
+    for (int g = 0; g < GPB; g++) {
+        const int li = threadIdx.x * GPB + g;
+        sum_t += s_til[li];
+        my_t[g] = sum_t;
+        if (s_rad[li] > 0) { my_v |= 1u << g; cnt_v++; }
+    }
+    uint32_t incl = sum_t, incl_v = cnt_v;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += t;
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o), tv = __shfl_up_sync(0xffffffffu, incl_v, o);
+        if (lane >= o) { incl += t; incl_v += tv; }
     }
-    const uint32_t bal = __ballot_sync(0xffffffffu, vis);
-    if (lane == 31) s_wt[warp] = incl;
-    if (lane == 0) s_wv[warp] = __popc(bal);
+    if (lane == 31) { s_wt[warp] = incl; s_wv[warp] = incl_v; }
     __syncthreads();
     uint32_t woff_t = 0, woff_v = 0, tot_t = 0, tot_v = 0;
 #pragma unroll
@@ -326,16 +347,22 @@ frame_preprocess_kernel(int P, const float* __restrict__ means3D, const float* _
             st_volatile_u64(scan_status + blk, FPS_PREFIX | (prefix + mine));
             s_pref_t = (uint32_t)prefix;
             s_pref_v = (uint32_t)(prefix >> 32);
-            if ((int)blk == (P + NT - 1) / NT - 1) {  // the last slab knows the totals
+            if ((int)blk == (P + SLAB - 1) / SLAB - 1) {  // the last slab knows the totals
                 status[0] = (uint32_t)prefix + tot_t;          // num_rendered
                 status[2] = (uint32_t)(prefix >> 32) + tot_v;  // number of visible Gaussians
             }
         }
     }
     __syncthreads();
-    if (idx < P) {
-        if (ORDERED) point_offsets[idx] = s_pref_t + woff_t + incl;
-        if (vis) vis_list[s_pref_v + woff_v + __popc(bal & ((1u << lane) - 1u))] = (uint32_t)idx;
+    const uint32_t before_t = s_pref_t + woff_t + incl - sum_t;      // tiles of everything before this thread's slots
+    uint32_t pos_v = s_pref_v + woff_v + incl_v - cnt_v;
+#pragma unroll
+    for (int g = 0; g < GPB; g++) {
+        const int idx = row0 + threadIdx.x * GPB + g;
+        if (idx < P) {
+            if (ORDERED) point_offsets[idx] = before_t + my_t[g];
+            if ((my_v >> g) & 1u) vis_list[pos_v++] = (uint32_t)idx;
+        }
     }
 }
 
@@ -1227,9 +1254,9 @@ void launch_frame_preprocess(const AsFrameArgs& a, const GeometryState& g, uint3
     const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
     constexpr int NT_ORDERED = FP_THREADS;  // 1024-thread blocks (a 4x shorter look-back chain) measured no faster
     const int nt = ordered ? NT_ORDERED : FP_THREADS;
-    const int blocks = (P + nt - 1) / nt;
+    const int blocks = (P + nt * FP_GPB - 1) / (nt * FP_GPB);
 #define ASB_PP(ISO_, ORD_, NT_)                                                                                     \
-    frame_preprocess_kernel<ISO_, ORD_, NT_><<<blocks, NT_, 0, st>>>(                                               \
+    frame_preprocess_kernel<ISO_, ORD_, NT_, FP_GPB><<<blocks, NT_, 0, st>>>(                                       \
         P, a.means3D, a.unnorm_rotations, a.logit_opacities, a.log_scales, a.cam_unnorm_rot, a.cam_rot_stride,      \
         a.cam_trans, a.cam_trans_stride, a.sil_w2c, a.viewmatrix, a.projmatrix, W, H, gx, gy, a.tan_fovx,           \
         a.tan_fovy, focal_x, focal_y, a.scale_modifier, a.radii, g.radii, g.means2D, g.depths, g.conic_opacity,     \
