@@ -453,14 +453,15 @@ def test_adam_in_chunks_equals_adam_in_one_launch():
         assert torch.equal(oa.exp_avg[:n], ob.exp_avg[:n]) and torch.equal(oa.exp_avg_sq[:n], ob.exp_avg_sq[:n])
 
 
-def test_mapping_get_loss_and_adam_steps_match_oracle():
+@pytest.mark.parametrize("width", [96, 90])   # 90: not a multiple of 4, the SSIM kernels then stage their tiles with scalar loads
+def test_mapping_get_loss_and_adam_steps_match_oracle(width):
     """get_loss(mapping=True) (0.8 L1 + 0.2 (1-SSIM) colour loss, masked mean depth loss, splatam.py:239-249)
     + Adam, three iterations: losses, gradients of all five tensors, and the parameters after the steps,
     against the CPU oracle (two-pass oracle rasterizer + torch autograd + torch.optim.Adam)."""
     from activesplat_b200 import splatam
     from activesplat_b200.frame import FusedAdam, PARAM_ORDER, workspace_for
     from oracle import splatam_oracle as so
-    params, cams, gt_rgb, gt_depth = _frame_case(P=2000, W=96, H=80, seed=21)
+    params, cams, gt_rgb, gt_depth = _frame_case(P=2000, W=width, H=80, seed=21)
     W, H, t_idx = cams[0].width, cams[0].height, 1
     lw = dict(im=0.5, depth=1.0)
     lrs = dict(means3D=1e-4, rgb_colors=2.5e-3, unnorm_rotations=1e-3, logit_opacities=5e-2, log_scales=1e-3,
