@@ -6,8 +6,9 @@
 // One CTA per 16x16 tile, one thread per pixel (same as the reference).  What differs:
 //   * the tile's instances were gathered into contiguous per-instance records in sorted order
 //     (ranges_gather_kernel / frame_tile_sort_gather_kernel), so a batch is THREE contiguous slabs that one
-//     elected thread pulls into shared memory with cp.async.bulk (TMA engine, SASS UBLKCP) on an mbarrier,
-//     multi-buffered: the copy of the next batches overlaps the blending of this one;
+//     thread pulls into shared memory with cp.async.bulk (TMA engine, SASS UBLKCP) on an mbarrier,
+//     multi-buffered: the copy of the next batches overlaps the blending of this one.  The warps of a CTA are not
+//     held together by a block barrier per batch: the last warp to leave a stage refills it;
 //   * C = 6 blends [rgb | z,1,z^2] in one sweep (the reference makes two full passes);
 //   * a warp owns a 16x2-pixel strip.  Per batch it keeps only the records whose ellipse of possible contribution
 //     reaches the strip, with the exact set of the strip's pixels inside that ellipse (cull_batch); a bit-matrix
