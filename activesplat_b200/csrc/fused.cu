@@ -436,6 +436,10 @@ frame_ranges_gather_kernel(const uint32_t* __restrict__ n_dev, uint32_t capacity
 // Sorting by (depth, id) reproduces the stable radix sort exactly: the reference emits instances in ascending
 // Gaussian id, so equal (tile, depth) keys stay in id order.
 constexpr int TS_THREADS = 256;
+#ifndef ASB_TS_GATHER
+#define ASB_TS_GATHER 2
+#endif
+constexpr int TS_GATHER = ASB_TS_GATHER;   // records a thread gathers per round (their scattered reads in flight together)
 constexpr int TS_CAP = 3584;  // instances per tile sorted in shared memory (28 KB: 8 CTAs per SM); larger buckets are sorted in place (slow)
 
 __global__ void __launch_bounds__(1024)
@@ -676,19 +680,38 @@ frame_tile_sort_gather_kernel(const uint2* __restrict__ ranges, uint64_t* __rest
         __syncthreads();
         bitonic_sort_ascending(ge, n, TS_THREADS);  // global memory is coherent within the block across the barriers
     }
-    for (int i = threadIdx.x; i < n; i += TS_THREADS) {
-        const uint64_t e = merged ? s_e[TS_CAP / 2 + i] : (in_smem ? s_e[i] : ge[i]);
-        const uint32_t id = (uint32_t)e;
-        const size_t o = (size_t)range.x + i;
-        point_list[o] = id;
-        const float2 m = __ldg(means2D + id);
-        const float4 co = __ldg(conic_opacity + id);
-        inst_conic[o] = co;
-        inst_geom[o] = make_float4(m.x, m.y, __uint_as_float((uint32_t)(e >> 32)), __uint_as_float(id));
-        const float z = __ldg(zsil + id);
-        const float* c = rgb + 3 * (size_t)id;
-        inst_feat[2 * o] = make_float4(__ldg(c), __ldg(c + 1), __ldg(c + 2), z);
-        inst_feat[2 * o + 1] = make_float4(1.f, z * z, pack_cull_extent(co), 0.f);
+    // TS_GATHER records per thread and round: the scattered reads of all are in flight before any is stored
+    for (int i0 = threadIdx.x; i0 < n; i0 += TS_GATHER * TS_THREADS) {
+        uint64_t e[TS_GATHER];
+        float2 m[TS_GATHER];
+        float4 co[TS_GATHER];
+        float z[TS_GATHER], c[TS_GATHER][3];
+        bool on[TS_GATHER];
+#pragma unroll
+        for (int u = 0; u < TS_GATHER; u++) {
+            const int i = i0 + u * TS_THREADS;
+            on[u] = i < n;
+            if (on[u]) {
+                e[u] = merged ? s_e[TS_CAP / 2 + i] : (in_smem ? s_e[i] : ge[i]);
+                const uint32_t id = (uint32_t)e[u];
+                m[u] = __ldg(means2D + id);
+                co[u] = __ldg(conic_opacity + id);
+                z[u] = __ldg(zsil + id);
+                const float* cp = rgb + 3 * (size_t)id;
+                c[u][0] = __ldg(cp); c[u][1] = __ldg(cp + 1); c[u][2] = __ldg(cp + 2);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < TS_GATHER; u++) {
+            if (!on[u]) continue;
+            const uint32_t id = (uint32_t)e[u];
+            const size_t o = (size_t)range.x + i0 + u * TS_THREADS;
+            point_list[o] = id;
+            inst_conic[o] = co[u];
+            inst_geom[o] = make_float4(m[u].x, m[u].y, __uint_as_float((uint32_t)(e[u] >> 32)), __uint_as_float(id));
+            inst_feat[2 * o] = make_float4(c[u][0], c[u][1], c[u][2], z[u]);
+            inst_feat[2 * o + 1] = make_float4(1.f, z[u] * z[u], pack_cull_extent(co[u]), 0.f);
+        }
     }
 }
 
