@@ -439,6 +439,10 @@ constexpr int TS_THREADS = 256;
 #ifndef ASB_TS_GATHER
 #define ASB_TS_GATHER 2
 #endif
+#ifndef ASB_TS_MERGE
+#define ASB_TS_MERGE 4
+#endif
+constexpr int TS_MERGE = ASB_TS_MERGE;     // runs whose lower bounds a thread searches together
 constexpr int TS_GATHER = ASB_TS_GATHER;   // records a thread gathers per round (their scattered reads in flight together)
 constexpr int TS_CAP = 3584;  // instances per tile sorted in shared memory (28 KB: 8 CTAs per SM); larger buckets are sorted in place (slow)
 
@@ -655,19 +659,27 @@ frame_tile_sort_gather_kernel(const uint2* __restrict__ ranges, uint64_t* __rest
         __syncthreads();
         for (int i = threadIdx.x; i < n; i += TS_THREADS) {
             const uint64_t key = s_e[i];
-            const int own = i >> 6;
-            int pos = i & 63;
-            for (int r = 0; r < nruns; r++) {
-                if (r == own) continue;
-                int lo = 0;  // number of keys of run r below `key`, 0..64 (padding keys are the maximum: never below)
-                if (s_e[64 * r + 63] < key) {
-                    lo = 64;
-                } else {
+            // final position = number of smaller keys = sum over the runs of a lower bound (in the key's own run that is
+            // its index).  TS_MERGE runs at a time, branch-free: their chains of dependent shared loads overlap.
+            int pos = 0;
+            for (int r0 = 0; r0 < nruns; r0 += TS_MERGE) {
+                int lo[TS_MERGE];
+                const uint64_t* run[TS_MERGE];
 #pragma unroll
-                    for (int step = 32; step > 0; step >>= 1)
-                        if (s_e[64 * r + lo + step - 1] < key) lo += step;
+                for (int u = 0; u < TS_MERGE; u++) {
+                    run[u] = s_e + 64 * min(r0 + u, nruns - 1);
+                    lo[u] = 0;
                 }
-                pos += lo;
+#pragma unroll
+                for (int step = 32; step > 0; step >>= 1)
+#pragma unroll
+                    for (int u = 0; u < TS_MERGE; u++)
+                        if (run[u][lo[u] + step - 1] < key) lo[u] += step;
+#pragma unroll
+                for (int u = 0; u < TS_MERGE; u++) {
+                    lo[u] += run[u][lo[u]] < key ? 1 : 0;   // 63 -> 64 when the whole run is below (padding keys never are)
+                    pos += r0 + u < nruns ? lo[u] : 0;
+                }
             }
             s_e[TS_CAP / 2 + pos] = key;
         }
