@@ -759,8 +759,12 @@ __device__ __forceinline__ float* grad_slot(float* base, size_t P, int seg_off, 
 
 // Backward of frame_preprocess_kernel.  grad_params: the flat segment layout above.
 // pose_acc ([blocks,16] partial sums): dL/dt (3) | dL/dR (9, row-major) | dL/dq_cam through quat_mult (4).
-template <bool ISO>
-__global__ void __launch_bounds__(FP_THREADS, 4)
+#ifndef ASB_PPB_MINBLOCKS
+#define ASB_PPB_MINBLOCKS 6
+#endif
+// CAM: the pose gradient is wanted (tracking, bundle adjustment); the mapping instantiation carries no pose accumulators
+template <bool ISO, bool CAM>
+__global__ void __launch_bounds__(FP_THREADS, CAM ? 4 : ASB_PPB_MINBLOCKS)
 frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ unnorm_rot,
                                  const float* __restrict__ logit_op, const float* __restrict__ log_scales,
                                  const float* __restrict__ cam_rot, int rs, const float* __restrict__ cam_trans, int ts,
@@ -769,7 +773,7 @@ frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const
                                  float tanfovy, float scale_modifier, const int* __restrict__ radii,
                                  const float* __restrict__ zsil, const uint32_t* __restrict__ vis_list,
                                  const uint32_t* __restrict__ status, float* __restrict__ gacc,
-                                 const float* __restrict__ gscale, int gaussians_grad, int camera_grad,
+                                 const float* __restrict__ gscale, int gaussians_grad, int camera_grad_,
                                  int accumulate, float* __restrict__ grad_params, float* __restrict__ grad_means2D,
                                  float* __restrict__ pose_acc) {
     __shared__ float view[16], proj[16];
@@ -801,9 +805,11 @@ frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const
     if (!has_dense_work) return;
     __syncthreads();
     const float gs = gscale ? __ldg(gscale) : 1.f;
-    float pacc[16];
+    constexpr bool camera_grad = CAM;
+    (void)camera_grad_;
+    float pacc[CAM ? 16 : 1];
 #pragma unroll
-    for (int k = 0; k < 16; k++) pacc[k] = 0.f;
+    for (int k = 0; k < (CAM ? 16 : 1); k++) pacc[k] = 0.f;
     // (B) the long per-Gaussian path runs densely over the compact list of visible Gaussians that the
     //     forward wrote (visible ones are usually a scattered minority): the first ceil(V/256) blocks are
     //     full, the rest are done after (A)
@@ -862,14 +868,14 @@ frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const
             for (int k = 0; k < 4; k++) d2 += q2[k] * g_qn[k];
 #pragma unroll
             for (int k = 0; k < 4; k++) g_qraw[k] = (g_qn[k] - q2[k] * d2) / a.qn_norm;
-            if (camera_grad) {
+            if constexpr (CAM) {
                 pacc[12] += q2[0] * g_rt[0] + q2[1] * g_rt[1] + q2[2] * g_rt[2] + q2[3] * g_rt[3];
                 pacc[13] += -q2[1] * g_rt[0] + q2[0] * g_rt[1] - q2[3] * g_rt[2] + q2[2] * g_rt[3];
                 pacc[14] += -q2[2] * g_rt[0] + q2[3] * g_rt[1] + q2[0] * g_rt[2] - q2[1] * g_rt[3];
                 pacc[15] += -q2[3] * g_rt[0] - q2[2] * g_rt[1] + q2[1] * g_rt[2] + q2[0] * g_rt[3];
             }
         }
-        if (camera_grad) {
+        if constexpr (CAM) {
             pacc[0] += dmean[0]; pacc[1] += dmean[1]; pacc[2] += dmean[2];
 #pragma unroll
             for (int i = 0; i < 3; i++) {
@@ -918,7 +924,7 @@ frame_preprocess_backward_kernel(int P, const float* __restrict__ means3D, const
         }
     }
     }  // slot loop
-    if (camera_grad) {
+    if constexpr (CAM) {
 #pragma unroll
         for (int k = 0; k < 16; k++) pacc[k] *= gs;
         block_reduce_store<16>(pacc, s_red, pose_acc + 16 * (size_t)blockIdx.x);
@@ -1350,18 +1356,20 @@ void launch_frame_preprocess_backward(const AsFrameArgs& a, const GeometryState&
     if (gaussians_grad && grad_params && accumulate == 0)
         cudaMemsetAsync(grad_params, 0, sizeof(float) * 14 * (size_t)P, st);
     accumulate = accumulate == 1 ? 1 : 0;
-    if (a.isotropic)
-        frame_preprocess_backward_kernel<true><<<blocks, FP_THREADS, 0, st>>>(
-            P, a.means3D, a.unnorm_rotations, a.logit_opacities, a.log_scales, a.cam_unnorm_rot, a.cam_rot_stride,
-            a.cam_trans, a.cam_trans_stride, a.sil_w2c, a.viewmatrix, a.projmatrix, h_x, h_y, a.tan_fovx, a.tan_fovy,
-            a.scale_modifier, g.radii, g.zsil, g.vis_list, a.status, g.gacc, gscale, gaussians_grad, camera_grad,
-            accumulate, grad_params, grad_means2D, pose_acc);
-    else
-        frame_preprocess_backward_kernel<false><<<blocks, FP_THREADS, 0, st>>>(
-            P, a.means3D, a.unnorm_rotations, a.logit_opacities, a.log_scales, a.cam_unnorm_rot, a.cam_rot_stride,
-            a.cam_trans, a.cam_trans_stride, a.sil_w2c, a.viewmatrix, a.projmatrix, h_x, h_y, a.tan_fovx, a.tan_fovy,
-            a.scale_modifier, g.radii, g.zsil, g.vis_list, a.status, g.gacc, gscale, gaussians_grad, camera_grad,
-            accumulate, grad_params, grad_means2D, pose_acc);
+#define ASB_PPB(ISO_, CAM_)                                                                                         \
+    frame_preprocess_backward_kernel<ISO_, CAM_><<<blocks, FP_THREADS, 0, st>>>(                                     \
+        P, a.means3D, a.unnorm_rotations, a.logit_opacities, a.log_scales, a.cam_unnorm_rot, a.cam_rot_stride,       \
+        a.cam_trans, a.cam_trans_stride, a.sil_w2c, a.viewmatrix, a.projmatrix, h_x, h_y, a.tan_fovx, a.tan_fovy,    \
+        a.scale_modifier, g.radii, g.zsil, g.vis_list, a.status, g.gacc, gscale, gaussians_grad, camera_grad,        \
+        accumulate, grad_params, grad_means2D, pose_acc)
+    if (a.isotropic) {
+        if (camera_grad) ASB_PPB(true, true);
+        else ASB_PPB(true, false);
+    } else {
+        if (camera_grad) ASB_PPB(false, true);
+        else ASB_PPB(false, false);
+    }
+#undef ASB_PPB
     if (camera_grad)
         pose_finalize_kernel<<<1, 256, 0, st>>>(a.cam_unnorm_rot, a.cam_rot_stride, pose_acc, blocks, a.status, grad_cam,
                                                 grad_cam_stride > 0 ? grad_cam_stride : 1);
